@@ -1,0 +1,163 @@
+// bc123_encode.cu -- BC1 / BC2 / BC3 surface encoders (sm_100a).
+//
+// Replaces TextureBlockCompression::CompressBC1/2/3 (Hork/Image/ImageEncoders.cpp:215-320):
+//   BC1: Encode_BC1(.., 5, false, false)         -> rgbcx::encode_bc1 level 5   (see bc1_block.cuh)
+//   BC2: 4-bit explicit alpha (ImageEncoders.cpp:152-157) + the BC1 colour block
+//   BC3: Encode_BC3(.., 5, bMaxQuality = true)   -> rgbcx::encode_bc3_hq = encode_bc4_hq on alpha
+//        (stride 4, radius 3, all modes; see bc4_search.cuh) + the BC1 colour block
+// Bit-exact contract for all three.
+//
+// Mapping: BC1/BC2 one lane per block; BC3 a 2-lane sub-warp per block (lane parity = BC4
+// alpha mode, the even lane also encodes the colour block).  128-thread CTAs, tiles of
+// 128 (BC1/2) or 64 (BC3) blocks staged by TMA bulk copies.  Algorithmic HBM bytes:
+// 4.5 B/px (BC1), 5 B/px (BC2/BC3).
+#include "hkbcn_common.cuh"
+#include "hkbcn_kernels.h"
+#include "bc4_search.cuh"
+#include "bc1_block.cuh"
+#include <stdio.h>
+#include <stdlib.h>
+#include <math.h>
+
+namespace hkbcn {
+
+template <int CODEC>
+__global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant__ EncodeParams P)
+{
+    constexpr int NT = 128;
+    constexpr int G = (CODEC == C_BC3) ? 2 : 1;
+    constexpr int TB = NT / G;
+    constexpr int BW = 16;
+    constexpr int ROWB = TB * BW;
+    __shared__ __align__(128) uint8_t stage[4 * ROWB];
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    uint32_t phase = 0;
+    const int k = threadIdx.x / G;
+    const int sub = threadIdx.x % G;
+
+    for (uint32_t tile = blockIdx.x; tile < P.totalTiles; tile += gridDim.x) {
+        const Level& L = P.lv[find_level(P, tile)];
+        const uint32_t b0 = (tile - L.tileBase) * TB;
+        const uint32_t nb = min((uint32_t)TB, L.nblocks - b0);
+        stage_tile<4, TB, NT>(L, b0, nb, stage, &bar, phase);
+
+        const bool valid = (uint32_t)k < nb;
+        uint32_t px[16];
+        if (valid) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                uint4 v = *(const uint4*)(stage + r * ROWB + k * BW);
+                px[r * 4 + 0] = v.x; px[r * 4 + 1] = v.y; px[r * 4 + 2] = v.z; px[r * 4 + 3] = v.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; i++) px[i] = 0;
+        }
+
+        if (CODEC == C_BC1) {
+            if (valid) *(uint2*)(L.dst + (size_t)(b0 + k) * 8) = bc1_encode_block(px);
+        } else if (CODEC == C_BC2) {
+            if (valid) {
+                uint32_t a[2] = {0, 0};
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    // min(int(a * (15.0f / 255.0f) + 0.5f), 15)   (ImageEncoders.cpp:154-155)
+                    int q = __float2int_rz(__fadd_rn(__fmul_rn((float)(px[i] >> 24), 15.0f / 255.0f), 0.5f));
+                    q = min(q, 15);
+                    a[i >> 3] |= (uint32_t)q << (4 * (i & 7));
+                }
+                uint2 c = bc1_encode_block(px);
+                *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(a[0], a[1], c.x, c.y);
+            }
+        } else { // BC3
+            uint32_t a2[8];
+            int minv = 255, maxv = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                int p0 = px[2 * i] >> 24, p1 = px[2 * i + 1] >> 24;
+                a2[i] = (uint32_t)p0 | ((uint32_t)p1 << 16);
+                minv = min(minv, min(p0, p1));
+                maxv = max(maxv, max(p0, p1));
+            }
+            uint32_t key = 0xFFFFFFFFu;
+            if (minv != maxv) key = bc4hq_search_mode(a2, minv, maxv, sub);
+            key = min(key, __shfl_xor_sync(0xFFFFFFFFu, key, 1));
+            if (valid && sub == 0) {
+                uint2 al = (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
+                uint2 c = bc1_encode_block(px);
+                *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(al.x, al.y, c.x, c.y);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+uint32_t bc123_tile_blocks(int codec) { return codec == C_BC3 ? 64 : 128; }
+
+// ---- a12: table generation (host) -------------------------------------------
+// prepare_bc1_single_color_table (rgbcx.cpp:485-527) in cBC1Ideal mode: for each 8-bit value
+// the (hi, lo) 5/6-bit pair whose 2/3-1/3 interpolant is closest, with a 3% endpoint-spread
+// penalty and ties broken towards hi == lo.
+static void gen_match(uint16_t* out, int size)
+{
+    uint8_t expand[64];
+    for (int i = 0; i < size; i++) expand[i] = (uint8_t)(size == 32 ? ((i << 3) | (i >> 2)) : ((i << 2) | (i >> 4)));
+    for (int i = 0; i < 256; i++) {
+        int lowest = 256, bh = 0, bl = 0;
+        for (int lo = 0; lo < size; lo++) {
+            for (int hi = 0; hi < size; hi++) {
+                int lo_e = expand[lo], hi_e = expand[hi];
+                int v = (hi_e * 2 + lo_e) / 3;
+                int e = abs(v - i) + (abs(hi_e - lo_e) * 3) / 100;
+                if (e < lowest || (e == lowest && lo == hi)) { bh = hi; bl = lo; lowest = e; }
+            }
+        }
+        out[i] = (uint16_t)(bh | (bl << 8));
+    }
+}
+// g_midpoint5/6 (rgbcx.cpp:693-694): midpoint between consecutive expanded 5/6-bit levels
+// in [0,1], written in the reference as 6-decimal literals; the last entry is 1e+37.
+static void gen_mid(float* out, int size)
+{
+    for (int i = 0; i < size - 1; i++) {
+        int a = size == 32 ? ((i << 3) | (i >> 2)) : ((i << 2) | (i >> 4));
+        int b = size == 32 ? (((i + 1) << 3) | ((i + 1) >> 2)) : (((i + 1) << 2) | ((i + 1) >> 4));
+        char buf[32];
+        snprintf(buf, sizeof(buf), "%.6f", (a + b) / 2.0 / 255.0);
+        out[i] = strtof(buf, nullptr);
+    }
+    out[size - 1] = 1e+37f;
+}
+
+cudaError_t bc1_upload_tables()
+{
+    uint16_t m5[256], m6[256];
+    float mid5[32], mid6[64];
+    gen_match(m5, 32);
+    gen_match(m6, 64);
+    gen_mid(mid5, 32);
+    gen_mid(mid6, 64);
+    cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(g_bc1_match5, m5, sizeof(m5))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_bc1_match6, m6, sizeof(m6))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_bc1_mid5, mid5, sizeof(mid5))) != cudaSuccess) return e;
+    return cudaMemcpyToSymbol(g_bc1_mid6, mid6, sizeof(mid6));
+}
+
+cudaError_t launch_bc123_encode(int codec, const EncodeParams& P, int sm_count, cudaStream_t stream)
+{
+    if (P.totalTiles == 0) return cudaSuccess;
+    uint32_t g = (uint32_t)sm_count * 8;
+    int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
+    if (codec == C_BC1) bc123_encode_kernel<C_BC1><<<grid, 128, 0, stream>>>(P);
+    else if (codec == C_BC2) bc123_encode_kernel<C_BC2><<<grid, 128, 0, stream>>>(P);
+    else bc123_encode_kernel<C_BC3><<<grid, 128, 0, stream>>>(P);
+    return cudaGetLastError();
+}
+
+} // namespace hkbcn

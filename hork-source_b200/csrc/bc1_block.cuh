@@ -1,0 +1,237 @@
+// bc1_block.cuh -- BC1 colour-block encoder for one 4x4 RGBA8 block (one thread).
+//
+// Behaviour contract: byte-identical to rgbcx::encode_bc1(level = 5, dst, px, false, false)
+// (ThirdParty/bc7enc_rdo/rgbcx.cpp:1692-1726 -> flags TwoLeastSquaresPasses|UseFasterMSEEval
+// -> :2263-2604, the `!needs_block_error` branch :2316-2371), the call behind
+// Encode_BC1/2/3 in Hork/Image/ImageEncoders.cpp:138-169.
+//
+// FP32 discipline: the reference is built without FMA contraction (baseline x86-64,
+// SURVEY.md 7), so every float op here is an explicitly rounded __fmul_rn/__fadd_rn/
+// __fdiv_rn in the reference's evaluation order; float->int casts truncate (__float2int_rz).
+#pragma once
+#include <stdint.h>
+
+namespace hkbcn {
+
+// a12 tables, filled by bc1_upload_tables(): optimal single-colour endpoints
+// (g_bc1_match5_equals_1 / g_bc1_match6_equals_1, rgbcx.cpp:485-527, cBC1Ideal) packed as
+// hi | lo << 8, and the 565 rounding midpoints (g_midpoint5/6, rgbcx.cpp:693-694).
+static __device__ uint16_t g_bc1_match5[256];
+static __device__ uint16_t g_bc1_match6[256];
+static __device__ float g_bc1_mid5[32];
+static __device__ float g_bc1_mid6[64];
+
+__device__ __forceinline__ int to_5(uint32_t v) { v = v * 31 + 128; return (int)(((v + (v >> 8)) >> 8) & 0xFF); }
+__device__ __forceinline__ int to_6(uint32_t v) { v = v * 63 + 128; return (int)(((v + (v >> 8)) >> 8) & 0xFF); }
+
+struct Bc1Ep { int lr, lg, lb, hr, hg, hb; };
+
+// rgbcx.cpp:915-950 (bc1_find_sels4_noerr) with bc1_get_block_colors4 in cBC1Ideal mode (:869-879).
+// Returns the 16 selectors packed 2 bits each (reference selector numbering 0..3 = l, 2/3l, 2/3h, h).
+__device__ __forceinline__ uint32_t bc1_find_sels4(const uint32_t px[16], const Bc1Ep& e)
+{
+    int r0 = (e.lr << 3) | (e.lr >> 2), g0 = (e.lg << 2) | (e.lg >> 4), b0 = (e.lb << 3) | (e.lb >> 2);
+    int r3 = (e.hr << 3) | (e.hr >> 2), g3 = (e.hg << 2) | (e.hg >> 4), b3 = (e.hb << 3) | (e.hb >> 2);
+    int r1 = (r0 * 2 + r3) / 3, g1 = (g0 * 2 + g3) / 3, b1 = (b0 * 2 + b3) / 3;
+    int r2 = (r3 * 2 + r0) / 3, g2 = (g3 * 2 + g0) / 3, b2 = (b3 * 2 + b0) / 3;
+    int ar = r3 - r0, ag = g3 - g0, ab = b3 - b0;
+    int d0 = r0 * ar + g0 * ag + b0 * ab;
+    int d1 = r1 * ar + g1 * ag + b1 * ab;
+    int d2 = r2 * ar + g2 * ag + b2 * ab;
+    int d3 = r3 * ar + g3 * ag + b3 * ab;
+    int t0 = d0 + d1, t1 = d1 + d2, t2 = d2 + d3;
+    ar *= 2; ag *= 2; ab *= 2;
+    uint32_t sels = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        int r = px[i] & 0xFF, g = (px[i] >> 8) & 0xFF, b = (px[i] >> 16) & 0xFF;
+        int d = r * ar + g * ag + b * ab;
+        int c = (d <= t0) + (d < t1) + (d < t2); // s_sels = {3,2,1,0}
+        sels |= (uint32_t)(3 - c) << (2 * i);
+    }
+    return sels;
+}
+
+// rgbcx.cpp:1194-1228 (precise_round_565) for one endpoint.
+__device__ __forceinline__ void round_565(float x0, float x1, float x2, int& r, int& g, int& b)
+{
+    r = __float2int_rz(__fmul_rn(x0, 31.0f));
+    g = __float2int_rz(__fmul_rn(x1, 63.0f));
+    b = __float2int_rz(__fmul_rn(x2, 31.0f));
+    if ((uint32_t)r > 31u) r = (~r >> 31) & 31;
+    if ((uint32_t)b > 31u) b = (~b >> 31) & 31;
+    if ((uint32_t)g > 63u) g = (~g >> 31) & 63;
+    r = (r + (x0 > g_bc1_mid5[r])) & 31;
+    g = (g + (x1 > g_bc1_mid6[g])) & 63;
+    b = (b + (x2 > g_bc1_mid5[b])) & 31;
+}
+
+// rgbcx.cpp:629-691 (encode_bc1_solid_block, allow_3color = false)
+__device__ __forceinline__ uint2 bc1_solid(uint32_t fr, uint32_t fg, uint32_t fb)
+{
+    uint32_t mr = g_bc1_match5[fr], mg = g_bc1_match6[fg], mb = g_bc1_match5[fb];
+    int max16 = (int)(((mr & 0xFF) << 11) | ((mg & 0xFF) << 5) | (mb & 0xFF));
+    int min16 = (int)(((mr >> 8) << 11) | ((mg >> 8) << 5) | (mb >> 8));
+    uint32_t mask = 0xAA;
+    if (min16 == max16) {
+        mask = 0;
+        if (min16 > 0) min16--;
+        else { max16 = 1; min16 = 0; mask = 0x55; }
+    }
+    if (max16 < min16) { int t = max16; max16 = min16; min16 = t; mask ^= 0x55; }
+    return make_uint2((uint32_t)max16 | ((uint32_t)min16 << 16), mask * 0x01010101u);
+}
+
+// rgbcx.cpp:1245-1300 (bc1_encode4): never emits a 3-colour block.
+__device__ __forceinline__ uint2 bc1_pack4(const Bc1Ep& e, uint32_t sels)
+{
+    uint32_t lc16 = ((uint32_t)e.lr << 11) | ((uint32_t)e.lg << 5) | (uint32_t)e.lb;
+    uint32_t hc16 = ((uint32_t)e.hr << 11) | ((uint32_t)e.hg << 5) | (uint32_t)e.hb;
+    if (lc16 == hc16) {
+        uint32_t mask = 0;
+        if (hc16 > 0) hc16--;
+        else { hc16 = 0; lc16 = 1; mask = 0x55; }
+        return make_uint2(lc16 | (hc16 << 16), mask * 0x01010101u);
+    }
+    uint32_t inv = 0;
+    if (lc16 < hc16) { uint32_t t = lc16; lc16 = hc16; hc16 = t; inv = 0x55555555u; }
+    // s_sel_trans = {0,2,3,1}: reference selector -> BC1 hardware selector
+    uint32_t packed = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t s = (sels >> (2 * i)) & 3;
+        packed |= ((0x78u >> (2 * s)) & 3u) << (2 * i); // 0b01'11'10'00
+    }
+    return make_uint2(lc16 | (hc16 << 16), packed ^ inv);
+}
+
+// The whole level-5 colour path.  px[i] = R | G<<8 | B<<16 | A<<24 (alpha ignored).
+__device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16])
+{
+    const uint32_t rgb0 = px[0] & 0xFFFFFFu;
+    const int fr = rgb0 & 0xFF, fg = (rgb0 >> 8) & 0xFF, fb = rgb0 >> 16;
+    bool solid = true;
+#pragma unroll
+    for (int i = 1; i < 16; i++) solid &= ((px[i] & 0xFFFFFFu) == rgb0);
+    if (solid) return bc1_solid(fr, fg, fb);
+
+    int min_r = fr, min_g = fg, min_b = fb, max_r = fr, max_g = fg, max_b = fb;
+    int total_r = fr, total_g = fg, total_b = fb;
+    bool gray = (fr == fg) && (fr == fb);
+#pragma unroll
+    for (int i = 1; i < 16; i++) {
+        int r = px[i] & 0xFF, g = (px[i] >> 8) & 0xFF, b = (px[i] >> 16) & 0xFF;
+        gray &= (r == g) && (r == b);
+        max_r = max(max_r, r); max_g = max(max_g, g); max_b = max(max_b, b);
+        min_r = min(min_r, r); min_g = min(min_g, g); min_b = min(min_b, b);
+        total_r += r; total_g += g; total_b += b;
+    }
+    const int avg_r = (total_r + 8) >> 4, avg_g = (total_g + 8) >> 4, avg_b = (total_b + 8) >> 4;
+
+    // ---- encode_bc1_pick_initial (rgbcx.cpp:1813-2175)
+    Bc1Ep e;
+    if (gray) {
+        if ((max_r - min_r) < 2) {
+            e.lr = e.lb = e.hr = e.hb = to_5(fr);
+            e.lg = e.hg = to_6(fr);
+        } else {
+            e.lr = e.lb = to_5(min_r); e.lg = to_6(min_r);
+            e.hr = e.hb = to_5(max_r); e.hg = to_6(max_r);
+        }
+    } else {
+        int ic0 = 0, ic1 = 0, ic2 = 0, ic3 = 0, ic4 = 0, ic5 = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            int r = (int)(px[i] & 0xFF) - avg_r, g = (int)((px[i] >> 8) & 0xFF) - avg_g, b = (int)((px[i] >> 16) & 0xFF) - avg_b;
+            ic0 += r * r; ic1 += r * g; ic2 += r * b; ic3 += g * g; ic4 += g * b; ic5 += b * b;
+        }
+        int saxis_r = 306, saxis_g = 601, saxis_b = 117;
+        float xr = (float)(max_r - min_r), xg = (float)(max_g - min_g), xb = (float)(max_b - min_b);
+        if (ic2 < 0) xr = -xr;
+        if (ic4 < 0) xg = -xg;
+        const float inv255 = 1.0f / 255.0f;
+        const float c0 = __fmul_rn((float)ic0, inv255), c1 = __fmul_rn((float)ic1, inv255), c2 = __fmul_rn((float)ic2, inv255);
+        const float c3 = __fmul_rn((float)ic3, inv255), c4 = __fmul_rn((float)ic4, inv255), c5 = __fmul_rn((float)ic5, inv255);
+#pragma unroll
+        for (int it = 0; it < 4; it++) {
+            float r = __fadd_rn(__fadd_rn(__fmul_rn(xr, c0), __fmul_rn(xg, c1)), __fmul_rn(xb, c2));
+            float g = __fadd_rn(__fadd_rn(__fmul_rn(xr, c1), __fmul_rn(xg, c3)), __fmul_rn(xb, c4));
+            float b = __fadd_rn(__fadd_rn(__fmul_rn(xr, c2), __fmul_rn(xg, c4)), __fmul_rn(xb, c5));
+            xr = r; xg = g; xb = b;
+        }
+        float k = fmaxf(fmaxf(fabsf(xr), fabsf(xg)), fabsf(xb));
+        if (k >= 2.0f) {
+            float m = __fdiv_rn(2048.0f, k);
+            saxis_r = __float2int_rz(__fmul_rn(xr, m));
+            saxis_g = __float2int_rz(__fmul_rn(xg, m));
+            saxis_b = __float2int_rz(__fmul_rn(xb, m));
+        }
+        saxis_r = (int)((uint32_t)saxis_r << 4);
+        saxis_g = (int)((uint32_t)saxis_g << 4);
+        saxis_b = (int)((uint32_t)saxis_b << 4);
+        int low_dot = 0x7FFFFFFF, high_dot = (int)0x80000000;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            int r = px[i] & 0xFF, g = (px[i] >> 8) & 0xFF, b = (px[i] >> 16) & 0xFF;
+            int dot = ((r * saxis_r + g * saxis_g + b * saxis_b) & ~0xF) + i;
+            low_dot = min(low_dot, dot);
+            high_dot = max(high_dot, dot);
+        }
+        uint32_t lc = 0, hc = 0;
+        const int low_c = low_dot & 15, high_c = high_dot & 15;
+#pragma unroll
+        for (int i = 0; i < 16; i++) { // register-array pick without dynamic indexing
+            if (i == low_c) lc = px[i];
+            if (i == high_c) hc = px[i];
+        }
+        e.lr = to_5(lc & 0xFF); e.lg = to_6((lc >> 8) & 0xFF); e.lb = to_5((lc >> 16) & 0xFF);
+        e.hr = to_5(hc & 0xFF); e.hg = to_6((hc >> 8) & 0xFF); e.hb = to_5((hc >> 16) & 0xFF);
+    }
+
+    uint32_t sels = bc1_find_sels4(px, e);
+
+    // ---- two least-squares passes (rgbcx.cpp:2333-2370; LS solve :727-773)
+#pragma unroll 1
+    for (int pass = 0; pass < 2; pass++) {
+        uint32_t wacc = 0, uq_r = 0, uq_g = 0, uq_b = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            uint32_t s = (sels >> (2 * i)) & 3;
+            // g_weight_vals4 = {0x000009, 0x010204, 0x040201, 0x090000}
+            wacc += s == 0 ? 0x000009u : s == 1 ? 0x010204u : s == 2 ? 0x040201u : 0x090000u;
+            uq_r += s * (px[i] & 0xFF);
+            uq_g += s * ((px[i] >> 8) & 0xFF);
+            uq_b += s * ((px[i] >> 16) & 0xFF);
+        }
+        const int q_r = total_r * 3 - (int)uq_r, q_g = total_g * 3 - (int)uq_g, q_b = total_b * 3 - (int)uq_b;
+        const float z00 = (float)((wacc >> 16) & 0xFF), z10 = (float)((wacc >> 8) & 0xFF), z11 = (float)(wacc & 0xFF);
+        float det = __fadd_rn(__fmul_rn(z00, z11), -__fmul_rn(z10, z10));
+        Bc1Ep t;
+        if (fabsf(det) < 1e-8f) {
+            // all selectors equal: treat as a solid block of the average colour (:2341-2350)
+            uint32_t mr = g_bc1_match5[avg_r], mg = g_bc1_match6[avg_g], mb = g_bc1_match5[avg_b];
+            t.lr = mr & 0xFF; t.lg = mg & 0xFF; t.lb = mb & 0xFF;
+            t.hr = mr >> 8; t.hg = mg >> 8; t.hb = mb >> 8;
+        } else {
+            det = __fdiv_rn(3.0f / 255.0f, det);
+            const float iz00 = __fmul_rn(z11, det), iz01 = __fmul_rn(-z10, det), iz10 = iz01, iz11 = __fmul_rn(z00, det);
+            const float fr_ = (float)uq_r, fg_ = (float)uq_g, fb_ = (float)uq_b;
+            const float qr = (float)q_r, qg = (float)q_g, qb = (float)q_b;
+            const float xl0 = __fadd_rn(__fmul_rn(iz00, fr_), __fmul_rn(iz01, qr));
+            const float xh0 = __fadd_rn(__fmul_rn(iz10, fr_), __fmul_rn(iz11, qr));
+            const float xl1 = __fadd_rn(__fmul_rn(iz00, fg_), __fmul_rn(iz01, qg));
+            const float xh1 = __fadd_rn(__fmul_rn(iz10, fg_), __fmul_rn(iz11, qg));
+            const float xl2 = __fadd_rn(__fmul_rn(iz00, fb_), __fmul_rn(iz01, qb));
+            const float xh2 = __fadd_rn(__fmul_rn(iz10, fb_), __fmul_rn(iz11, qb));
+            // call site passes (trial_h*, trial_l*) for (xl, xh): xl rounds into the HIGH endpoint (:2355)
+            round_565(xl0, xl1, xl2, t.hr, t.hg, t.hb);
+            round_565(xh0, xh1, xh2, t.lr, t.lg, t.lb);
+        }
+        if (e.lr == t.lr && e.lg == t.lg && e.lb == t.lb && e.hr == t.hr && e.hg == t.hg && e.hb == t.hb) break;
+        sels = bc1_find_sels4(px, t);
+        e = t;
+    }
+    return bc1_pack4(e, sels);
+}
+
+} // namespace hkbcn

@@ -1,0 +1,581 @@
+// bcn_decode.cu -- BC1..BC7 / BC6H surface decoders (sm_100a).
+//
+// Bit-exact contract with the decoders Hork wires behind Decode_BC*
+// (Hork/Image/ImageEncoders.cpp:77-136):
+//   BC1/2/3  bcdec__color_block / __sharp_alpha_block / __smooth_alpha_block (ThirdParty/bcdec/bcdec.h:93-210)
+//   BC4/5    bcdec__smooth_alpha_block                                         (bcdec.h:170-210, 264-272)
+//   BC6H     bcdec_bc6h_half / bcdec_bc6h_float                                 (bcdec.h:375-902)
+//   BC7      bc7decomp::unpack_bc7                                              (ThirdParty/bc7enc_rdo/bc7decomp.cpp:594-634)
+//
+// HBM-bound: 8/16 B in, 16..192 B out per block.  One thread decodes one block; the 32
+// threads of a warp hold 32 horizontally adjacent blocks, so each of the 4 row stores of a
+// warp is one contiguous run (32 x 16 B = 512 B for RGBA8) written with 128-bit stores --
+// no shared-memory transpose needed.  BC4 packs 4 blocks per thread to reach 128-bit stores.
+#include "hkbcn_common.cuh"
+#include "hkbcn_kernels.h"
+#include "bcn_tables.cuh"
+
+namespace hkbcn {
+
+// ---------------------------------------------------------------- BC1 colour block
+// bcdec.h:93-151.  out[i] = 0xAABBGGRR of pixel i.
+__device__ __forceinline__ void decode_color_block(uint2 blk, bool onlyOpaque, uint32_t out[16])
+{
+    uint32_t c0 = blk.x & 0xFFFF, c1 = blk.x >> 16;
+    uint32_t r0 = (((c0 >> 11) & 0x1F) * 527 + 23) >> 6;
+    uint32_t g0 = (((c0 >> 5) & 0x3F) * 259 + 33) >> 6;
+    uint32_t b0 = ((c0 & 0x1F) * 527 + 23) >> 6;
+    uint32_t r1 = (((c1 >> 11) & 0x1F) * 527 + 23) >> 6;
+    uint32_t g1 = (((c1 >> 5) & 0x3F) * 259 + 33) >> 6;
+    uint32_t b1 = ((c1 & 0x1F) * 527 + 23) >> 6;
+    uint32_t ref[4];
+    ref[0] = 0xFF000000u | (b0 << 16) | (g0 << 8) | r0;
+    ref[1] = 0xFF000000u | (b1 << 16) | (g1 << 8) | r1;
+    if (c0 > c1 || onlyOpaque) {
+        ref[2] = 0xFF000000u | (((2 * b0 + b1 + 1) / 3) << 16) | (((2 * g0 + g1 + 1) / 3) << 8) | ((2 * r0 + r1 + 1) / 3);
+        ref[3] = 0xFF000000u | (((b0 + 2 * b1 + 1) / 3) << 16) | (((g0 + 2 * g1 + 1) / 3) << 8) | ((r0 + 2 * r1 + 1) / 3);
+    } else {
+        ref[2] = 0xFF000000u | (((b0 + b1 + 1) >> 1) << 16) | (((g0 + g1 + 1) >> 1) << 8) | ((r0 + r1 + 1) >> 1);
+        ref[3] = 0;
+    }
+    uint32_t idx = blk.y;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t s = (idx >> (2 * i)) & 3;
+        out[i] = s == 0 ? ref[0] : s == 1 ? ref[1] : s == 2 ? ref[2] : ref[3];
+    }
+}
+
+// bcdec.h:170-210: 8-entry alpha palette + 16 x 3-bit indices.
+__device__ __forceinline__ void decode_smooth_alpha(uint2 blk, uint32_t out[16])
+{
+    uint32_t a0 = blk.x & 0xFF, a1 = (blk.x >> 8) & 0xFF;
+    uint32_t a[8];
+    a[0] = a0;
+    a[1] = a1;
+    if (a0 > a1) {
+        a[2] = (6 * a0 + a1 + 1) / 7;
+        a[3] = (5 * a0 + 2 * a1 + 1) / 7;
+        a[4] = (4 * a0 + 3 * a1 + 1) / 7;
+        a[5] = (3 * a0 + 4 * a1 + 1) / 7;
+        a[6] = (2 * a0 + 5 * a1 + 1) / 7;
+        a[7] = (a0 + 6 * a1 + 1) / 7;
+    } else {
+        a[2] = (4 * a0 + a1 + 1) / 5;
+        a[3] = (3 * a0 + 2 * a1 + 1) / 5;
+        a[4] = (2 * a0 + 3 * a1 + 1) / 5;
+        a[5] = (a0 + 4 * a1 + 1) / 5;
+        a[6] = 0;
+        a[7] = 255;
+    }
+    // pack the palette into two registers so the per-pixel pick is a byte-permute
+    uint32_t plo = a[0] | (a[1] << 8) | (a[2] << 16) | (a[3] << 24);
+    uint32_t phi = a[4] | (a[5] << 8) | (a[6] << 16) | (a[7] << 24);
+    uint64_t idx = (((uint64_t)blk.y << 32) | blk.x) >> 16;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t s = (uint32_t)(idx >> (3 * i)) & 7;
+        out[i] = __byte_perm(plo, phi, s) & 0xFF;
+    }
+}
+
+// ---------------------------------------------------------------- BC7
+struct Bits128 {
+    uint64_t lo, hi;
+    uint32_t pos;
+    __device__ __forceinline__ uint32_t read(uint32_t n)
+    {
+        // n in [0, 8]
+        uint64_t v;
+        if (pos >= 64) v = hi >> (pos - 64);
+        else if (pos == 0) v = lo;
+        else v = (lo >> pos) | (hi << (64 - pos));
+        pos += n;
+        return (uint32_t)v & ((1u << n) - 1u);
+    }
+};
+
+__device__ __forceinline__ uint32_t bc7_weight(uint32_t bits, uint32_t i)
+{
+    // g_bc7_weights2/3/4 (bc7decomp.cpp:31-33), nibble/byte packed
+    if (bits == 2) return (0x402B1500u >> (8 * i)) & 0xFF;                        // 0,21,43,64
+    if (bits == 3) return (uint32_t)((0x40372E251B120900ull >> (8 * i)) & 0xFF);  // 0,9,18,27,37,46,55,64
+    const uint64_t lo = 0x1E1A15110D090400ull, hi = 0x403C37332F2B2622ull;        // 0,4,9,...,64
+    return (uint32_t)(((i < 8 ? lo : hi) >> (8 * (i & 7))) & 0xFF);
+}
+
+// bc7decomp.cpp:168-634 semantics; out[i] = 0xAABBGGRR.
+__device__ void decode_bc7_block(uint4 blk, uint32_t out[16])
+{
+    uint32_t b0 = blk.x & 0xFF;
+    if (b0 == 0) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) out[i] = 0;
+        return;
+    }
+    const uint32_t mode = __ffs(b0) - 1;
+    // per-mode format constants, nibble packed (index = mode)
+    const uint32_t NS = (0x21112323u >> (4 * mode)) & 0xF;   // subsets          3,2,3,2,1,1,1,2
+    const uint32_t PB = (0x60006664u >> (4 * mode)) & 0xF;   // partition bits   4,6,6,6,0,0,0,6
+    const uint32_t CB = (0x57757564u >> (4 * mode)) & 0xF;   // colour bits      4,6,5,7,5,7,7,5
+    const uint32_t AB = (0x57860000u >> (4 * mode)) & 0xF;   // alpha bits       0,0,0,0,6,8,7,5
+    const uint32_t IB = (0x24222233u >> (4 * mode)) & 0xF;   // index bits       3,3,2,2,2,2,4,2
+    const uint32_t IB2 = (0x00230000u >> (4 * mode)) & 0xF;  // 2nd index bits   0,0,0,0,3,2,0,0
+    const bool uniqueP = (0xC9u >> mode) & 1;                // modes 0,3,6,7
+    const bool sharedP = mode == 1;
+
+    Bits128 bs;
+    bs.lo = ((uint64_t)blk.y << 32) | blk.x;
+    bs.hi = ((uint64_t)blk.w << 32) | blk.z;
+    bs.pos = mode + 1;
+    const uint32_t part = bs.read(PB);
+    uint32_t rot = 0, idxSel = 0;
+    if (mode == 4 || mode == 5) rot = bs.read(2);
+    if (mode == 4) idxSel = bs.read(1);
+
+    const uint32_t NE = NS * 2;
+    uint32_t ep[6][4]; // [endpoint][channel]
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint32_t nb = c < 3 ? CB : AB;
+#pragma unroll
+        for (int e = 0; e < 6; e++) {
+            if ((uint32_t)e < NE) ep[e][c] = nb ? bs.read(nb) : 255u;
+        }
+    }
+    uint32_t pbits[6];
+#pragma unroll
+    for (int e = 0; e < 6; e++) pbits[e] = 0;
+    if (uniqueP) {
+#pragma unroll
+        for (int e = 0; e < 6; e++)
+            if ((uint32_t)e < NE) pbits[e] = bs.read(1);
+    } else if (sharedP) {
+        uint32_t p0 = bs.read(1), p1 = bs.read(1);
+        pbits[0] = pbits[1] = p0;
+        pbits[2] = pbits[3] = p1;
+    }
+    const bool hasP = uniqueP || sharedP;
+#pragma unroll
+    for (int e = 0; e < 6; e++) {
+        if ((uint32_t)e >= NE) continue;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t nb = c < 3 ? CB : AB;
+            if (nb == 0) continue; // alpha stays 255
+            uint32_t v = ep[e][c], tb = nb;
+            if (hasP) {
+                v = (v << 1) | pbits[e];
+                tb = nb + 1;
+            }
+            v <<= (8 - tb);
+            v |= v >> tb;
+            ep[e][c] = v;
+        }
+    }
+
+    // subsets and anchors
+    uint32_t subsetMask = 0; // 2 bits per pixel
+    uint32_t anchor1 = 0xFF, anchor2 = 0xFF;
+    if (NS == 2) {
+        uint32_t m = kShape2[part];
+#pragma unroll
+        for (int i = 0; i < 16; i++) subsetMask |= ((m >> i) & 1u) << (2 * i);
+        anchor1 = kAnchor2[part];
+    } else if (NS == 3) {
+        subsetMask = kShape3[part];
+        anchor1 = kAnchor3a[part];
+        anchor2 = kAnchor3b[part];
+    }
+
+    uint32_t idx1[16], idx2[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t n = IB - ((i == 0 || (uint32_t)i == anchor1 || (uint32_t)i == anchor2) ? 1u : 0u);
+        idx1[i] = bs.read(n);
+    }
+    if (IB2) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) idx2[i] = bs.read(IB2 - (i == 0 ? 1u : 0u));
+    }
+
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const uint32_t s = (subsetMask >> (2 * i)) & 3;
+        uint32_t l[4], h[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            l[c] = s == 0 ? ep[0][c] : s == 1 ? ep[2][c] : ep[4][c];
+            h[c] = s == 0 ? ep[1][c] : s == 1 ? ep[3][c] : ep[5][c];
+        }
+        uint32_t cw, aw;
+        if (IB2 == 0) {
+            cw = aw = bc7_weight(IB, idx1[i]);
+        } else if (idxSel) {
+            // mode 4, index selection bit set: colour uses the 3-bit set, alpha the 2-bit set
+            cw = bc7_weight(IB2, idx2[i]);
+            aw = bc7_weight(IB, idx1[i]);
+        } else {
+            cw = bc7_weight(IB, idx1[i]);
+            aw = bc7_weight(IB2, idx2[i]);
+        }
+        uint32_t r = (l[0] * (64 - cw) + h[0] * cw + 32) >> 6;
+        uint32_t g = (l[1] * (64 - cw) + h[1] * cw + 32) >> 6;
+        uint32_t b = (l[2] * (64 - cw) + h[2] * cw + 32) >> 6;
+        uint32_t a = (l[3] * (64 - aw) + h[3] * aw + 32) >> 6;
+        if (rot == 1) { uint32_t t = a; a = r; r = t; }
+        else if (rot == 2) { uint32_t t = a; a = g; g = t; }
+        else if (rot == 3) { uint32_t t = a; a = b; b = t; }
+        out[i] = r | (g << 8) | (b << 16) | (a << 24);
+    }
+}
+
+// ---------------------------------------------------------------- BC6H
+// Header bit layouts of the 14 BC6H modes (D3D11 BC6H format), as token strings
+// "<field><lsb>[:<count>][r]": field in {rw,rx,ry,rz,gw,..,bz,d}; the bits are consumed
+// from the block LSB-first right after the 2/5 mode bits; 'r' = the bits arrive MSB-first
+// (bcdec__bitstream_read_bits_r, bcdec.h:235-246).  Parsed once on the host into
+// g_bc6h_layout (uint16 per token: field | lsb<<4 | count<<8 | rev<<12).
+static const char* const kBc6hLayoutStr[14] = {
+    /* 1  00    */ "gy4,by4,bz4,rw0:10,gw0:10,bw0:10,rx0:5,gz4,gy0:4,gx0:5,bz0,gz0:4,bx0:5,bz1,by0:4,ry0:5,bz2,rz0:5,bz3,d0:5",
+    /* 2  01    */ "gy5,gz4,gz5,rw0:7,bz0,bz1,by4,gw0:7,by5,bz2,gy4,bw0:7,bz3,bz5,bz4,rx0:6,gy0:4,gx0:6,gz0:4,bx0:6,by0:4,ry0:6,rz0:6,d0:5",
+    /* 3  00010 */ "rw0:10,gw0:10,bw0:10,rx0:5,rw10,gy0:4,gx0:4,gw10,bz0,gz0:4,bx0:4,bw10,bz1,by0:4,ry0:5,bz2,rz0:5,bz3,d0:5",
+    /* 4  00110 */ "rw0:10,gw0:10,bw0:10,rx0:4,rw10,gz4,gy0:4,gx0:5,gw10,gz0:4,bx0:4,bw10,bz1,by0:4,ry0:4,bz0,bz2,rz0:4,gy4,bz3,d0:5",
+    /* 5  01010 */ "rw0:10,gw0:10,bw0:10,rx0:4,rw10,by4,gy0:4,gx0:4,gw10,bz0,gz0:4,bx0:5,bw10,by0:4,ry0:4,bz1,bz2,rz0:4,bz4,bz3,d0:5",
+    /* 6  01110 */ "rw0:9,by4,gw0:9,gy4,bw0:9,bz4,rx0:5,gz4,gy0:4,gx0:5,bz0,gz0:4,bx0:5,bz1,by0:4,ry0:5,bz2,rz0:5,bz3,d0:5",
+    /* 7  10010 */ "rw0:8,gz4,by4,gw0:8,bz2,gy4,bw0:8,bz3,bz4,rx0:6,gy0:4,gx0:5,bz0,gz0:4,bx0:5,bz1,by0:4,ry0:6,rz0:6,d0:5",
+    /* 8  10110 */ "rw0:8,bz0,by4,gw0:8,gy5,gy4,bw0:8,gz5,bz4,rx0:5,gz4,gy0:4,gx0:6,gz0:4,bx0:5,bz1,by0:4,ry0:5,bz2,rz0:5,bz3,d0:5",
+    /* 9  11010 */ "rw0:8,bz1,by4,gw0:8,by5,gy4,bw0:8,bz5,bz4,rx0:5,gz4,gy0:4,gx0:5,bz0,gz0:4,bx0:6,by0:4,ry0:5,bz2,rz0:5,bz3,d0:5",
+    /* 10 11110 */ "rw0:6,gz4,bz0,bz1,by4,gw0:6,gy5,by5,bz2,gy4,bw0:6,gz5,bz3,bz5,bz4,rx0:6,gy0:4,gx0:6,gz0:4,bx0:6,by0:4,ry0:6,rz0:6,d0:5",
+    /* 11 00011 */ "rw0:10,gw0:10,bw0:10,rx0:10,gx0:10,bx0:10",
+    /* 12 00111 */ "rw0:10,gw0:10,bw0:10,rx0:9,rw10,gx0:9,gw10,bx0:9,bw10",
+    /* 13 01011 */ "rw0:10,gw0:10,bw0:10,rx0:8,rw10:2r,gx0:8,gw10:2r,bx0:8,bw10:2r",
+    /* 14 01111 */ "rw0:10,gw0:10,bw0:10,rx0:4,rw10:6r,gx0:4,gw10:6r,bx0:4,bw10:6r",
+};
+#define BC6H_MAX_TOKENS 28
+__device__ uint16_t g_bc6h_layout[14 * BC6H_MAX_TOKENS];
+
+cudaError_t decode_upload_tables()
+{
+    uint16_t tab[14 * BC6H_MAX_TOKENS];
+    for (int m = 0; m < 14; m++) {
+        const char* s = kBc6hLayoutStr[m];
+        int n = 0;
+        while (*s) {
+            int ch = (*s == 'r') ? 0 : (*s == 'g') ? 1 : (*s == 'b') ? 2 : 3;
+            int field;
+            if (ch == 3) { field = 12; s += 1; }
+            else { int w = s[1] == 'w' ? 0 : s[1] == 'x' ? 1 : s[1] == 'y' ? 2 : 3; field = ch * 4 + w; s += 2; }
+            int lsb = 0, cnt = 1, rev = 0;
+            while (*s >= '0' && *s <= '9') lsb = lsb * 10 + (*s++ - '0');
+            if (*s == ':') { s++; cnt = 0; while (*s >= '0' && *s <= '9') cnt = cnt * 10 + (*s++ - '0'); }
+            if (*s == 'r') { rev = 1; s++; }
+            if (*s == ',') s++;
+            tab[m * BC6H_MAX_TOKENS + n++] = (uint16_t)(field | (lsb << 4) | (cnt << 8) | (rev << 12));
+        }
+        for (; n < BC6H_MAX_TOKENS; n++) tab[m * BC6H_MAX_TOKENS + n] = 0xFFFF;
+    }
+    return cudaMemcpyToSymbol(g_bc6h_layout, tab, sizeof(tab));
+}
+
+// bcdec.h:289-329
+__device__ __forceinline__ int bc6h_unquantize(int val, int bits, bool isSigned)
+{
+    int unq;
+    if (!isSigned) {
+        if (bits >= 15) unq = val;
+        else if (val == 0) unq = 0;
+        else if (val == ((1 << bits) - 1)) unq = 0xFFFF;
+        else unq = ((val << 16) + 0x8000) >> bits;
+    } else {
+        if (bits >= 16) unq = val;
+        else {
+            int s = 0;
+            if (val < 0) { s = 1; val = -val; }
+            if (val == 0) unq = 0;
+            else if (val >= ((1 << (bits - 1)) - 1)) unq = 0x7FFF;
+            else unq = ((val << 15) + 0x4000) >> (bits - 1);
+            if (s) unq = -unq;
+        }
+    }
+    return unq;
+}
+// bcdec.h:331-346
+__device__ __forceinline__ uint32_t bc6h_finish(int val, bool isSigned)
+{
+    if (!isSigned) return (uint32_t)((val * 31) >> 6) & 0xFFFF;
+    val = (val < 0) ? -(((-val) * 31) >> 5) : (val * 31) >> 5;
+    uint32_t s = 0;
+    if (val < 0) { s = 0x8000; val = -val; }
+    return (s | (uint32_t)val) & 0xFFFF;
+}
+__device__ __forceinline__ int sext(int v, int bits) { return (v << (32 - bits)) >> (32 - bits); }
+
+// bcdec__half_to_float_quick (bcdec.h:348-373): exact half -> float, Inf/NaN payload kept.
+__device__ __forceinline__ uint32_t half_bits_to_float_bits(uint32_t h)
+{
+    uint32_t em = h & 0x7FFF, sign = (h & 0x8000) << 16;
+    uint32_t e = em >> 10;
+    uint32_t o;
+    if (e == 31) o = (em << 13) + ((127 - 15) << 23) + ((128 - 16) << 23);
+    else if (e == 0) o = __float_as_uint((float)em * 5.9604644775390625e-8f); // m * 2^-24, exact
+    else o = (em << 13) + ((127 - 15) << 23);
+    return o | sign;
+}
+
+// out[i*3+c] = half bits of pixel i channel c.  `lay` = layout table in shared memory.
+__device__ void decode_bc6h_block(uint4 blk, bool isSigned, const uint16_t* lay, uint16_t out[48])
+{
+    Bits128 bs;
+    bs.lo = ((uint64_t)blk.y << 32) | blk.x;
+    bs.hi = ((uint64_t)blk.w << 32) | blk.z;
+    bs.pos = 0;
+    uint32_t code = bs.read(2);
+    if (code > 1) code |= bs.read(3) << 2;
+    // 5-bit code -> mode index 0..13 (-1 reserved)
+    int mode;
+    if (code < 2) mode = (int)code;
+    else if ((code & 3) == 2) mode = 2 + (int)(code >> 2);      // 00010,00110,...,11110 -> 2..9
+    else if (code < 16) mode = 10 + (int)(code >> 2);           // 00011,00111,01011,01111 -> 10..13
+    else mode = -1;                                             // 10011,10111,11011,11111
+    if (mode < 0) {
+#pragma unroll
+        for (int i = 0; i < 48; i++) out[i] = 0;
+        return;
+    }
+    int f[13];
+#pragma unroll
+    for (int i = 0; i < 13; i++) f[i] = 0;
+    const uint16_t* t = lay + mode * BC6H_MAX_TOKENS;
+#pragma unroll 1
+    for (int k = 0; k < BC6H_MAX_TOKENS; k++) {
+        uint32_t tk = t[k];
+        if (tk == 0xFFFF) break;
+        uint32_t field = tk & 15, lsb = (tk >> 4) & 15, cnt = (tk >> 8) & 15, rev = tk >> 12;
+        uint32_t v = bs.read(cnt);
+        if (rev) v = __brev(v) >> (32 - cnt);
+        v <<= lsb;
+        // dynamic register-array index avoided: predicated select over the 13 fields
+#pragma unroll
+        for (int i = 0; i < 13; i++)
+            if (field == (uint32_t)i) f[i] |= (int)v;
+    }
+    // actual_bits_count (bcdec.h:376-381), nibble packed per mode (W-1 stored for W to fit 16)
+    const int W = (int)((0xFBA957778AAA69ull >> (4 * mode)) & 0xF) + 1; // 10,7,11,11,11,9,8,8,8,6,10,11,12,16
+    const int dR = (int)((0x489A6556544565ull >> (4 * mode)) & 0xF);     // 5,6,5,4,4,5,6,5,5,6,10,9,8,4
+    const int dG = (int)((0x489A6565545465ull >> (4 * mode)) & 0xF);     // 5,6,4,5,4,5,5,6,5,6,10,9,8,4
+    const int dB = (int)((0x489A6655554465ull >> (4 * mode)) & 0xF);     // 5,6,4,4,5,5,5,5,6,6,10,9,8,4
+    const bool two = mode < 10;
+    const int part = two ? f[12] : 0;
+    const int ne = two ? 4 : 2;
+
+    if (isSigned) {
+        f[0] = sext(f[0], W);
+        f[4] = sext(f[4], W);
+        f[8] = sext(f[8], W);
+    }
+    const bool transformed = (mode != 9 && mode != 10);
+    if (transformed || isSigned) {
+#pragma unroll
+        for (int i = 1; i < 4; i++) {
+            if (i < ne) {
+                f[i] = sext(f[i], dR);
+                f[4 + i] = sext(f[4 + i], dG);
+                f[8 + i] = sext(f[8 + i], dB);
+            }
+        }
+    }
+    if (transformed) {
+        const int mask = (1 << W) - 1;
+#pragma unroll
+        for (int i = 1; i < 4; i++) {
+            if (i < ne) {
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    int v = (f[c * 4 + i] + f[c * 4]) & mask;
+                    if (isSigned) v = sext(v, W);
+                    f[c * 4 + i] = v;
+                }
+            }
+        }
+    }
+    int ep[3][4];
+#pragma unroll
+    for (int c = 0; c < 3; c++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) ep[c][i] = (i < ne) ? bc6h_unquantize(f[c * 4 + i], W, isSigned) : 0;
+
+    const uint32_t shape = two ? kShape2[part] : 0;
+    const uint32_t anchor = two ? kAnchor2[part] : 0xFF;
+    const uint32_t ib = two ? 3 : 4;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t n = ib - ((i == 0 || (uint32_t)i == anchor) ? 1u : 0u);
+        uint32_t idx = bs.read(n);
+        int w = (int)bc7_weight(ib, idx); // aWeight3 / aWeight4 == the BC7 3/4-bit weights
+        int s = (shape >> i) & 1;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            int a = s ? ep[c][2] : ep[c][0];
+            int b = s ? ep[c][3] : ep[c][1];
+            int v = (a * (64 - w) + b * w + 32) >> 6;
+            out[i * 3 + c] = (uint16_t)bc6h_finish(v, isSigned);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- kernels
+// One thread = one block.  VEC = destination rows may be written with vector stores.
+template <int CODEC, bool VEC>
+__global__ void __launch_bounds__(256) decode_kernel(const DecodeParams P)
+{
+    __shared__ uint16_t s_lay[CODEC == C_BC6H ? 14 * BC6H_MAX_TOKENS : 1];
+    if (CODEC == C_BC6H) {
+        for (int i = threadIdx.x; i < 14 * BC6H_MAX_TOKENS; i += blockDim.x) s_lay[i] = g_bc6h_layout[i];
+        __syncthreads();
+    }
+    for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < P.nblocks; b += gridDim.x * blockDim.x) {
+        const uint32_t by = b / P.nbx, bx = b - by * P.nbx;
+        uint8_t* drow = P.dst + (size_t)by * 4 * P.dstRowStride;
+
+        if (CODEC == C_BC1 || CODEC == C_BC2 || CODEC == C_BC3 || CODEC == C_BC7) {
+            uint32_t px[16];
+            if (CODEC == C_BC1) {
+                uint2 blk = __ldg((const uint2*)P.src + b);
+                decode_color_block(blk, false, px);
+            } else if (CODEC == C_BC7) {
+                uint4 blk = __ldg((const uint4*)P.src + b);
+                decode_bc7_block(blk, px);
+            } else {
+                uint4 blk = __ldg((const uint4*)P.src + b);
+                decode_color_block(make_uint2(blk.z, blk.w), true, px);
+                if (CODEC == C_BC2) {
+                    // bcdec__sharp_alpha_block (bcdec.h:153-168): 4-bit alpha * 17
+                    uint64_t a = ((uint64_t)blk.y << 32) | blk.x;
+#pragma unroll
+                    for (int i = 0; i < 16; i++) px[i] = (px[i] & 0x00FFFFFFu) | ((((uint32_t)(a >> (4 * i)) & 0xF) * 17u) << 24);
+                } else {
+                    uint32_t al[16];
+                    decode_smooth_alpha(make_uint2(blk.x, blk.y), al);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) px[i] = (px[i] & 0x00FFFFFFu) | (al[i] << 24);
+                }
+            }
+            uint8_t* d = drow + (size_t)bx * 16;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (VEC) *(uint4*)(d + r * P.dstRowStride) = make_uint4(px[r * 4], px[r * 4 + 1], px[r * 4 + 2], px[r * 4 + 3]);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        uint8_t* q = d + r * P.dstRowStride + j * 4;
+                        uint32_t v = px[r * 4 + j];
+                        q[0] = v; q[1] = v >> 8; q[2] = v >> 16; q[3] = v >> 24;
+                    }
+                }
+            }
+        } else if (CODEC == C_BC4) {
+            uint32_t v[16];
+            decode_smooth_alpha(__ldg((const uint2*)P.src + b), v);
+            uint8_t* d = drow + (size_t)bx * 4;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                uint32_t w = v[r * 4] | (v[r * 4 + 1] << 8) | (v[r * 4 + 2] << 16) | (v[r * 4 + 3] << 24);
+                if (VEC) *(uint32_t*)(d + r * P.dstRowStride) = w;
+                else {
+                    uint8_t* q = d + r * P.dstRowStride;
+                    q[0] = w; q[1] = w >> 8; q[2] = w >> 16; q[3] = w >> 24;
+                }
+            }
+        } else if (CODEC == C_BC5) {
+            uint4 blk = __ldg((const uint4*)P.src + b);
+            uint32_t v0[16], v1[16];
+            decode_smooth_alpha(make_uint2(blk.x, blk.y), v0);
+            decode_smooth_alpha(make_uint2(blk.z, blk.w), v1);
+            uint8_t* d = drow + (size_t)bx * 8;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                uint32_t w0 = v0[r * 4] | (v1[r * 4] << 8) | (v0[r * 4 + 1] << 16) | (v1[r * 4 + 1] << 24);
+                uint32_t w1 = v0[r * 4 + 2] | (v1[r * 4 + 2] << 8) | (v0[r * 4 + 3] << 16) | (v1[r * 4 + 3] << 24);
+                if (VEC) *(uint2*)(d + r * P.dstRowStride) = make_uint2(w0, w1);
+                else {
+                    uint8_t* q = d + r * P.dstRowStride;
+                    q[0] = w0; q[1] = w0 >> 8; q[2] = w0 >> 16; q[3] = w0 >> 24;
+                    q[4] = w1; q[5] = w1 >> 8; q[6] = w1 >> 16; q[7] = w1 >> 24;
+                }
+            }
+        } else { // BC6H -> RGB16F / RGB32F
+            uint16_t h[48];
+            decode_bc6h_block(__ldg((const uint4*)P.src + b), P.is_signed != 0, s_lay, h);
+            if (!P.f32out) {
+                uint8_t* d = drow + (size_t)bx * 24;
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    uint8_t* q = d + r * P.dstRowStride;
+                    if (VEC) {
+#pragma unroll
+                        for (int j = 0; j < 3; j++) {
+                            const uint16_t* s = h + r * 12 + j * 4;
+                            ((uint2*)q)[j] = make_uint2(s[0] | ((uint32_t)s[1] << 16), s[2] | ((uint32_t)s[3] << 16));
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 12; j++) { q[2 * j] = h[r * 12 + j] & 0xFF; q[2 * j + 1] = h[r * 12 + j] >> 8; }
+                    }
+                }
+            } else {
+                uint8_t* d = drow + (size_t)bx * 48;
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    uint8_t* q = d + r * P.dstRowStride;
+                    if (VEC) {
+#pragma unroll
+                        for (int j = 0; j < 3; j++) {
+                            const uint16_t* s = h + r * 12 + j * 4;
+                            ((uint4*)q)[j] = make_uint4(half_bits_to_float_bits(s[0]), half_bits_to_float_bits(s[1]),
+                                                         half_bits_to_float_bits(s[2]), half_bits_to_float_bits(s[3]));
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 12; j++) {
+                            uint32_t v = half_bits_to_float_bits(h[r * 12 + j]);
+                            uint8_t* qq = q + 4 * j;
+                            qq[0] = v; qq[1] = v >> 8; qq[2] = v >> 16; qq[3] = v >> 24;
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int CODEC>
+static cudaError_t launch_decode_t(const DecodeParams& P, int sm_count, cudaStream_t stream)
+{
+    // required alignment of a destination row segment for the vector path
+    size_t need = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 8 : (CODEC == C_BC6H) ? (P.f32out ? 16 : 8) : 16;
+    bool vec = (((size_t)P.dst % need) == 0) && ((P.dstRowStride % need) == 0);
+    uint32_t ctas = (P.nblocks + 255) / 256;
+    uint32_t cap = (uint32_t)sm_count * 8 * 4; // a few waves of 8 CTAs/SM; grid-stride beyond that
+    if (ctas > cap) ctas = cap;
+    if (ctas == 0) return cudaSuccess;
+    if (vec) decode_kernel<CODEC, true><<<ctas, 256, 0, stream>>>(P);
+    else decode_kernel<CODEC, false><<<ctas, 256, 0, stream>>>(P);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_decode(const DecodeParams& P, int sm_count, cudaStream_t stream)
+{
+    switch (P.codec) {
+    case C_BC1: return launch_decode_t<C_BC1>(P, sm_count, stream);
+    case C_BC2: return launch_decode_t<C_BC2>(P, sm_count, stream);
+    case C_BC3: return launch_decode_t<C_BC3>(P, sm_count, stream);
+    case C_BC4: return launch_decode_t<C_BC4>(P, sm_count, stream);
+    case C_BC5: return launch_decode_t<C_BC5>(P, sm_count, stream);
+    case C_BC6H: return launch_decode_t<C_BC6H>(P, sm_count, stream);
+    case C_BC7: return launch_decode_t<C_BC7>(P, sm_count, stream);
+    }
+    return cudaErrorInvalidValue;
+}
+
+} // namespace hkbcn

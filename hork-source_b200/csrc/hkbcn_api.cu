@@ -1,0 +1,446 @@
+// hkbcn_api.cu -- the C-ABI layer (include/hkbcn.h) over the sm_100a kernels.
+//
+// Host side of the drop-in boundary for Hk::TextureBlockCompression
+// (Hork/Image/ImageEncoders.h:37-87).  Owns per-device state (stream, lazily grown
+// device scratch), builds the launch descriptors, moves host buffers, and reports
+// errors as status codes -- the reference's functions return void and cannot fail;
+// this path can (no device, out of memory) and never falls back to the CPU.
+#include "../../include/hkbcn.h"
+#include "hkbcn_kernels.h"
+
+#include <atomic>
+#include <mutex>
+#include <thread>
+#include <vector>
+#include <string>
+#include <algorithm>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+using namespace hkbcn;
+
+namespace {
+
+thread_local char t_err[512] = "";
+void set_err(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof(t_err), fmt, ap);
+    va_end(ap);
+}
+
+struct Device {
+    int          id = -1;
+    int          sm_count = 0;
+    cudaStream_t stream = nullptr;
+    void*        d_src = nullptr; size_t src_cap = 0;
+    void*        d_dst = nullptr; size_t dst_cap = 0;
+    std::mutex   mu; // serialises host-pointer calls that share the scratch buffers
+};
+
+std::mutex            g_mu;
+bool                  g_init = false;
+std::vector<Device*>  g_devs;      // selected devices
+std::atomic<uint64_t> g_launches{0};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            set_err("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);   \
+            return HKBCN_ERR_CUDA;                                                                 \
+        }                                                                                          \
+    } while (0)
+
+int codec_of(int fmt)
+{
+    switch (fmt) {
+    case HKBCN_BC1_UNORM: case HKBCN_BC1_UNORM_SRGB: return C_BC1;
+    case HKBCN_BC2_UNORM: case HKBCN_BC2_UNORM_SRGB: return C_BC2;
+    case HKBCN_BC3_UNORM: case HKBCN_BC3_UNORM_SRGB: return C_BC3;
+    case HKBCN_BC4_UNORM: case HKBCN_BC4_SNORM: return C_BC4;
+    case HKBCN_BC5_UNORM: case HKBCN_BC5_SNORM: return C_BC5;
+    case HKBCN_BC6H_UFLOAT: case HKBCN_BC6H_SFLOAT: return C_BC6H;
+    case HKBCN_BC7_UNORM: case HKBCN_BC7_UNORM_SRGB: return C_BC7;
+    }
+    return -1;
+}
+int blk_bytes(int codec) { return (codec == C_BC1 || codec == C_BC4) ? 8 : 16; }
+int src_bpp(int codec, uint32_t flags)
+{
+    switch (codec) {
+    case C_BC4: return 1;
+    case C_BC5: return 2;
+    case C_BC6H: return (flags & HKBCN_FLAG_SRC_F16) ? 8 : 16;
+    default: return 4;
+    }
+}
+int dst_bpp(int codec, uint32_t flags)
+{
+    switch (codec) {
+    case C_BC4: return 1;
+    case C_BC5: return 2;
+    case C_BC6H: return (flags & HKBCN_FLAG_DST_F32) ? 12 : 6;
+    default: return 4;
+    }
+}
+uint32_t tile_blocks(int codec)
+{
+    switch (codec) {
+    case C_BC4: return bc45_tile_blocks(1);
+    case C_BC5: return bc45_tile_blocks(2);
+    case C_BC1: case C_BC2: case C_BC3: return bc123_tile_blocks(codec);
+    case C_BC7: return bc7_tile_blocks();
+    case C_BC6H: return bc6h_tile_blocks();
+    }
+    return 64;
+}
+
+int ensure_init()
+{
+    if (g_init) return HKBCN_OK;
+    return hkbcn_init(0);
+}
+
+Device* dev_at(int i) { return (i >= 0 && i < (int)g_devs.size()) ? g_devs[i] : nullptr; }
+
+int grow(void** p, size_t* cap, size_t need)
+{
+    if (*cap >= need) return HKBCN_OK;
+    if (*p) { cudaFree(*p); *p = nullptr; *cap = 0; }
+    size_t want = std::max(need, (size_t)1 << 20);
+    CK(cudaMalloc(p, want));
+    *cap = want;
+    return HKBCN_OK;
+}
+
+// Append one surface to a launch descriptor.
+void add_level(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h)
+{
+    Level& L = P.lv[P.nLevels++];
+    const uint32_t bpp = src_bpp(codec, flags);
+    const uint32_t tb = tile_blocks(codec);
+    L.src = (const uint8_t*)src;
+    L.dst = (uint8_t*)dst;
+    L.nbx = w / 4;
+    L.nblocks = (w / 4) * (h / 4);
+    L.rowStride = w * bpp;
+    L.tileBase = P.totalTiles;
+    // TMA bulk path: base 16-B aligned and every block-row segment a multiple of 16 B
+    L.bulkOk = (((size_t)src & 15) == 0 && ((L.nbx * 4 * bpp) & 15) == 0 && (L.rowStride & 15) == 0) ? 1u : 0u;
+    L.pad = 0;
+    P.totalTiles += (L.nblocks + tb - 1) / tb;
+}
+
+int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P, cudaStream_t st)
+{
+    if (P.totalTiles == 0) return HKBCN_OK;
+    cudaError_t e = cudaSuccess;
+    switch (codec) {
+    case C_BC4: e = launch_bc45_encode(1, P, D->sm_count, st); break;
+    case C_BC5: e = launch_bc45_encode(2, P, D->sm_count, st); break;
+    case C_BC1: case C_BC2: case C_BC3: e = launch_bc123_encode(codec, P, D->sm_count, st); break;
+    case C_BC7: e = launch_bc7_encode(P, D->sm_count, st); break;
+    case C_BC6H: e = launch_bc6h_encode(fmt == HKBCN_BC6H_SFLOAT, (P.flags & HKBCN_FLAG_SRC_F16) != 0, P, D->sm_count, st); break;
+    default: set_err("bad codec"); return HKBCN_ERR_BAD_FORMAT;
+    }
+    if (e == cudaErrorNotSupported) { set_err("encoder for format %d not built yet", fmt); return HKBCN_ERR_UNSUPPORTED; }
+    if (e != cudaSuccess) { set_err("kernel launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+// level i of a chain: max(w>>i,4) x max(h>>i,4) texels (compressed dims clamp to >= 4, Image.cpp:412-416)
+inline uint32_t mip_dim(uint32_t d, uint32_t i) { uint32_t v = d >> i; return v < 4 ? 4 : v; }
+
+int build_chain(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips)
+{
+    if (mips == 0 || mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range 1..%d", mips, HKBCN_MAX_LEVELS); return HKBCN_ERR_BAD_ARG; }
+    memset(&P, 0, sizeof(P));
+    P.flags = flags;
+    const uint8_t* s = (const uint8_t*)src;
+    uint8_t* d = (uint8_t*)dst;
+    for (uint32_t i = 0; i < mips; i++) {
+        uint32_t lw = mip_dim(w, i), lh = mip_dim(h, i);
+        add_level(P, codec, flags, s, d, lw, lh);
+        s += (size_t)lw * lh * src_bpp(codec, flags);
+        d += (size_t)(lw / 4) * (lh / 4) * blk_bytes(codec);
+    }
+    return HKBCN_OK;
+}
+
+size_t chain_src_bytes(int codec, uint32_t flags, uint32_t w, uint32_t h, uint32_t mips)
+{
+    size_t n = 0;
+    for (uint32_t i = 0; i < mips; i++) n += (size_t)mip_dim(w, i) * mip_dim(h, i) * src_bpp(codec, flags);
+    return n;
+}
+
+int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags)
+{
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips);
+    const size_t dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
+    if (dbytes == 0) return HKBCN_OK;
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    int rc;
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src, sbytes, cudaMemcpyHostToDevice, D->stream));
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, w, h, mips)) != HKBCN_OK) return rc;
+    if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* hkbcn_last_error(void) { return t_err; }
+const char* hkbcn_version(void) { return "hkbcn 0.1 (sm_100a)"; }
+
+int hkbcn_init(uint32_t device_mask)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_init) return HKBCN_OK;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        set_err("no CUDA device available (%s); this library has no CPU fallback", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+        return HKBCN_ERR_NO_DEVICE;
+    }
+    for (int i = 0; i < n; i++) {
+        if (device_mask && !(device_mask & (1u << i))) continue;
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, i));
+        if (prop.major != 10) {
+            set_err("device %d (%s, sm_%d%d) is not sm_100; kernels are built for sm_100a only", i, prop.name, prop.major, prop.minor);
+            continue;
+        }
+        CK(cudaSetDevice(i));
+        Device* D = new Device();
+        D->id = i;
+        D->sm_count = prop.multiProcessorCount;
+        CK(cudaStreamCreateWithFlags(&D->stream, cudaStreamNonBlocking));
+        // a12: lookup tables consumed by the encoders / BC6H decoder
+        CK(decode_upload_tables());
+        CK(bc1_upload_tables());
+        cudaError_t te = bc7_upload_tables();
+        if (te != cudaSuccess && te != cudaErrorNotSupported) { set_err("bc7 table upload: %s", cudaGetErrorString(te)); return HKBCN_ERR_CUDA; }
+        g_devs.push_back(D);
+    }
+    if (g_devs.empty()) {
+        if (!t_err[0]) set_err("no sm_100 device selected by mask 0x%x", device_mask);
+        return HKBCN_ERR_NO_DEVICE;
+    }
+    CK(cudaSetDevice(g_devs[0]->id));
+    g_init = true;
+    return HKBCN_OK;
+}
+
+void hkbcn_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (Device* D : g_devs) {
+        cudaSetDevice(D->id);
+        if (D->d_src) cudaFree(D->d_src);
+        if (D->d_dst) cudaFree(D->d_dst);
+        if (D->stream) cudaStreamDestroy(D->stream);
+        delete D;
+    }
+    g_devs.clear();
+    g_init = false;
+}
+
+int hkbcn_device_count(void) { return (int)g_devs.size(); }
+uint64_t hkbcn_launch_count(void) { return g_launches.load(); }
+
+int hkbcn_block_bytes(int fmt) { int c = codec_of(fmt); return c < 0 ? HKBCN_ERR_BAD_FORMAT : blk_bytes(c); }
+int hkbcn_src_texel_bytes(int fmt, uint32_t flags) { int c = codec_of(fmt); return c < 0 ? HKBCN_ERR_BAD_FORMAT : src_bpp(c, flags); }
+int hkbcn_dst_texel_bytes(int fmt, uint32_t flags) { int c = codec_of(fmt); return c < 0 ? HKBCN_ERR_BAD_FORMAT : dst_bpp(c, flags); }
+
+// Image.cpp:188-216 for block-compressed formats: log2(max(w,h)/4) + 1 (dims < 4 count as 4)
+uint32_t hkbcn_calc_num_mips(uint32_t width, uint32_t height)
+{
+    uint32_t m = std::max(width, height) / 4;
+    uint32_t n = 1;
+    while (m > 1) { m >>= 1; n++; }
+    return n;
+}
+
+size_t hkbcn_chain_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips)
+{
+    int c = codec_of(fmt);
+    if (c < 0) return 0;
+    size_t n = 0;
+    for (uint32_t i = 0; i < num_mips; i++) n += (size_t)(mip_dim(width, i) / 4) * (mip_dim(height, i) / 4) * blk_bytes(c) * slices;
+    return n;
+}
+
+int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK; // reference: zero blocks, nothing written
+    return compress_host_on(g_devs[0], fmt, src, dst, width & ~3u, height & ~3u, 1, flags) ;
+}
+
+int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if ((width & 3) || (height & 3)) { set_err("chain dims must be multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+    return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags);
+}
+
+int hkbcn_encode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, uint32_t flags)
+{
+    // n packed 4x4 blocks == a surface 4 texels wide and 4*n tall
+    if (n_blocks == 0) return HKBCN_OK;
+    if (n_blocks > 0x3FFFFFFFu) { set_err("too many blocks"); return HKBCN_ERR_BAD_ARG; }
+    return hkbcn_compress(fmt, src, dst, 4, (uint32_t)n_blocks * 4, flags);
+}
+
+int hkbcn_compress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t flags, void* stream)
+{
+    return hkbcn_compress_chain_dev(device, fmt, d_src, d_dst, width & ~3u, height & ~3u, 1, flags, stream);
+}
+
+int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                             uint32_t flags, void* stream)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = dev_at(device);
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK;
+    CK(cudaSetDevice(D->id));
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, flags, d_src, d_dst, width, height, num_mips)) != HKBCN_OK) return rc;
+    return launch_encode(D, fmt, codec, P, (cudaStream_t)stream);
+}
+
+int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, size_t dst_row_stride,
+                         uint32_t flags, void* stream)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = dev_at(device);
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    DecodeParams P;
+    P.src = (const uint8_t*)d_src;
+    P.dst = (uint8_t*)d_dst;
+    P.nbx = width / 4;
+    P.nblocks = (width / 4) * (height / 4);
+    P.dstRowStride = dst_row_stride;
+    P.codec = codec;
+    P.is_signed = fmt == HKBCN_BC6H_SFLOAT;
+    P.f32out = (flags & HKBCN_FLAG_DST_F32) != 0;
+    if (P.nblocks == 0) return HKBCN_OK;
+    CK(cudaSetDevice(D->id));
+    cudaError_t e = launch_decode(P, D->sm_count, (cudaStream_t)stream);
+    if (e != cudaSuccess) { set_err("decode launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+int hkbcn_decompress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, size_t dst_row_stride, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    const uint32_t nbx = width / 4, nby = height / 4;
+    if (nbx == 0 || nby == 0) return HKBCN_OK;
+    if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    const size_t rowBytes = (size_t)nbx * 4 * dst_bpp(codec, flags);
+    if (dst_row_stride < rowBytes) { set_err("dst_row_stride %zu < row bytes %zu", dst_row_stride, rowBytes); return HKBCN_ERR_BAD_ARG; }
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    const size_t sbytes = (size_t)nbx * nby * blk_bytes(codec);
+    // device image is tightly packed (stride = rowBytes rounded to 16 for vector stores)
+    const size_t dstride = (rowBytes + 15) & ~(size_t)15;
+    const size_t dbytes = dstride * nby * 4;
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src, sbytes, cudaMemcpyHostToDevice, D->stream));
+    rc = hkbcn_decompress_dev(0, fmt, D->d_src, D->d_dst, nbx * 4, nby * 4, dstride, flags, D->stream);
+    if (rc) return rc;
+    CK(cudaMemcpy2DAsync(dst, dst_row_stride, D->d_dst, dstride, rowBytes, (size_t)nby * 4, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_decode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, size_t dst_row_stride, uint32_t flags)
+{
+    if (n_blocks == 0) return HKBCN_OK;
+    if (n_blocks > 0x3FFFFFFFu) { set_err("too many blocks"); return HKBCN_ERR_BAD_ARG; }
+    return hkbcn_decompress(fmt, src, dst, 4, (uint32_t)n_blocks * 4, dst_row_stride, flags);
+}
+
+int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (n_jobs == 0) return HKBCN_OK;
+    if (!jobs) { set_err("null jobs"); return HKBCN_ERR_BAD_ARG; }
+    const size_t nd = g_devs.size();
+    // greedy longest-processing-time assignment by pixel-count-weighted cost
+    auto cost = [](const hkbcn_job& j) {
+        int c = codec_of(j.fmt);
+        double wgt = c == C_BC7 ? 40.0 : c == C_BC6H ? 400.0 : (c == C_BC4) ? 4.0 : (c == C_BC5) ? 8.0 : (c == C_BC3) ? 5.0 : 1.0;
+        return wgt * (double)j.width * (double)j.height;
+    };
+    std::vector<size_t> order(n_jobs);
+    for (size_t i = 0; i < n_jobs; i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return cost(jobs[a]) > cost(jobs[b]); });
+    std::vector<std::vector<size_t>> bins(nd);
+    std::vector<double> load(nd, 0.0);
+    for (size_t idx : order) {
+        size_t best = 0;
+        for (size_t d = 1; d < nd; d++) if (load[d] < load[best]) best = d;
+        bins[best].push_back(idx);
+        load[best] += cost(jobs[idx]);
+    }
+    std::vector<std::thread> th;
+    std::vector<int> first_err(nd, 0);
+    std::vector<std::string> err_msg(nd);
+    for (size_t d = 0; d < nd; d++) {
+        th.emplace_back([&, d]() {
+            for (size_t idx : bins[d]) {
+                hkbcn_job& j = jobs[idx];
+                if (j.width / 4 == 0 || j.height / 4 == 0) { j.status = HKBCN_OK; continue; }
+                j.status = compress_host_on(g_devs[d], j.fmt, j.src, j.dst, j.width & ~3u, j.height & ~3u, 1, j.flags);
+                if (j.status && !first_err[d]) { first_err[d] = j.status; err_msg[d] = t_err; }
+            }
+        });
+    }
+    for (auto& t : th) t.join();
+    for (size_t d = 0; d < nd; d++)
+        if (first_err[d]) { set_err("%s", err_msg[d].c_str()); return first_err[d]; }
+    return HKBCN_OK;
+}
+
+void* hkbcn_alloc_pinned(size_t bytes)
+{
+    if (ensure_init()) return nullptr;
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { set_err("cudaHostAlloc(%zu) failed", bytes); return nullptr; }
+    return p;
+}
+void hkbcn_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+} // extern "C"

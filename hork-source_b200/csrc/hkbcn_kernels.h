@@ -1,0 +1,39 @@
+// hkbcn_kernels.h -- internal launcher interface between the C-ABI layer and the .cu files.
+#pragma once
+#include "hkbcn_common.cuh"
+
+namespace hkbcn {
+
+// codec ids used internally (format family, independent of sRGB/SNORM tagging)
+enum Codec { C_BC1 = 0, C_BC2, C_BC3, C_BC4, C_BC5, C_BC6H, C_BC7 };
+
+// ---- encode -----------------------------------------------------------------
+uint32_t bc45_tile_blocks(int channels);
+cudaError_t launch_bc45_encode(int channels, const EncodeParams& P, int sm_count, cudaStream_t stream);
+
+uint32_t bc123_tile_blocks(int codec);
+cudaError_t launch_bc123_encode(int codec, const EncodeParams& P, int sm_count, cudaStream_t stream);
+cudaError_t bc1_upload_tables(); // a12: single-colour match + 565 midpoint tables
+
+uint32_t bc7_tile_blocks();
+cudaError_t launch_bc7_encode(const EncodeParams& P, int sm_count, cudaStream_t stream);
+cudaError_t bc7_upload_tables();
+
+uint32_t bc6h_tile_blocks();
+cudaError_t launch_bc6h_encode(bool is_signed, bool src_f16, const EncodeParams& P, int sm_count, cudaStream_t stream);
+
+// ---- decode -----------------------------------------------------------------
+struct DecodeParams {
+    const uint8_t* src;       // blocks
+    uint8_t*       dst;       // texels
+    uint32_t       nbx;       // blocks per row
+    uint32_t       nblocks;
+    size_t         dstRowStride; // bytes
+    int            codec;
+    uint32_t       is_signed; // BC6H
+    uint32_t       f32out;    // BC6H
+};
+cudaError_t launch_decode(const DecodeParams& P, int sm_count, cudaStream_t stream);
+cudaError_t decode_upload_tables(); // BC6H header layout table
+
+} // namespace hkbcn

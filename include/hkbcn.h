@@ -1,0 +1,153 @@
+/*
+ * hkbcn.h -- C ABI of the B200-native BCn block-compression path.
+ *
+ * Drop-in boundary for Hork/Image's TextureBlockCompression entry points
+ * (reference: Hork/Image/ImageEncoders.h:37-87).  Plain pointers and sizes only;
+ * every function returns 0 on success or a negative hkbcn_status.  There is NO
+ * CPU fallback: when no CUDA device / kernel image is usable the call fails with
+ * HKBCN_ERR_NO_DEVICE / HKBCN_ERR_CUDA and hkbcn_last_error() says why.
+ *
+ * Layout conventions (identical to the reference, ImageEncoders.cpp:215-557):
+ *   source surface  : tightly packed row-major texels, rowStride = Width * bpp
+ *   compressed      : tightly packed blocks, row-major block order
+ *   Width/4, Height/4 truncate; callers guarantee multiples of 4 (Image.cpp:412-413)
+ */
+#ifndef HKBCN_H
+#define HKBCN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#  define HKBCN_API __declspec(dllexport)
+#else
+#  define HKBCN_API __attribute__((visibility("default")))
+#endif
+
+/* Format ids == Hk::TEXTURE_FORMAT enum values (Hork/Image/Image.h:122-148). */
+typedef enum hkbcn_format {
+    HKBCN_BC1_UNORM      = 54, /* TEXTURE_FORMAT_BC1_UNORM      : RGBA8 in (alpha ignored), 8 B/block  */
+    HKBCN_BC1_UNORM_SRGB = 55,
+    HKBCN_BC2_UNORM      = 56, /* RGBA8 in, 16 B/block */
+    HKBCN_BC2_UNORM_SRGB = 57,
+    HKBCN_BC3_UNORM      = 58, /* RGBA8 in, 16 B/block */
+    HKBCN_BC3_UNORM_SRGB = 59,
+    HKBCN_BC4_UNORM      = 60, /* R8 in, 8 B/block */
+    HKBCN_BC4_SNORM      = 61,
+    HKBCN_BC5_UNORM      = 62, /* RG8 in, 16 B/block */
+    HKBCN_BC5_SNORM      = 63,
+    HKBCN_BC6H_UFLOAT    = 64, /* RGBA32F in (alpha ignored), 16 B/block */
+    HKBCN_BC6H_SFLOAT    = 65,
+    HKBCN_BC7_UNORM      = 66, /* RGBA8 in, 16 B/block */
+    HKBCN_BC7_UNORM_SRGB = 67
+} hkbcn_format;
+
+typedef enum hkbcn_status {
+    HKBCN_OK              =  0,
+    HKBCN_ERR_BAD_FORMAT  = -1,
+    HKBCN_ERR_BAD_ARG     = -2,
+    HKBCN_ERR_NO_DEVICE   = -3, /* no CUDA device, or device is not sm_100 */
+    HKBCN_ERR_CUDA        = -4, /* a CUDA runtime call failed; see hkbcn_last_error() */
+    HKBCN_ERR_NOT_INIT    = -5,
+    HKBCN_ERR_UNSUPPORTED = -6
+} hkbcn_status;
+
+/* flags for hkbcn_compress* */
+enum {
+    HKBCN_FLAG_NONE        = 0,
+    HKBCN_FLAG_SRC_F16     = 1u << 0, /* BC6H: source texels are RGBA16F (Encode_BC6h_f16, ImageEncoders.cpp:187) */
+    HKBCN_FLAG_FAST        = 1u << 1  /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:171-185) */
+};
+/* flags for hkbcn_decompress* */
+enum {
+    HKBCN_FLAG_DST_F32     = 1u << 8  /* BC6H: decode to RGB32F (Decode_BC6h_f32) instead of RGB16F (Decode_BC6h_f16) */
+};
+
+/* ---- lifetime ---------------------------------------------------------------
+ * Replaces the C++ static constructor `CompressionParams compressionParams`
+ * (ImageEncoders.cpp:52-68: rgbcx::init + bc7enc_compress_block_init + params).
+ * device_mask: bit i set = use CUDA device i; 0 = all visible devices.
+ * Called lazily by every other entry point with device_mask = 0. */
+HKBCN_API int hkbcn_init(uint32_t device_mask);
+HKBCN_API void hkbcn_shutdown(void);
+HKBCN_API int hkbcn_device_count(void);          /* devices selected by hkbcn_init */
+HKBCN_API const char* hkbcn_last_error(void);    /* thread-local message of the last failure */
+HKBCN_API const char* hkbcn_version(void);
+
+/* ---- format queries (TexFormat[] table, Image.cpp:49-119) -------------------- */
+HKBCN_API int hkbcn_block_bytes(int fmt);        /* 8 or 16; <0 on bad format */
+HKBCN_API int hkbcn_src_texel_bytes(int fmt, uint32_t flags); /* 1, 2, 4, 8 or 16 */
+HKBCN_API int hkbcn_dst_texel_bytes(int fmt, uint32_t flags); /* decoded texel size: 1,2,4,6,12 */
+/* CalcNumMips for a compressed format (Image.cpp:188-216): log2(max(w,h)/4)+1 */
+HKBCN_API uint32_t hkbcn_calc_num_mips(uint32_t width, uint32_t height);
+/* bytes of a full ImageStorage-layout chain (Image.cpp:363-467): all slices of mip 0, then mip 1, ... */
+HKBCN_API size_t hkbcn_chain_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips);
+
+/* ---- whole-surface compress, host pointers ----------------------------------
+ * Replaces CompressBC1/2/3/4/5/7(pSrc,pDest,Width,Height) (ImageEncoders.cpp:215,251,287,323,359,524)
+ * and CompressBC6h(pSrc,pDest,Width,Height,bSigned) (:395; fmt selects signedness).
+ * Quality presets are the reference's hard-coded ones: BC1/2/3 level 5, BC3/4/5 hq,
+ * BC7 uber level 4 perceptual.  Synchronous; dst holds (w/4)*(h/4)*block_bytes on return.
+ * Every block is encoded (the reference's CompressBC6h drops numBlocks%16 tail blocks,
+ * ImageEncoders.cpp:426-427; this does not). */
+HKBCN_API int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t flags);
+
+/* Whole-surface decode, host pointers.  The reference only has per-block Decode_BC*
+ * (ImageEncoders.cpp:77-136); this is that call applied to every block of the surface,
+ * written at dst_row_stride bytes per texel row.  BC6H output is RGB (3 components). */
+HKBCN_API int hkbcn_decompress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height,
+                               size_t dst_row_stride, uint32_t flags);
+
+/* ---- per-block entry points (ImageEncoders.h:48-64), host pointers ----------
+ * n_blocks contiguous 4x4 blocks (src: n * 16 texels, dst: n * block_bytes). The
+ * reference signatures are the n_blocks == 1 case. */
+HKBCN_API int hkbcn_encode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, uint32_t flags);
+/* dst: n_blocks decoded blocks, each 4 rows of 4 texels at dst_row_stride bytes/row
+ * inside its own 4*dst_row_stride bytes (Decode_BC*(pSrc,pDest,RowStride)). */
+HKBCN_API int hkbcn_decode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, size_t dst_row_stride, uint32_t flags);
+
+/* ---- device-pointer variants (no PCIe; `stream` is a cudaStream_t or NULL) ---
+ * Asynchronous with respect to the host: work is enqueued on `stream` of `device`. */
+HKBCN_API int hkbcn_compress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                 uint32_t flags, void* stream);
+HKBCN_API int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                   size_t dst_row_stride, uint32_t flags, void* stream);
+
+/* Compress a whole pre-built mip chain resident on the device in ONE launch.
+ * d_src: levels back to back (level i is max(w>>i,4) x max(h>>i,4) texels, tightly packed);
+ * d_dst: ImageStorage layout for one slice (Image.cpp:498-574).  */
+HKBCN_API int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                       uint32_t num_mips, uint32_t flags, void* stream);
+/* Host-pointer form: src = the same back-to-back level layout in host memory. */
+HKBCN_API int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height,
+                                   uint32_t num_mips, uint32_t flags);
+
+/* ---- batch API: independent surfaces sharded over the selected GPUs ---------
+ * No collective: each job is sent whole to one GPU (greedy by pixel-cost), results land
+ * directly in the caller's dst ("host gather").  Replaces one-process-per-texture use of
+ * the importers (Tools/TextureImporter/Main.cpp:236). */
+typedef struct hkbcn_job {
+    int         fmt;
+    uint32_t    width, height;
+    uint32_t    flags;
+    const void* src;   /* host */
+    void*       dst;   /* host */
+    int         status;/* out */
+} hkbcn_job;
+HKBCN_API int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs);
+
+/* ---- instrumentation --------------------------------------------------------
+ * Number of kernels this library launched since init (bench.py's gpu_launches). */
+HKBCN_API uint64_t hkbcn_launch_count(void);
+/* Pinned host memory helpers so callers can avoid a pageable-memory staging copy. */
+HKBCN_API void* hkbcn_alloc_pinned(size_t bytes);
+HKBCN_API void hkbcn_free_pinned(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HKBCN_H */
