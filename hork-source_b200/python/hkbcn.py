@@ -1,0 +1,147 @@
+"""ctypes binding of libhkbcn.so (include/hkbcn.h) -- test / bench glue only.
+
+The product is the C-ABI library and the C++ shim in hork-source_b200/host; this module
+lets tests/ and bench.py call the same entry points.  Function names mirror
+Hk::TextureBlockCompression (reference: Hork/Image/ImageEncoders.h:37-87).
+
+There is no CPU fallback: if the library or a B200 is missing, calls raise HkbcnError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libhkbcn.so")
+
+# Hk::TEXTURE_FORMAT values (Hork/Image/Image.h:122-148)
+BC1_UNORM, BC1_UNORM_SRGB, BC2_UNORM, BC2_UNORM_SRGB, BC3_UNORM, BC3_UNORM_SRGB = 54, 55, 56, 57, 58, 59
+BC4_UNORM, BC4_SNORM, BC5_UNORM, BC5_SNORM, BC6H_UFLOAT, BC6H_SFLOAT, BC7_UNORM, BC7_UNORM_SRGB = 60, 61, 62, 63, 64, 65, 66, 67
+
+FLAG_SRC_F16 = 1 << 0
+FLAG_FAST = 1 << 1
+FLAG_DST_F32 = 1 << 8
+
+EXPORTS = [
+    "hkbcn_init", "hkbcn_shutdown", "hkbcn_device_count", "hkbcn_last_error", "hkbcn_version",
+    "hkbcn_block_bytes", "hkbcn_src_texel_bytes", "hkbcn_dst_texel_bytes", "hkbcn_calc_num_mips", "hkbcn_chain_bytes",
+    "hkbcn_compress", "hkbcn_decompress", "hkbcn_encode_blocks", "hkbcn_decode_blocks",
+    "hkbcn_compress_dev", "hkbcn_decompress_dev", "hkbcn_compress_chain_dev", "hkbcn_compress_chain",
+    "hkbcn_compress_batch", "hkbcn_launch_count", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
+]
+
+
+class HkbcnError(RuntimeError):
+    pass
+
+
+class Job(C.Structure):
+    _fields_ = [("fmt", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("flags", C.c_uint32),
+                ("src", C.c_void_p), ("dst", C.c_void_p), ("status", C.c_int)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libhkbcn.so (built in-tree by __graft_entry__.build()); fail loudly if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise HkbcnError(f"{LIB_PATH} not built -- run `python __graft_entry__.py build` (no CPU fallback exists)")
+        L = C.CDLL(LIB_PATH)
+        L.hkbcn_last_error.restype = C.c_char_p
+        L.hkbcn_version.restype = C.c_char_p
+        L.hkbcn_init.argtypes = [C.c_uint32]
+        L.hkbcn_chain_bytes.restype = C.c_size_t
+        L.hkbcn_chain_bytes.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_calc_num_mips.restype = C.c_uint32
+        L.hkbcn_calc_num_mips.argtypes = [C.c_uint32, C.c_uint32]
+        L.hkbcn_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_decompress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_uint32]
+        L.hkbcn_encode_blocks.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32]
+        L.hkbcn_decode_blocks.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_uint32]
+        L.hkbcn_compress_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.hkbcn_decompress_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_uint32, C.c_void_p]
+        L.hkbcn_compress_chain_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.hkbcn_compress_chain.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_compress_batch.argtypes = [C.POINTER(Job), C.c_size_t]
+        L.hkbcn_launch_count.restype = C.c_uint64
+        L.hkbcn_alloc_pinned.restype = C.c_void_p
+        L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
+        L.hkbcn_free_pinned.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise HkbcnError(f"hkbcn status {rc}: {lib().hkbcn_last_error().decode()}")
+
+
+def init(mask=0):
+    check(lib().hkbcn_init(mask))
+
+
+def block_bytes(fmt):
+    return lib().hkbcn_block_bytes(fmt)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def compress(fmt, src, width, height, flags=0):
+    """CompressBC*(pSrc, pDest, Width, Height): src = numpy array of the tightly packed surface."""
+    src = np.ascontiguousarray(src)
+    nb = (width // 4) * (height // 4)
+    dst = np.zeros(nb * block_bytes(fmt), np.uint8)
+    check(lib().hkbcn_compress(fmt, _ptr(src), _ptr(dst), width, height, flags))
+    return dst
+
+
+def compress_chain(fmt, src, width, height, mips, flags=0):
+    src = np.ascontiguousarray(src)
+    dst = np.zeros(lib().hkbcn_chain_bytes(fmt, width, height, 1, mips), np.uint8)
+    check(lib().hkbcn_compress_chain(fmt, _ptr(src), _ptr(dst), width, height, mips, flags))
+    return dst
+
+
+def encode_blocks(fmt, src, n, flags=0):
+    """Encode_BC*(pSrc, pDest, ...) applied to n packed 4x4 blocks."""
+    src = np.ascontiguousarray(src)
+    dst = np.zeros(n * block_bytes(fmt), np.uint8)
+    check(lib().hkbcn_encode_blocks(fmt, _ptr(src), _ptr(dst), n, flags))
+    return dst
+
+
+def decompress(fmt, blocks, width, height, flags=0, row_stride=None):
+    blocks = np.ascontiguousarray(blocks)
+    tb = lib().hkbcn_dst_texel_bytes(fmt, flags)
+    if row_stride is None:
+        row_stride = (width // 4) * 4 * tb
+    dst = np.zeros(row_stride * (height // 4) * 4, np.uint8)
+    check(lib().hkbcn_decompress(fmt, _ptr(blocks), _ptr(dst), width, height, row_stride, flags))
+    return dst
+
+
+def decode_blocks(fmt, blocks, n, row_stride, flags=0):
+    """Decode_BC*(pSrc, pDest, RowStride) applied to n blocks (each into its own 4*row_stride bytes)."""
+    blocks = np.ascontiguousarray(blocks)
+    dst = np.zeros(n * 4 * row_stride, np.uint8)
+    check(lib().hkbcn_decode_blocks(fmt, _ptr(blocks), _ptr(dst), n, row_stride, flags))
+    return dst
+
+
+def compress_batch(jobs):
+    """jobs: list of (fmt, src ndarray, width, height, flags) -> list of ndarray outputs."""
+    arr = (Job * len(jobs))()
+    keep, outs = [], []
+    for i, (fmt, src, w, h, flags) in enumerate(jobs):
+        src = np.ascontiguousarray(src)
+        dst = np.zeros((w // 4) * (h // 4) * block_bytes(fmt), np.uint8)
+        keep.append(src)
+        outs.append(dst)
+        arr[i] = Job(fmt, w, h, flags, src.ctypes.data, dst.ctypes.data, 0)
+    check(lib().hkbcn_compress_batch(arr, len(jobs)))
+    return outs
