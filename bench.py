@@ -1,0 +1,349 @@
+#!/usr/bin/env python3
+"""bench.py -- BC7 encode throughput of the B200 path, next to the reference's CPU encoder.
+
+Workload (BASELINE.json configs[2], the one `metric` is quoted on): BC7 RGBA encode of a 4096x4096
+synthetic albedo with its full mip chain (11 levels, 22,369,616 px, 1,398,101 blocks) at the reference's
+quality preset (bc7enc uber level 4, perceptual).  One "step" = one pass over the whole chain.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          this repo's CUDA path (through the C ABI)
+  python bench.py --impl reference ...                          the reference's own bc7enc on the host cores
+
+value  : Mpix/s, inputs resident in HBM, CUDA-event time of the launches, max over ranks
+e2e    : same metric through hkbcn_compress_chain() with HOST (pinned) buffers, H2D + kernel + D2H in the timed region
+N > 1  : launched by torchrun, one rank per GPU, every rank encodes its own texture (weak scaling, no collective
+         on the data path; torch.distributed is used for the barrier and the max-over-ranks only)
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "hork-source_b200", "python"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+BC7 = 66
+SIZE = 4096
+SEED = 0xB2000004
+METRIC = "bc7_encode_mpix_per_s"
+
+
+# ----------------------------------------------------------------------------- workload
+def make_chain(seed, size=SIZE):
+    """level 0 = synth.albedo_rgba8 (SURVEY.md 8d 'albedo-B'); levels 1.. = 2x2 box average (synthetic chain:
+    the reference's stbir Mitchell cascade is a 'next' row, not part of this path).  Cached in /tmp between
+    the two arms of one round-end run."""
+    import synth
+    cache = f"/tmp/hkbcn_bench_{seed:x}_{size}.npy"
+    if os.path.exists(cache):
+        lvl0 = np.load(cache)
+    else:
+        lvl0 = synth.albedo_rgba8(size, size, seed).reshape(size, size, 4)
+        try:
+            np.save(cache + ".tmp.npy", lvl0)
+            os.replace(cache + ".tmp.npy", cache)
+        except OSError:
+            pass
+    levels = [lvl0]
+    while levels[-1].shape[0] > 4:
+        a = levels[-1].astype(np.uint16)
+        levels.append(((a[0::2, 0::2] + a[1::2, 0::2] + a[0::2, 1::2] + a[1::2, 1::2] + 2) >> 2).astype(np.uint8))
+    return levels
+
+
+def chain_pixels(levels):
+    return int(sum(l.shape[0] * l.shape[1] for l in levels))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback"
+
+
+# ----------------------------------------------------------------------------- reference arm (CPU)
+def ref_sample(levels):
+    """bounded sample of the workload for CPU timing: mip levels 1.. (2048^2 and below, 5,592,400 px = 25% of the chain)"""
+    return levels[1:]
+
+
+def time_reference(levels, steps, warmup):
+    """the reference's own bc7enc_compress_block (oracle/_ref, unmodified sources) over all host threads,
+    contiguous block ranges per thread (the decomposition CompressBC6h uses, ImageEncoders.cpp:426-486)"""
+    import refshim
+    if not refshim.have_ref():
+        raise SystemExit("oracle/_ref/libhkref.so missing: run `python __graft_entry__.py build` where /root/reference exists")
+    cores = refshim.hw_threads()
+    sample = ref_sample(levels)
+    px = chain_pixels(sample)
+
+    def one():
+        for l in sample:
+            refshim.compress(BC7, l, l.shape[1], l.shape[0], cores)
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = (time.perf_counter() - t0) / steps
+    return px / dt / 1e6, dt, cores, f"mip levels 1..{len(levels) - 1} of the chain ({px} px of {chain_pixels(levels)})"
+
+
+def run_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    levels = make_chain(SEED)
+    v, dt, cores, sample = time_reference(levels, max(1, args.steps), args.warmup)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic",
+        "config": workload_config(levels, args.gpus),
+        "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_config(levels, n):
+    return {"workload": f"BC7_UNORM encode, {SIZE}x{SIZE} RGBA8 synthetic albedo + full mip chain ({len(levels)} levels, {chain_pixels(levels)} px), "
+                        "bc7enc uber level 4 perceptual preset (Hk::TextureBlockCompression::CompressBC7)",
+            "textures_per_gpu": 1, "parallelism": f"{n} independent textures, one per GPU, no collective",
+            "mips": "2x2 box average of the synthetic level 0", "l2": "256 MiB buffer written between timed steps"}
+
+
+# ----------------------------------------------------------------------------- CUDA arm
+def run_gpu(args):
+    import torch
+    import hkbcn
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- this path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if dist:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    L = hkbcn.lib()
+    hkbcn.init(1 << local)  # library device 0 == cuda:local
+    levels = make_chain(SEED + rank)
+    mips, px = len(levels), chain_pixels(levels)
+    src_np = np.concatenate([l.ravel() for l in levels])
+    dst_bytes = L.hkbcn_chain_bytes(BC7, SIZE, SIZE, 1, mips)
+    assert dst_bytes == px  # 16 B per 16 px
+
+    # device-resident input / output (torch = allocator + stream/event plumbing only)
+    d_src = torch.from_numpy(src_np).cuda()
+    d_dst = torch.empty(dst_bytes, dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream()
+
+    def step():
+        hkbcn.check(L.hkbcn_compress_chain_dev(0, BC7, d_src.data_ptr(), d_dst.data_ptr(), SIZE, SIZE, mips, 0, C.c_void_p(stream.cuda_stream)))
+
+    for i in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = L.hkbcn_launch_count()
+    evs = []
+    barrier()
+    for i in range(args.steps):
+        flush.fill_(i & 255)  # evict the input from the 126 MB L2 (untimed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        step()
+        e1.record(stream)
+        evs.append((e0, e1))
+    barrier()
+    launches = L.hkbcn_launch_count() - launches0
+    ms_total = max_over_ranks(sum(a.elapsed_time(b) for a, b in evs))
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = world * px / (ms_step * 1e-3) / 1e6
+
+    # ---- end to end through the C ABI with host buffers (H2D + kernel + D2H inside the timed region)
+    h_src = L.hkbcn_alloc_pinned(src_np.nbytes)
+    h_dst = L.hkbcn_alloc_pinned(dst_bytes)
+    if not h_src or not h_dst:
+        raise SystemExit("pinned allocation failed: " + L.hkbcn_last_error().decode())
+    C.memmove(h_src, src_np.ctypes.data, src_np.nbytes)
+    e2e_steps = max(1, min(args.steps, 10))
+
+    def e2e_step():
+        hkbcn.check(L.hkbcn_compress_chain(BC7, h_src, h_dst, SIZE, SIZE, mips, 0))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+    barrier()
+    # the two paths must agree byte for byte
+    host_out = np.ctypeslib.as_array(C.cast(h_dst, C.POINTER(C.c_uint8)), shape=(dst_bytes,))
+    if not np.array_equal(host_out, d_dst.cpu().numpy()):
+        raise SystemExit("bench.py: host-pointer and device-pointer encodes differ")
+    e2e_value = world * px / e2e_s / 1e6
+
+    if rank == 0:
+        hbm, which = peaks()
+        achieved = 5.0 * px / (ms_step * 1e-3) / 1e9  # algorithmic bytes: 4 B/px read + 1 B/px written
+        out = {
+            "metric": METRIC, "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic",
+            "config": workload_config(levels, world),
+            "e2e": {"value": e2e_value, "unit": "Mpix/s", "h2d_bytes_per_step": int(src_np.nbytes), "d2h_bytes_per_step": int(dst_bytes),
+                    "ms_per_step": e2e_s * 1e3, "api": "hkbcn_compress_chain (host pointers, pinned)"},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "bc7_encode_kernel", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                         "traffic": ncu_traffic(), "peak_source": which,
+                         "note": "BC7 encode is ALU-bound by ~3 orders of magnitude (north_star: evidence is SM ALU-pipe utilisation, see 'alu'); "
+                                 "the HBM-bound kernels of this path are the decoders, see 'decode'"},
+            "alu": alu_model(px // 16, ms_step, clocks),
+        }
+        if world == 1:
+            out["decode"] = decode_sweep(torch, hkbcn, L, d_dst, stream, flush, hbm)
+            v, dt, cores, sample = time_reference(levels, 1, 0)
+            out["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample}
+        print(json.dumps(out))
+    L.hkbcn_free_pinned(h_src)
+    L.hkbcn_free_pinned(h_dst)
+    if dist:
+        dist.destroy_process_group()
+
+
+def decode_sweep(torch, hkbcn, L, bc7_blocks, stream, flush, hbm):
+    """HBM-bound half of the path: whole-surface decode of 4096^2 per format, algorithmic bytes/px of SURVEY.md 8d."""
+    n = SIZE
+    nblk = (n // 4) * (n // 4)
+    out = {}
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    for name, fmt, blk, tex, flags in (("BC1", 54, 8, 4, 0), ("BC3", 58, 16, 4, 0), ("BC4", 60, 8, 1, 0), ("BC5", 62, 16, 2, 0),
+                                       ("BC7", 66, 16, 4, 0), ("BC6H_f16", 64, 16, 6, 0)):
+        if fmt == 66:
+            src = bc7_blocks[: nblk * 16]
+        else:
+            src = torch.randint(0, 256, (nblk * blk,), dtype=torch.uint8, device="cuda", generator=gen)
+        dst = torch.empty(n * n * tex, dtype=torch.uint8, device="cuda")
+        times = []
+        for i in range(8):
+            flush.fill_(i)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            hkbcn.check(L.hkbcn_decompress_dev(0, fmt, src.data_ptr(), dst.data_ptr(), n, n, n * tex, flags, C.c_void_p(stream.cuda_stream)))
+            e1.record(stream)
+            torch.cuda.synchronize()
+            if i >= 3:
+                times.append(e0.elapsed_time(e1))
+        ms = float(np.mean(times))
+        gbs = (nblk * blk + n * n * tex) / (ms * 1e-3) / 1e9
+        out[name] = {"GB/s": gbs, "frac": gbs / hbm, "Gpix/s": n * n / (ms * 1e-3) / 1e9, "ms": ms}
+    return out
+
+
+def _profile_json():
+    try:
+        with open(os.path.join(ROOT, "profiles", "bc7_encode_ncu.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
+def ncu_traffic():
+    """dram bytes per launch of bc7_encode_kernel from the committed `ncu --set full` capture (profiles/), or null"""
+    return _profile_json().get("dram_bytes_per_launch")
+
+
+def alu_model(blocks, ms_step, clocks):
+    """issue-slot utilisation: warp instructions per 4x4 block (counted by ncu, profiles/bc7_encode_ncu.json) x blocks
+    / (SMs x 4 schedulers x clock x time).  null until the profile exists."""
+    ipb = _profile_json().get("warp_inst_per_block")
+    if not ipb or not clocks or not clocks.get("sm_mhz"):
+        return None
+    peak = 148 * 4 * clocks["sm_mhz"] * 1e6
+    rate = ipb * blocks / (ms_step * 1e-3)
+    return {"warp_inst_per_block": ipb, "issue_rate_ginst_s": rate / 1e9, "issue_peak_ginst_s": peak / 1e9, "issue_frac": rate / peak}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

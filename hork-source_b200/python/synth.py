@@ -28,19 +28,23 @@ def hash01(seed, x, y, c=0, o=0):
 
 
 def value_noise(w, h, seed, c, octaves, base_cell=64, wrap=True):
-    """fractal value noise in [0,1], periodic when wrap (so mip wrap filtering is seamless)."""
-    yy, xx = np.mgrid[0:h, 0:w]
+    """fractal value noise in [0,1], periodic when wrap (so mip wrap filtering is seamless).
+    The hash is evaluated on the cell lattice only and gathered per pixel."""
+    ys, xs = np.arange(h), np.arange(w)
     acc = np.zeros((h, w), np.float64)
     amp, tot = 1.0, 0.0
     for o in range(octaves):
         cell = max(base_cell >> o, 1)
-        gx, gy = xx // cell, yy // cell
-        fx, fy = (xx % cell) / cell, (yy % cell) / cell
+        gx, gy = xs // cell, ys // cell
+        fx, fy = (xs % cell) / cell, (ys % cell) / cell
         fx, fy = fx * fx * (3 - 2 * fx), fy * fy * (3 - 2 * fy)
         nx, ny = max(w // cell, 1), max(h // cell, 1)
-        x1, y1 = (gx + 1) % nx if wrap else gx + 1, (gy + 1) % ny if wrap else gy + 1
-        v00, v10 = hash01(seed, gx, gy, c, o), hash01(seed, x1, gy, c, o)
-        v01, v11 = hash01(seed, gx, y1, c, o), hash01(seed, x1, y1, c, o)
+        x1, y1 = ((gx + 1) % nx, (gy + 1) % ny) if wrap else (gx + 1, gy + 1)
+        ly, lx = np.mgrid[0:int(max(gy.max(), y1.max())) + 1, 0:int(max(gx.max(), x1.max())) + 1]
+        lat = hash01(seed, lx, ly, c, o)
+        fx, fy = fx[None, :], fy[:, None]
+        v00, v10 = lat[np.ix_(gy, gx)], lat[np.ix_(gy, x1)]
+        v01, v11 = lat[np.ix_(y1, gx)], lat[np.ix_(y1, x1)]
         acc += amp * ((v00 * (1 - fx) + v10 * fx) * (1 - fy) + (v01 * (1 - fx) + v11 * fx) * fy)
         tot += amp
         amp *= 0.5
@@ -55,14 +59,19 @@ def albedo_rgba8(w, h, seed, alpha="opaque"):
     for c in range(3):
         img[..., c] = np.clip(0.65 * luma + 0.35 * value_noise(w, h, seed, 1 + c, 5, 32) + 0.04 * (hash01(seed, *np.mgrid[0:h, 0:w][::-1], 7 + c) - 0.5), 0, 1)
     yy, xx = np.mgrid[0:h, 0:w]
-    cx, cy = xx // 16, yy // 16
-    sel = hash01(seed, cx, cy, 11)
+    ncy, ncx = (h + 15) // 16, (w + 15) // 16
+    lcy, lcx = np.mgrid[0:ncy, 0:ncx]
+    iy, ix = np.arange(h) // 16, np.arange(w) // 16
+
+    def cell(ch):  # hash of the 16x16 cell each pixel lies in
+        return hash01(seed, lcx, lcy, ch)[np.ix_(iy, ix)]
+    sel = cell(11)
     flat = sel < 0.05
     edge = (sel >= 0.05) & (sel < 0.13)
+    half = ((xx % 16) + (yy % 16) * (cell(15) - 0.5) * 2) > 8
     for c in range(3):
-        cellcol = hash01(seed, cx, cy, 12 + c)
+        cellcol = cell(12 + c)
         img[..., c] = np.where(flat, cellcol, img[..., c])
-        half = ((xx % 16) + (yy % 16) * (hash01(seed, cx, cy, 15) - 0.5) * 2) > 8
         img[..., c] = np.where(edge & half, 1.0 - cellcol, img[..., c])
     if alpha == "opaque":
         img[..., 3] = 1.0
