@@ -5,31 +5,31 @@
 // compressionParams.bc7_params[4] (:59-63; ThirdParty/bc7enc_rdo/bc7enc.cpp:2402-2438).
 // See bc7_block.cuh for the per-block algorithm and the parity contract.
 //
-// Kernel shape: persistent 256-thread CTAs, 2 per SM.  A CTA stages a tile of 128 consecutive
-// blocks (8 KB of RGBA8) into shared memory with TMA bulk copies, splits the tile into opaque and
-// alpha blocks (the two classes run different mode sets, bc7enc.cpp:2428-2437), and its 8 warps
-// then encode two blocks each per step, 16 lanes per block, first all opaque pairs, then all alpha
-// pairs -- so a warp never holds blocks of different classes and stays converged.
+// Kernel shape: persistent 128-thread CTAs.  A CTA stages a tile of 256 consecutive blocks (16 KB of RGBA8)
+// into shared memory with TMA bulk copies, sorts the tile's blocks into opaque ones and ones with alpha
+// (the two classes run different mode sets, bc7enc.cpp:2428-2437; sorted so that at most one warp per tile
+// holds both), and every thread then encodes one block at a time from a transposed copy of its 16 texels.
 // Algorithmic HBM bytes: 5 B/px; the kernel is ALU-bound by about three orders of magnitude.
 #include "hkbcn_common.cuh"
 #include "hkbcn_kernels.h"
-#include "bc7_block.cuh"
-#include <string.h>
+#include "bc7_thread.cuh"
+#include "bc7_host_tables.h"
 
 namespace hkbcn {
 
 __device__ bc7::Tables g_bc7_tables;
 
-constexpr int BC7_NT = 256;
-constexpr int BC7_TB = 128;
+constexpr int BC7_NT = 128;
+constexpr int BC7_TB = 256;
 
-__global__ void __launch_bounds__(BC7_NT, 2) bc7_encode_kernel(const __grid_constant__ EncodeParams P)
+__global__ void __launch_bounds__(BC7_NT, 4) bc7_encode_kernel(const __grid_constant__ EncodeParams P)
 {
     constexpr int ROWB = BC7_TB * 16;
     __shared__ __align__(128) uint8_t stage[4 * ROWB];
     __shared__ __align__(16) bc7::Tables T;
+    __shared__ __align__(16) uint32_t tpx[16 * BC7_NT];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ uint8_t list[2][BC7_TB];
+    __shared__ uint8_t order[BC7_TB];
     __shared__ uint32_t count[2];
 
     {
@@ -43,9 +43,9 @@ __global__ void __launch_bounds__(BC7_NT, 2) bc7_encode_kernel(const __grid_cons
     }
     __syncthreads();
     uint32_t phase = 0;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int base = lane & 16, lane16 = lane & 15;
-    const uint32_t hm = 0xFFFFu << base;
+    bc7::Block blk;
+    blk.px = tpx + threadIdx.x;
+    blk.stride = BC7_NT;
 
     for (uint32_t tile = blockIdx.x; tile < P.totalTiles; tile += gridDim.x) {
         const Level& L = P.lv[find_level(P, tile)];
@@ -55,40 +55,44 @@ __global__ void __launch_bounds__(BC7_NT, 2) bc7_encode_kernel(const __grid_cons
         stage_tile<4, BC7_TB, BC7_NT>(L, b0, nb, stage, &bar, phase);
         __syncthreads();
 
-        // classify: class 1 = some texel has alpha < 255 (bc7enc.cpp:2428-2436)
-        if (threadIdx.x < nb) {
-            uint32_t m = 0xFFFFFFFFu;
+        // class 1 = some texel has alpha < 255 (bc7enc.cpp:2428-2436); count, then place opaque blocks first
+        uint32_t cls[BC7_TB / BC7_NT], slot[BC7_TB / BC7_NT];
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const uint4 v = *(const uint4*)(stage + r * ROWB + threadIdx.x * 16);
-                m &= v.x & v.y & v.z & v.w;
+        for (int q = 0; q < BC7_TB / BC7_NT; q++) {
+            const uint32_t k = threadIdx.x + q * BC7_NT;
+            cls[q] = 2;
+            if (k < nb) {
+                uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const uint4 v = *(const uint4*)(stage + r * ROWB + k * 16);
+                    m &= v.x & v.y & v.z & v.w;
+                }
+                cls[q] = (m >> 24) != 255u;
+                slot[q] = atomicAdd(&count[cls[q]], 1u);
             }
-            const int cls = (m >> 24) != 255u;
-            list[cls][atomicAdd(&count[cls], 1u)] = (uint8_t)threadIdx.x;
         }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < BC7_TB / BC7_NT; q++)
+            if (cls[q] < 2) order[slot[q] + (cls[q] ? count[0] : 0)] = (uint8_t)(threadIdx.x + q * BC7_NT);
         __syncthreads();
 
 #pragma unroll 1
-        for (int cls = 0; cls < 2; cls++) {
-            const uint32_t n = count[cls];
-#pragma unroll 1
-            for (uint32_t pair = warp; pair * 2 < n; pair += BC7_NT / 32) {
-                const uint32_t slot = pair * 2 + (base >> 4);
-                const uint32_t k = list[cls][min(slot, n - 1)]; // odd tail: both halves encode the last block
-                const uint32_t packed = *(const uint32_t*)(stage + (lane16 >> 2) * ROWB + k * 16 + (lane16 & 3) * 4);
-                bc7::Px p;
-                p.r = packed & 255;
-                p.g = (packed >> 8) & 255;
-                p.b = (packed >> 16) & 255;
-                p.a = packed >> 24;
-                p.l = p.r * 109 + p.g * 366 + p.b * 37;
-                p.cr = (p.r << 9) - p.l;
-                p.cb = (p.b << 9) - p.l;
-                const uint4 out = cls ? bc7::encode_alpha(hm, base, lane16, p, packed, T) : bc7::encode_opaque(hm, base, lane16, p, packed, T);
-                if (lane16 == 0 && slot < n) *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
+        for (uint32_t item = threadIdx.x; item < nb; item += BC7_NT) {
+            const uint32_t k = order[item];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const uint4 v = *(const uint4*)(stage + r * ROWB + k * 16);
+                tpx[(4 * r + 0) * BC7_NT + threadIdx.x] = v.x;
+                tpx[(4 * r + 1) * BC7_NT + threadIdx.x] = v.y;
+                tpx[(4 * r + 2) * BC7_NT + threadIdx.x] = v.z;
+                tpx[(4 * r + 3) * BC7_NT + threadIdx.x] = v.w;
             }
+            const uint4 out = (item >= count[0]) ? bc7::encode_alpha(blk, T) : bc7::encode_opaque(blk, T);
+            *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }
-        __syncthreads(); // stage / lists are reused by the next tile
+        __syncthreads(); // stage / order are reused by the next tile
     }
 }
 
@@ -97,85 +101,19 @@ uint32_t bc7_tile_blocks() { return BC7_TB; }
 cudaError_t launch_bc7_encode(const EncodeParams& P, int sm_count, cudaStream_t stream)
 {
     if (P.totalTiles == 0) return cudaSuccess;
-    const uint32_t g = (uint32_t)sm_count * 2;
+    const uint32_t g = (uint32_t)sm_count * 4;
     const int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
     bc7_encode_kernel<<<grid, BC7_NT, 0, stream>>>(P);
     return cudaGetLastError();
 }
 
-// ---- a12: tables of bc7enc_compress_block_init (bc7enc.cpp:124-285), regenerated by the same loops --
+// ---- a12: lookup tables (bc7_host_tables.h) ----------------------------------------------------
 cudaError_t bc7_upload_tables()
 {
     static bc7::Tables* H = nullptr;
     if (!H) {
         H = new bc7::Tables();
-        memset(H, 0, sizeof(*H));
-        // perceptual weight scaling of bc7enc_compress_block (bc7enc.cpp:2409-2417) must give the constants the kernel uses
-        const float pr_weight = (.5f / (1.0f - .2126f)) * (.5f / (1.0f - .2126f));
-        const float pb_weight = (.5f / (1.0f - .0722f)) * (.5f / (1.0f - .0722f));
-        if ((int)(128 * 4.0f) != bc7::WY || (int)(64 * 4.0f * pr_weight) != bc7::WCR || (int)(16 * 4.0f * pb_weight) != bc7::WCB || 32 * 4 != bc7::WA)
-            return cudaErrorInvalidValue;
-        for (uint32_t p = 0; p < 2; p++) {
-            for (uint32_t i = 0; i < 32; i++) {
-                uint32_t vl = ((i << 1) | p) << 2;
-                vl |= (vl >> 6);
-                uint32_t in = i + 1 < 31 ? i + 1 : 31;
-                uint32_t vh = ((in << 1) | p) << 2;
-                vh |= (vh >> 6);
-                H->mid7[i][p] = (i == 31) ? 1.0f : (vl / 255.0f + vh / 255.0f) / 2.0f;
-            }
-            for (uint32_t i = 0; i < 64; i++) {
-                uint32_t vl = ((i << 1) | p) << 1;
-                vl |= (vl >> 7);
-                uint32_t in = i + 1 < 63 ? i + 1 : 63;
-                uint32_t vh = ((in << 1) | p) << 1;
-                vh |= (vh >> 7);
-                H->mid1[i][p] = (i == 63) ? 1.0f : (vl / 255.0f + vh / 255.0f) / 2.0f;
-            }
-        }
-        for (uint32_t i = 0; i < 128; i++) {
-            uint32_t vl = (i << 1);
-            vl |= (vl >> 7);
-            uint32_t in = i + 1 < 127 ? i + 1 : 127;
-            uint32_t vh = in << 1;
-            vh |= (vh >> 7);
-            H->mid5[i] = (i == 127) ? 1.0f : (vl / 255.0f + vh / 255.0f) / 2.0f;
-        }
-        // mode 1: 6-bit endpoints + shared p-bit, selector 2 of 8 (weight 18)
-        for (int c = 0; c < 256; c++)
-            for (uint32_t lp = 0; lp < 2; lp++) {
-                uint32_t best_err = 0xFFFF, bl = 0, bh = 0;
-                for (uint32_t l = 0; l < 64; l++) {
-                    uint32_t low = ((l << 1) | lp) << 1;
-                    low |= (low >> 7);
-                    for (uint32_t h = 0; h < 64; h++) {
-                        uint32_t high = ((h << 1) | lp) << 1;
-                        high |= (high >> 7);
-                        const int k = (int)((low * (64 - 18) + high * 18 + 32) >> 6);
-                        const uint32_t err = (uint32_t)((k - c) * (k - c));
-                        if (err < best_err) { best_err = err; bl = l; bh = h; }
-                    }
-                }
-                H->opt1[c][lp] = best_err | (bl << 16) | (bh << 24);
-            }
-        // mode 7: 5-bit endpoints + per-endpoint p-bits, selector 1 of 4 (weight 21)
-        for (int c = 0; c < 256; c++)
-            for (uint32_t hp = 0; hp < 2; hp++)
-                for (uint32_t lp = 0; lp < 2; lp++) {
-                    uint32_t best_err = 0xFFFF, bl = 0, bh = 0;
-                    for (uint32_t l = 0; l < 32; l++) {
-                        uint32_t low = ((l << 1) | lp) << 2;
-                        low |= (low >> 6);
-                        for (uint32_t h = 0; h < 32; h++) {
-                            uint32_t high = ((h << 1) | hp) << 2;
-                            high |= (high >> 6);
-                            const int k = (int)((low * (64 - 21) + high * 21 + 32) >> 6);
-                            const uint32_t err = (uint32_t)((k - c) * (k - c));
-                            if (err < best_err) { best_err = err; bl = l; bh = h; }
-                        }
-                    }
-                    H->opt7[c][hp][lp] = best_err | (bl << 16) | (bh << 24);
-                }
+        if (!bc7::fill_tables(H)) return cudaErrorInvalidValue;
     }
     return cudaMemcpyToSymbol(g_bc7_tables, H, sizeof(bc7::Tables));
 }

@@ -58,7 +58,8 @@ def compare(img, w, h, name):
         pg = 10 * np.log10(255 ** 2 / max(mg, 1e-12))
         pr = 10 * np.log10(255 ** 2 / max(mr, 1e-12))
         out[cls] = dict(blocks=int(sel.sum()), psnr_gpu=pg, psnr_ref=pr, perr_gpu=float(eg.mean()), perr_ref=float(er.mean()),
-                        worse=float((eg > er).mean()), better=float((eg < er).mean()), same=float((eg == er).mean()))
+                        worse=float((eg > er).mean()), better=float((eg < er).mean()), same=float((eg == er).mean()),
+                        identical=float((got.reshape(-1, 16)[sel] == ref.reshape(-1, 16)[sel]).all(1).mean()))
         print(f"{name:>14} {cls:>6}: n={sel.sum():6d} PSNR gpu {pg:7.3f} ref {pr:7.3f} (d {pg - pr:+.3f} dB) | perceptual err/block gpu {eg.mean():10.1f} "
               f"ref {er.mean():10.1f} (ratio {eg.mean() / max(er.mean(), 1e-9):.4f}) | worse {100 * (eg > er).mean():5.1f}% better {100 * (eg < er).mean():5.1f}% "
               f"same {100 * (eg == er).mean():5.1f}% identical-bytes {100 * (got.reshape(-1, 16)[sel] == ref.reshape(-1, 16)[sel]).all(1).mean():5.1f}%")
