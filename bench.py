@@ -263,7 +263,7 @@ def run_gpu(args):
                     "ms_per_step": e2e_s * 1e3, "api": "hkbcn_compress_chain (host pointers, pinned)"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "bc7_encode_kernel", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                         "traffic": ncu_traffic(), "peak_source": which,
+                         "traffic": ncu_traffic(px), "peak_source": which,
                          "note": "BC7 encode is ALU-bound by ~3 orders of magnitude (north_star: evidence is SM ALU-pipe utilisation, see 'alu'); "
                                  "the HBM-bound kernels of this path are the decoders, see 'decode'"},
             "alu": alu_model(px // 16, ms_step, clocks),
@@ -316,9 +316,11 @@ def _profile_json():
         return {}
 
 
-def ncu_traffic():
-    """dram bytes per launch of bc7_encode_kernel from the committed `ncu --set full` capture (profiles/), or null"""
-    return _profile_json().get("dram_bytes_per_launch")
+def ncu_traffic(px):
+    """dram bytes per launch of bc7_encode_kernel: bytes per pixel from the committed `ncu --set full` capture
+    (profiles/bc7_encode_ncu.json, taken on a 2048^2 surface) x the pixels of one launch; null without a capture"""
+    per_px = _profile_json().get("dram_bytes_per_px")
+    return per_px * px if per_px else None
 
 
 def alu_model(blocks, ms_step, clocks):
