@@ -1,0 +1,706 @@
+// bc6h_thread.cuh -- BC6H block encoder, device side (sm_100a): one thread per 4x4 block.
+//
+// Replaces bc6h_enc::EncodeBC6HU / EncodeBC6HS (ThirdParty/bc6h_enc/bc6h_enc.h:3650-3660 -> D3DX_BC6H::Encode,
+// :2910-2952) as Hk::TextureBlockCompression::CompressBC6h / Encode_BC6h_f32 / _f16 call it
+// (Hork/Image/ImageEncoders.cpp:187-205, 395-521), including the float -> half conversion the reference plugs in
+// (BC6H_FLOAT_TO_HALF = Hork/Core/half.c:802 half_from_float, ImageEncoders.cpp:43-44).
+//
+// Same search as the reference: for each of the 14 modes, a rough fit per shape (bounding-box diagonal + 8 Newton
+// steps, OptimizeRGB :2534-2742; error against the unquantised palette, MapColors :3505-3530), the best 8 of 32
+// shapes (1 of 1 for the one-region modes) refined (Refine :3420-3465: quantise, assign indices, fix-up swap,
+// per-channel logarithmic endpoint perturbation, OptimizeEndPoints :3271-3293), best total kept.
+// Float expressions keep the reference's operand order (--fmad=false).
+//
+// One observation removes most of the rough-fit work without changing any result: RoughMSE depends on the mode only
+// through its region count and index precision, which are the same for modes 1-10 (two regions, 3-bit indices) and
+// for modes 11-14 (one region, 4-bit), so the shape ranking and the unquantised endpoints are computed once per
+// family instead of once per mode.
+//
+// Kept reference behaviours that matter for parity: OptimizeEndPoints selects region p's texels with
+// g_aPartitionTable[p] instead of [uPartitions] (:3284), so in two-region modes region 0 is optimised over all 16
+// texels; palette searches stop at the first error increase (:3148-3153); half_from_float rounds halves up.
+#pragma once
+#ifndef HKBCN_HOST_EMU
+#include <cuda_runtime.h>
+#endif
+#include <stdint.h>
+#include <float.h>
+#include "bcn_tables.cuh"
+
+namespace hkbcn {
+namespace bc6h {
+
+constexpr int F16MAX = 0x7bff;
+
+// ms_aInfo (bc6h_enc.h:2408-2425): mode code, regions - 1, transformed endpoints, index bits, endpoint precisions
+// prec[0] = RGBAPrec[0][0] (A of region 0), [1] = [0][1] (B of region 0), [2] = [1][0], [3] = [1][1]
+struct Mode {
+    uint8_t code, parts, transformed, iprec;
+    uint8_t prec[4][3];
+};
+#ifdef HKBCN_HOST_EMU
+static const Mode kModes[14] = {
+#else
+__device__ const Mode kModes[14] = {
+#endif
+    {0x00, 1, 1, 3, {{10, 10, 10}, {5, 5, 5}, {5, 5, 5}, {5, 5, 5}}},  {0x01, 1, 1, 3, {{7, 7, 7}, {6, 6, 6}, {6, 6, 6}, {6, 6, 6}}},
+    {0x02, 1, 1, 3, {{11, 11, 11}, {5, 4, 4}, {5, 4, 4}, {5, 4, 4}}},  {0x06, 1, 1, 3, {{11, 11, 11}, {4, 5, 4}, {4, 5, 4}, {4, 5, 4}}},
+    {0x0a, 1, 1, 3, {{11, 11, 11}, {4, 4, 5}, {4, 4, 5}, {4, 4, 5}}},  {0x0e, 1, 1, 3, {{9, 9, 9}, {5, 5, 5}, {5, 5, 5}, {5, 5, 5}}},
+    {0x12, 1, 1, 3, {{8, 8, 8}, {6, 5, 5}, {6, 5, 5}, {6, 5, 5}}},     {0x16, 1, 1, 3, {{8, 8, 8}, {5, 6, 5}, {5, 6, 5}, {5, 6, 5}}},
+    {0x1a, 1, 1, 3, {{8, 8, 8}, {5, 5, 6}, {5, 5, 6}, {5, 5, 6}}},     {0x1e, 1, 0, 3, {{6, 6, 6}, {6, 6, 6}, {6, 6, 6}, {6, 6, 6}}},
+    {0x03, 0, 0, 4, {{10, 10, 10}, {10, 10, 10}, {0, 0, 0}, {0, 0, 0}}}, {0x07, 0, 1, 4, {{11, 11, 11}, {9, 9, 9}, {0, 0, 0}, {0, 0, 0}}},
+    {0x0b, 0, 1, 4, {{12, 12, 12}, {8, 8, 8}, {0, 0, 0}, {0, 0, 0}}},  {0x0f, 0, 1, 4, {{16, 16, 16}, {4, 4, 4}, {0, 0, 0}, {0, 0, 0}}},
+};
+
+// the thread's block: HDR texel i component c at f[(3 * i + c) * stride], its half-bit integer at ip[(3 * i + c) * stride]
+struct Block {
+    const float* f;
+    const int*   ip;
+    int          stride;
+    __device__ __forceinline__ float hdr(int i, int c) const { return f[(3 * i + c) * stride]; }
+    __device__ __forceinline__ int px(int i, int c) const { return ip[(3 * i + c) * stride]; }
+};
+
+struct Ep {
+    int A[3], B[3];
+};
+
+// Hork/Core/half.c:802-864 half_from_float, restated: round-half-up on bit 12 of the mantissa, denormals by shifting the
+// mantissa with its hidden bit (shift counts taken mod 32, as the x86 shifts the reference compiles to do), Inf/NaN kept.
+__device__ __forceinline__ uint32_t half_from_float_bits(uint32_t f)
+{
+    const uint32_t f_s = f & 0x80000000u, f_e = f & 0x7f800000u, f_m = f & 0x007fffffu;
+    const uint32_t h_s = (f_s >> 16) & 0xFFFFu;
+    const uint32_t e_amount = (f_e >> 23) & 0xFFFFu;
+    const uint32_t e_half_bias = e_amount - 0x70u;
+    const uint32_t m_rounded = f_m + ((f_m & 0x1000u) << 1);
+    const uint32_t m_denorm = (m_rounded | 0x00800000u) >> ((1u - e_half_bias) & 31u);
+    const uint32_t h_m_denorm = m_denorm >> 13;
+    const uint32_t m_nan = f_m >> 13;
+    const uint32_t h_em_nan = 0x7c00u | m_nan;
+    const uint32_t h_e_norm_overflow = (e_half_bias + 1u) << 10;
+    const uint32_t h_em_norm = (e_half_bias << 10) | (m_rounded >> 13);
+    const bool is_h_denorm = ((~(0x70u - e_amount)) >> 31) != 0;
+    const bool is_f_e_flagged = ((0x8fu - e_half_bias) >> 31) != 0;
+    const bool is_f_m_eqz = ((f_m - 1u) >> 31) != 0;
+    const bool is_h_nan_eqz = ((m_nan - 1u) >> 31) != 0;
+    const bool is_f_inf = is_f_e_flagged && is_f_m_eqz;
+    const bool is_f_nan_underflow = is_f_e_flagged && is_h_nan_eqz;
+    const bool is_e_overflow = ((0x1fu - e_half_bias) >> 31) != 0;
+    const bool is_h_inf = is_e_overflow || is_f_inf;
+    const bool is_f_snan = ((~((f & 0x7fc00000u) - 0x7fc00000u)) >> 31) != 0;
+    const bool is_m_norm_overflow = ((0u - (m_rounded & 0x00800000u)) >> 31) != 0;
+    uint32_t r = is_m_norm_overflow ? h_e_norm_overflow : h_em_norm;
+    r = is_f_e_flagged ? h_em_nan : r;
+    r = is_f_nan_underflow ? 0x7c01u : r;
+    r = is_h_inf ? 0x7c00u : r;
+    r = is_h_denorm ? h_m_denorm : r;
+    r = is_f_snan ? 0x7e00u : r;
+    return (h_s | r) & 0xFFFFu;
+}
+
+// INTColor::F16ToINT (bc6h_enc.h:967-989)
+__device__ __forceinline__ int f16_to_int(uint32_t h, bool isSigned)
+{
+    if (isSigned) {
+        const int s = h & 0x8000;
+        int v = h & 0x7fff;
+        if (v > F16MAX) v = F16MAX;
+        return s ? -v : v;
+    }
+    return (h & 0x8000) ? 0 : (int)h;
+}
+
+// D3DX_BC6H::Quantize / Unquantize / FinishUnquantize (bc6h_enc.h:2954-3031)
+__device__ __forceinline__ int quantize(int v, int prec, bool isSigned)
+{
+    if (isSigned) {
+        const bool neg = v < 0;
+        if (neg) v = -v;
+        int q = (prec >= 16) ? v : (v << (prec - 1)) / (F16MAX + 1);
+        return neg ? -q : q;
+    }
+    return (prec >= 15) ? v : (v << prec) / (F16MAX + 1);
+}
+__device__ __forceinline__ int unquantize(int comp, int bits, bool isSigned)
+{
+    if (isSigned) {
+        if (bits >= 16) return comp;
+        const bool neg = comp < 0;
+        if (neg) comp = -comp;
+        int unq;
+        if (comp == 0) unq = 0;
+        else if (comp >= ((1 << (bits - 1)) - 1)) unq = 0x7FFF;
+        else unq = ((comp << 15) + 0x4000) >> (bits - 1);
+        return neg ? -unq : unq;
+    }
+    if (bits >= 15) return comp;
+    if (comp == 0) return 0;
+    if (comp == ((1 << bits) - 1)) return 0xFFFF;
+    return ((comp << 16) + 0x8000) >> bits;
+}
+__device__ __forceinline__ int finish_unquantize(int comp, bool isSigned)
+{
+    if (isSigned) return (comp < 0) ? -(((-comp) * 31) >> 5) : (comp * 31) >> 5;
+    return (comp * 31) >> 6;
+}
+
+// NBits (bc6h_enc.h:2512-2532): bits needed to store n
+__device__ __forceinline__ int nbits(int n, bool isSigned)
+{
+    if (n == 0) return 0;
+    int nb = 0;
+    if (n > 0) {
+        for (; n; ++nb, n >>= 1) {}
+        return nb + (isSigned ? 1 : 0);
+    }
+    for (; n < -1; ++nb, n >>= 1) {}
+    return nb + 1;
+}
+
+template <int N> __device__ __forceinline__ constexpr int weight_of(int s) { return N == 8 ? (s * 64 + 3) / 7 : (s * 64 + 7) / 15; } // g_aWeights3 / 4
+
+// squared distance of texel i to a palette entry, as Norm() (bc6h_enc.h:2503-2509)
+__device__ __forceinline__ float norm3(int r, int g, int b, int pr, int pg, int pb)
+{
+    const float dr = (float)r - (float)pr, dg = (float)g - (float)pg, db = (float)b - (float)pb;
+    return dr * dr + dg * dg + db * db;
+}
+
+// GeneratePaletteQuantized (bc6h_enc.h:3073-3124): N interpolants between the unquantised endpoints
+template <int N> __device__ __forceinline__ void palette_quantized(const Ep& e, const uint8_t prec[3], bool isSigned, int pal[N][3])
+{
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const int a = unquantize(e.A[c], prec[c], isSigned), b = unquantize(e.B[c], prec[c], isSigned);
+#pragma unroll
+        for (int j = 0; j < N; j++) {
+            const int w = weight_of<N>(j);
+            pal[j][c] = finish_unquantize((a * (64 - w) + b * w + 32) >> 6, isSigned);
+        }
+    }
+}
+
+// Search shared by MapColors / MapColorsQuantized / AssignIndices (bc6h_enc.h:3137-3156, 3338-3357, 3514-3526): entry 0,
+// then entries in order while the error does not increase and is not yet zero; returns the error, idx = entry kept.
+template <int N> __device__ __forceinline__ float nearest_entry(int r, int g, int b, const int pal[N][3], int& idx)
+{
+    float best = norm3(r, g, b, pal[0][0], pal[0][1], pal[0][2]);
+    idx = 0;
+    bool open = true;
+#pragma unroll
+    for (int j = 1; j < N; j++) {
+        open = open && best > 0.0f;
+        const float e = norm3(r, g, b, pal[j][0], pal[j][1], pal[j][2]);
+        if (open && e > best) open = false;
+        if (open && e < best) {
+            best = e;
+            idx = j;
+        }
+    }
+    return best;
+}
+
+// MapColorsQuantized (bc6h_enc.h:3127-3158): total error of the texels in `mask` against the palette of `e`
+template <int N> __device__ __forceinline__ float map_colors_quantized(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned)
+{
+    int pal[N][3];
+    palette_quantized<N>(e, prec, isSigned, pal);
+    float tot = 0.0f;
+#pragma unroll 1
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+        int idx;
+        tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
+    }
+    return tot;
+}
+
+// PerturbOne (bc6h_enc.h:3160-3219): logarithmic search on one component of one endpoint.  Returns the best error,
+// `out` = the moved endpoints.
+template <int N, int CH>
+__device__ __forceinline__ float perturb_one(const Block& blk, uint32_t mask, const uint8_t prec[3], bool isSigned, const Ep& old_e, Ep& out,
+                                             float old_err, int do_b)
+{
+    const int uPrec = prec[CH];
+    float min_err = old_err;
+    int beststep = 0;
+    Ep tmp = old_e;
+    out = old_e;
+#pragma unroll 1
+    for (int step = 1 << (uPrec - 1); step; step >>= 1) {
+        bool improved = false;
+#pragma unroll 1
+        for (int sign = -1; sign <= 1; sign += 2) {
+            if (do_b == 0) {
+                tmp.A[CH] = out.A[CH] + sign * step;
+                if (tmp.A[CH] < 0 || tmp.A[CH] >= (1 << uPrec)) continue;
+            } else {
+                tmp.B[CH] = out.B[CH] + sign * step;
+                if (tmp.B[CH] < 0 || tmp.B[CH] >= (1 << uPrec)) continue;
+            }
+            const float err = map_colors_quantized<N>(blk, mask, tmp, prec, isSigned);
+            if (err < min_err) {
+                improved = true;
+                min_err = err;
+                beststep = sign * step;
+            }
+        }
+        if (improved) {
+            if (do_b == 0) out.A[CH] += beststep;
+            else out.B[CH] += beststep;
+        }
+    }
+    return min_err;
+}
+
+// one channel of OptimizeOne (bc6h_enc.h:3233-3267)
+template <int N, int CH>
+__device__ __forceinline__ void optimize_channel(const Block& blk, uint32_t mask, const uint8_t prec[3], bool isSigned, Ep& opt, float& opt_err)
+{
+    Ep new_a, new_b, ne;
+    int do_b;
+    const float err0 = perturb_one<N, CH>(blk, mask, prec, isSigned, opt, new_a, opt_err, 0);
+    const float err1 = perturb_one<N, CH>(blk, mask, prec, isSigned, opt, new_b, opt_err, 1);
+    if (err0 < err1) {
+        if (err0 >= opt_err) return;
+        opt.A[CH] = new_a.A[CH];
+        opt_err = err0;
+        do_b = 1;
+    } else {
+        if (err1 >= opt_err) return;
+        opt.B[CH] = new_b.B[CH];
+        opt_err = err1;
+        do_b = 0;
+    }
+#pragma unroll 1
+    for (;;) {
+        const float err = perturb_one<N, CH>(blk, mask, prec, isSigned, opt, ne, opt_err, do_b);
+        if (err >= opt_err) break;
+        if (do_b == 0) opt.A[CH] = ne.A[CH];
+        else opt.B[CH] = ne.B[CH];
+        opt_err = err;
+        do_b = 1 - do_b;
+    }
+}
+
+// OptimizeOne (bc6h_enc.h:3221-3269)
+template <int N>
+__device__ __forceinline__ void optimize_one(const Block& blk, uint32_t mask, const uint8_t prec[3], bool isSigned, float org_err, const Ep& org, Ep& opt)
+{
+    float opt_err = org_err;
+    opt = org;
+    optimize_channel<N, 0>(blk, mask, prec, isSigned, opt, opt_err);
+    optimize_channel<N, 1>(blk, mask, prec, isSigned, opt, opt_err);
+    optimize_channel<N, 2>(blk, mask, prec, isSigned, opt, opt_err);
+}
+
+// AssignIndices (bc6h_enc.h:3321-3357): idx = 4 bits per texel; err[p] per region.  shape: bit i = region of texel i.
+template <int N, int NR>
+__device__ __forceinline__ void assign_indices(const Block& blk, uint32_t shape, const Ep e[NR], const uint8_t prec[3], bool isSigned, uint64_t& idx,
+                                               float err[NR])
+{
+    int pal[NR][N][3];
+#pragma unroll
+    for (int p = 0; p < NR; p++) {
+        palette_quantized<N>(e[p], prec, isSigned, pal[p]);
+        err[p] = 0.0f;
+    }
+    idx = 0;
+#pragma unroll 1
+    for (int i = 0; i < 16; i++) {
+        const int region = NR == 2 ? (int)((shape >> i) & 1) : 0;
+        int j0, j1 = 0;
+        const float e0 = nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal[0], j0);
+        float e1 = 0.0f;
+        if (NR == 2) e1 = nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal[NR - 1], j1);
+        if (region == 0) err[0] += e0;
+        else err[NR - 1] += e1;
+        idx |= (uint64_t)(region ? j1 : j0) << (4 * i);
+    }
+}
+
+// SwapIndices (bc6h_enc.h:3295-3318): make the fix-up texel of every region have a 0 high index bit
+template <int N, int NR> __device__ __forceinline__ void swap_indices(uint32_t shape, int fix1, Ep e[NR], uint64_t& idx)
+{
+#pragma unroll
+    for (int p = 0; p < NR; p++) {
+        const int fi = p ? fix1 : 0;
+        if ((idx >> (4 * fi)) & (N >> 1)) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                const int t = e[p].A[c];
+                e[p].A[c] = e[p].B[c];
+                e[p].B[c] = t;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                const int region = NR == 2 ? (int)((shape >> j) & 1) : 0;
+                if (region == p) {
+                    const uint64_t s = (idx >> (4 * j)) & 15;
+                    idx = (idx & ~(15ull << (4 * j))) | ((uint64_t)(N - 1 - s) << (4 * j));
+                }
+            }
+        }
+    }
+}
+
+// TransformForward / TransformInverse (bc6h_enc.h:2479-2501), EndPointsFit (:3033-3071)
+template <int NR> __device__ __forceinline__ void transform_forward(Ep e[NR])
+{
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        e[0].B[c] -= e[0].A[c];
+        if (NR == 2) {
+            e[NR - 1].A[c] -= e[0].A[c];
+            e[NR - 1].B[c] -= e[0].A[c];
+        }
+    }
+}
+__device__ __forceinline__ int sign_extend(int x, int nb) { return ((x & (1 << (nb - 1))) ? ((~0) ^ ((1 << nb) - 1)) : 0) | x; }
+template <int NR> __device__ __forceinline__ void transform_inverse(Ep e[NR], const uint8_t prec[3], bool isSigned)
+{
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const int wrap = (1 << prec[c]) - 1;
+        e[0].B[c] = (e[0].B[c] + e[0].A[c]) & wrap;
+        if (isSigned) e[0].B[c] = sign_extend(e[0].B[c], prec[c]);
+        if (NR == 2) {
+            e[NR - 1].A[c] = (e[NR - 1].A[c] + e[0].A[c]) & wrap;
+            e[NR - 1].B[c] = (e[NR - 1].B[c] + e[0].A[c]) & wrap;
+            if (isSigned) {
+                e[NR - 1].A[c] = sign_extend(e[NR - 1].A[c], prec[c]);
+                e[NR - 1].B[c] = sign_extend(e[NR - 1].B[c], prec[c]);
+            }
+        }
+    }
+}
+template <int NR> __device__ __forceinline__ bool endpoints_fit(const Mode& M, bool isSigned, const Ep e[NR])
+{
+    const bool tr = M.transformed || isSigned;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        if (nbits(e[0].A[c], isSigned) > M.prec[0][c] || nbits(e[0].B[c], tr) > M.prec[1][c]) return false;
+    }
+    if (NR == 2) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            if (nbits(e[NR - 1].A[c], tr) > M.prec[2][c] || nbits(e[NR - 1].B[c], tr) > M.prec[3][c]) return false;
+        }
+    }
+    return true;
+}
+
+// OptimizeRGB with cSteps = 4 (bc6h_enc.h:2534-2742) over the HDR texels in `mask`: X / Y = fitted endpoints.
+__device__ __forceinline__ void optimize_rgb4(const Block& blk, uint32_t mask, float X[3], float Y[3])
+{
+    const float pC[4] = {3.0f / 3.0f, 2.0f / 3.0f, 1.0f / 3.0f, 0.0f / 3.0f};
+    const float pD[4] = {0.0f / 3.0f, 1.0f / 3.0f, 2.0f / 3.0f, 3.0f / 3.0f};
+    constexpr float fEpsilon = (0.25f / 64.0f) * (0.25f / 64.0f);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        X[c] = FLT_MAX;
+        Y[c] = -FLT_MAX;
+    }
+#pragma unroll 1
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            const float v = blk.hdr(i, c);
+            if (v < X[c]) X[c] = v;
+            if (v > Y[c]) Y[c] = v;
+        }
+    }
+    const float AB[3] = {Y[0] - X[0], Y[1] - X[1], Y[2] - X[2]};
+    const float fAB = AB[0] * AB[0] + AB[1] * AB[1] + AB[2] * AB[2];
+    if (fAB < FLT_MIN) return; // single colour
+    const float fABInv = 1.0f / fAB;
+    float Dir[3] = {AB[0] * fABInv, AB[1] * fABInv, AB[2] * fABInv};
+    const float Mid[3] = {(X[0] + Y[0]) * 0.5f, (X[1] + Y[1]) * 0.5f, (X[2] + Y[2]) * 0.5f};
+    float fDir[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll 1
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+        const float pr = (blk.hdr(i, 0) - Mid[0]) * Dir[0], pg = (blk.hdr(i, 1) - Mid[1]) * Dir[1], pb = (blk.hdr(i, 2) - Mid[2]) * Dir[2];
+        float f;
+        f = pr + pg + pb; fDir[0] += f * f;
+        f = pr + pg - pb; fDir[1] += f * f;
+        f = pr - pg + pb; fDir[2] += f * f;
+        f = pr - pg - pb; fDir[3] += f * f;
+    }
+    float fDirMax = fDir[0];
+    int iDirMax = 0;
+#pragma unroll
+    for (int d = 1; d < 4; d++)
+        if (fDir[d] > fDirMax) {
+            fDirMax = fDir[d];
+            iDirMax = d;
+        }
+    if (iDirMax & 2) { const float t = X[1]; X[1] = Y[1]; Y[1] = t; }
+    if (iDirMax & 1) { const float t = X[2]; X[2] = Y[2]; Y[2] = t; }
+    if (fAB < 1.0f / 4096.0f) return; // two colours
+    const float fSteps = 3.0f;
+#pragma unroll 1
+    for (int it = 0; it < 8; it++) {
+        float st[4][3];
+#pragma unroll
+        for (int s = 0; s < 4; s++)
+#pragma unroll
+            for (int c = 0; c < 3; c++) st[s][c] = X[c] * pC[s] + Y[c] * pD[s];
+        Dir[0] = Y[0] - X[0];
+        Dir[1] = Y[1] - X[1];
+        Dir[2] = Y[2] - X[2];
+        const float fLen = Dir[0] * Dir[0] + Dir[1] * Dir[1] + Dir[2] * Dir[2];
+        if (fLen < (1.0f / 4096.0f)) break;
+        const float fScale = fSteps / fLen;
+        Dir[0] *= fScale;
+        Dir[1] *= fScale;
+        Dir[2] *= fScale;
+        float d2X = 0.0f, d2Y = 0.0f, dX[3] = {0.0f, 0.0f, 0.0f}, dY[3] = {0.0f, 0.0f, 0.0f};
+#pragma unroll 1
+        for (int i = 0; i < 16; i++) {
+            if (!((mask >> i) & 1)) continue;
+            const float p0 = blk.hdr(i, 0), p1 = blk.hdr(i, 1), p2 = blk.hdr(i, 2);
+            const float fDot = (p0 - X[0]) * Dir[0] + (p1 - X[1]) * Dir[1] + (p2 - X[2]) * Dir[2];
+            int s;
+            if (fDot <= 0.0f) s = 0;
+            else if (fDot >= fSteps) s = 3;
+            else s = (int)(uint32_t)(fDot + 0.5f);
+            const float sr = s == 0 ? st[0][0] : s == 1 ? st[1][0] : s == 2 ? st[2][0] : st[3][0];
+            const float sg = s == 0 ? st[0][1] : s == 1 ? st[1][1] : s == 2 ? st[2][1] : st[3][1];
+            const float sb = s == 0 ? st[0][2] : s == 1 ? st[1][2] : s == 2 ? st[2][2] : st[3][2];
+            const float cs = s == 0 ? pC[0] : s == 1 ? pC[1] : s == 2 ? pC[2] : pC[3];
+            const float ds = s == 0 ? pD[0] : s == 1 ? pD[1] : s == 2 ? pD[2] : pD[3];
+            const float diff[3] = {sr - p0, sg - p1, sb - p2};
+            const float fC = cs * (1.0f / 8.0f), fD = ds * (1.0f / 8.0f);
+            d2X += fC * cs;
+            d2Y += fD * ds;
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                dX[c] += fC * diff[c];
+                dY[c] += fD * diff[c];
+            }
+        }
+        if (d2X > 0.0f) {
+            const float f = -1.0f / d2X;
+#pragma unroll
+            for (int c = 0; c < 3; c++) X[c] += dX[c] * f;
+        }
+        if (d2Y > 0.0f) {
+            const float f = -1.0f / d2Y;
+#pragma unroll
+            for (int c = 0; c < 3; c++) Y[c] += dY[c] * f;
+        }
+        if ((dX[0] * dX[0] < fEpsilon) && (dX[1] * dX[1] < fEpsilon) && (dX[2] * dX[2] < fEpsilon) && (dY[0] * dY[0] < fEpsilon) &&
+            (dY[1] * dY[1] < fEpsilon) && (dY[2] * dY[2] < fEpsilon))
+            break;
+    }
+}
+
+// Unquantised endpoints + rough error of one region (the body of RoughMSE's loop, bc6h_enc.h:3580-3632).
+// N = palette size of the family (8: two regions, 16: one region).
+template <int N> __device__ __forceinline__ float rough_region(const Block& blk, uint32_t mask, bool isSigned, Ep& e)
+{
+    const int np = __popc(mask);
+    if (np <= 2) {
+        // one or two texels: the texels themselves, no error added (:3598-3609)
+        const int i0 = __ffs(mask) - 1;
+        const int i1 = np == 2 ? 31 - __clz(mask) : i0;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            e.A[c] = blk.px(i0, c);
+            e.B[c] = blk.px(i1, c);
+        }
+        return 0.0f;
+    }
+    float X[3], Y[3];
+    optimize_rgb4(blk, mask, X, Y);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const int a = f16_to_int(half_from_float_bits(__float_as_uint(X[c])), isSigned);
+        const int b = f16_to_int(half_from_float_bits(__float_as_uint(Y[c])), isSigned);
+        e.A[c] = min(F16MAX, max(isSigned ? -F16MAX : 0, a));
+        e.B[c] = min(F16MAX, max(isSigned ? -F16MAX : 0, b));
+    }
+    // MapColors (:3505-3530) against the unquantised palette (:3467-3503)
+    int pal[N][3];
+#pragma unroll
+    for (int j = 0; j < N; j++) {
+        const int w = weight_of<N>(j);
+#pragma unroll
+        for (int c = 0; c < 3; c++) pal[j][c] = (e.A[c] * (64 - w) + e.B[c] * w + 32) >> 6;
+    }
+    float tot = 0.0f;
+#pragma unroll 1
+    for (int i = 0; i < 16; i++) {
+        if (!((mask >> i) & 1)) continue;
+        int idx;
+        tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
+    }
+    return tot;
+}
+
+// Header bit layouts of the 14 modes, one uint16 per token: field | lsb << 4 | count << 8 | rev << 12 (0xFFFF = end);
+// field = channel * 4 + {0: A of region 0 (w), 1: B of region 0 (x), 2: A of region 1 (y), 3: B of region 1 (z)}, 12 = shape.
+// Built on the host from the token strings in bc6h_layout.h (the same table the decoder uses).
+struct Layout {
+    uint16_t tok[14][28];
+};
+
+struct Bits128 {
+    uint64_t lo = 0, hi = 0;
+    int      pos = 0;
+    __device__ __forceinline__ void put(uint64_t v, int n)
+    {
+        if (n == 0) return;
+        if (pos < 64) {
+            lo |= v << pos;
+            if (pos + n > 64) hi |= v >> (64 - pos);
+        } else {
+            hi |= v << (pos - 64);
+        }
+        pos += n;
+    }
+};
+
+// EmitBlock (bc6h_enc.h:3378-3418)
+template <int N, int NR>
+__device__ __forceinline__ uint4 emit_block(const Layout& L, int mode, uint32_t shapeIdx, int fix1, const Ep e[NR], uint64_t idx)
+{
+    const Mode& M = kModes[mode];
+    Bits128 B;
+    B.put(M.code, mode < 2 ? 2 : 5);
+#pragma unroll 1
+    for (int k = 0; k < 28; k++) {
+        const uint32_t t = L.tok[mode][k];
+        if (t == 0xFFFFu) break;
+        const int field = t & 15, lsb = (t >> 4) & 15, cnt = (t >> 8) & 15, rev = (t >> 12) & 1;
+        int v;
+        if (field == 12) v = (int)shapeIdx;
+        else {
+            const int ch = field >> 2, w = field & 3;
+            const Ep& ep = (NR == 2 && (w & 2)) ? e[NR - 1] : e[0];
+            const int a = ch == 0 ? ep.A[0] : ch == 1 ? ep.A[1] : ep.A[2];
+            const int b = ch == 0 ? ep.B[0] : ch == 1 ? ep.B[1] : ep.B[2];
+            v = (w & 1) ? b : a;
+        }
+        uint32_t bits = ((uint32_t)v >> lsb) & ((1u << cnt) - 1u);
+        if (rev) bits = __brev(bits) >> (32 - cnt);
+        B.put(bits, cnt);
+    }
+    constexpr int IB = N == 8 ? 3 : 4;
+#pragma unroll 1
+    for (int i = 0; i < 16; i++) {
+        const bool fix = i == 0 || (NR == 2 && i == fix1);
+        const uint32_t s = (uint32_t)(idx >> (4 * i)) & 15u;
+        B.put(fix ? (s & ((1u << (IB - 1)) - 1u)) : s, fix ? IB - 1 : IB);
+    }
+    return make_uint4((uint32_t)B.lo, (uint32_t)(B.lo >> 32), (uint32_t)B.hi, (uint32_t)(B.hi >> 32));
+}
+
+// Refine (bc6h_enc.h:3420-3465) for one (mode, shape): `unq` = the shape's unquantised endpoints from the rough fit.
+// Updates best_err / out when this candidate wins.
+template <int N, int NR>
+__device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mode, bool isSigned, uint32_t shapeIdx, const Ep unq[NR], float& best_err,
+                                       uint4& out)
+{
+    const Mode& M = kModes[mode];
+    const uint32_t shape = NR == 2 ? kShape2[shapeIdx] : 0u;
+    const int fix1 = NR == 2 ? kAnchor2[shapeIdx] : 0;
+    const uint8_t* prec = M.prec[0];
+    Ep org[NR], opt[NR];
+    float org_err[NR], opt_err[NR];
+    uint64_t org_idx, opt_idx;
+    // QuantizeEndPts (:3359-3376)
+#pragma unroll
+    for (int p = 0; p < NR; p++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            org[p].A[c] = quantize(unq[p].A[c], prec[c], isSigned);
+            org[p].B[c] = quantize(unq[p].B[c], prec[c], isSigned);
+        }
+    assign_indices<N, NR>(blk, shape, org, prec, isSigned, org_idx, org_err);
+    swap_indices<N, NR>(shape, fix1, org, org_idx);
+    if (M.transformed) transform_forward<NR>(org);
+    if (!endpoints_fit<NR>(M, isSigned, org)) return;
+    if (M.transformed) transform_inverse<NR>(org, prec, isSigned);
+    // OptimizeEndPoints (:3271-3293): region 0 over g_aPartitionTable[0] (every texel), region 1 over its own texels
+    optimize_one<N>(blk, 0xFFFFu, prec, isSigned, org_err[0], org[0], opt[0]);
+    if (NR == 2) optimize_one<N>(blk, shape, prec, isSigned, org_err[NR - 1], org[NR - 1], opt[NR - 1]);
+    assign_indices<N, NR>(blk, shape, opt, prec, isSigned, opt_idx, opt_err);
+    swap_indices<N, NR>(shape, fix1, opt, opt_idx);
+    float org_tot = 0.0f, opt_tot = 0.0f;
+#pragma unroll
+    for (int p = 0; p < NR; p++) {
+        org_tot += org_err[p];
+        opt_tot += opt_err[p];
+    }
+    if (M.transformed) transform_forward<NR>(opt);
+#ifdef BC6H_DEBUG
+    printf("MY  refine mode %d shape %d org %.1f opt %.1f best %.1f fit %d\n", mode, (int)shapeIdx, org_tot, opt_tot, best_err, (int)endpoints_fit<NR>(M, isSigned, opt));
+#endif
+    if (endpoints_fit<NR>(M, isSigned, opt) && opt_tot < org_tot && opt_tot < best_err) {
+        best_err = opt_tot;
+        out = emit_block<N, NR>(L, mode, shapeIdx, fix1, opt, opt_idx);
+    } else if (org_tot < best_err) {
+        if (M.transformed) transform_forward<NR>(org);
+        best_err = org_tot;
+        out = emit_block<N, NR>(L, mode, shapeIdx, fix1, org, org_idx);
+    }
+}
+
+// D3DX_BC6H::Encode (bc6h_enc.h:2910-2952)
+__device__ __forceinline__ uint4 encode_block(const Block& blk, const Layout& L, bool isSigned)
+{
+    float best_err = FLT_MAX;
+    uint4 out = make_uint4(0, 0, 0, 0);
+    // ---- two-region family (modes 1-10): rough error of the 32 shapes, best 8 by the reference's partial bubble sort
+    float rough[32];
+    uint8_t order[32];
+#pragma unroll 1
+    for (int s = 0; s < 32; s++) {
+        const uint32_t m1 = kShape2[s], m0 = ~m1 & 0xFFFFu;
+        Ep e;
+        float err = rough_region<8>(blk, m0, isSigned, e);
+        err += rough_region<8>(blk, m1, isSigned, e);
+        rough[s] = err;
+        order[s] = (uint8_t)s;
+    }
+#pragma unroll 1
+    for (int i = 0; i < 8; i++)
+#pragma unroll 1
+        for (int j = i + 1; j < 32; j++)
+            if (rough[i] > rough[j]) {
+                const float tf = rough[i]; rough[i] = rough[j]; rough[j] = tf;
+                const uint8_t ts = order[i]; order[i] = order[j]; order[j] = ts;
+            }
+#ifdef BC6H_DEBUG
+    printf("MY  mode 0 order:");
+    for (int i = 0; i < 8; i++) printf(" %d(%.1f)", order[i], rough[i]);
+    printf("\n");
+#endif
+    // unquantised endpoints of the 8 ranked shapes (the reference keeps all 32 in aUnqEndPts; only these are read again)
+    Ep unq8[8][2];
+#pragma unroll 1
+    for (int i = 0; i < 8; i++) {
+        rough_region<8>(blk, ~kShape2[order[i]] & 0xFFFFu, isSigned, unq8[i][0]);
+        rough_region<8>(blk, kShape2[order[i]], isSigned, unq8[i][1]);
+    }
+    // mode-major, rank-minor, as the reference visits them (:2916-2950): the first candidate reaching the minimum wins
+#pragma unroll 1
+    for (int mode = 0; mode < 10 && best_err > 0.0f; mode++)
+#pragma unroll 1
+        for (int i = 0; i < 8 && best_err > 0.0f; i++) refine<8, 2>(blk, L, mode, isSigned, order[i], unq8[i], best_err, out);
+    // ---- one-region family (modes 11-14): a single shape
+    if (best_err > 0.0f) {
+        Ep unq1[1];
+        rough_region<16>(blk, 0xFFFFu, isSigned, unq1[0]);
+#pragma unroll 1
+        for (int mode = 10; mode < 14 && best_err > 0.0f; mode++) refine<16, 1>(blk, L, mode, isSigned, 0, unq1, best_err, out);
+    }
+    return out;
+}
+
+} // namespace bc6h
+} // namespace hkbcn
