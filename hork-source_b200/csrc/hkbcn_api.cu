@@ -235,6 +235,7 @@ int hkbcn_init(uint32_t device_mask)
         CK(bc1_upload_tables());
         cudaError_t te = bc7_upload_tables();
         if (te != cudaSuccess && te != cudaErrorNotSupported) { set_err("bc7 table upload: %s", cudaGetErrorString(te)); return HKBCN_ERR_CUDA; }
+        CK(bc6h_upload_tables());
         g_devs.push_back(D);
     }
     if (g_devs.empty()) {

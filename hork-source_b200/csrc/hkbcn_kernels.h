@@ -21,6 +21,7 @@ cudaError_t bc7_upload_tables();
 
 uint32_t bc6h_tile_blocks();
 cudaError_t launch_bc6h_encode(bool is_signed, bool src_f16, const EncodeParams& P, int sm_count, cudaStream_t stream);
+cudaError_t bc6h_upload_tables(); // header bit layouts of the 14 modes
 
 // ---- decode -----------------------------------------------------------------
 struct DecodeParams {

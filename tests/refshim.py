@@ -7,6 +7,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libhkref.so")
+REF0_PATH = os.path.join(ROOT, "oracle", "_ref", "libhkref0.so")  # same sources, -ftrivial-auto-var-init=zero (oracle/Makefile)
 ORACLE_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
 
 # hkbcn / Hk::TEXTURE_FORMAT id -> shim codec id (ref_shim.cpp: F_BC1.. = 0..7)
@@ -15,16 +16,16 @@ _SRC_BPP = {0: 4, 1: 4, 2: 4, 3: 1, 4: 2, 5: 16, 6: 16, 7: 4}
 _BLK = {0: 8, 1: 16, 2: 16, 3: 8, 4: 16, 5: 16, 6: 16, 7: 16}
 
 _ref = None
+_ref0 = None
 
 
 def have_ref():
     return os.path.exists(REF_PATH)
 
 
-def ref():
-    global _ref
-    if _ref is None:
-        L = C.CDLL(REF_PATH)
+def _load(path):
+    if True:
+        L = C.CDLL(path)
         L.ref_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int]
         L.ref_decompress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_int, C.c_int]
         L.ref_encode_block.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
@@ -38,8 +39,23 @@ def ref():
         L.ref_half_from_float.argtypes = [C.c_uint32]
         L.ref_half_to_float.restype = C.c_uint32
         L.ref_half_to_float.argtypes = [C.c_uint16]
-        _ref = L
+    return L
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = _load(REF_PATH)
     return _ref
+
+
+def ref0():
+    """The reference built with every automatic variable zero-initialised: the bit-exact oracle of the BC6H encoder
+    (bc6h_enc.h:3134-3150 reads an uninitialised `pad`; see oracle/Makefile)."""
+    global _ref0
+    if _ref0 is None:
+        _ref0 = _load(REF0_PATH)
+    return _ref0
 
 
 def _p(a):
@@ -50,12 +66,22 @@ def hw_threads():
     return ref().ref_hw_threads()
 
 
-def compress(fmt, src, w, h, nthreads=0):
+def compress(fmt, src, w, h, nthreads=0, lib=None):
     """reference Compress* over the surface; nthreads=0 -> all hardware threads."""
     f = _FMT[fmt]
     src = np.ascontiguousarray(src)
     dst = np.zeros((w // 4) * (h // 4) * _BLK[f], np.uint8)
-    ref().ref_compress(f, _p(src), _p(dst), w, h, nthreads if nthreads else hw_threads())
+    (lib or ref()).ref_compress(f, _p(src), _p(dst), w, h, nthreads if nthreads else hw_threads())
+    return dst
+
+
+def encode_bc6h_f16_blocks(src_half, n, signed=False, lib=None):
+    """Encode_BC6h_f16 (ImageEncoders.cpp:187-197) over n packed blocks of 16 RGBA16F texels."""
+    src_half = np.ascontiguousarray(src_half)
+    dst = np.zeros(n * 16, np.uint8)
+    L = lib or ref()
+    for i in range(n):
+        L.ref_encode_bc6h_f16(src_half.ctypes.data + i * 128, dst.ctypes.data + i * 16, int(signed))
     return dst
 
 
