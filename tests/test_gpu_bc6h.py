@@ -56,7 +56,11 @@ def check(img, w, h, fmt, name, flags=0, src=None):
     print(f"{name}: {nb} blocks, identical to ref0 {100 * same.mean():.3f}%, psnr gpu {pg:.3f} ref {pr:.3f}, err/block gpu {eg:.1f} ref {er:.1f}")
     assert same.all(), f"{name}: blocks {np.flatnonzero(~same)[:8]} differ from the zero-init reference build"
     assert pg >= pr - PSNR_TOL_DB, f"{name}: PSNR {pg:.3f} dB vs reference {pr:.3f} dB"
-    assert eg <= er * (1 + 1e-9), f"{name}: mean block error {eg:.2f} vs reference {er:.2f}"
+    # "never worse per block on average": exact against the defined-behaviour build (identical blocks => identical error);
+    # against the as-shipped build, whose result moves with stack leftovers, the 0.05 dB band is the bar
+    e0 = quality(ref0, img, w, h, fmt)[1]
+    assert eg <= e0, f"{name}: mean block error {eg:.2f} vs zero-init reference {e0:.2f}"
+    assert eg <= er * 10 ** (PSNR_TOL_DB / 10), f"{name}: mean block error {eg:.2f} vs as-shipped reference {er:.2f}"
 
 
 @pytest.mark.parametrize("face", [0, 1])
