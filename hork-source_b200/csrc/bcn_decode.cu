@@ -15,6 +15,7 @@
 #include "hkbcn_kernels.h"
 #include "bcn_tables.cuh"
 #include "bc6h_layout.h"
+#include "bcn_decode_lean.cuh"
 
 namespace hkbcn {
 
@@ -513,10 +514,88 @@ __global__ void __launch_bounds__(256) decode_kernel(const DecodeParams P)
     }
 }
 
+
+// ---------------------------------------------------------------- lean BC1..BC5 kernels (bcn_decode_lean.cuh)
+// One thread = one 16-byte-per-row work item: 1 block (BC1/2/3), 2 adjacent blocks (BC5) or 4 adjacent blocks (BC4), so
+// every row store is one 128-bit streaming store and a warp's 32 stores form one 512-byte run.  Used when the
+// destination is 16-byte aligned and the block row divides into whole items; decode_kernel below is the general path.
+template <int CODEC>
+__global__ void __launch_bounds__(256) decode_lean_kernel(const DecodeParams P, const uint32_t itemsPerRow, const uint32_t nItems)
+{
+    constexpr int K = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 2 : 1;      // blocks per item
+    constexpr int IB = K * ((CODEC == C_BC1 || CODEC == C_BC4) ? 8 : 16);   // source bytes per item
+    const uint32_t stride = gridDim.x * 256u;
+    uint32_t item = blockIdx.x * 256u + threadIdx.x;
+    uint32_t by = item / itemsPerRow, ix = item - by * itemsPerRow;
+    const uint32_t dby = stride / itemsPerRow, dix = stride - dby * itemsPerRow;
+    for (; item < nItems; item += stride) {
+        uint4 o[4];
+        if (CODEC == C_BC1) {
+            const uint2 b = __ldcs((const uint2*)(P.src + (size_t)item * IB));
+            uint32_t px[16];
+            lean::decode_bc1(b.x, b.y, px);
+#pragma unroll
+            for (int r = 0; r < 4; r++) o[r] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+        } else if (CODEC == C_BC2 || CODEC == C_BC3) {
+            const uint4 b = __ldcs((const uint4*)(P.src + (size_t)item * IB));
+            uint32_t px[16];
+            if (CODEC == C_BC2) lean::decode_bc2(b.x, b.y, b.z, b.w, px);
+            else lean::decode_bc3(b.x, b.y, b.z, b.w, px);
+#pragma unroll
+            for (int r = 0; r < 4; r++) o[r] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+        } else if (CODEC == C_BC4) {
+            const uint4 b0 = __ldcs((const uint4*)(P.src + (size_t)item * IB)), b1 = __ldcs((const uint4*)(P.src + (size_t)item * IB) + 1);
+            uint32_t a[4][4];
+            lean::alpha_rows(b0.x, b0.y, a[0]);
+            lean::alpha_rows(b0.z, b0.w, a[1]);
+            lean::alpha_rows(b1.x, b1.y, a[2]);
+            lean::alpha_rows(b1.z, b1.w, a[3]);
+#pragma unroll
+            for (int r = 0; r < 4; r++) o[r] = make_uint4(a[0][r], a[1][r], a[2][r], a[3][r]);
+        } else { // BC5
+            const uint4 b0 = __ldcs((const uint4*)(P.src + (size_t)item * IB)), b1 = __ldcs((const uint4*)(P.src + (size_t)item * IB) + 1);
+            uint32_t a[4][4];
+            lean::alpha_rows(b0.x, b0.y, a[0]);
+            lean::alpha_rows(b0.z, b0.w, a[1]);
+            lean::alpha_rows(b1.x, b1.y, a[2]);
+            lean::alpha_rows(b1.z, b1.w, a[3]);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                lean::bc5_row(a[0][r], a[1][r], o[r].x, o[r].y);
+                lean::bc5_row(a[2][r], a[3][r], o[r].z, o[r].w);
+            }
+        }
+        uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)ix * 16;
+#pragma unroll
+        for (int r = 0; r < 4; r++) __stcs((uint4*)(d + r * P.dstRowStride), o[r]);
+        ix += dix;
+        by += dby;
+        if (ix >= itemsPerRow) { ix -= itemsPerRow; by++; }
+    }
+}
+
+template <int CODEC>
+static bool try_launch_lean(const DecodeParams& P, int sm_count, cudaStream_t stream, cudaError_t& err)
+{
+    constexpr uint32_t K = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 2 : 1;
+    if (((size_t)P.dst & 15) || (P.dstRowStride & 15) || ((size_t)P.src & 15) || (P.nbx % K)) return false;
+    const uint32_t ipr = P.nbx / K, nItems = P.nblocks / K;
+    uint32_t ctas = (nItems + 255) / 256;
+    const uint32_t cap = (uint32_t)sm_count * 8 * 4;
+    if (ctas > cap) ctas = cap;
+    decode_lean_kernel<CODEC><<<ctas, 256, 0, stream>>>(P, ipr, nItems);
+    err = cudaGetLastError();
+    return true;
+}
+
 template <int CODEC>
 static cudaError_t launch_decode_t(const DecodeParams& P, int sm_count, cudaStream_t stream)
 {
     // required alignment of a destination row segment for the vector path
+    if constexpr (CODEC == C_BC1 || CODEC == C_BC2 || CODEC == C_BC3 || CODEC == C_BC4 || CODEC == C_BC5) {
+        cudaError_t e;
+        if (try_launch_lean<CODEC>(P, sm_count, stream, e)) return e;
+    }
     size_t need = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 8 : (CODEC == C_BC6H) ? (P.f32out ? 16 : 8) : 16;
     bool vec = (((size_t)P.dst % need) == 0) && ((P.dstRowStride % need) == 0);
     uint32_t ctas = (P.nblocks + 255) / 256;
