@@ -16,6 +16,7 @@
 #include "bcn_tables.cuh"
 #include "bc6h_layout.h"
 #include "bcn_decode_lean.cuh"
+#include "bc7_decode_lean.cuh"
 
 namespace hkbcn {
 
@@ -236,11 +237,14 @@ __device__ void decode_bc7_block(uint4 blk, uint32_t out[16])
 // header bit layouts: bc6h_layout.h
 __device__ uint16_t g_bc6h_layout[14 * BC6H_MAX_TOKENS];
 
+cudaError_t bc7dec_upload_tables();
 cudaError_t decode_upload_tables()
 {
     uint16_t tab[14][BC6H_MAX_TOKENS];
     bc6h_parse_layout(tab);
-    return cudaMemcpyToSymbol(g_bc6h_layout, tab, sizeof(tab));
+    cudaError_t e = cudaMemcpyToSymbol(g_bc6h_layout, tab, sizeof(tab));
+    if (e != cudaSuccess) return e;
+    return bc7dec_upload_tables();
 }
 
 // bcdec.h:289-329
@@ -588,6 +592,98 @@ static bool try_launch_lean(const DecodeParams& P, int sm_count, cudaStream_t st
     return true;
 }
 
+
+// ---------------------------------------------------------------- lean BC7 kernel (bc7_decode_lean.cuh)
+// A CTA takes a tile of 256 consecutive blocks: coalesced 16-byte loads into shared memory, a counting sort of the
+// tile's blocks by mode (warp-aggregated with match_any, so a warp runs one mode's code path instead of up to eight),
+// one block per thread decoded by the mode's specialised routine, texels staged in shared memory in tile order and
+// written out as 128-bit streaming stores, a warp covering 512 contiguous bytes of each texel row.
+__device__ lean7::Tables g_bc7dec_tables;
+constexpr int D7_NT = 256;
+
+// modes 0, 2, 4: the general decoder, kept out of line so that it does not set the lean kernel's register budget
+__device__ __noinline__ void decode_bc7_general(uint4 blk, uint4* stage_col)
+{
+    uint32_t px[16];
+    decode_bc7_block(blk, px);
+#pragma unroll
+    for (int r = 0; r < 4; r++) stage_col[r * D7_NT] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+}
+
+__global__ void __launch_bounds__(D7_NT, 4) decode_bc7_lean_kernel(const DecodeParams P, const uint32_t nTiles)
+{
+    __shared__ uint4 s_blk[D7_NT];
+    __shared__ uint4 s_stage[4][D7_NT];
+    __shared__ uint32_t s_pal[16 * D7_NT];
+    __shared__ lean7::Tables s_T;
+    __shared__ uint32_t s_cnt[10];
+    __shared__ uint8_t s_order[D7_NT];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    {
+        const uint32_t* g = (const uint32_t*)&g_bc7dec_tables;
+        uint32_t* d = (uint32_t*)&s_T;
+        for (uint32_t i = tid; i < sizeof(lean7::Tables) / 4; i += D7_NT) d[i] = g[i];
+    }
+    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
+        const uint32_t b = tile * D7_NT + tid;
+        const bool valid = b < P.nblocks;
+        uint32_t mode = 9; // 9 = no block
+        if (valid) {
+            const uint4 blk = __ldcs((const uint4*)P.src + b);
+            s_blk[tid] = blk;
+            mode = (blk.x & 0xFFu) ? (uint32_t)__ffs(blk.x & 0xFFu) - 1u : 8u;
+        }
+        if (tid < 10) s_cnt[tid] = 0;
+        __syncthreads(); // also orders the table copy and the previous tile's reads of s_stage / s_order
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, mode);
+        const uint32_t leader = (uint32_t)__ffs(peers) - 1u, rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&s_cnt[mode], (uint32_t)__popc(peers));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        __syncthreads();
+        if (valid) {
+            uint32_t start = 0;
+#pragma unroll
+            for (uint32_t m = 0; m < 9; m++) start += (m < mode) ? s_cnt[m] : 0u;
+            s_order[start + base + rank] = (uint8_t)tid;
+        }
+        __syncthreads();
+        const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - tile * D7_NT);
+        if (tid < nvalid) {
+            const uint32_t k = s_order[tid];
+            const uint4 blk = s_blk[k];
+            uint32_t px[16];
+            if (lean7::decode_bc7(blk.x, blk.y, blk.z, blk.w, s_T, s_pal + tid, D7_NT, px)) {
+#pragma unroll
+                for (int r = 0; r < 4; r++) s_stage[r][k] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+            } else {
+                decode_bc7_general(blk, &s_stage[0][k]);
+            }
+        }
+        __syncthreads();
+        if (valid) {
+            const uint32_t by = b / P.nbx, bx = b - by * P.nbx;
+            uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16;
+#pragma unroll
+            for (int r = 0; r < 4; r++) __stcs((uint4*)(d + r * P.dstRowStride), s_stage[r][tid]);
+        }
+    }
+}
+
+cudaError_t bc7dec_upload_tables()
+{
+    static lean7::Tables H;
+    static const uint16_t shape2[64] = {
+        0xCCCC, 0x8888, 0xEEEE, 0xECC8, 0xC880, 0xFEEC, 0xFEC8, 0xEC80, 0xC800, 0xFFEC, 0xFE80, 0xE800, 0xFFE8, 0xFF00, 0xFFF0, 0xF000,
+        0xF710, 0x008E, 0x7100, 0x08CE, 0x008C, 0x7310, 0x3100, 0x8CCE, 0x088C, 0x3110, 0x6666, 0x366C, 0x17E8, 0x0FF0, 0x718E, 0x399C,
+        0xAAAA, 0xF0F0, 0x5A5A, 0x33CC, 0x3C3C, 0x55AA, 0x9696, 0xA55A, 0x73CE, 0x13C8, 0x324C, 0x3BDC, 0x6996, 0xC33C, 0x9966, 0x0660,
+        0x0272, 0x04E4, 0x4E40, 0x2720, 0xC936, 0x936C, 0x39C6, 0x639C, 0x9336, 0x9CC6, 0x817E, 0xE718, 0xCCF0, 0x0FCC, 0x7744, 0xEE22};
+    static const uint8_t anchor2[64] = {15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 2, 8, 2, 2, 8, 8, 15, 2, 8, 2, 2, 8, 8, 2, 2,
+                                        15, 15, 6, 8, 2, 8, 15, 15, 2, 8, 2, 2, 2, 15, 15, 6, 6, 2, 6, 8, 15, 15, 2, 2, 15, 15, 15, 15, 15, 2, 2, 15};
+    lean7::fill_tables(&H, shape2, anchor2);
+    return cudaMemcpyToSymbol(g_bc7dec_tables, &H, sizeof(H));
+}
+
 template <int CODEC>
 static cudaError_t launch_decode_t(const DecodeParams& P, int sm_count, cudaStream_t stream)
 {
@@ -595,6 +691,14 @@ static cudaError_t launch_decode_t(const DecodeParams& P, int sm_count, cudaStre
     if constexpr (CODEC == C_BC1 || CODEC == C_BC2 || CODEC == C_BC3 || CODEC == C_BC4 || CODEC == C_BC5) {
         cudaError_t e;
         if (try_launch_lean<CODEC>(P, sm_count, stream, e)) return e;
+    }
+    if constexpr (CODEC == C_BC7) {
+        if (!((size_t)P.dst & 15) && !(P.dstRowStride & 15) && !((size_t)P.src & 15)) {
+            const uint32_t nTiles = (P.nblocks + D7_NT - 1) / D7_NT;
+            const uint32_t cap = (uint32_t)sm_count * 16;
+            decode_bc7_lean_kernel<<<nTiles < cap ? nTiles : cap, D7_NT, 0, stream>>>(P, nTiles);
+            return cudaGetLastError();
+        }
     }
     size_t need = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 8 : (CODEC == C_BC6H) ? (P.f32out ? 16 : 8) : 16;
     bool vec = (((size_t)P.dst % need) == 0) && ((P.dstRowStride % need) == 0);

@@ -36,7 +36,7 @@ static long check_rgba(int fmt, const uint32_t w[4])
     case 1: lean::decode_bc2(w[0], w[1], w[2], w[3], px); break;
     case 2: lean::decode_bc3(w[0], w[1], w[2], w[3], px); break;
 #ifdef WITH_BC7
-    case 7: lean7::decode_bc7(w[0], w[1], w[2], w[3], px); break;
+    case 7: if (!lean7::decode_bc7_host(w[0], w[1], w[2], w[3], px)) return 0; break; // modes 0, 2, 4: general decoder
 #endif
     }
     ref_decode(fmt, w, want, 16, 0);
