@@ -69,10 +69,31 @@ HKD uint32_t spread_to_bytes(uint32_t x)
     }
 }
 
+// Per-thread palette scratch of the two-subset modes: 16 entries, entry e of thread t at byte e * 1024 + 4 * t of a
+// 16 KB shared array (entry-major: conflict-free whatever the lanes' entries are).  On the host: a plain array.
+#ifdef HKBCN_HOST_EMU
+struct Pal {
+    uint32_t* a;
+    void st(int e, uint32_t v) const { a[e] = v; }
+    uint32_t ld(uint32_t c, int i) const { return a[(c >> (4 * i)) & 15u]; } // entry = nibble i of c
+};
+#else
+struct Pal {
+    char*    base; // the shared array (uniform)
+    uint32_t t4;   // 4 * threadIdx.x (< 1024)
+    __device__ __forceinline__ void st(int e, uint32_t v) const { *(uint32_t*)(base + (e * 1024 + t4)) = v; }
+    __device__ __forceinline__ uint32_t ld(uint32_t c, int i) const
+    {
+        const uint32_t sh = (4 * i >= 10) ? (c >> (4 * i - 10)) : (c << (10 - 4 * i));
+        return *(const uint32_t*)(base + ((sh & 0x3C00u) | t4)); // SHF + LOP3 + LDS [R + UR]
+    }
+};
+#endif
+
 // Palette of a two-subset mode: Xb = bytes [s0.lo, s0.hi, s1.lo, s1.hi] of one channel (8-bit endpoints).
-// Writes entry (s << 3 | k) to pal[(s << 3 | k) * stride] for k < 2^IB.
+// Writes entry (s << 3 | k) for k < 2^IB.
 template <int IB, bool HAS_ALPHA>
-HKD void two_subset_palette(uint32_t Rb, uint32_t Gb, uint32_t Bb, uint32_t Ab, uint32_t* pal, int stride)
+HKD void two_subset_palette(uint32_t Rb, uint32_t Gb, uint32_t Bb, uint32_t Ab, const Pal& pal)
 {
     const uint32_t K = 0x80u;
     const uint32_t Ar = hk_prmt(Rb, K, 0x2404), Ag = hk_prmt(Gb, K, 0x2404), Ab_ = hk_prmt(Bb, K, 0x2404), Aa = hk_prmt(Ab, K, 0x2404);
@@ -86,23 +107,23 @@ HKD void two_subset_palette(uint32_t Rb, uint32_t Gb, uint32_t Bb, uint32_t Ab, 
         uint32_t u;
         if (HAS_ALPHA) u = hk_prmt(Vb, Da * w4 + Aa, 0x7351);
         else u = hk_prmt(Vb, 0xFFFFFFFFu, 0x7371);   // [b.s0, FF, b.s1, FF]
-        pal[k * stride] = hk_prmt(t, u, 0x5410);
-        pal[(8 + k) * stride] = hk_prmt(t, u, 0x7632);
+        pal.st(k, hk_prmt(t, u, 0x5410));
+        pal.st(8 + k, hk_prmt(t, u, 0x7632));
     }
 }
 
 // texels of a two-subset block from the combined nibble streams (subset << 3 | index)
-HKD void two_subset_texels(uint32_t c0, uint32_t c1, const uint32_t* pal, int stride, uint32_t px[16])
+HKD void two_subset_texels(uint32_t c0, uint32_t c1, const Pal& pal, uint32_t px[16])
 {
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-        px[i] = pal[((c0 >> (4 * i)) & 15u) * stride];
-        px[8 + i] = pal[((c1 >> (4 * i)) & 15u) * stride];
+        px[i] = pal.ld(c0, i);
+        px[8 + i] = pal.ld(c1, i);
     }
 }
 
 // ---- mode 1: 2 subsets, 6-bit RGB + shared p-bit per subset, 3-bit indices (bc7decomp.cpp:168-260 family)
-HKD void decode_mode1(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, uint32_t* pal, int stride, uint32_t px[16])
+HKD void decode_mode1(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, const Pal& pal, uint32_t px[16])
 {
     const uint32_t part = (w0 >> 2) & 63u;
     const uint32_t pb = ((w2 >> 16) & 1u) * 0x0101u + ((w2 >> 17) & 1u) * 0x01010000u;
@@ -112,7 +133,7 @@ HKD void decode_mode1(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const 
     Rb = Rb * 2u + ((Rb >> 6) & 0x01010101u); // 7 -> 8 bits: (v << 1) | (v >> 6)
     Gb = Gb * 2u + ((Gb >> 6) & 0x01010101u);
     Bb = Bb * 2u + ((Bb >> 6) & 0x01010101u);
-    two_subset_palette<3, false>(Rb, Gb, Bb, 0xFFFFFFFFu, pal, stride);
+    two_subset_palette<3, false>(Rb, Gb, Bb, 0xFFFFFFFFu, pal);
     // 46 index bits from bit 82; implicit zeros after texel 0's two bits and the anchor's
     unsigned long long S = ((unsigned long long)(w3 >> 18) << 32) | hk_funnel_r(w2, w3, 18);
     S += S & ~3ull;
@@ -120,7 +141,7 @@ HKD void decode_mode1(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const 
     const uint32_t lo = (uint32_t)S, hi = (uint32_t)(S >> 32);
     const uint32_t c0 = lean::spread3(lo & 0x00FFFFFFu) | T.nib[part][0];
     const uint32_t c1 = lean::spread3(hk_funnel_r(lo, hi, 24) & 0x00FFFFFFu) | T.nib[part][1];
-    two_subset_texels(c0, c1, pal, stride, px);
+    two_subset_texels(c0, c1, pal, px);
 }
 
 // 16 two-bit indices (32 bits) -> two nibble streams
@@ -136,24 +157,24 @@ HKD void spread2_stream(uint32_t S, uint32_t& c0, uint32_t& c1)
 HKD uint32_t pbits_to_bytes(uint32_t nib) { return ((nib & 15u) * 0x00204081u) & 0x01010101u; }
 
 // ---- mode 3: 2 subsets, 7-bit RGB + p-bit per endpoint, 2-bit indices
-HKD void decode_mode3(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, uint32_t* pal, int stride, uint32_t px[16])
+HKD void decode_mode3(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, const Pal& pal, uint32_t px[16])
 {
     const uint32_t part = (w0 >> 4) & 63u;
     const uint32_t pb = pbits_to_bytes(hk_funnel_r(w2, w3, 30)); // bits 94..97
     const uint32_t Rb = spread_to_bytes<7>(hk_funnel_r(w0, w1, 10) & 0x0FFFFFFFu) * 2u + pb;
     const uint32_t Gb = spread_to_bytes<7>(hk_funnel_r(w1, w2, 6) & 0x0FFFFFFFu) * 2u + pb;
     const uint32_t Bb = spread_to_bytes<7>((w2 >> 2) & 0x0FFFFFFFu) * 2u + pb;
-    two_subset_palette<2, false>(Rb, Gb, Bb, 0xFFFFFFFFu, pal, stride);
+    two_subset_palette<2, false>(Rb, Gb, Bb, 0xFFFFFFFFu, pal);
     uint32_t S = w3 >> 2; // 30 index bits from bit 98
     S += S & ~1u;
     S += S & T.ins2[part];
     uint32_t c0, c1;
     spread2_stream(S, c0, c1);
-    two_subset_texels(c0 | T.nib[part][0], c1 | T.nib[part][1], pal, stride, px);
+    two_subset_texels(c0 | T.nib[part][0], c1 | T.nib[part][1], pal, px);
 }
 
 // ---- mode 7: 2 subsets, 5-bit RGBA + p-bit per endpoint, 2-bit indices
-HKD void decode_mode7(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, uint32_t* pal, int stride, uint32_t px[16])
+HKD void decode_mode7(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, const Pal& pal, uint32_t px[16])
 {
     const uint32_t part = (w0 >> 8) & 63u;
     const uint32_t pb = pbits_to_bytes(hk_funnel_r(w2, w3, 30));
@@ -165,13 +186,13 @@ HKD void decode_mode7(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const 
     Gb = Gb * 4u + ((Gb >> 4) & 0x03030303u);
     Bb = Bb * 4u + ((Bb >> 4) & 0x03030303u);
     Ab = Ab * 4u + ((Ab >> 4) & 0x03030303u);
-    two_subset_palette<2, true>(Rb, Gb, Bb, Ab, pal, stride);
+    two_subset_palette<2, true>(Rb, Gb, Bb, Ab, pal);
     uint32_t S = w3 >> 2;
     S += S & ~1u;
     S += S & T.ins2[part];
     uint32_t c0, c1;
     spread2_stream(S, c0, c1);
-    two_subset_texels(c0 | T.nib[part][0], c1 | T.nib[part][1], pal, stride, px);
+    two_subset_texels(c0 | T.nib[part][0], c1 | T.nib[part][1], pal, px);
 }
 
 // packed lanes {x, y} (bytes 0 and 2) -> A = lanes * 256 + 128
@@ -198,46 +219,61 @@ HKD void decode_mode6(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32
     }
 }
 
+// four-entry byte table [e0, e1, e2, e3] of one channel for the 2-bit weights {0, 21, 43, 64}: lanes = two entries,
+// V = l * 4(64 - w) + h * 4w + 128, results in bytes 1 and 3
+HKD uint32_t table2(uint32_t l, uint32_t h)
+{
+    const uint32_t V01 = l * (256u | (172u << 16)) + h * (84u << 16) + 0x00800080u;
+    const uint32_t V23 = l * 84u + h * (172u | (256u << 16)) + 0x00800080u;
+    return hk_prmt(V01, V23, 0x7531);
+}
+
 // ---- mode 5: 1 subset, 7-bit RGB + 8-bit A, 2-bit colour and 2-bit alpha indices, rotation
+// Channel byte tables looked up four texels at a time (as BC3 in bcn_decode_lean.cuh); the rotation swaps which
+// table / selector stream feeds which output channel, once per block.
 HKD void decode_mode5(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t px[16])
 {
     // fields: rot 6, r0 8, r1 15, g0 22, g1 29, b0 36, b1 43, a0 50, a1 58, colour indices 66 (31 bits), alpha indices 97 (31 bits)
     const uint32_t rot = (w0 >> 6) & 3u;
-    uint32_t Lrg = ((w0 >> 8) & 0x7Fu) | (((w0 >> 22) & 0x7Fu) << 16);
-    uint32_t Hrg = ((w0 >> 15) & 0x7Fu) | ((hk_funnel_r(w0, w1, 29) & 0x7Fu) << 16);
-    Lrg = Lrg * 2u + ((Lrg >> 6) & 0x00010001u);
-    Hrg = Hrg * 2u + ((Hrg >> 6) & 0x00010001u);
-    uint32_t lb = (w1 >> 4) & 0x7Fu, hb = (w1 >> 11) & 0x7Fu;
-    lb = lb * 2u + (lb >> 6);
-    hb = hb * 2u + (hb >> 6);
-    const uint32_t la = (w1 >> 18) & 0xFFu, ha = hk_funnel_r(w1, w2, 26) & 0xFFu;
-    const uint32_t Arg = lanes_A(Lrg), Aba = lanes_A(lb | (la << 16));
-    const uint32_t Drg = (Hrg - Lrg) << 2, Db = (hb - lb) << 2, Da = (ha - la) << 18;
+    uint32_t r0 = (w0 >> 8) & 0x7Fu, r1 = (w0 >> 15) & 0x7Fu, g0 = (w0 >> 22) & 0x7Fu, g1 = hk_funnel_r(w0, w1, 29) & 0x7Fu;
+    uint32_t b0 = (w1 >> 4) & 0x7Fu, b1 = (w1 >> 11) & 0x7Fu;
+    r0 = r0 * 2u + (r0 >> 6); r1 = r1 * 2u + (r1 >> 6);
+    g0 = g0 * 2u + (g0 >> 6); g1 = g1 * 2u + (g1 >> 6);
+    b0 = b0 * 2u + (b0 >> 6); b1 = b1 * 2u + (b1 >> 6);
+    const uint32_t a0 = (w1 >> 18) & 0xFFu, a1 = hk_funnel_r(w1, w2, 26) & 0xFFu;
+    const uint32_t tr = table2(r0, r1), tg = table2(g0, g1), tb = table2(b0, b1), ta = table2(a0, a1);
     uint32_t cS = hk_funnel_r(w2, w3, 2) & 0x7FFFFFFFu, aS = w3 >> 1;
     cS += cS & ~1u; // texel 0's implicit zero
     aS += aS & ~1u;
-    const uint32_t sel = rot == 0 ? 0x7531u : rot == 1 ? 0x1537u : rot == 2 ? 0x3571u : 0x5731u;
-    const uint32_t W2 = 0x402B1500u; // g_bc7_weights2 = {0, 21, 43, 64}
+    uint32_t cs[2], as[2];
+    lean::spread2(cS, cs);
+    lean::spread2(aS, as);
+    // output channel c = (table, selectors): the rotated channel trades places with alpha
+    const uint32_t tR = rot == 1 ? ta : tr, tG = rot == 2 ? ta : tg, tB = rot == 3 ? ta : tb;
+    const uint32_t tA = rot == 0 ? ta : rot == 1 ? tr : rot == 2 ? tg : tb;
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const uint32_t cw = hk_prmt(W2, 0, (cS >> (2 * i)) & 3u), aw = hk_prmt(W2, 0, (aS >> (2 * i)) & 3u);
-        px[i] = hk_prmt(Drg * cw + Arg, Db * cw + Da * aw + Aba, sel);
+    for (int h = 0; h < 2; h++) {
+        const uint32_t sR = rot == 1 ? as[h] : cs[h], sG = rot == 2 ? as[h] : cs[h], sB = rot == 3 ? as[h] : cs[h], sA = rot == 0 ? as[h] : cs[h];
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const int sh = 16 * q;
+            lean::transpose_row(hk_prmt(tR, 0, sR >> sh), hk_prmt(tG, 0, sG >> sh), hk_prmt(tB, 0, sB >> sh), hk_prmt(tA, 0, sA >> sh), px + 4 * (2 * h + q));
+        }
     }
 }
 
 // Decode one block with the lean paths; returns false for modes 0, 2, 4 (caller uses the general decoder).
-// pal: 16 entries of scratch at pal[k * stride] (two-subset modes only).
-HKD bool decode_bc7(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, uint32_t* pal, int stride, uint32_t px[16])
+HKD bool decode_bc7(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const Tables& T, const Pal& pal, uint32_t px[16])
 {
     const uint32_t low = w0 & 0xFFu;
     if (low & 1u) return false;
-    if (low & 2u) { decode_mode1(w0, w1, w2, w3, T, pal, stride, px); return true; }
+    if (low & 2u) { decode_mode1(w0, w1, w2, w3, T, pal, px); return true; }
     if (low & 4u) return false;
-    if (low & 8u) { decode_mode3(w0, w1, w2, w3, T, pal, stride, px); return true; }
+    if (low & 8u) { decode_mode3(w0, w1, w2, w3, T, pal, px); return true; }
     if (low & 16u) return false;
     if (low & 32u) { decode_mode5(w0, w1, w2, w3, px); return true; }
     if (low & 64u) { decode_mode6(w0, w1, w2, w3, px); return true; }
-    if (low & 128u) { decode_mode7(w0, w1, w2, w3, T, pal, stride, px); return true; }
+    if (low & 128u) { decode_mode7(w0, w1, w2, w3, T, pal, px); return true; }
 #pragma unroll
     for (int i = 0; i < 16; i++) px[i] = 0; // reserved mode: transparent black (bc7decomp.cpp:628-630)
     return true;
@@ -250,8 +286,9 @@ static inline bool decode_bc7_host(uint32_t w0, uint32_t w1, uint32_t w2, uint32
     static Tables T;
     static bool init = false;
     if (!init) { fill_tables(&T, kShape2, kAnchor2); init = true; }
-    uint32_t pal[16];
-    return decode_bc7(w0, w1, w2, w3, T, pal, 1, px);
+    uint32_t scratch[16];
+    const Pal pal{scratch};
+    return decode_bc7(w0, w1, w2, w3, T, pal, px);
 }
 #endif
 

@@ -596,77 +596,89 @@ static bool try_launch_lean(const DecodeParams& P, int sm_count, cudaStream_t st
 // ---------------------------------------------------------------- lean BC7 kernel (bc7_decode_lean.cuh)
 // A CTA takes a tile of 256 consecutive blocks: coalesced 16-byte loads into shared memory, a counting sort of the
 // tile's blocks by mode (warp-aggregated with match_any, so a warp runs one mode's code path instead of up to eight),
-// one block per thread decoded by the mode's specialised routine, texels staged in shared memory in tile order and
-// written out as 128-bit streaming stores, a warp covering 512 contiguous bytes of each texel row.
+// one block per thread decoded by the mode's specialised routine and written straight to its place with 128-bit
+// streaming stores (sorted lanes of one mode are mostly neighbouring blocks, so the 16-byte stores of a warp still pair
+// up into full sectors).  Sort buffers are double-buffered by tile parity, which leaves two barriers per tile.
 __device__ lean7::Tables g_bc7dec_tables;
 constexpr int D7_NT = 256;
 
 // modes 0, 2, 4: the general decoder, kept out of line so that it does not set the lean kernel's register budget
-__device__ __noinline__ void decode_bc7_general(uint4 blk, uint4* stage_col)
+__device__ __noinline__ void decode_bc7_general(uint4 blk, uint8_t* d, size_t rowStride)
 {
     uint32_t px[16];
     decode_bc7_block(blk, px);
 #pragma unroll
-    for (int r = 0; r < 4; r++) stage_col[r * D7_NT] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+    for (int r = 0; r < 4; r++) __stcs((uint4*)(d + r * rowStride), make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]));
 }
 
 __global__ void __launch_bounds__(D7_NT, 4) decode_bc7_lean_kernel(const DecodeParams P, const uint32_t nTiles)
 {
-    __shared__ uint4 s_blk[D7_NT];
-    __shared__ uint4 s_stage[4][D7_NT];
-    __shared__ uint32_t s_pal[16 * D7_NT];
+    __shared__ uint4 s_blk[2][D7_NT];
+    __shared__ __align__(16) uint32_t s_pal[16 * D7_NT];
     __shared__ lean7::Tables s_T;
-    __shared__ uint32_t s_cnt[10];
-    __shared__ uint8_t s_order[D7_NT];
+    __shared__ __align__(16) uint32_t s_cnt[2][12];
+    __shared__ uint8_t s_order[2][D7_NT];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     {
         const uint32_t* g = (const uint32_t*)&g_bc7dec_tables;
         uint32_t* d = (uint32_t*)&s_T;
         for (uint32_t i = tid; i < sizeof(lean7::Tables) / 4; i += D7_NT) d[i] = g[i];
     }
-    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
-        const uint32_t b = tile * D7_NT + tid;
+    if (tid < 24) (&s_cnt[0][0])[tid] = 0;
+    const lean7::Pal pal{(char*)s_pal, tid * 4u};
+    // block coordinates of the tile's first block, advanced incrementally (no division in the loop)
+    const uint32_t step = gridDim.x * D7_NT;
+    uint32_t t0 = blockIdx.x * D7_NT;
+    uint32_t by0 = t0 / P.nbx, bx0 = t0 - by0 * P.nbx;
+    const uint32_t dby = step / P.nbx, dbx = step - dby * P.nbx;
+    uint32_t par = 0;
+    __syncthreads();
+    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x, par ^= 1u) {
+        const uint32_t b = t0 + tid;
         const bool valid = b < P.nblocks;
         uint32_t mode = 9; // 9 = no block
         if (valid) {
             const uint4 blk = __ldcs((const uint4*)P.src + b);
-            s_blk[tid] = blk;
+            s_blk[par][tid] = blk;
             mode = (blk.x & 0xFFu) ? (uint32_t)__ffs(blk.x & 0xFFu) - 1u : 8u;
         }
-        if (tid < 10) s_cnt[tid] = 0;
-        __syncthreads(); // also orders the table copy and the previous tile's reads of s_stage / s_order
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, mode);
         const uint32_t leader = (uint32_t)__ffs(peers) - 1u, rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
         uint32_t base = 0;
-        if (lane == leader) base = atomicAdd(&s_cnt[mode], (uint32_t)__popc(peers));
+        if (lane == leader) base = atomicAdd(&s_cnt[par][mode], (uint32_t)__popc(peers));
         base = __shfl_sync(0xFFFFFFFFu, base, leader);
         __syncthreads();
         if (valid) {
-            uint32_t start = 0;
+            const uint4 c0 = *(const uint4*)&s_cnt[par][0], c1 = *(const uint4*)&s_cnt[par][4];
+            const uint32_t c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+            uint32_t start = base + rank;
 #pragma unroll
-            for (uint32_t m = 0; m < 9; m++) start += (m < mode) ? s_cnt[m] : 0u;
-            s_order[start + base + rank] = (uint8_t)tid;
+            for (uint32_t m = 0; m < 8; m++) start += (m < mode) ? c[m] : 0u;
+            s_order[par][start] = (uint8_t)tid;
         }
         __syncthreads();
-        const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - tile * D7_NT);
+        if (tid < 12) s_cnt[par][tid] = 0; // next used two tiles from now, behind two more barriers
+        const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - t0);
         if (tid < nvalid) {
-            const uint32_t k = s_order[tid];
-            const uint4 blk = s_blk[k];
+            const uint32_t k = s_order[par][tid];
+            const uint4 blk = s_blk[par][k];
+            uint32_t bx = bx0 + k, by = by0;
+            while (bx >= P.nbx) { bx -= P.nbx; by++; }
+            uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16;
             uint32_t px[16];
-            if (lean7::decode_bc7(blk.x, blk.y, blk.z, blk.w, s_T, s_pal + tid, D7_NT, px)) {
+            if (lean7::decode_bc7(blk.x, blk.y, blk.z, blk.w, s_T, pal, px)) {
 #pragma unroll
-                for (int r = 0; r < 4; r++) s_stage[r][k] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+                for (int r = 0; r < 4; r++) __stcs((uint4*)(d + r * P.dstRowStride), make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]));
             } else {
-                decode_bc7_general(blk, &s_stage[0][k]);
+                decode_bc7_general(blk, d, P.dstRowStride);
             }
         }
-        __syncthreads();
-        if (valid) {
-            const uint32_t by = b / P.nbx, bx = b - by * P.nbx;
-            uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16;
-#pragma unroll
-            for (int r = 0; r < 4; r++) __stcs((uint4*)(d + r * P.dstRowStride), s_stage[r][tid]);
-        }
+        t0 += step;
+        by0 += dby;
+        bx0 += dbx;
+        if (bx0 >= P.nbx) { bx0 -= P.nbx; by0++; }
+        // no barrier here: the next tile writes the other parity's buffers, last read one tile ago and fenced by this
+        // tile's two barriers; s_pal columns are thread-private
     }
 }
 

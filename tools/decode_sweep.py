@@ -30,12 +30,15 @@ def peak():
         return 6650.0
 
 
+OPAQUE = False
+
+
 def real_blocks(torch, hkbcn, L, name, n, stream):
     """encode a synthetic n x n image once (tiled from a 512^2 source) so the decoder sees a realistic mode mix"""
     import synth
     t = 512
     if name == "BC7":
-        a = synth.albedo_rgba8(t, t, 0xB2000005, "mask").reshape(t, t, 4)
+        a = (synth.albedo_rgba8(t, t, 0xB2000004) if OPAQUE else synth.albedo_rgba8(t, t, 0xB2000005, "mask")).reshape(t, t, 4)
         img = np.tile(a, (n // t, n // t, 1))
         fmt = 66
     else:
@@ -55,8 +58,11 @@ def main():
     ap.add_argument("--formats", default=",".join(FORMATS))
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--real", action="store_true")
+    ap.add_argument("--opaque", action="store_true", help="--real BC7 input: opaque albedo (modes 1/6) instead of the alpha-mask variant")
     ap.add_argument("--json", default="")
     args = ap.parse_args()
+    global OPAQUE
+    OPAQUE = args.opaque
     import torch
     import hkbcn
     L = hkbcn.lib()
