@@ -160,36 +160,93 @@ def workload_config(levels, n):
             "mips": "2x2 box average of the synthetic level 0", "l2": "256 MiB buffer written between timed steps"}
 
 
+# ----------------------------------------------------------------------------- sharding (no data-path collective)
+def rank_seed(rank):
+    """textures are independent units: rank r encodes its own texture, generated from seed SEED + r"""
+    return SEED + rank
+
+
+class Ranks:
+    """torch.distributed plumbing only: barrier and max-over-ranks of the timed region.  nccl on GPUs, gloo on CPU
+    (tests/test_bench_shard_cpu.py runs the same code path with world_size 2 on CPU)."""
+
+    def __init__(self, use_cuda):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.use_cuda = use_cuda
+        self.dist = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+            if use_cuda:
+                dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            else:
+                dist.init_process_group("gloo")
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+        if self.use_cuda:
+            import torch
+            torch.cuda.synchronize()
+
+    def max(self, x):
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda" if self.use_cuda else "cpu")
+        if self.dist:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum(self, x):
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda" if self.use_cuda else "cpu")
+        if self.dist:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.dist:
+            self.dist.destroy_process_group()
+
+
+def whole_job_value(ranks, px_this_rank, ms_this_rank):
+    """whole-job Mpix/s = pixels all ranks processed / max-over-ranks time"""
+    ms = ranks.max(ms_this_rank)
+    px = ranks.sum(px_this_rank)
+    return px / (ms * 1e-3) / 1e6, ms
+
+
+def run_selftest(args):
+    """CPU check of the N > 1 plumbing (gloo): every rank derives its shard, reports a synthetic time, rank 0 prints
+    the aggregate exactly as the CUDA arm does.  No kernels, no oracle."""
+    ranks = Ranks(use_cuda=False)
+    px = 1000 * (ranks.rank + 1)
+    ms = 10.0 * (ranks.rank + 1)
+    ranks.barrier()
+    value, ms_max = whole_job_value(ranks, px, ms)
+    if ranks.rank == 0:
+        print(json.dumps({"selftest": True, "n_gpus": ranks.world, "value": value, "ms_per_step": ms_max,
+                          "seeds": [rank_seed(r) for r in range(ranks.world)]}))
+    ranks.close()
+
+
 # ----------------------------------------------------------------------------- CUDA arm
 def run_gpu(args):
     import torch
     import hkbcn
 
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- this path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    def barrier():
-        if dist:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        if dist:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    ranks = Ranks(use_cuda=True)
+    rank, local, world, dist = ranks.rank, ranks.local, ranks.world, ranks.dist
+    barrier, max_over_ranks = ranks.barrier, ranks.max
 
     L = hkbcn.lib()
     hkbcn.init(1 << local)  # library device 0 == cuda:local
-    levels = make_chain(SEED + rank)
+    levels = make_chain(rank_seed(rank))
     mips, px = len(levels), chain_pixels(levels)
     src_np = np.concatenate([l.ravel() for l in levels])
     dst_bytes = L.hkbcn_chain_bytes(BC7, SIZE, SIZE, 1, mips)
@@ -222,10 +279,8 @@ def run_gpu(args):
         evs.append((e0, e1))
     barrier()
     launches = L.hkbcn_launch_count() - launches0
-    ms_total = max_over_ranks(sum(a.elapsed_time(b) for a, b in evs))
+    value, ms_step = whole_job_value(ranks, px, sum(a.elapsed_time(b) for a, b in evs) / args.steps)
     clocks = sampler.stop() if rank == 0 else None
-    ms_step = ms_total / args.steps
-    value = world * px / (ms_step * 1e-3) / 1e6
 
     # ---- end to end through the C ABI with host buffers (H2D + kernel + D2H inside the timed region)
     h_src = L.hkbcn_alloc_pinned(src_np.nbytes)
@@ -270,41 +325,79 @@ def run_gpu(args):
         }
         if world == 1:
             out["decode"] = decode_sweep(torch, hkbcn, L, d_dst, stream, flush, hbm)
+            out["encode_other_formats"] = encode_others(torch, hkbcn, L, stream, flush)
             v, dt, cores, sample = time_reference(levels, 1, 0)
             out["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample}
         print(json.dumps(out))
     L.hkbcn_free_pinned(h_src)
     L.hkbcn_free_pinned(h_dst)
-    if dist:
-        dist.destroy_process_group()
+    ranks.close()
+
+
+def _timed(torch, stream, flush, fn, iters, skip=2):
+    times = []
+    for i in range(iters + skip):
+        flush.fill_(i & 255)  # evict L2 between iterations (untimed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        if i >= skip:
+            times.append(e0.elapsed_time(e1))
+    return float(np.mean(times))
 
 
 def decode_sweep(torch, hkbcn, L, bc7_blocks, stream, flush, hbm):
-    """HBM-bound half of the path: whole-surface decode of 4096^2 per format, algorithmic bytes/px of SURVEY.md 8d."""
-    n = SIZE
-    nblk = (n // 4) * (n // 4)
+    """HBM-bound half of the path (BASELINE.json configs[4] 'decode bandwidth sweep'): whole-surface decode per format at
+    4096^2, 8192^2 and 16384^2, algorithmic bytes/px of SURVEY.md 8d (block bytes read + texel bytes written).  BC7 and BC6H
+    inputs are blocks this library's encoders produced (the mode mix of real content), tiled up to size; the others are
+    uniform random bits (every selector and both palette modes)."""
+    import synth
     out = {}
     gen = torch.Generator(device="cuda").manual_seed(7)
+    base7 = bc7_blocks[: (SIZE // 4) ** 2 * 16].view(SIZE // 4, SIZE // 4, 16)
+    hdr = torch.from_numpy(np.ascontiguousarray(synth.sky_rgba32f(512, 512, 0xB2000006, 0)).view(np.uint8).ravel()).cuda()
+    base6 = torch.empty(128 * 128 * 16, dtype=torch.uint8, device="cuda")
+    hkbcn.check(L.hkbcn_compress_dev(0, 64, hdr.data_ptr(), base6.data_ptr(), 512, 512, 0, C.c_void_p(stream.cuda_stream)))
+    torch.cuda.synchronize()
+    base6 = base6.view(128, 128, 16)
     for name, fmt, blk, tex, flags in (("BC1", 54, 8, 4, 0), ("BC3", 58, 16, 4, 0), ("BC4", 60, 8, 1, 0), ("BC5", 62, 16, 2, 0),
-                                       ("BC7", 66, 16, 4, 0), ("BC6H_f16", 64, 16, 6, 0)):
-        if fmt == 66:
-            src = bc7_blocks[: nblk * 16]
-        else:
-            src = torch.randint(0, 256, (nblk * blk,), dtype=torch.uint8, device="cuda", generator=gen)
-        dst = torch.empty(n * n * tex, dtype=torch.uint8, device="cuda")
-        times = []
-        for i in range(8):
-            flush.fill_(i)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            hkbcn.check(L.hkbcn_decompress_dev(0, fmt, src.data_ptr(), dst.data_ptr(), n, n, n * tex, flags, C.c_void_p(stream.cuda_stream)))
-            e1.record(stream)
-            torch.cuda.synchronize()
-            if i >= 3:
-                times.append(e0.elapsed_time(e1))
-        ms = float(np.mean(times))
-        gbs = (nblk * blk + n * n * tex) / (ms * 1e-3) / 1e9
-        out[name] = {"GB/s": gbs, "frac": gbs / hbm, "Gpix/s": n * n / (ms * 1e-3) / 1e9, "ms": ms}
+                                       ("BC7", 66, 16, 4, 0), ("BC6H_f16", 64, 16, 6, 0), ("BC6H_f32", 64, 16, 12, 1 << 8)):
+        out[name] = {}
+        for n in (4096, 8192, 16384):
+            nb = n // 4
+            if fmt == 66:
+                src = base7.repeat(nb // base7.shape[0], nb // base7.shape[1], 1).contiguous().view(-1)
+            elif fmt == 64:
+                src = base6.repeat(nb // 128, nb // 128, 1).contiguous().view(-1)
+            else:
+                src = torch.randint(0, 256, (nb * nb * blk,), dtype=torch.uint8, device="cuda", generator=gen)
+            dst = torch.empty(n * n * tex, dtype=torch.uint8, device="cuda")
+            ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_decompress_dev(
+                0, fmt, src.data_ptr(), dst.data_ptr(), n, n, n * tex, flags, C.c_void_p(stream.cuda_stream))), 5, 3)
+            gbs = (nb * nb * blk + n * n * tex) / (ms * 1e-3) / 1e9
+            out[name][str(n)] = {"GB/s": round(gbs, 1), "frac": round(gbs / hbm, 4), "Gpix/s": round(n * n / (ms * 1e-3) / 1e9, 2), "us": round(ms * 1e3, 1)}
+            del src, dst
+    return out
+
+
+def encode_others(torch, hkbcn, L, stream, flush):
+    """the other encoders of the path on BASELINE.json's configs (level 0 only), device-resident, Mpix/s"""
+    import synth
+    out = {}
+    for name, fmt, n, img in (("BC1_2048", 54, 2048, lambda: synth.albedo_rgba8(2048, 2048, 0xB2000001)),
+                              ("BC3_2048", 58, 2048, lambda: synth.albedo_rgba8(2048, 2048, 0xB2000005, "mask")),
+                              ("BC4_4096", 60, 4096, lambda: synth.roughness_r8(4096, 4096, 0xB2000002)),
+                              ("BC5_4096", 62, 4096, lambda: synth.normals_rg8(4096, 4096, 0xB2000003)),
+                              ("BC7_alpha_2048", 66, 2048, lambda: synth.albedo_rgba8(2048, 2048, 0xB2000005, "mask")),
+                              ("BC6H_1024", 64, 1024, lambda: synth.sky_rgba32f(1024, 1024, 0xB2000006, 0))):
+        d_src = torch.from_numpy(np.ascontiguousarray(img()).view(np.uint8).ravel()).cuda()
+        d_dst = torch.empty((n // 4) ** 2 * hkbcn.block_bytes(fmt), dtype=torch.uint8, device="cuda")
+        ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_compress_dev(
+            0, fmt, d_src.data_ptr(), d_dst.data_ptr(), n, n, 0, C.c_void_p(stream.cuda_stream))), 3, 1)
+        out[name] = {"Mpix/s": round(n * n / ms / 1e3, 1), "ms": round(ms, 3)}
+        del d_src, d_dst
     return out
 
 
@@ -340,8 +433,11 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--selftest-shard", action="store_true", help="CPU/gloo check of the N>1 plumbing (used by tests/)")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.selftest_shard:
+        run_selftest(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)

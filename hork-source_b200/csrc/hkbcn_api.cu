@@ -392,6 +392,36 @@ int hkbcn_decode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, si
     return hkbcn_decompress(fmt, src, dst, 4, (uint32_t)n_blocks * 4, dst_row_stride, flags);
 }
 
+// Host-only planning step of hkbcn_compress_batch (no device needed): greedy longest-processing-time assignment of whole
+// jobs to n_gpus bins by pixel-count-weighted cost.  device_of_job[i] = bin of job i.  Deterministic.
+static void plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job)
+{
+    auto cost = [](const hkbcn_job& j) {
+        int c = codec_of(j.fmt);
+        double wgt = c == C_BC7 ? 40.0 : c == C_BC6H ? 8000.0 : (c == C_BC4) ? 4.0 : (c == C_BC5) ? 8.0 : (c == C_BC3) ? 5.0 : (c == C_BC2) ? 1.2 : 1.0;
+        return wgt * (double)j.width * (double)j.height;
+    };
+    std::vector<size_t> order(n_jobs);
+    for (size_t i = 0; i < n_jobs; i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return cost(jobs[a]) > cost(jobs[b]); });
+    std::vector<double> load((size_t)n_gpus, 0.0);
+    for (size_t idx : order) {
+        size_t best = 0;
+        for (size_t d = 1; d < (size_t)n_gpus; d++) if (load[d] < load[best]) best = d;
+        device_of_job[idx] = (int)best;
+        load[best] += cost(jobs[idx]);
+    }
+}
+
+int hkbcn_plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job)
+{
+    if (n_gpus <= 0 || (n_jobs && (!jobs || !device_of_job))) { set_err("bad arguments"); return HKBCN_ERR_BAD_ARG; }
+    for (size_t i = 0; i < n_jobs; i++)
+        if (codec_of(jobs[i].fmt) < 0) { set_err("job %zu: bad format %d", i, jobs[i].fmt); return HKBCN_ERR_BAD_FORMAT; }
+    plan_batch(jobs, n_jobs, n_gpus, device_of_job);
+    return HKBCN_OK;
+}
+
 int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
 {
     int rc = ensure_init();
@@ -399,23 +429,10 @@ int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
     if (n_jobs == 0) return HKBCN_OK;
     if (!jobs) { set_err("null jobs"); return HKBCN_ERR_BAD_ARG; }
     const size_t nd = g_devs.size();
-    // greedy longest-processing-time assignment by pixel-count-weighted cost
-    auto cost = [](const hkbcn_job& j) {
-        int c = codec_of(j.fmt);
-        double wgt = c == C_BC7 ? 40.0 : c == C_BC6H ? 400.0 : (c == C_BC4) ? 4.0 : (c == C_BC5) ? 8.0 : (c == C_BC3) ? 5.0 : 1.0;
-        return wgt * (double)j.width * (double)j.height;
-    };
-    std::vector<size_t> order(n_jobs);
-    for (size_t i = 0; i < n_jobs; i++) order[i] = i;
-    std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return cost(jobs[a]) > cost(jobs[b]); });
+    std::vector<int> assign(n_jobs);
+    plan_batch(jobs, n_jobs, (int)nd, assign.data());
     std::vector<std::vector<size_t>> bins(nd);
-    std::vector<double> load(nd, 0.0);
-    for (size_t idx : order) {
-        size_t best = 0;
-        for (size_t d = 1; d < nd; d++) if (load[d] < load[best]) best = d;
-        bins[best].push_back(idx);
-        load[best] += cost(jobs[idx]);
-    }
+    for (size_t i = 0; i < n_jobs; i++) bins[(size_t)assign[i]].push_back(i);
     std::vector<std::thread> th;
     std::vector<int> first_err(nd, 0);
     std::vector<std::string> err_msg(nd);

@@ -27,7 +27,7 @@ EXPORTS = [
     "hkbcn_block_bytes", "hkbcn_src_texel_bytes", "hkbcn_dst_texel_bytes", "hkbcn_calc_num_mips", "hkbcn_chain_bytes",
     "hkbcn_compress", "hkbcn_decompress", "hkbcn_encode_blocks", "hkbcn_decode_blocks",
     "hkbcn_compress_dev", "hkbcn_decompress_dev", "hkbcn_compress_chain_dev", "hkbcn_compress_chain",
-    "hkbcn_compress_batch", "hkbcn_launch_count", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
+    "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
 ]
 
 
@@ -66,6 +66,7 @@ def lib():
         L.hkbcn_compress_chain_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         L.hkbcn_compress_chain.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
         L.hkbcn_compress_batch.argtypes = [C.POINTER(Job), C.c_size_t]
+        L.hkbcn_plan_batch.argtypes = [C.POINTER(Job), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
         L.hkbcn_launch_count.restype = C.c_uint64
         L.hkbcn_alloc_pinned.restype = C.c_void_p
         L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
@@ -145,3 +146,13 @@ def compress_batch(jobs):
         arr[i] = Job(fmt, w, h, flags, src.ctypes.data, dst.ctypes.data, 0)
     check(lib().hkbcn_compress_batch(arr, len(jobs)))
     return outs
+
+
+def plan_batch(jobs, n_gpus):
+    """jobs: list of (fmt, width, height) -> list of GPU indices (host-only planning step of compress_batch)."""
+    arr = (Job * len(jobs))()
+    for i, (fmt, w, h) in enumerate(jobs):
+        arr[i] = Job(fmt, w, h, 0, None, None, 0)
+    out = (C.c_int * len(jobs))()
+    check(lib().hkbcn_plan_batch(arr, len(jobs), n_gpus, out))
+    return list(out)

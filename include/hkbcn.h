@@ -139,6 +139,9 @@ typedef struct hkbcn_job {
     int         status;/* out */
 } hkbcn_job;
 HKBCN_API int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs);
+/* The planning step of hkbcn_compress_batch on its own (host only, no device needed): device_of_job[i] = index (0..n_gpus-1)
+ * of the GPU job i would be sent to.  Greedy longest-processing-time by pixel count x per-format cost weight; deterministic. */
+HKBCN_API int hkbcn_plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job);
 
 /* ---- instrumentation --------------------------------------------------------
  * Number of kernels this library launched since init (bench.py's gpu_launches). */
