@@ -17,6 +17,8 @@
 #include "bc6h_layout.h"
 #include "bcn_decode_lean.cuh"
 #include "bc7_decode_lean.cuh"
+#include "bc6h_decode_lean.cuh"
+#include <cuda_fp16.h>
 
 namespace hkbcn {
 
@@ -603,13 +605,18 @@ static bool try_launch_lean(const DecodeParams& P, int sm_count, cudaStream_t st
 __device__ lean7::Tables g_bc7dec_tables;
 constexpr int D7_NT = 256;
 
-// modes 0, 2, 4: the general decoder, kept out of line so that it does not set the lean kernel's register budget
-__device__ __noinline__ void decode_bc7_general(uint4 blk, uint4* stage_col)
+// modes 0, 2, 4: the general decoder, kept out of line so that it does not set the lean kernel's register budget.
+// Called only from warp-converged code in a loop of its own after the tile loop (every lane of the warp calls, `store`
+// selects the lanes that hold such a block): a call from a divergent branch inside the tile loop returned to lean-path
+// lanes with clobbered warp-uniform registers, and a converged call inside the loop made the loop spill.
+__device__ __noinline__ void decode_bc7_general(uint4 blk, uint8_t* d, size_t rowStride, bool store)
 {
     uint32_t px[16];
     decode_bc7_block(blk, px);
+    if (store) {
 #pragma unroll
-    for (int r = 0; r < 4; r++) stage_col[r * D7_NT] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+        for (int r = 0; r < 4; r++) *(uint4*)(d + r * rowStride) = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
+    }
 }
 
 __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes)
@@ -640,7 +647,7 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
     uint32_t t0 = blockIdx.x * D7_NT;
     uint32_t by0 = t0 / P.nbx, bx0 = t0 - by0 * P.nbx;
     const uint32_t dby = step / P.nbx, dbx = step - dby * P.nbx;
-    uint32_t par = 0;
+    uint32_t par = 0, anyGeneral = 0;
     __syncthreads();
     for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x, par ^= 1u) {
         const uint32_t b = t0 + tid;
@@ -649,7 +656,8 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
         if (valid) {
             const uint4 blk = __ldcs((const uint4*)P.src + b);
             s_blk[par][tid] = blk;
-            mode = (blk.x & 0xFFu) ? (uint32_t)__ffs(blk.x & 0xFFu) - 1u : 8u;
+            // sort key: modes 0, 2, 4 (general decoder) first, then 1, 3, 5, 6, 7 and the reserved mode
+            mode = (blk.x & 0xFFu) ? (0x76524130u >> (4u * ((uint32_t)__ffs(blk.x & 0xFFu) - 1u))) & 15u : 8u;
         }
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, mode);
         const uint32_t leader = (uint32_t)__ffs(peers) - 1u, rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
@@ -668,20 +676,20 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
             s_order[par][start] = (uint8_t)tid;
         }
         __syncthreads();
-        if (tid < 12) s_cnt[par][tid] = 0; // next used two tiles from now, behind barriers
+        const uint32_t nGeneral = s_cnt[par][0] + s_cnt[par][1] + s_cnt[par][2]; // sorted slots [0, nGeneral)
+        if (tid >= 3 && tid < 12) s_cnt[par][tid] = 0; // next used two tiles from now, behind barriers; [0..2] after the next barrier
         const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - t0);
-        if (tid < nvalid) {
+        if (tid >= nGeneral && tid < nvalid) {
             const uint32_t k = s_order[par][tid];
             const uint4 blk = s_blk[par][k];
             uint32_t px[16];
-            if (lean7::decode_bc7(blk.x, blk.y, blk.z, blk.w, s_T, pal, px)) {
+            lean7::decode_bc7(blk.x, blk.y, blk.z, blk.w, s_T, pal, px);
 #pragma unroll
-                for (int r = 0; r < 4; r++) s_stage[r][k] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
-            } else {
-                decode_bc7_general(blk, &s_stage[0][k]);
-            }
+            for (int r = 0; r < 4; r++) s_stage[r][k] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
         }
+        anyGeneral |= nGeneral; // their texels are written by the loop after this one
         __syncthreads();
+        if (tid < 3) s_cnt[par][tid] = 0;
         if (ROWS) {
             if (tid == 0) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -702,7 +710,152 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
         bx0 += dbx;
         if (bx0 >= P.nbx) { bx0 -= P.nbx; by0++; }
     }
+    if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); // stores complete, not only read
+    // Blocks of modes 0, 2, 4 (none in anything the reference's encoder presets emit): a second pass over this CTA's tiles
+    // through the general decoder, one block per thread, every lane calling.
+    if (__syncthreads_or((int)anyGeneral)) {
+        for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
+            const uint32_t b = tile * D7_NT + tid;
+            const bool valid = b < P.nblocks;
+            uint4 blk = make_uint4(0, 0, 0, 0);
+            if (valid) blk = __ldg((const uint4*)P.src + b);
+            const uint32_t low = blk.x & 0xFFu;
+            const uint32_t m = low ? (uint32_t)__ffs(low) - 1u : 8u;
+            const bool general = valid && (m == 0 || m == 2 || m == 4);
+            if (__any_sync(0xFFFFFFFFu, general)) {
+                const uint32_t by = b / P.nbx, bx = b - by * P.nbx;
+                decode_bc7_general(blk, P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16, P.dstRowStride, general);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- lean BC6H kernel (bc6h_decode_lean.cuh)
+// Same shape as the BC7 kernel: 256-block tiles, counting sort by mode (14 modes + reserved), one block per thread through
+// the mode's specialised routine, texel rows staged in shared memory (RGB16F: 24 B per block row, RGB32F: 48 B) and written
+// with TMA bulk stores.
+#ifndef BC6D_OCC
+#define BC6D_OCC 3
+#endif
+template <bool F32>
+struct Bc6hSink {
+    uint8_t* col; // this block's first row in the stage
+    __device__ __forceinline__ void row(int r, const uint32_t w[6]) const
+    {
+        if (!F32) {
+            uint2* d = (uint2*)(col + r * (D7_NT * 24));
+            d[0] = make_uint2(w[0], w[1]);
+            d[1] = make_uint2(w[2], w[3]);
+            d[2] = make_uint2(w[4], w[5]);
+        } else {
+            // exact half -> float (bcdec__half_to_float_quick, bcdec.h:348-373; decoder outputs are always finite)
+            float4* d = (float4*)(col + r * (D7_NT * 48));
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                const float2 a = __half22float2(*(const __half2*)&w[2 * j]), b = __half22float2(*(const __half2*)&w[2 * j + 1]);
+                d[j] = make_float4(a.x, a.y, b.x, b.y);
+            }
+        }
+    }
+};
+
+template <bool F32, bool SIGNED, bool ROWS>
+__global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const DecodeParams P, const uint32_t nTiles)
+{
+    constexpr int RB = F32 ? 48 : 24; // bytes of one block row
+    __shared__ uint4 s_blk[2][D7_NT];
+    extern __shared__ __align__(128) uint8_t s_stage[]; // 4 * D7_NT * RB bytes (dynamic: 48 KB for RGB32F)
+    __shared__ lean7::Tables s_T;
+    __shared__ __align__(16) uint32_t s_cnt[2][16];
+    __shared__ uint8_t s_order[2][D7_NT];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    {
+        const uint32_t* g = (const uint32_t*)&g_bc7dec_tables;
+        uint32_t* d = (uint32_t*)&s_T;
+        for (uint32_t i = tid; i < sizeof(lean7::Tables) / 4; i += D7_NT) d[i] = g[i];
+    }
+    if (tid < 32) (&s_cnt[0][0])[tid] = 0;
+    const uint32_t step = gridDim.x * D7_NT;
+    uint32_t t0 = blockIdx.x * D7_NT;
+    uint32_t by0 = t0 / P.nbx, bx0 = t0 - by0 * P.nbx;
+    const uint32_t dby = step / P.nbx, dbx = step - dby * P.nbx;
+    uint32_t par = 0;
+    __syncthreads();
+    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x, par ^= 1u) {
+        const uint32_t b = t0 + tid;
+        const bool valid = b < P.nblocks;
+        uint32_t mode = 15; // 15 = no block
+        if (valid) {
+            const uint4 blk = __ldcs((const uint4*)P.src + b);
+            s_blk[par][tid] = blk;
+            mode = lean6::mode_of(blk.x);
+        }
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, mode);
+        const uint32_t leader = (uint32_t)__ffs(peers) - 1u, rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&s_cnt[par][mode], (uint32_t)__popc(peers));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncthreads();
+        if (valid) {
+            const uint4 c0 = *(const uint4*)&s_cnt[par][0], c1 = *(const uint4*)&s_cnt[par][4], c2 = *(const uint4*)&s_cnt[par][8],
+                        c3 = *(const uint4*)&s_cnt[par][12];
+            const uint32_t c[15] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w, c2.x, c2.y, c2.z, c2.w, c3.x, c3.y, c3.z};
+            uint32_t start = base + rank;
+#pragma unroll
+            for (uint32_t m = 0; m < 15; m++) start += (m < mode) ? c[m] : 0u;
+            s_order[par][start] = (uint8_t)tid;
+        }
+        __syncthreads();
+        if (tid < 16) s_cnt[par][tid] = 0;
+        const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - t0);
+        if (tid < nvalid) {
+            const uint32_t k = s_order[par][tid];
+            const uint4 blk = s_blk[par][k];
+            Bc6hSink<F32> sink{s_stage + k * RB};
+            lean6::decode_bc6h<SIGNED>(blk.x, blk.y, blk.z, blk.w, s_T, sink);
+        }
+        __syncthreads();
+        if (ROWS) {
+            if (tid == 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                uint8_t* d = P.dst + (size_t)by0 * 4 * P.dstRowStride + (size_t)bx0 * RB;
+#pragma unroll
+                for (int r = 0; r < 4; r++) bulk_s2g(d + r * P.dstRowStride, s_stage + r * (D7_NT * RB), nvalid * RB);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        } else if (valid) {
+            uint32_t bx = bx0 + tid, by = by0;
+            while (bx >= P.nbx) { bx -= P.nbx; by++; }
+            uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * RB;
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int j = 0; j < RB / 8; j++)
+                    __stcs((uint2*)(d + r * P.dstRowStride) + j, *(const uint2*)(s_stage + r * (D7_NT * RB) + tid * RB + j * 8));
+        }
+        t0 += step;
+        by0 += dby;
+        bx0 += dbx;
+        if (bx0 >= P.nbx) { bx0 -= P.nbx; by0++; }
+    }
     if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+template <bool F32, bool SIGNED>
+static cudaError_t launch_bc6h_lean(const DecodeParams& P, uint32_t grid, uint32_t nTiles, bool rows, cudaStream_t stream)
+{
+    constexpr int stage = 4 * D7_NT * (F32 ? 48 : 24);
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[rows]) {
+        cudaError_t e = rows ? cudaFuncSetAttribute(decode_bc6h_lean_kernel<F32, SIGNED, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage)
+                             : cudaFuncSetAttribute(decode_bc6h_lean_kernel<F32, SIGNED, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage);
+        if (e != cudaSuccess) return e;
+        attr_set[rows] = true; // per process; attributes are per device context but the value never changes
+    }
+    if (rows) decode_bc6h_lean_kernel<F32, SIGNED, true><<<grid, D7_NT, stage, stream>>>(P, nTiles);
+    else decode_bc6h_lean_kernel<F32, SIGNED, false><<<grid, D7_NT, stage, stream>>>(P, nTiles);
+    return cudaGetLastError();
 }
 
 cudaError_t bc7dec_upload_tables()
@@ -734,6 +887,15 @@ static cudaError_t launch_decode_t(const DecodeParams& P, int sm_count, cudaStre
             if (P.nbx % D7_NT == 0) decode_bc7_lean_kernel<true><<<nTiles < cap ? nTiles : cap, D7_NT, 0, stream>>>(P, nTiles);
             else decode_bc7_lean_kernel<false><<<nTiles < cap ? nTiles : cap, D7_NT, 0, stream>>>(P, nTiles);
             return cudaGetLastError();
+        }
+    }
+    if constexpr (CODEC == C_BC6H) {
+        if (!((size_t)P.dst & 7) && !(P.dstRowStride & 7) && !((size_t)P.src & 15)) {
+            const uint32_t nTiles = (P.nblocks + D7_NT - 1) / D7_NT;
+            const uint32_t cap = (uint32_t)sm_count * 8, grid = nTiles < cap ? nTiles : cap;
+            const bool rows = (P.nbx % D7_NT == 0) && !((size_t)P.dst & 15) && !(P.dstRowStride & 15);
+            if (P.f32out) return P.is_signed ? launch_bc6h_lean<true, true>(P, grid, nTiles, rows, stream) : launch_bc6h_lean<true, false>(P, grid, nTiles, rows, stream);
+            return P.is_signed ? launch_bc6h_lean<false, true>(P, grid, nTiles, rows, stream) : launch_bc6h_lean<false, false>(P, grid, nTiles, rows, stream);
         }
     }
     size_t need = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 8 : (CODEC == C_BC6H) ? (P.f32out ? 16 : 8) : 16;

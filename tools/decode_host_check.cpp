@@ -13,6 +13,7 @@
 #include "../hork-source_b200/csrc/bcn_decode_lean.cuh"
 #ifdef WITH_BC7
 #include "../hork-source_b200/csrc/bc7_decode_lean.cuh"
+#include "../hork-source_b200/csrc/bc6h_decode_lean.cuh"
 #endif
 
 using namespace hkbcn;
@@ -50,6 +51,25 @@ static long check_alpha(const uint32_t w[2])
     return memcmp(row, want, 16) != 0;
 }
 
+#ifdef WITH_BC7
+struct HostSink {
+    uint32_t rows[4][6];
+    void row(int r, const uint32_t w[6]) { memcpy(rows[r], w, 24); }
+};
+static long check_bc6h(const uint32_t w[4], bool isSigned)
+{
+    static lean7::Tables T;
+    static bool init = false;
+    if (!init) { lean7::fill_tables(&T, kShape2, kAnchor2); init = true; }
+    HostSink sink;
+    if (isSigned) lean6::decode_bc6h<true>(w[0], w[1], w[2], w[3], T, sink);
+    else lean6::decode_bc6h<false>(w[0], w[1], w[2], w[3], T, sink);
+    uint32_t want[4][6];
+    ref_decode(isSigned ? 6 : 5, w, want, 24, 0);
+    return memcmp(sink.rows, want, 96) != 0;
+}
+#endif
+
 int main(int argc, char** argv)
 {
     if (argc < 2) { fprintf(stderr, "usage: %s libhkref.so [n]\n", argv[0]); return 2; }
@@ -86,6 +106,18 @@ int main(int argc, char** argv)
         bad += check_alpha(w); total++;
 #ifdef WITH_BC7
         bad += check_rgba(7, w); total++;
+        bad += check_bc6h(w, false); total++;
+        bad += check_bc6h(w, true); total++;
+        {   // BC6H: force each of the 14 mode codes in turn, and extreme endpoint fields now and then
+            static const uint32_t codes[14] = {0, 1, 2, 6, 10, 14, 18, 22, 26, 30, 3, 7, 11, 15};
+            uint32_t h[4] = {w[0], w[1], w[2], w[3]};
+            const int mi = (int)(i % 14);
+            h[0] = mi < 2 ? ((h[0] & ~3u) | codes[mi]) : ((h[0] & ~31u) | codes[mi]);
+            if ((i & 31) == 0) { h[0] |= 0xFFFFFFE0u; h[1] = 0xFFFFFFFFu; }
+            if ((i & 31) == 1) { h[0] &= 31u; h[1] = 0; }
+            bad += check_bc6h(h, false); total++;
+            bad += check_bc6h(h, true); total++;
+        }
         // force each mode in turn so the rare high modes get the same coverage
         uint32_t m[4] = {w[0], w[1], w[2], w[3]};
         const int mode = (int)(i & 7);
