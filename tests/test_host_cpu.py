@@ -71,3 +71,14 @@ def test_bc7_block_function_matches_reference_on_host(host_check, tmp_path):
     blocks = np.concatenate(parts)
     last = run_check(host_check, blocks, tmp_path)
     assert last == f"{len(blocks)} blocks, 0 differ", last
+
+
+@pytest.mark.skipif(not refshim.have_ref(), reason="oracle/_ref not built")
+def test_lean_decoders_match_reference_on_host(tmp_path):
+    """the register-level BC1-5 / BC7 / BC6H block decoders of the CUDA kernels (bcn_decode_lean.cuh, bc7_decode_lean.cuh,
+    bc6h_decode_lean.cuh), compiled for the host with PRMT emulated, against bcdec / bc7decomp: per-channel exhaustive endpoint
+    pairs, all alpha endpoint pairs, random blocks with every BC7 / BC6H mode forced in turn, signed and unsigned."""
+    exe = str(tmp_path / "decode_host_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-DWITH_BC7", "-o", exe, os.path.join(ROOT, "tools", "decode_host_check.cpp"), "-ldl"], check=True)
+    out = subprocess.run([exe, refshim.REF_PATH, "60000"], capture_output=True, text=True, check=True).stdout.strip().splitlines()[-1]
+    assert out.endswith(", 0 differ") and int(out.split()[0]) > 500000, out
