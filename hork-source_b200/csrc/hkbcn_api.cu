@@ -12,6 +12,8 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <map>
+#include <math.h>
 #include <string>
 #include <algorithm>
 #include <stdarg.h>
@@ -38,6 +40,12 @@ struct Device {
     void*        d_src = nullptr; size_t src_cap = 0;
     void*        d_dst = nullptr; size_t dst_cap = 0;
     std::mutex   mu; // serialises host-pointer calls that share the scratch buffers
+    // mip cascade: decode tables and tap tables (one pair per in/out size, filter and edge mode), built on first use
+    float*       lut_srgb = nullptr;
+    float*       lut_lin = nullptr;
+    struct Taps { int* idx; float* w; int T; };
+    std::map<uint64_t, Taps> taps;
+    std::mutex   taps_mu;
 };
 
 std::mutex            g_mu;
@@ -236,6 +244,19 @@ int hkbcn_init(uint32_t device_mask)
         cudaError_t te = bc7_upload_tables();
         if (te != cudaSuccess && te != cudaErrorNotSupported) { set_err("bc7 table upload: %s", cudaGetErrorString(te)); return HKBCN_ERR_CUDA; }
         CK(bc6h_upload_tables());
+        {
+            // stbir's uint8 decode: sRGB -> linear (stb_image_resize.h:634-640, tabulated there) and v / 255
+            float srgb[256], lin[256];
+            for (int v = 0; v < 256; v++) {
+                const double f = v / 255.0;
+                srgb[v] = (float)(f <= 0.04045 ? f / 12.92 : pow((f + 0.055) / 1.055, 2.4));
+                lin[v] = (float)v / 255.0f;
+            }
+            CK(cudaMalloc((void**)&D->lut_srgb, sizeof(srgb)));
+            CK(cudaMalloc((void**)&D->lut_lin, sizeof(lin)));
+            CK(cudaMemcpy(D->lut_srgb, srgb, sizeof(srgb), cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(D->lut_lin, lin, sizeof(lin), cudaMemcpyHostToDevice));
+        }
         g_devs.push_back(D);
     }
     if (g_devs.empty()) {
@@ -254,6 +275,10 @@ void hkbcn_shutdown(void)
         cudaSetDevice(D->id);
         if (D->d_src) cudaFree(D->d_src);
         if (D->d_dst) cudaFree(D->d_dst);
+        if (D->lut_srgb) cudaFree(D->lut_srgb);
+        if (D->lut_lin) cudaFree(D->lut_lin);
+        for (auto& kv : D->taps) { cudaFree(kv.second.idx); cudaFree(kv.second.w); }
+        D->taps.clear();
         if (D->stream) cudaStreamDestroy(D->stream);
         delete D;
     }
@@ -300,6 +325,157 @@ int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, ui
     if (rc) return rc;
     if ((width & 3) || (height & 3)) { set_err("chain dims must be multiples of 4"); return HKBCN_ERR_BAD_ARG; }
     return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags);
+}
+
+
+// ---- mip cascade (Image.cpp:1755-1803 / :1852-1899) ----------------------------------------------
+static int get_taps(Device* D, int in_size, int out_size, int filter, int edge, Device::Taps& out)
+{
+    const uint64_t key = ((uint64_t)in_size << 40) | ((uint64_t)out_size << 16) | ((uint64_t)filter << 8) | (uint64_t)edge;
+    std::lock_guard<std::mutex> lk(D->taps_mu);
+    auto it = D->taps.find(key);
+    if (it != D->taps.end()) { out = it->second; return HKBCN_OK; }
+    std::vector<int> idx;
+    std::vector<float> w;
+    Device::Taps t{nullptr, nullptr, 0};
+    build_axis_taps(in_size, out_size, filter, edge, idx, w, t.T);
+    CK(cudaMalloc((void**)&t.idx, idx.size() * sizeof(int)));
+    CK(cudaMalloc((void**)&t.w, w.size() * sizeof(float)));
+    CK(cudaMemcpy(t.idx, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.w, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice));
+    D->taps[key] = t;
+    out = t;
+    return HKBCN_OK;
+}
+
+static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint32_t h, uint32_t mips, const hkbcn_mip_config* cfg,
+                            uint32_t flags, cudaStream_t st)
+{
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (codec == C_BC6H && (flags & HKBCN_FLAG_SRC_F16)) { set_err("mip cascade of RGBA16F sources is not supported (the importers resample RGBA32F)"); return HKBCN_ERR_UNSUPPORTED; }
+    if (mips == 0 || mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range", mips); return HKBCN_ERR_BAD_ARG; }
+    const int edge = cfg && cfg->edge_mode ? cfg->edge_mode : 3, filter = cfg && cfg->filter ? cfg->filter : 5;
+    if (edge < 1 || edge > 4 || filter < 1 || filter > 5) { set_err("bad edge mode %d / filter %d", edge, filter); return HKBCN_ERR_BAD_ARG; }
+    const uint32_t bpp = src_bpp(codec, flags);
+    const bool f32 = codec == C_BC6H;
+    const int channels = f32 ? 4 : (int)bpp;
+    // TexFormat[].bHasAlpha (Image.cpp:105-118): BC1/2/3/7 carry alpha, BC4/5/6H do not
+    const bool has_alpha = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3 || codec == C_BC7) && !(cfg && cfg->no_alpha);
+    const bool srgb = fmt == HKBCN_BC1_UNORM_SRGB || fmt == HKBCN_BC2_UNORM_SRGB || fmt == HKBCN_BC3_UNORM_SRGB || fmt == HKBCN_BC7_UNORM_SRGB;
+    uint8_t* cur = (uint8_t*)d_chain;
+    for (uint32_t i = 1; i < mips; i++) {
+        const uint32_t iw = mip_dim(w, i - 1), ih = mip_dim(h, i - 1), ow = mip_dim(w, i), oh = mip_dim(h, i);
+        uint8_t* next = cur + (size_t)iw * ih * bpp;
+        Device::Taps tx, ty;
+        int rc;
+        if ((rc = get_taps(D, (int)iw, (int)ow, filter, edge, tx)) != HKBCN_OK) return rc;
+        if ((rc = get_taps(D, (int)ih, (int)oh, filter, edge, ty)) != HKBCN_OK) return rc;
+        ResizeParams P;
+        P.src = cur; P.dst = next;
+        P.ix = tx.idx; P.wx = tx.w; P.iy = ty.idx; P.wy = ty.w;
+        P.lut = srgb ? D->lut_srgb : D->lut_lin;
+        P.in_w = (int)iw; P.in_h = (int)ih; P.out_w = (int)ow; P.out_h = (int)oh; P.Tx = tx.T; P.Ty = ty.T;
+        P.alpha = has_alpha ? channels - 1 : -1;
+        P.weight = (has_alpha && !(cfg && cfg->alpha_premultiplied)) ? 1 : 0;
+        P.srgb = srgb ? 1 : 0;
+        cudaError_t e = launch_mip_resize(P, channels, f32, st);
+        if (e != cudaSuccess) { set_err("mip resize launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        cur = next;
+    }
+    return HKBCN_OK;
+}
+
+int hkbcn_mip_taps(int in_size, int out_size, int filter, int edge_mode, int* idx, float* weight, int capacity, int* taps_per_output)
+{
+    if (in_size <= 0 || out_size <= 0 || out_size > in_size || filter < 1 || filter > 5 || edge_mode < 1 || edge_mode > 4 || !taps_per_output) {
+        set_err("bad arguments (downsampling only: out_size <= in_size)");
+        return HKBCN_ERR_BAD_ARG;
+    }
+    std::vector<int> i;
+    std::vector<float> w;
+    int T = 0;
+    build_axis_taps(in_size, out_size, filter, edge_mode, i, w, T);
+    *taps_per_output = T;
+    if ((size_t)capacity < i.size()) { set_err("capacity %d < %zu", capacity, i.size()); return HKBCN_ERR_BAD_ARG; }
+    if (idx) memcpy(idx, i.data(), i.size() * sizeof(int));
+    if (weight) memcpy(weight, w.data(), w.size() * sizeof(float));
+    return HKBCN_OK;
+}
+
+size_t hkbcn_chain_src_bytes(int fmt, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags)
+{
+    const int codec = codec_of(fmt);
+    return codec < 0 ? 0 : chain_src_bytes(codec, flags, width, height, num_mips);
+}
+
+int hkbcn_generate_mips_dev(int device, int fmt, void* d_chain, uint32_t width, uint32_t height, uint32_t num_mips,
+                            const hkbcn_mip_config* cfg, uint32_t flags, void* stream)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = dev_at(device);
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    if (!d_chain) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    CK(cudaSetDevice(D->id));
+    return generate_mips_on(D, fmt, d_chain, width, height, num_mips, cfg, flags, (cudaStream_t)stream);
+}
+
+int hkbcn_generate_mips(int fmt, const void* src_level0, void* dst_chain, uint32_t width, uint32_t height, uint32_t num_mips,
+                        const hkbcn_mip_config* cfg, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (!src_level0 || !dst_chain || !width || !height) { set_err("null pointer or empty surface"); return HKBCN_ERR_BAD_ARG; }
+    Device* D = g_devs[0];
+    const size_t sbytes = chain_src_bytes(codec, flags, width, height, num_mips);
+    const size_t l0 = (size_t)width * height * src_bpp(codec, flags);
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src_level0, l0, cudaMemcpyHostToDevice, D->stream));
+    if ((rc = generate_mips_on(D, fmt, D->d_src, width, height, num_mips, cfg, flags, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(dst_chain, D->d_src, sbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_import_chain_dev(int device, int fmt, void* d_chain, void* d_dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                           const hkbcn_mip_config* cfg, uint32_t flags, void* stream)
+{
+    int rc = hkbcn_generate_mips_dev(device, fmt, d_chain, width, height, num_mips, cfg, flags, stream);
+    if (rc) return rc;
+    return hkbcn_compress_chain_dev(device, fmt, d_chain, d_dst, width, height, num_mips, flags, stream);
+}
+
+int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                       const hkbcn_mip_config* cfg, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if ((width & 3) || (height & 3) || !width || !height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+    if (!src_level0 || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    Device* D = g_devs[0];
+    const size_t sbytes = chain_src_bytes(codec, flags, width, height, num_mips);
+    const size_t l0 = (size_t)width * height * src_bpp(codec, flags);
+    const size_t dbytes = hkbcn_chain_bytes(fmt, width, height, 1, num_mips);
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src_level0, l0, cudaMemcpyHostToDevice, D->stream)); // level 0 only crosses PCIe
+    if ((rc = generate_mips_on(D, fmt, D->d_src, width, height, num_mips, cfg, flags, D->stream)) != HKBCN_OK) return rc;
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, width, height, num_mips)) != HKBCN_OK) return rc;
+    if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
 }
 
 int hkbcn_encode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, uint32_t flags)

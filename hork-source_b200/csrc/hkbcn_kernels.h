@@ -37,4 +37,25 @@ struct DecodeParams {
 cudaError_t launch_decode(const DecodeParams& P, int sm_count, cudaStream_t stream);
 cudaError_t decode_upload_tables(); // BC6H header layout table
 
+// ---- mip cascade (mip_resize.cu) ---------------------------------------------
+struct ResizeParams {
+    const uint8_t* src;
+    uint8_t*       dst;
+    const int*     ix;  // taps of the x axis: output column i reads ix[i*Tx + k] with weight wx[i*Tx + k]
+    const float*   wx;
+    const int*     iy;
+    const float*   wy;
+    const float*   lut; // 256 floats: decode of a uint8 colour channel (sRGB table or v / 255)
+    int            in_w, in_h, out_w, out_h, Tx, Ty;
+    int            alpha;  // alpha channel index (decoded / encoded linearly) or -1
+    int            weight; // 1: colour is weighted by alpha before filtering and un-weighted after (not premultiplied input)
+    int            srgb;
+};
+cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
+
+} // namespace hkbcn
+
+#include <vector>
+namespace hkbcn {
+void build_axis_taps(int in_size, int out_size, int filter, int edge, std::vector<int>& idx, std::vector<float>& w, int& T);
 } // namespace hkbcn

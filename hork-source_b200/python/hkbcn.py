@@ -27,12 +27,17 @@ EXPORTS = [
     "hkbcn_block_bytes", "hkbcn_src_texel_bytes", "hkbcn_dst_texel_bytes", "hkbcn_calc_num_mips", "hkbcn_chain_bytes",
     "hkbcn_compress", "hkbcn_decompress", "hkbcn_encode_blocks", "hkbcn_decode_blocks",
     "hkbcn_compress_dev", "hkbcn_decompress_dev", "hkbcn_compress_chain_dev", "hkbcn_compress_chain",
-    "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
+    "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
+    "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
 ]
 
 
 class HkbcnError(RuntimeError):
     pass
+
+
+class MipConfig(C.Structure):
+    _fields_ = [("edge_mode", C.c_int), ("filter", C.c_int), ("no_alpha", C.c_int), ("alpha_premultiplied", C.c_int)]
 
 
 class Job(C.Structure):
@@ -67,6 +72,13 @@ def lib():
         L.hkbcn_compress_chain.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
         L.hkbcn_compress_batch.argtypes = [C.POINTER(Job), C.c_size_t]
         L.hkbcn_plan_batch.argtypes = [C.POINTER(Job), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
+        L.hkbcn_mip_taps.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.hkbcn_chain_src_bytes.restype = C.c_size_t
+        L.hkbcn_chain_src_bytes.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_generate_mips_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32, C.c_void_p]
+        L.hkbcn_generate_mips.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32]
+        L.hkbcn_import_chain_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32, C.c_void_p]
+        L.hkbcn_import_chain.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32]
         L.hkbcn_launch_count.restype = C.c_uint64
         L.hkbcn_alloc_pinned.restype = C.c_void_p
         L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
@@ -156,3 +168,29 @@ def plan_batch(jobs, n_gpus):
     out = (C.c_int * len(jobs))()
     check(lib().hkbcn_plan_batch(arr, len(jobs), n_gpus, out))
     return list(out)
+
+
+def mip_taps(in_size, out_size, filter=5, edge=3):
+    """(idx[out, T], weight[out, T]) of one axis -- host only"""
+    T = C.c_int(0)
+    cap = out_size * 64
+    idx = np.zeros(cap, np.int32)
+    w = np.zeros(cap, np.float32)
+    check(lib().hkbcn_mip_taps(in_size, out_size, filter, edge, _ptr(idx), _ptr(w), cap, C.byref(T)))
+    return idx[: out_size * T.value].reshape(out_size, T.value), w[: out_size * T.value].reshape(out_size, T.value)
+
+
+def import_chain(fmt, level0, width, height, mips, cfg=None, flags=0):
+    """the import cascade (Image.cpp:1755-1803): level 0 in, compressed chain out; mips generated on the device"""
+    level0 = np.ascontiguousarray(level0)
+    dst = np.zeros(lib().hkbcn_chain_bytes(fmt, width, height, 1, mips), np.uint8)
+    check(lib().hkbcn_import_chain(fmt, _ptr(level0), _ptr(dst), width, height, mips, C.byref(cfg) if cfg else None, flags))
+    return dst
+
+
+def generate_mips(fmt, level0, width, height, mips, cfg=None, flags=0):
+    """uncompressed chain (levels back to back, level 0 first) as uint8 bytes"""
+    level0 = np.ascontiguousarray(level0)
+    dst = np.zeros(lib().hkbcn_chain_src_bytes(fmt, width, height, mips, flags), np.uint8)
+    check(lib().hkbcn_generate_mips(fmt, _ptr(level0), _ptr(dst), width, height, mips, C.byref(cfg) if cfg else None, flags))
+    return dst

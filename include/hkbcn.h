@@ -126,6 +126,37 @@ HKBCN_API int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, v
 HKBCN_API int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height,
                                    uint32_t num_mips, uint32_t flags);
 
+/* ---- device-side mip cascade ------------------------------------------------
+ * The importers build every mip level on the CPU from the previous one with stbir_resize and compress it
+ * (Image.cpp:1755-1803 for BC1-5/BC7, :1852-1899 for BC6H; ImageMipmapConfig, Image.h:361-371).  These entry points do the
+ * same cascade on the device, so only level 0 crosses PCIe.  Contract against stbir: +-1 LSB per uint8 channel. */
+typedef struct hkbcn_mip_config {
+    int edge_mode;            /* IMAGE_RESAMPLE_EDGE_MODE (Image.h:330): 1 clamp, 2 reflect, 3 wrap, 4 zero; 0 = default (wrap) */
+    int filter;               /* IMAGE_RESAMPLE_FILTER (Image.h:339): 1 box, 2 triangle, 3 cubic b-spline, 4 catmull-rom, 5 mitchell; 0 = default (mitchell) */
+    int no_alpha;             /* IMAGE_STORAGE_NO_ALPHA: the fourth channel is colour, no alpha weighting */
+    int alpha_premultiplied;  /* IMAGE_STORAGE_ALPHA_PREMULTIPLIED */
+} hkbcn_mip_config;
+/* The resampling taps of one axis (host only, no device needed): output texel i = sum over k < *taps_per_output of
+ * weight[i * T + k] * input[idx[i * T + k]], in ascending input order -- stbir's downsampling contributors after
+ * normalisation and edge mapping (stb_image_resize.h:1024-1200).  capacity = entries available in idx / weight. */
+HKBCN_API int hkbcn_mip_taps(int in_size, int out_size, int filter, int edge_mode, int* idx, float* weight, int capacity,
+                             int* taps_per_output);
+/* bytes of the uncompressed chain (levels back to back) for `fmt`'s source texel type */
+HKBCN_API size_t hkbcn_chain_src_bytes(int fmt, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags);
+/* d_chain: hkbcn_chain_src_bytes() bytes on `device` with level 0 filled in; levels 1.. are written after it.
+ * The source texel type and the sRGB / alpha handling follow `fmt` as in the importers (cfg may be NULL: defaults). */
+HKBCN_API int hkbcn_generate_mips_dev(int device, int fmt, void* d_chain, uint32_t width, uint32_t height, uint32_t num_mips,
+                                      const hkbcn_mip_config* cfg, uint32_t flags, void* stream);
+/* host pointers: level 0 in, the uncompressed chain (level 0 included) out, hkbcn_chain_src_bytes() bytes */
+HKBCN_API int hkbcn_generate_mips(int fmt, const void* src_level0, void* dst_chain, uint32_t width, uint32_t height,
+                                  uint32_t num_mips, const hkbcn_mip_config* cfg, uint32_t flags);
+/* generate the mips in d_chain, then compress the whole chain into d_dst (ImageStorage layout): the import cascade */
+HKBCN_API int hkbcn_import_chain_dev(int device, int fmt, void* d_chain, void* d_dst, uint32_t width, uint32_t height,
+                                     uint32_t num_mips, const hkbcn_mip_config* cfg, uint32_t flags, void* stream);
+/* host pointers: level 0 in (width x height source texels), full compressed chain out */
+HKBCN_API int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                                 const hkbcn_mip_config* cfg, uint32_t flags);
+
 /* ---- batch API: independent surfaces sharded over the selected GPUs ---------
  * No collective: each job is sent whole to one GPU (greedy by pixel-cost), results land
  * directly in the caller's dst ("host gather").  Replaces one-process-per-texture use of
