@@ -35,25 +35,47 @@ METRIC = "bc7_encode_mpix_per_s"
 
 
 # ----------------------------------------------------------------------------- workload
-def make_chain(seed, size=SIZE):
-    """level 0 = synth.albedo_rgba8 (SURVEY.md 8d 'albedo-B'); levels 1.. = 2x2 box average (synthetic chain:
-    the reference's stbir Mitchell cascade is a 'next' row, not part of this path).  Cached in /tmp between
-    the two arms of one round-end run."""
+def make_level0(seed, size=SIZE):
+    """level 0 = synth.albedo_rgba8 (SURVEY.md 8d 'albedo-B').  Cached in /tmp between the two arms of one round-end run."""
     import synth
     cache = f"/tmp/hkbcn_bench_{seed:x}_{size}.npy"
     if os.path.exists(cache):
-        lvl0 = np.load(cache)
-    else:
-        lvl0 = synth.albedo_rgba8(size, size, seed).reshape(size, size, 4)
-        try:
-            np.save(cache + ".tmp.npy", lvl0)
-            os.replace(cache + ".tmp.npy", cache)
-        except OSError:
-            pass
-    levels = [lvl0]
+        return np.load(cache)
+    lvl0 = synth.albedo_rgba8(size, size, seed).reshape(size, size, 4)
+    try:
+        np.save(cache + ".tmp.npy", lvl0)
+        os.replace(cache + ".tmp.npy", cache)
+    except OSError:
+        pass
+    return lvl0
+
+
+def split_levels(chain_u8, size=SIZE):
+    levels, off, n = [], 0, size
+    while True:
+        levels.append(chain_u8[off:off + n * n * 4].reshape(n, n, 4))
+        off += n * n * 4
+        if n == 4:
+            return levels
+        n //= 2
+
+
+def make_chain_gpu(seed, size=SIZE):
+    """the importers' chain (Image.cpp:1755-1803: level i from level i-1, Mitchell / wrap, alpha-weighted, linear) built by
+    this library's device-side cascade -- bit-identical to stbir for linear formats (tests/test_gpu_mips.py)"""
+    import hkbcn
+    lvl0 = make_level0(seed, size)
+    mips = hkbcn.lib().hkbcn_calc_num_mips(size, size)
+    return split_levels(hkbcn.generate_mips(BC7, lvl0, size, size, mips), size)
+
+
+def make_chain_ref(seed, size=SIZE):
+    """the same chain built by the reference's own stbir_resize (reference arm only)"""
+    import refshim
+    levels = [make_level0(seed, size)]
     while levels[-1].shape[0] > 4:
-        a = levels[-1].astype(np.uint16)
-        levels.append(((a[0::2, 0::2] + a[1::2, 0::2] + a[0::2, 1::2] + a[1::2, 1::2] + 2) >> 2).astype(np.uint8))
+        n = levels[-1].shape[0] // 2
+        levels.append(refshim.stbir_resize(levels[-1], n, n, alpha_channel=3, flags=0, edge=3, filt=5, space=0))
     return levels
 
 
@@ -141,7 +163,7 @@ def time_reference(levels, steps, warmup):
 def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    levels = make_chain(SEED)
+    levels = make_chain_ref(SEED)
     v, dt, cores, sample = time_reference(levels, max(1, args.steps), args.warmup)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -157,7 +179,7 @@ def workload_config(levels, n):
     return {"workload": f"BC7_UNORM encode, {SIZE}x{SIZE} RGBA8 synthetic albedo + full mip chain ({len(levels)} levels, {chain_pixels(levels)} px), "
                         "bc7enc uber level 4 perceptual preset (Hk::TextureBlockCompression::CompressBC7)",
             "textures_per_gpu": 1, "parallelism": f"{n} independent textures, one per GPU, no collective",
-            "mips": "2x2 box average of the synthetic level 0", "l2": "256 MiB buffer written between timed steps"}
+            "mips": "the importers' cascade: stbir Mitchell / wrap, alpha-weighted, linear (ImageMipmapConfig defaults)", "l2": "256 MiB buffer written between timed steps"}
 
 
 # ----------------------------------------------------------------------------- sharding (no data-path collective)
@@ -246,7 +268,7 @@ def run_gpu(args):
 
     L = hkbcn.lib()
     hkbcn.init(1 << local)  # library device 0 == cuda:local
-    levels = make_chain(rank_seed(rank))
+    levels = make_chain_gpu(rank_seed(rank))
     mips, px = len(levels), chain_pixels(levels)
     src_np = np.concatenate([l.ravel() for l in levels])
     dst_bytes = L.hkbcn_chain_bytes(BC7, SIZE, SIZE, 1, mips)
@@ -307,6 +329,26 @@ def run_gpu(args):
         raise SystemExit("bench.py: host-pointer and device-pointer encodes differ")
     e2e_value = world * px / e2e_s / 1e6
 
+    # ---- the importers' whole cascade through the C ABI: level 0 in (host), mips generated on the device, chain encoded,
+    # compressed chain out (host).  Only level 0 crosses PCIe.  Same bytes out as the pre-built chain (the cascade is
+    # bit-identical to stbir for linear formats).
+    l0_bytes = SIZE * SIZE * 4
+
+    def import_step():
+        hkbcn.check(L.hkbcn_import_chain(BC7, h_src, h_dst, SIZE, SIZE, mips, None, 0))
+    for _ in range(2):
+        import_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        import_step()
+    torch.cuda.synchronize()
+    imp_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+    barrier()
+    if not np.array_equal(host_out, d_dst.cpu().numpy()):
+        raise SystemExit("bench.py: import cascade and pre-built chain encodes differ")
+    import_value = world * px / imp_s / 1e6
+
     if rank == 0:
         hbm, which = peaks()
         achieved = 5.0 * px / (ms_step * 1e-3) / 1e9  # algorithmic bytes: 4 B/px read + 1 B/px written
@@ -316,6 +358,8 @@ def run_gpu(args):
             "config": workload_config(levels, world),
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "h2d_bytes_per_step": int(src_np.nbytes), "d2h_bytes_per_step": int(dst_bytes),
                     "ms_per_step": e2e_s * 1e3, "api": "hkbcn_compress_chain (host pointers, pinned)"},
+            "import_chain": {"value": import_value, "unit": "Mpix/s", "ms_per_step": imp_s * 1e3, "h2d_bytes_per_step": l0_bytes,
+                             "d2h_bytes_per_step": int(dst_bytes), "api": "hkbcn_import_chain (level 0 in, device mip cascade + encode, chain out)"},
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "bc7_encode_kernel", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                          "traffic": ncu_traffic(px), "peak_source": which,
@@ -328,6 +372,13 @@ def run_gpu(args):
             out["encode_other_formats"] = encode_others(torch, hkbcn, L, stream, flush)
             v, dt, cores, sample = time_reference(levels, 1, 0)
             out["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample}
+            # the CPU side of the import cascade: the reference's stbir_resize is single-threaded as shipped
+            import refshim
+            t0 = time.perf_counter()
+            cur = levels[0]
+            while cur.shape[0] > 4:
+                cur = refshim.stbir_resize(cur, cur.shape[1] // 2, cur.shape[0] // 2, alpha_channel=3, flags=0, edge=3, filt=5, space=0)
+            out["import_chain"]["cpu_stbir_cascade_ms"] = (time.perf_counter() - t0) * 1e3
         print(json.dumps(out))
     L.hkbcn_free_pinned(h_src)
     L.hkbcn_free_pinned(h_dst)
