@@ -194,38 +194,41 @@ HKD uint32_t mode_of(uint32_t w0)
     return code < 16u ? 10u + (code >> 2) : 14u;
 }
 
-template <int MODE, bool SIGNED, class Sink>
-HKD void decode_mode(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const lean7::Tables& T, Sink& sink)
-{
-    int e[12];
-    uint32_t part;
-    endpoints<MODE, SIGNED>(w0, w1, w2, w3, e, part);
-    texels<SIGNED, (MODE < 10)>(e, part, w2, w3, T, sink);
-}
-
+// The fourteen modes differ in the header only: the switch leaves the twelve unquantised endpoints, and the texel code (two
+// thirds of the work) runs once for all two-region modes and once for all one-region modes, so a warp that straddles a
+// mode boundary of the sorted tile diverges over the parse, not over the texels, and the kernel carries two texel bodies
+// instead of fourteen.
 template <bool SIGNED, class Sink>
 HKD void decode_bc6h(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const lean7::Tables& T, Sink& sink)
 {
-    switch (mode_of(w0)) {
-    case 0: decode_mode<0, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 1: decode_mode<1, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 2: decode_mode<2, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 3: decode_mode<3, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 4: decode_mode<4, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 5: decode_mode<5, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 6: decode_mode<6, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 7: decode_mode<7, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 8: decode_mode<8, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 9: decode_mode<9, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 10: decode_mode<10, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 11: decode_mode<11, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 12: decode_mode<12, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    case 13: decode_mode<13, SIGNED>(w0, w1, w2, w3, T, sink); break;
-    default: {
+    int e[12];
+    uint32_t part = 0;
+    const uint32_t mode = mode_of(w0);
+    switch (mode) {
+    case 0: endpoints<0, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 1: endpoints<1, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 2: endpoints<2, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 3: endpoints<3, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 4: endpoints<4, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 5: endpoints<5, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 6: endpoints<6, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 7: endpoints<7, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 8: endpoints<8, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 9: endpoints<9, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 10: endpoints<10, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 11: endpoints<11, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 12: endpoints<12, SIGNED>(w0, w1, w2, w3, e, part); break;
+    case 13: endpoints<13, SIGNED>(w0, w1, w2, w3, e, part); break;
+    default:
+#pragma unroll
+        for (int i = 0; i < 12; i++) e[i] = 0;
+    }
+    if (mode < 10) texels<SIGNED, true>(e, part, w2, w3, T, sink);
+    else if (mode < 14) texels<SIGNED, false>(e, part, w2, w3, T, sink);
+    else {
         const uint32_t z[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll
         for (int r = 0; r < 4; r++) sink.row(r, z);
-    }
     }
 }
 

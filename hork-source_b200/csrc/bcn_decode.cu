@@ -521,6 +521,39 @@ __global__ void __launch_bounds__(256) decode_kernel(const DecodeParams P)
 }
 
 
+// Persistent grids: D7_WAVES x (CTAs that fit on the device at once), so every CTA is resident from the start and all of
+// them finish within one tile of each other (a grid of 1.6 or 3.2 waves leaves the last partial wave half empty).
+#ifndef D7_WAVES
+#define D7_WAVES 1
+#endif
+#ifndef DL_WAVES
+#define DL_WAVES 1
+#endif
+template <class K>
+static uint32_t resident_grid(K kernel, int smem, int sm_count, uint32_t nTiles, int* cache, uint32_t waves = D7_WAVES)
+{
+    if (*cache == 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, 256, (size_t)smem) != cudaSuccess || n < 1) n = 1;
+        *cache = n;
+    }
+    const uint32_t g = (uint32_t)sm_count * (uint32_t)*cache * waves;
+    return nTiles < g ? nTiles : g;
+}
+// Share of a CTA's tiles that is strided rather than claimed.  Measured (BC7 / BC6H, 16384^2): all claimed 82.6 / 73.3 % of
+// HBM peak, half 82.4 / 70.9, three quarters 77.0 / 66.5, all strided 72.2 / 65.0 -- so everything after the first tile is
+// claimed; the knob stays for tools/build_variant.sh.
+#ifndef D7_STATIC_NUM
+#define D7_STATIC_NUM 0
+#define D7_STATIC_DEN 1
+#endif
+static uint32_t static_rounds(uint32_t nTiles, uint32_t grid)
+{
+    const uint32_t k = (nTiles / grid) * D7_STATIC_NUM / D7_STATIC_DEN;
+    return k < 1 ? 1 : k; // tile 0 of a CTA is always its blockIdx
+}
+
+
 // ---------------------------------------------------------------- lean BC1..BC5 kernels (bcn_decode_lean.cuh)
 // One thread = one 16-byte-per-row work item: 1 block (BC1/2/3), 2 adjacent blocks (BC5) or 4 adjacent blocks (BC4), so
 // every row store is one 128-bit streaming store and a warp's 32 stores form one 512-byte run.  Used when the
@@ -586,9 +619,8 @@ static bool try_launch_lean(const DecodeParams& P, int sm_count, cudaStream_t st
     constexpr uint32_t K = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 2 : 1;
     if (((size_t)P.dst & 15) || (P.dstRowStride & 15) || ((size_t)P.src & 15) || (P.nbx % K)) return false;
     const uint32_t ipr = P.nbx / K, nItems = P.nblocks / K;
-    uint32_t ctas = (nItems + 255) / 256;
-    const uint32_t cap = (uint32_t)sm_count * 8 * 4;
-    if (ctas > cap) ctas = cap;
+    static int occ = 0;
+    const uint32_t ctas = resident_grid(decode_lean_kernel<CODEC>, 0, sm_count, (nItems + 255) / 256, &occ, DL_WAVES);
     decode_lean_kernel<CODEC><<<ctas, 256, 0, stream>>>(P, ipr, nItems);
     err = cudaGetLastError();
     return true;
@@ -625,8 +657,58 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint3
 }
 
 // ROWS: every tile is one run of 256 blocks inside a block row (nbx % 256 == 0) and rows are 16-byte aligned -> bulk stores
+// Tile scheduling (BC7 and BC6H kernels): the grid is one resident wave; a CTA's first tile is its blockIdx, every later
+// one comes from a device counter (P.sched[0]) claimed two tiles ahead by thread 0, so the atomic's latency sits behind
+// the sort and SMs that run faster (nearer memory partitions, fewer divergent warps) simply take more tiles.
+// Static striding measured 5-8 % slower at one wave, and several waves of short-lived CTAs lose the prefetch.
+// P.sched[1] counts finished CTAs; the last one zeroes both words for the next launch.
+// The claim made at the top of tile i is for tile i + 2; its result is parked in shared memory after the sort's second
+// barrier (s_next[(i + 1) & 1] = the tile after tile i + 1), so no register carries it through the decode.
+// claim_issue returns a ticket, claim_value turns it into the tile index; the two are apart (top of the tile / after the
+// sort's second barrier) so that the atomic's round trip is waited for at the second, not the first.
+// The counter is a float (exact to 2^24 tiles = 4 G blocks; its zero is the integer zero) on purpose: an integer add of a
+// constant -- atomicAdd, atom.add, atom.inc alike -- is warp-aggregated by ptxas, and the SHFL that hands the result back
+// waits for the atomic on the spot.
+__device__ __forceinline__ uint32_t claim_issue(const DecodeParams& P, uint32_t i, uint32_t kStatic)
+{
+    if (i < kStatic) return blockIdx.x + i * gridDim.x;
+    uint32_t old;
+    asm volatile("atom.global.add.f32 %0, [%1], 0f3F800000;" : "=r"(old) : "l"(P.sched) : "memory");
+    return old;
+}
+__device__ __forceinline__ uint32_t claim_value(uint32_t ticket, uint32_t i, uint32_t kStatic)
+{
+    return i < kStatic ? ticket : kStatic * gridDim.x + (uint32_t)__uint_as_float(ticket);
+}
+__device__ __forceinline__ void finish_claims(const DecodeParams& P)
+{
+    __threadfence();
+    if (atomicAdd(P.sched + 1, 1u) == gridDim.x - 1u) {
+        P.sched[0] = 0;
+        P.sched[1] = 0;
+    }
+}
+// ROWS kernels: block row of a tile = tile / (nbx / 256) as a multiply-high by ceil(2^32 / d); exact while tile * d < 2^32
+// (checked by the launcher); rowMagic 0 = one tile per row
+__device__ __forceinline__ uint32_t tile_row(uint32_t tile, uint32_t rowMagic) { return rowMagic ? __umulhi(tile, rowMagic) : tile; }
+static uint32_t row_magic(uint32_t nbx)
+{
+    const uint32_t d = nbx / D7_NT;
+    return d <= 1 ? 0u : (uint32_t)(0x100000000ull / d) + 1u;
+}
+static bool row_magic_ok(uint32_t nbx, uint32_t nTiles) { return (unsigned long long)nTiles * (nbx / D7_NT) < 0x100000000ull; }
+__device__ __forceinline__ void fetch_tile(const DecodeParams& P, uint32_t tile, void* s_dst, uint64_t* bar)
+{
+    const uint32_t n = min((uint32_t)D7_NT, P.nblocks - tile * D7_NT) * 16u;
+    mbar_arrive_expect_tx(bar, n);
+    bulk_g2s(s_dst, P.src + (size_t)tile * D7_NT * 16, n, bar);
+}
+
+#ifndef D7_OCC
+#define D7_OCC 5
+#endif
 template <bool ROWS>
-__global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeParams P, const uint32_t nTiles)
+__global__ void __launch_bounds__(D7_NT, D7_OCC) decode_bc7_lean_kernel(const DecodeParams P, const uint32_t nTiles, const uint32_t kStatic, const uint32_t rowMagic)
 {
     __shared__ uint4 s_blk[2][D7_NT];
     __shared__ __align__(128) uint4 s_stage[4][D7_NT];
@@ -634,6 +716,8 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
     __shared__ lean7::Tables s_T;
     __shared__ __align__(16) uint32_t s_cnt[2][12];
     __shared__ uint8_t s_order[2][D7_NT];
+    __shared__ __align__(8) uint64_t s_bar[2]; // s_bar[p] completes when the bulk copy into s_blk[p] has landed
+    __shared__ uint32_t s_next[2];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     {
         const uint32_t* g = (const uint32_t*)&g_bc7dec_tables;
@@ -641,23 +725,37 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
         for (uint32_t i = tid; i < sizeof(lean7::Tables) / 4; i += D7_NT) d[i] = g[i];
     }
     if (tid < 24) (&s_cnt[0][0])[tid] = 0;
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        fence_mbar_init();
+        fetch_tile(P, blockIdx.x, &s_blk[0][0], &s_bar[0]); // grid <= nTiles
+        s_next[0] = claim_value(claim_issue(P, 1, kStatic), 1, kStatic);
+    }
     const lean7::Pal pal{(char*)s_pal, tid * 4u};
-    // block coordinates of the tile's first block, advanced incrementally (no division in the loop)
-    const uint32_t step = gridDim.x * D7_NT;
-    uint32_t t0 = blockIdx.x * D7_NT;
-    uint32_t by0 = t0 / P.nbx, bx0 = t0 - by0 * P.nbx;
-    const uint32_t dby = step / P.nbx, dbx = step - dby * P.nbx;
-    uint32_t par = 0, anyGeneral = 0;
+    uint32_t tile = blockIdx.x, it = 0; // it: tiles done by this CTA; buffer parity it & 1, mbarrier phase (it >> 1) & 1
     __syncthreads();
-    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x, par ^= 1u) {
-        const uint32_t b = t0 + tid;
-        const bool valid = b < P.nblocks;
+    // Sort, decode and store the lean-mode blocks of one tile; returns how many blocks of modes 0, 2, 4 it holds.
+    auto lean_tile = [&](const uint32_t tile, const uint32_t it) -> uint32_t {
+        const uint32_t par = it & 1u;
+        const uint32_t t0 = tile * D7_NT;
+        const bool valid = t0 + tid < P.nblocks;
+        uint32_t claimed = 0;
+        if (tid == 0) {
+            // the tile after this one is fetched by a bulk copy while this one is sorted and decoded (no registers held,
+            // no load latency in front of the sort); s_blk[par ^ 1] was last read before the previous tile's final barrier
+            const uint32_t nxt = s_next[par];
+            if (nxt < nTiles) {
+                fetch_tile(P, nxt, &s_blk[par ^ 1u][0], &s_bar[par ^ 1u]);
+                claimed = claim_issue(P, it + 2, kStatic);
+            }
+        }
+        mbar_wait(&s_bar[par], (it >> 1) & 1u);
         uint32_t mode = 9; // 9 = no block
         if (valid) {
-            const uint4 blk = __ldcs((const uint4*)P.src + b);
-            s_blk[par][tid] = blk;
             // sort key: modes 0, 2, 4 (general decoder) first, then 1, 3, 5, 6, 7 and the reserved mode
-            mode = (blk.x & 0xFFu) ? (0x76524130u >> (4u * ((uint32_t)__ffs(blk.x & 0xFFu) - 1u))) & 15u : 8u;
+            const uint32_t low = s_blk[par][tid].x & 0xFFu;
+            mode = low ? (0x76524130u >> (4u * ((uint32_t)__ffs(low) - 1u))) & 15u : 8u;
         }
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, mode);
         const uint32_t leader = (uint32_t)__ffs(peers) - 1u, rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
@@ -676,6 +774,7 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
             s_order[par][start] = (uint8_t)tid;
         }
         __syncthreads();
+        if (tid == 0) s_next[par ^ 1u] = s_next[par] < nTiles ? claim_value(claimed, it + 2, kStatic) : nTiles;
         const uint32_t nGeneral = s_cnt[par][0] + s_cnt[par][1] + s_cnt[par][2]; // sorted slots [0, nGeneral)
         if (tid >= 3 && tid < 12) s_cnt[par][tid] = 0; // next used two tiles from now, behind barriers; [0..2] after the next barrier
         const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - t0);
@@ -687,46 +786,65 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
 #pragma unroll
             for (int r = 0; r < 4; r++) s_stage[r][k] = make_uint4(px[4 * r], px[4 * r + 1], px[4 * r + 2], px[4 * r + 3]);
         }
-        anyGeneral |= nGeneral; // their texels are written by the loop after this one
         __syncthreads();
         if (tid < 3) s_cnt[par][tid] = 0;
         if (ROWS) {
             if (tid == 0) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                uint8_t* d = P.dst + (size_t)by0 * 4 * P.dstRowStride + (size_t)bx0 * 16;
+                const uint32_t by = tile_row(tile, rowMagic), bx = t0 - by * P.nbx;
+                uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16;
 #pragma unroll
                 for (int r = 0; r < 4; r++) bulk_s2g(d + r * P.dstRowStride, &s_stage[r][0], nvalid * 16u);
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
         } else if (valid) {
-            uint32_t bx = bx0 + tid, by = by0;
-            while (bx >= P.nbx) { bx -= P.nbx; by++; }
+            const uint32_t b = t0 + tid, by = b / P.nbx, bx = b - by * P.nbx;
             uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16;
 #pragma unroll
             for (int r = 0; r < 4; r++) __stcs((uint4*)(d + r * P.dstRowStride), s_stage[r][tid]);
         }
-        t0 += step;
-        by0 += dby;
-        bx0 += dbx;
-        if (bx0 >= P.nbx) { bx0 -= P.nbx; by0++; }
+        return nGeneral;
+    };
+    // Hot loop: tiles of the modes encoders emit.  It ends at the first tile that also holds blocks of modes 0, 2, 4 (none
+    // in anything the reference's encoder presets produce); from there the CTA runs the second loop, which adds the
+    // general decoder after each tile.  The two loops are separate on purpose: a __noinline__ call from a divergent
+    // branch returned to the other lanes with clobbered warp-uniform registers, and a converged call anywhere inside the
+    // hot loop's nest made ptxas keep the sixteen texels of every block in local memory.
+    bool general = false;
+    while (tile < nTiles) {
+        if (lean_tile(tile, it)) { // uniform
+            general = true;
+            break;
+        }
+        tile = s_next[it & 1u]; // rewritten two tiles from now
+        it++;
     }
-    if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); // stores complete, not only read
-    // Blocks of modes 0, 2, 4 (none in anything the reference's encoder presets emit): a second pass over this CTA's tiles
-    // through the general decoder, one block per thread, every lane calling.
-    if (__syncthreads_or((int)anyGeneral)) {
-        for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
+    if (general) {
+        for (;;) {
+            // the tile's own stores (which carried stale texels for these blocks) are complete first
+            if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+            __syncthreads();
             const uint32_t b = tile * D7_NT + tid;
             const bool valid = b < P.nblocks;
             uint4 blk = make_uint4(0, 0, 0, 0);
-            if (valid) blk = __ldg((const uint4*)P.src + b);
+            if (valid) blk = s_blk[it & 1u][tid]; // still there: the next bulk copy into it is issued by the next tile
             const uint32_t low = blk.x & 0xFFu;
             const uint32_t m = low ? (uint32_t)__ffs(low) - 1u : 8u;
-            const bool general = valid && (m == 0 || m == 2 || m == 4);
-            if (__any_sync(0xFFFFFFFFu, general)) {
+            const bool mine = valid && (m == 0 || m == 2 || m == 4);
+            if (__any_sync(0xFFFFFFFFu, mine)) { // every lane calls
                 const uint32_t by = b / P.nbx, bx = b - by * P.nbx;
-                decode_bc7_general(blk, P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16, P.dstRowStride, general);
+                decode_bc7_general(blk, P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * 16, P.dstRowStride, mine);
             }
+            __syncthreads();
+            tile = s_next[it & 1u];
+            it++;
+            if (tile >= nTiles) break;
+            lean_tile(tile, it);
         }
+    }
+    if (tid == 0) {
+        if (ROWS) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); // stores complete, not only read
+        finish_claims(P);
     }
 }
 
@@ -735,7 +853,7 @@ __global__ void __launch_bounds__(D7_NT, 5) decode_bc7_lean_kernel(const DecodeP
 // the mode's specialised routine, texel rows staged in shared memory (RGB16F: 24 B per block row, RGB32F: 48 B) and written
 // with TMA bulk stores.
 #ifndef BC6D_OCC
-#define BC6D_OCC 3
+#define BC6D_OCC 5
 #endif
 template <bool F32>
 struct Bc6hSink {
@@ -760,7 +878,7 @@ struct Bc6hSink {
 };
 
 template <bool F32, bool SIGNED, bool ROWS>
-__global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const DecodeParams P, const uint32_t nTiles)
+__global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const DecodeParams P, const uint32_t nTiles, const uint32_t kStatic, const uint32_t rowMagic)
 {
     constexpr int RB = F32 ? 48 : 24; // bytes of one block row
     __shared__ uint4 s_blk[2][D7_NT];
@@ -775,21 +893,32 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
         for (uint32_t i = tid; i < sizeof(lean7::Tables) / 4; i += D7_NT) d[i] = g[i];
     }
     if (tid < 32) (&s_cnt[0][0])[tid] = 0;
-    const uint32_t step = gridDim.x * D7_NT;
-    uint32_t t0 = blockIdx.x * D7_NT;
-    uint32_t by0 = t0 / P.nbx, bx0 = t0 - by0 * P.nbx;
-    const uint32_t dby = step / P.nbx, dbx = step - dby * P.nbx;
-    uint32_t par = 0;
+    __shared__ __align__(8) uint64_t s_bar[2]; // as in the BC7 kernel: bulk-copied block tiles, tiles claimed from P.sched
+    __shared__ uint32_t s_next[2];
+    if (tid == 0) {
+        mbar_init(&s_bar[0], 1);
+        mbar_init(&s_bar[1], 1);
+        fence_mbar_init();
+        fetch_tile(P, blockIdx.x, &s_blk[0][0], &s_bar[0]); // grid <= nTiles
+        s_next[0] = claim_value(claim_issue(P, 1, kStatic), 1, kStatic);
+    }
+    uint32_t tile = blockIdx.x, it = 0;
     __syncthreads();
-    for (uint32_t tile = blockIdx.x; tile < nTiles; tile += gridDim.x, par ^= 1u) {
-        const uint32_t b = t0 + tid;
-        const bool valid = b < P.nblocks;
-        uint32_t mode = 15; // 15 = no block
-        if (valid) {
-            const uint4 blk = __ldcs((const uint4*)P.src + b);
-            s_blk[par][tid] = blk;
-            mode = lean6::mode_of(blk.x);
+    while (tile < nTiles) {
+        const uint32_t par = it & 1u;
+        const uint32_t t0 = tile * D7_NT;
+        const bool valid = t0 + tid < P.nblocks;
+        uint32_t claimed = 0;
+        if (tid == 0) {
+            const uint32_t nxt = s_next[par];
+            if (nxt < nTiles) {
+                fetch_tile(P, nxt, &s_blk[par ^ 1u][0], &s_bar[par ^ 1u]);
+                claimed = claim_issue(P, it + 2, kStatic);
+            }
         }
+        mbar_wait(&s_bar[par], (it >> 1) & 1u);
+        uint32_t mode = 15; // 15 = no block
+        if (valid) mode = lean6::mode_of(s_blk[par][tid].x);
         const uint32_t peers = __match_any_sync(0xFFFFFFFFu, mode);
         const uint32_t leader = (uint32_t)__ffs(peers) - 1u, rank = (uint32_t)__popc(peers & ((1u << lane) - 1u));
         uint32_t base = 0;
@@ -808,6 +937,7 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
         }
         __syncthreads();
         if (tid < 16) s_cnt[par][tid] = 0;
+        if (tid == 0) s_next[par ^ 1u] = s_next[par] < nTiles ? claim_value(claimed, it + 2, kStatic) : nTiles;
         const uint32_t nvalid = min((uint32_t)D7_NT, P.nblocks - t0);
         if (tid < nvalid) {
             const uint32_t k = s_order[par][tid];
@@ -819,14 +949,14 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
         if (ROWS) {
             if (tid == 0) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                const uint32_t by0 = tile_row(tile, rowMagic), bx0 = t0 - by0 * P.nbx;
                 uint8_t* d = P.dst + (size_t)by0 * 4 * P.dstRowStride + (size_t)bx0 * RB;
 #pragma unroll
                 for (int r = 0; r < 4; r++) bulk_s2g(d + r * P.dstRowStride, s_stage + r * (D7_NT * RB), nvalid * RB);
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             }
         } else if (valid) {
-            uint32_t bx = bx0 + tid, by = by0;
-            while (bx >= P.nbx) { bx -= P.nbx; by++; }
+            const uint32_t b = t0 + tid, by = b / P.nbx, bx = b - by * P.nbx;
             uint8_t* d = P.dst + (size_t)by * 4 * P.dstRowStride + (size_t)bx * RB;
 #pragma unroll
             for (int r = 0; r < 4; r++)
@@ -834,27 +964,34 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
                 for (int j = 0; j < RB / 8; j++)
                     __stcs((uint2*)(d + r * P.dstRowStride) + j, *(const uint2*)(s_stage + r * (D7_NT * RB) + tid * RB + j * 8));
         }
-        t0 += step;
-        by0 += dby;
-        bx0 += dbx;
-        if (bx0 >= P.nbx) { bx0 -= P.nbx; by0++; }
+        tile = s_next[par];
+        it++;
     }
-    if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    if (tid == 0) {
+        if (ROWS) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        finish_claims(P);
+    }
 }
 
 template <bool F32, bool SIGNED>
-static cudaError_t launch_bc6h_lean(const DecodeParams& P, uint32_t grid, uint32_t nTiles, bool rows, cudaStream_t stream)
+static cudaError_t launch_bc6h_lean(const DecodeParams& P, int sm_count, uint32_t nTiles, bool rows, cudaStream_t stream)
 {
     constexpr int stage = 4 * D7_NT * (F32 ? 48 : 24);
     static bool attr_set[2] = {false, false};
+    static int occ[2] = {0, 0};
     if (!attr_set[rows]) {
         cudaError_t e = rows ? cudaFuncSetAttribute(decode_bc6h_lean_kernel<F32, SIGNED, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage)
                              : cudaFuncSetAttribute(decode_bc6h_lean_kernel<F32, SIGNED, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage);
         if (e != cudaSuccess) return e;
         attr_set[rows] = true; // per process; attributes are per device context but the value never changes
     }
-    if (rows) decode_bc6h_lean_kernel<F32, SIGNED, true><<<grid, D7_NT, stage, stream>>>(P, nTiles);
-    else decode_bc6h_lean_kernel<F32, SIGNED, false><<<grid, D7_NT, stage, stream>>>(P, nTiles);
+    if (rows) {
+        const uint32_t grid = resident_grid(decode_bc6h_lean_kernel<F32, SIGNED, true>, stage, sm_count, nTiles, &occ[1]);
+        decode_bc6h_lean_kernel<F32, SIGNED, true><<<grid, D7_NT, stage, stream>>>(P, nTiles, static_rounds(nTiles, grid), row_magic(P.nbx));
+    } else {
+        const uint32_t grid = resident_grid(decode_bc6h_lean_kernel<F32, SIGNED, false>, stage, sm_count, nTiles, &occ[0]);
+        decode_bc6h_lean_kernel<F32, SIGNED, false><<<grid, D7_NT, stage, stream>>>(P, nTiles, static_rounds(nTiles, grid), row_magic(P.nbx));
+    }
     return cudaGetLastError();
 }
 
@@ -883,19 +1020,23 @@ static cudaError_t launch_decode_t(const DecodeParams& P, int sm_count, cudaStre
     if constexpr (CODEC == C_BC7) {
         if (!((size_t)P.dst & 15) && !(P.dstRowStride & 15) && !((size_t)P.src & 15)) {
             const uint32_t nTiles = (P.nblocks + D7_NT - 1) / D7_NT;
-            const uint32_t cap = (uint32_t)sm_count * 16;
-            if (P.nbx % D7_NT == 0) decode_bc7_lean_kernel<true><<<nTiles < cap ? nTiles : cap, D7_NT, 0, stream>>>(P, nTiles);
-            else decode_bc7_lean_kernel<false><<<nTiles < cap ? nTiles : cap, D7_NT, 0, stream>>>(P, nTiles);
+            static int occ[2] = {0, 0};
+            if (P.nbx % D7_NT == 0 && row_magic_ok(P.nbx, nTiles)) {
+                const uint32_t grid = resident_grid(decode_bc7_lean_kernel<true>, 0, sm_count, nTiles, &occ[1]);
+                decode_bc7_lean_kernel<true><<<grid, D7_NT, 0, stream>>>(P, nTiles, static_rounds(nTiles, grid), row_magic(P.nbx));
+            } else {
+                const uint32_t grid = resident_grid(decode_bc7_lean_kernel<false>, 0, sm_count, nTiles, &occ[0]);
+                decode_bc7_lean_kernel<false><<<grid, D7_NT, 0, stream>>>(P, nTiles, static_rounds(nTiles, grid), row_magic(P.nbx));
+            }
             return cudaGetLastError();
         }
     }
     if constexpr (CODEC == C_BC6H) {
         if (!((size_t)P.dst & 7) && !(P.dstRowStride & 7) && !((size_t)P.src & 15)) {
             const uint32_t nTiles = (P.nblocks + D7_NT - 1) / D7_NT;
-            const uint32_t cap = (uint32_t)sm_count * 8, grid = nTiles < cap ? nTiles : cap;
-            const bool rows = (P.nbx % D7_NT == 0) && !((size_t)P.dst & 15) && !(P.dstRowStride & 15);
-            if (P.f32out) return P.is_signed ? launch_bc6h_lean<true, true>(P, grid, nTiles, rows, stream) : launch_bc6h_lean<true, false>(P, grid, nTiles, rows, stream);
-            return P.is_signed ? launch_bc6h_lean<false, true>(P, grid, nTiles, rows, stream) : launch_bc6h_lean<false, false>(P, grid, nTiles, rows, stream);
+            const bool rows = (P.nbx % D7_NT == 0) && row_magic_ok(P.nbx, nTiles) && !((size_t)P.dst & 15) && !(P.dstRowStride & 15);
+            if (P.f32out) return P.is_signed ? launch_bc6h_lean<true, true>(P, sm_count, nTiles, rows, stream) : launch_bc6h_lean<true, false>(P, sm_count, nTiles, rows, stream);
+            return P.is_signed ? launch_bc6h_lean<false, true>(P, sm_count, nTiles, rows, stream) : launch_bc6h_lean<false, false>(P, sm_count, nTiles, rows, stream);
         }
     }
     size_t need = (CODEC == C_BC4) ? 4 : (CODEC == C_BC5) ? 8 : (CODEC == C_BC6H) ? (P.f32out ? 16 : 8) : 16;

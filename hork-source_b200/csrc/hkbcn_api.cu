@@ -46,6 +46,11 @@ struct Device {
     struct Taps { int* idx; float* w; int T; };
     std::map<uint64_t, Taps> taps;
     std::mutex   taps_mu;
+    // tile counters of the persistent decode kernels: a ring of zeroed word pairs, one pair per launch (a kernel leaves its
+    // pair zeroed again), so launches in flight on different streams never share one
+    uint32_t*    sched = nullptr;
+    std::atomic<uint32_t> sched_seq{0};
+    static constexpr uint32_t SCHED_SLOTS = 256;
 };
 
 std::mutex            g_mu;
@@ -257,6 +262,8 @@ int hkbcn_init(uint32_t device_mask)
             CK(cudaMemcpy(D->lut_srgb, srgb, sizeof(srgb), cudaMemcpyHostToDevice));
             CK(cudaMemcpy(D->lut_lin, lin, sizeof(lin), cudaMemcpyHostToDevice));
         }
+        CK(cudaMalloc((void**)&D->sched, Device::SCHED_SLOTS * 32));
+        CK(cudaMemset(D->sched, 0, Device::SCHED_SLOTS * 32));
         g_devs.push_back(D);
     }
     if (g_devs.empty()) {
@@ -277,6 +284,7 @@ void hkbcn_shutdown(void)
         if (D->d_dst) cudaFree(D->d_dst);
         if (D->lut_srgb) cudaFree(D->lut_srgb);
         if (D->lut_lin) cudaFree(D->lut_lin);
+        if (D->sched) cudaFree(D->sched);
         for (auto& kv : D->taps) { cudaFree(kv.second.idx); cudaFree(kv.second.w); }
         D->taps.clear();
         if (D->stream) cudaStreamDestroy(D->stream);
@@ -525,6 +533,7 @@ int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, ui
     P.codec = codec;
     P.is_signed = fmt == HKBCN_BC6H_SFLOAT;
     P.f32out = (flags & HKBCN_FLAG_DST_F32) != 0;
+    P.sched = D->sched + 8 * (D->sched_seq.fetch_add(1, std::memory_order_relaxed) % Device::SCHED_SLOTS); // one 32-byte sector each
     if (P.nblocks == 0) return HKBCN_OK;
     CK(cudaSetDevice(D->id));
     cudaError_t e = launch_decode(P, D->sm_count, (cudaStream_t)stream);

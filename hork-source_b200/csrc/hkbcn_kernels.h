@@ -33,6 +33,7 @@ struct DecodeParams {
     int            codec;
     uint32_t       is_signed; // BC6H
     uint32_t       f32out;    // BC6H
+    uint32_t*      sched;     // two zeroed words of device memory: tile counter and finished-CTA counter (BC6H / BC7 kernels)
 };
 cudaError_t launch_decode(const DecodeParams& P, int sm_count, cudaStream_t stream);
 cudaError_t decode_upload_tables(); // BC6H header layout table

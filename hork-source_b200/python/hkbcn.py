@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libhkbcn.so")
+# HKBCN_LIB: an alternative build of the same library (kernel experiments from tools/), never a different implementation
+LIB_PATH = os.environ.get("HKBCN_LIB") or os.path.join(os.path.dirname(_HERE), "libhkbcn.so")
 
 # Hk::TEXTURE_FORMAT values (Hork/Image/Image.h:122-148)
 BC1_UNORM, BC1_UNORM_SRGB, BC2_UNORM, BC2_UNORM_SRGB, BC3_UNORM, BC3_UNORM_SRGB = 54, 55, 56, 57, 58, 59

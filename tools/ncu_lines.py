@@ -1,0 +1,25 @@
+#!/usr/bin/env python3
+"""Per-source-line instruction and stall-sample totals of an .ncu-rep captured with --import-source on (-lineinfo build).
+usage: ncu_lines.py report.ncu-rep [top-n]"""
+import csv
+import subprocess
+import sys
+
+rep = sys.argv[1]
+top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+rows, fname, hdr = [], "", None
+for r in csv.reader(out.splitlines()):
+    if not r:
+        continue
+    if r[0] == "File Path":
+        fname = r[1].split("/")[-1]
+    elif r[0] == "Line No":
+        hdr = r
+        ci, cs = hdr.index("Instructions Executed"), hdr.index("# Samples")
+    elif hdr and len(r) > ci and r[2] == "-" and r[0].isdigit():
+        rows.append((fname, int(r[0]), r[1].strip(), int(r[ci] or 0), int(r[cs] or 0)))
+ti, ts = sum(x[3] for x in rows), sum(x[4] for x in rows)
+print(f"total warp instructions {ti}, samples {ts}")
+for f, ln, src, n, s in sorted(rows, key=lambda x: -x[3])[:top]:
+    print(f"{100 * n / ti:5.1f}% inst {100 * s / max(ts, 1):5.1f}% smp  {f}:{ln}  {src[:110]}")

@@ -13,13 +13,22 @@ import synth  # noqa: E402
 
 fmt, n = int(sys.argv[1]), int(sys.argv[2])
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-decode = len(sys.argv) > 4 and sys.argv[4] == "decode"
+decode = len(sys.argv) > 4 and sys.argv[4] in ("decode", "decode32")
+f32 = len(sys.argv) > 4 and sys.argv[4] == "decode32"
 hkbcn.init()
 bpp = hkbcn.lib().hkbcn_src_texel_bytes(fmt, 0)
 if decode:
-    blocks = synth.random_blocks((n // 4) ** 2, 1, 5)[: (n // 4) ** 2 * hkbcn.block_bytes(fmt)] if fmt != 66 else hkbcn.compress(66, synth.albedo_rgba8(n, n, 4), n, n)
+    if fmt == 66:
+        blocks = hkbcn.compress(66, synth.albedo_rgba8(n, n, 4), n, n)
+    elif fmt in (64, 65):
+        # BC6H encode is slow: a 256^2 sky encoded once, its blocks tiled up to n x n
+        t = 256
+        b = np.asarray(hkbcn.compress(fmt, synth.sky_rgba32f(t, t, 6), t, t)).reshape(t // 4, t // 4, 16)
+        blocks = np.ascontiguousarray(np.tile(b, (n // t, n // t, 1))).ravel()
+    else:
+        blocks = synth.random_blocks((n // 4) ** 2, 1, 5)[: (n // 4) ** 2 * hkbcn.block_bytes(fmt)]
     for _ in range(reps):
-        out = hkbcn.decompress(fmt, blocks, n, n)
+        out = hkbcn.decompress(fmt, blocks, n, n, flags=(1 << 8) if f32 else 0) if f32 else hkbcn.decompress(fmt, blocks, n, n)
 else:
     if bpp == 4:
         img = synth.albedo_rgba8(n, n, 0xB2000004, "mask" if len(sys.argv) > 4 and sys.argv[4] == "mask" else "opaque")
