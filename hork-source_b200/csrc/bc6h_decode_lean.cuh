@@ -11,6 +11,8 @@
 //   * index streams are re-expanded to fixed-width fields exactly as for BC7 modes 1 and 6 (same bit positions: 82 / 65).
 // Plain integer code: tools/decode_host_check.cpp compiles it for the CPU against the reference.
 #pragma once
+#include <math.h>
+#include <string.h>
 #include "bc7_decode_lean.cuh"
 
 namespace hkbcn {
@@ -104,16 +106,53 @@ HKD void endpoints(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, int e[12]
     }
 }
 
-// One interpolated + finished channel value, returned with the half in bytes 1..2 (bits 8..23).
-// unsigned: A = a*256 + 128, D = 4(b - a).  signed: A = a*64 + 32, D = b - a (bcdec.h:331-346 finish_unquantize).
-template <bool SIGNED>
-HKD uint32_t channel(int A, int D, int w)
+// ---- texels on the FMA pipe ---------------------------------------------------------------------------------------
+// The integer version of the texel loop (IMAD, SHF, IMAD per channel, six LOP3 selects per two-region texel, SHF / PRMT
+// weight lookups) ran the ALU pipe -- half rate on sm_100: LOP3, SHF, PRMT, SEL, ISETP -- at 73 % with the FMA pipe at 36 %
+// (profiles/r1_bc6h_decode_lean_ncu.txt).  Everything below is exact in fp32 (all values are integers or half-integers
+// below 2^24), so the interpolation moves to FFMA / FADD and the weights and region masks come from shared-memory tables:
+//   unsigned: x = D*w + A with A = 256a + 128, D = 4(b - a) is 4(a(64-w) + bw + 32) < 2^24; v = x >> 8.
+//             y = (x - 126) + 1.5*2^31 rounds to a multiple of 256 (the ulp there) and can never tie (x is a multiple of 4),
+//             so the float's bit pattern is bits(1.5*2^31) + v; (bits * 124 - bits(C) * 124) = v * 124 has
+//             bcdec's (v * 31) >> 6 in bytes 1..2, where the PRMT that packs two halfs picks it up.
+//   signed:   x = D*w + A with A = 64a + 32, D = b - a; v = x >> 6 = round((x - 31.5) / 64), ulp 64 at 1.5*2^29.
+#ifdef HKBCN_HOST_EMU
+static inline float hk_fma(float a, float b, float c) { return fmaf(a, b, c); }
+static inline float hk_add(float a, float b) { return a + b; }
+static inline uint32_t hk_fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static inline float hk_bitsf(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+#else
+HKD float hk_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+HKD float hk_add(float a, float b) { return __fadd_rn(a, b); }
+HKD uint32_t hk_fbits(float f) { return __float_as_uint(f); }
+HKD float hk_bitsf(uint32_t u) { return __uint_as_float(u); }
+#endif
+
+// aWeight3 / aWeight4 as floats and the region of every texel of the 32 two-region shapes as 0.0f / 1.0f.
+// m is texel-major so that a warp's lookups (one texel, 32 shapes) fall into 32 different banks.
+struct FTab {
+    float w3[8], w4[16];
+    float m[16][32];
+};
+inline void fill_ftab(FTab* F, const uint16_t* shape2)
 {
+    static const int w3[8] = {0, 9, 18, 27, 37, 46, 55, 64}, w4[16] = {0, 4, 9, 13, 17, 21, 26, 30, 34, 38, 43, 47, 51, 55, 60, 64};
+    for (int i = 0; i < 8; i++) F->w3[i] = (float)w3[i];
+    for (int i = 0; i < 16; i++) F->w4[i] = (float)w4[i];
+    for (int s = 0; s < 32; s++)
+        for (int i = 0; i < 16; i++) F->m[i][s] = ((shape2[s] >> i) & 1) ? 1.0f : 0.0f;
+}
+
+// One interpolated + finished channel value, returned with the half in bytes 1..2 (bits 8..23).
+template <bool SIGNED>
+HKD uint32_t channel(float A, float D, float w)
+{
+    const float x = hk_fma(D, w, A);
     if (!SIGNED) {
-        const uint32_t v = (uint32_t)(D * w + A) >> 8;
-        return v * 124u;
+        const uint32_t yb = hk_fbits(hk_add(x, 3221225472.0f)); // 1.5 * 2^31 = 0x4F400000
+        return yb * 124u - 0x4F400000u * 124u;
     } else {
-        const int v = (D * w + A) >> 6;
+        const int v = (int)(hk_fbits(hk_add(x, 805306368.0f)) - 0x4E400000u); // 1.5 * 2^29
         const int a = v < 0 ? -v : v;
         const uint32_t mag = (uint32_t)(a * 31) >> 5;
         return (mag | ((v < 0 && mag != 0) ? 0x8000u : 0u)) << 8;
@@ -122,18 +161,19 @@ HKD uint32_t channel(int A, int D, int w)
 
 // Texel rows of one block.  sink.row(r, w) receives the six output words of texel row r (RGB16F x 4, bcdec's layout).
 template <bool SIGNED, bool TWO, class Sink>
-HKD void texels(const int e[12], uint32_t part, uint32_t w2, uint32_t w3, const lean7::Tables& T, Sink& sink)
+HKD void texels(const int e[12], uint32_t part, uint32_t w2, uint32_t w3, const lean7::Tables& T, const FTab& F, Sink& sink)
 {
-    int A[2][3], D[2][3];
+    float A[2][3], D[2][3];
 #pragma unroll
     for (int s = 0; s < (TWO ? 2 : 1); s++)
 #pragma unroll
         for (int c = 0; c < 3; c++) {
             const int a = e[c * 4 + 2 * s], b = e[c * 4 + 2 * s + 1];
-            A[s][c] = SIGNED ? a * 64 + 32 : a * 256 + 128;
-            D[s][c] = SIGNED ? b - a : 4 * (b - a);
+            A[s][c] = SIGNED ? hk_add((float)(a * 64), 0.5f) : (float)(a * 256 + 2); // A - 31.5 / A - 126: see above
+            D[s][c] = SIGNED ? (float)(b - a) : (float)(4 * (b - a));
         }
-    uint32_t lo, hi, shape = 0;
+    uint32_t lo, hi;
+    const float* mrow = &F.m[0][0];
     if (TWO) {
         // 46 index bits from bit 82; implicit zeros after texel 0's two bits and the anchor's (as BC7 mode 1)
         unsigned long long S = ((unsigned long long)(w3 >> 18) << 32) | hk_funnel_r(w2, w3, 18);
@@ -141,36 +181,37 @@ HKD void texels(const int e[12], uint32_t part, uint32_t w2, uint32_t w3, const 
         S += S & (((unsigned long long)T.ins3[part][1] << 32) | T.ins3[part][0]);
         lo = (uint32_t)S;
         hi = (uint32_t)(S >> 32);
-        // subset bits back from the nibble table: bit 4k+3 of nib[h] = subset of texel 8h+k
-        shape = part; // resolved per texel below through T.nib
+        mrow = &F.m[0][part];
+#pragma unroll
+        for (int c = 0; c < 3; c++) { // region 1 as an offset from region 0
+            A[1][c] = hk_add(A[1][c], -A[0][c]);
+            D[1][c] = hk_add(D[1][c], -D[0][c]);
+        }
     } else {
         lo = w2 & ~1u; // texel 0: 3 bits at 65..67 -> a 4-bit field with its top bit clear, after >> 1 below
         hi = w3;
     }
-    (void)shape;
-    const uint32_t W3lo = 0x1B120900u, W3hi = 0x40372E25u; // aWeight3 = {0, 9, 18, 27, 37, 46, 55, 64}
-    const uint32_t n0 = TWO ? T.nib[part][0] : 0u, n1 = TWO ? T.nib[part][1] : 0u;
 #pragma unroll
     for (int r = 0; r < 4; r++) {
         uint32_t y[12];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int i = 4 * r + k;
-            int w;
-            int a0, a1, a2, d0, d1, d2;
+            float w, a0, a1, a2, d0, d1, d2;
             if (TWO) {
+                // byte offset of the weight: 4 * ((S >> 3i) & 7)
                 const int p = 3 * i;
-                const uint32_t idx = (p + 3 <= 32 ? (lo >> p) : p >= 32 ? (hi >> (p - 32)) : hk_funnel_r(lo, hi, p)) & 7u;
-                w = (int)hk_prmt(W3lo, W3hi, idx);
-                const uint32_t nb = i < 8 ? n0 : n1;
-                const int m = -(int)((nb >> (4 * (i & 7) + 3)) & 1u); // all ones for subset 1
-                a0 = A[0][0] ^ ((A[0][0] ^ A[1][0]) & m); d0 = D[0][0] ^ ((D[0][0] ^ D[1][0]) & m);
-                a1 = A[0][1] ^ ((A[0][1] ^ A[1][1]) & m); d1 = D[0][1] ^ ((D[0][1] ^ D[1][1]) & m);
-                a2 = A[0][2] ^ ((A[0][2] ^ A[1][2]) & m); d2 = D[0][2] ^ ((D[0][2] ^ D[1][2]) & m);
+                const uint32_t off = p == 0 ? (lo << 2) : p + 3 <= 32 ? (lo >> (p - 2)) : p >= 34 ? (hi >> (p - 34)) : p >= 32 ? (hi << (34 - p)) : hk_funnel_r(lo, hi, p - 2);
+                w = *(const float*)((const char*)F.w3 + (off & 0x1Cu));
+                const float m = mrow[32 * i];
+                a0 = hk_fma(m, A[1][0], A[0][0]); d0 = hk_fma(m, D[1][0], D[0][0]);
+                a1 = hk_fma(m, A[1][1], A[0][1]); d1 = hk_fma(m, D[1][1], D[0][1]);
+                a2 = hk_fma(m, A[1][2], A[0][2]); d2 = hk_fma(m, D[1][2], D[0][2]);
             } else {
                 const uint32_t word = i < 8 ? lo : hi;
-                const uint32_t idx = i == 0 ? ((word >> 1) & 7u) : ((word >> (4 * (i & 7))) & 15u);
-                w = (int)((idx * 68u + 8u) >> 4); // aWeight4
+                const int q = 4 * (i & 7);
+                const uint32_t off = i == 0 ? ((word << 1) & 0x1Cu) : q == 0 ? ((word << 2) & 0x3Cu) : ((word >> (q - 2)) & 0x3Cu);
+                w = *(const float*)((const char*)F.w4 + off);
                 a0 = A[0][0]; a1 = A[0][1]; a2 = A[0][2];
                 d0 = D[0][0]; d1 = D[0][1]; d2 = D[0][2];
             }
@@ -199,7 +240,7 @@ HKD uint32_t mode_of(uint32_t w0)
 // mode boundary of the sorted tile diverges over the parse, not over the texels, and the kernel carries two texel bodies
 // instead of fourteen.
 template <bool SIGNED, class Sink>
-HKD void decode_bc6h(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const lean7::Tables& T, Sink& sink)
+HKD void decode_bc6h(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const lean7::Tables& T, const FTab& F, Sink& sink)
 {
     int e[12];
     uint32_t part = 0;
@@ -223,8 +264,8 @@ HKD void decode_bc6h(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, const l
 #pragma unroll
         for (int i = 0; i < 12; i++) e[i] = 0;
     }
-    if (mode < 10) texels<SIGNED, true>(e, part, w2, w3, T, sink);
-    else if (mode < 14) texels<SIGNED, false>(e, part, w2, w3, T, sink);
+    if (mode < 10) texels<SIGNED, true>(e, part, w2, w3, T, F, sink);
+    else if (mode < 14) texels<SIGNED, false>(e, part, w2, w3, T, F, sink);
     else {
         const uint32_t z[6] = {0, 0, 0, 0, 0, 0};
 #pragma unroll

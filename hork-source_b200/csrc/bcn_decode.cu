@@ -635,6 +635,7 @@ static bool try_launch_lean(const DecodeParams& P, int sm_count, cudaStream_t st
 // writing the sorted blocks straight from the decoding lanes (scattered 16-byte stores) costs 10 us of 60 at 8192^2.
 // Sort buffers are double-buffered by tile parity; three barriers per tile.
 __device__ lean7::Tables g_bc7dec_tables;
+__device__ lean6::FTab g_bc6h_ftab;
 constexpr int D7_NT = 256;
 
 // modes 0, 2, 4: the general decoder, kept out of line so that it does not set the lean kernel's register budget.
@@ -887,10 +888,14 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
     __shared__ __align__(16) uint32_t s_cnt[2][16];
     __shared__ uint8_t s_order[2][D7_NT];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    __shared__ lean6::FTab s_F;
     {
         const uint32_t* g = (const uint32_t*)&g_bc7dec_tables;
         uint32_t* d = (uint32_t*)&s_T;
         for (uint32_t i = tid; i < sizeof(lean7::Tables) / 4; i += D7_NT) d[i] = g[i];
+        const uint32_t* gf = (const uint32_t*)&g_bc6h_ftab;
+        uint32_t* df = (uint32_t*)&s_F;
+        for (uint32_t i = tid; i < sizeof(lean6::FTab) / 4; i += D7_NT) df[i] = gf[i];
     }
     if (tid < 32) (&s_cnt[0][0])[tid] = 0;
     __shared__ __align__(8) uint64_t s_bar[2]; // as in the BC7 kernel: bulk-copied block tiles, tiles claimed from P.sched
@@ -926,14 +931,17 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
         base = __shfl_sync(0xFFFFFFFFu, base, leader);
         if (ROWS && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncthreads();
-        if (valid) {
-            const uint4 c0 = *(const uint4*)&s_cnt[par][0], c1 = *(const uint4*)&s_cnt[par][4], c2 = *(const uint4*)&s_cnt[par][8],
-                        c3 = *(const uint4*)&s_cnt[par][12];
-            const uint32_t c[15] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w, c2.x, c2.y, c2.z, c2.w, c3.x, c3.y, c3.z};
-            uint32_t start = base + rank;
+        {
+            // exclusive prefix of the sixteen counts, once per warp: lane m scans, every lane picks its mode's with a shuffle
+            const uint32_t cnt = s_cnt[par][lane & 15u];
+            uint32_t inc = cnt;
 #pragma unroll
-            for (uint32_t m = 0; m < 15; m++) start += (m < mode) ? c[m] : 0u;
-            s_order[par][start] = (uint8_t)tid;
+            for (int d = 1; d < 16; d <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, inc, d, 16);
+                if ((lane & 15u) >= (uint32_t)d) inc += up;
+            }
+            const uint32_t pre = __shfl_sync(0xFFFFFFFFu, inc - cnt, mode);
+            if (valid) s_order[par][pre + base + rank] = (uint8_t)tid;
         }
         __syncthreads();
         if (tid < 16) s_cnt[par][tid] = 0;
@@ -943,7 +951,7 @@ __global__ void __launch_bounds__(D7_NT, BC6D_OCC) decode_bc6h_lean_kernel(const
             const uint32_t k = s_order[par][tid];
             const uint4 blk = s_blk[par][k];
             Bc6hSink<F32> sink{s_stage + k * RB};
-            lean6::decode_bc6h<SIGNED>(blk.x, blk.y, blk.z, blk.w, s_T, sink);
+            lean6::decode_bc6h<SIGNED>(blk.x, blk.y, blk.z, blk.w, s_T, s_F, sink);
         }
         __syncthreads();
         if (ROWS) {
@@ -1006,6 +1014,10 @@ cudaError_t bc7dec_upload_tables()
     static const uint8_t anchor2[64] = {15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 15, 2, 8, 2, 2, 8, 8, 15, 2, 8, 2, 2, 8, 8, 2, 2,
                                         15, 15, 6, 8, 2, 8, 15, 15, 2, 8, 2, 2, 2, 15, 15, 6, 6, 2, 6, 8, 15, 15, 2, 2, 15, 15, 15, 15, 15, 2, 2, 15};
     lean7::fill_tables(&H, shape2, anchor2);
+    static lean6::FTab F;
+    lean6::fill_ftab(&F, shape2);
+    cudaError_t e = cudaMemcpyToSymbol(g_bc6h_ftab, &F, sizeof(F));
+    if (e != cudaSuccess) return e;
     return cudaMemcpyToSymbol(g_bc7dec_tables, &H, sizeof(H));
 }
 

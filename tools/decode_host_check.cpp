@@ -60,10 +60,11 @@ static long check_bc6h(const uint32_t w[4], bool isSigned)
 {
     static lean7::Tables T;
     static bool init = false;
-    if (!init) { lean7::fill_tables(&T, kShape2, kAnchor2); init = true; }
+    static lean6::FTab F;
+    if (!init) { lean7::fill_tables(&T, kShape2, kAnchor2); lean6::fill_ftab(&F, kShape2); init = true; }
     HostSink sink;
-    if (isSigned) lean6::decode_bc6h<true>(w[0], w[1], w[2], w[3], T, sink);
-    else lean6::decode_bc6h<false>(w[0], w[1], w[2], w[3], T, sink);
+    if (isSigned) lean6::decode_bc6h<true>(w[0], w[1], w[2], w[3], T, F, sink);
+    else lean6::decode_bc6h<false>(w[0], w[1], w[2], w[3], T, F, sink);
     uint32_t want[4][6];
     ref_decode(isSigned ? 6 : 5, w, want, 24, 0);
     return memcmp(sink.rows, want, 96) != 0;
