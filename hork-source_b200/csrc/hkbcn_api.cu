@@ -9,6 +9,8 @@
 #include "hkbcn_kernels.h"
 
 #include <atomic>
+#include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -212,6 +214,7 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
     CK(cudaStreamSynchronize(D->stream));
     return HKBCN_OK;
 }
+
 
 } // namespace
 
@@ -459,16 +462,15 @@ int hkbcn_import_chain_dev(int device, int fmt, void* d_chain, void* d_dst, uint
     return hkbcn_compress_chain_dev(device, fmt, d_chain, d_dst, width, height, num_mips, flags, stream);
 }
 
-int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
-                       const hkbcn_mip_config* cfg, uint32_t flags)
+// level 0 in host memory -> device mip cascade -> encode -> compressed chain in host memory, on one device
+static int import_host_on(Device* D, int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                   const hkbcn_mip_config* cfg, uint32_t flags)
 {
-    int rc = ensure_init();
-    if (rc) return rc;
+    int rc;
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
     if ((width & 3) || (height & 3) || !width || !height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
     if (!src_level0 || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
-    Device* D = g_devs[0];
     const size_t sbytes = chain_src_bytes(codec, flags, width, height, num_mips);
     const size_t l0 = (size_t)width * height * src_bpp(codec, flags);
     const size_t dbytes = hkbcn_chain_bytes(fmt, width, height, 1, num_mips);
@@ -477,13 +479,22 @@ int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t widt
     if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
     if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
     CK(cudaMemcpyAsync(D->d_src, src_level0, l0, cudaMemcpyHostToDevice, D->stream)); // level 0 only crosses PCIe
-    if ((rc = generate_mips_on(D, fmt, D->d_src, width, height, num_mips, cfg, flags, D->stream)) != HKBCN_OK) return rc;
+    if (num_mips > 1 && (rc = generate_mips_on(D, fmt, D->d_src, width, height, num_mips, cfg, flags, D->stream)) != HKBCN_OK) return rc;
     EncodeParams P;
     if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, width, height, num_mips)) != HKBCN_OK) return rc;
     if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
     CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
     CK(cudaStreamSynchronize(D->stream));
     return HKBCN_OK;
+}
+
+
+int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                       const hkbcn_mip_config* cfg, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    return import_host_on(g_devs[0], fmt, src_level0, dst, width, height, num_mips, cfg, flags);
 }
 
 int hkbcn_encode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, uint32_t flags)
@@ -633,6 +644,156 @@ int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
     }
     for (auto& t : th) t.join();
     for (size_t d = 0; d < nd; d++)
+        if (first_err[d]) { set_err("%s", err_msg[d].c_str()); return first_err[d]; }
+    return HKBCN_OK;
+}
+
+// ---- .texture files (row f2) ------------------------------------------------------------------------------------------
+static void put_u32(uint8_t* p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
+static uint32_t get_u32(const uint8_t* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }
+
+int hkbcn_texture_header(const hkbcn_texture_desc* d, uint32_t payload_bytes, void* dst30)
+{
+    if (!d || !dst30) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    uint8_t* p = (uint8_t*)dst30;
+    // MakeResourceMagic(RESOURCE_TEXTURE, 1) written with WriteUInt32: 'H', 'k', 4, 1
+    p[0] = 'H'; p[1] = 'k'; p[2] = 4; p[3] = 1;
+    p[4] = (uint8_t)d->type;
+    put_u32(p + 5, d->width);
+    put_u32(p + 9, d->height);
+    put_u32(p + 13, d->depth);
+    put_u32(p + 17, d->num_mips);
+    p[21] = (uint8_t)d->fmt;
+    put_u32(p + 22, d->storage_flags);
+    put_u32(p + 26, payload_bytes);
+    return HKBCN_OK;
+}
+
+int hkbcn_write_texture(const char* path, const hkbcn_texture_desc* d, const void* payload, size_t payload_bytes)
+{
+    if (!path || !d || (!payload && payload_bytes)) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    if (payload_bytes > 0xFFFFFFFFull) { set_err("payload of %zu bytes does not fit the format's u32 size field", payload_bytes); return HKBCN_ERR_BAD_ARG; }
+    uint8_t h[HKBCN_TEXTURE_HEADER_BYTES];
+    hkbcn_texture_header(d, (uint32_t)payload_bytes, h);
+    FILE* f = fopen(path, "wb");
+    if (!f) { set_err("cannot open %s for writing", path); return HKBCN_ERR_BAD_ARG; }
+    const bool ok = fwrite(h, 1, sizeof(h), f) == sizeof(h) && (payload_bytes == 0 || fwrite(payload, 1, payload_bytes, f) == payload_bytes);
+    if (fclose(f) != 0 || !ok) { set_err("short write to %s", path); return HKBCN_ERR_BAD_ARG; }
+    return HKBCN_OK;
+}
+
+int hkbcn_read_texture(const char* path, hkbcn_texture_desc* d, void* payload, size_t capacity, size_t* payload_bytes)
+{
+    if (!path || !d) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    FILE* f = fopen(path, "rb");
+    if (!f) { set_err("cannot open %s", path); return HKBCN_ERR_BAD_ARG; }
+    uint8_t h[HKBCN_TEXTURE_HEADER_BYTES];
+    if (fread(h, 1, sizeof(h), f) != sizeof(h) || h[0] != 'H' || h[1] != 'k' || h[2] != 4 || h[3] != 1) {
+        fclose(f);
+        set_err("%s is not a version-1 texture resource", path);
+        return HKBCN_ERR_BAD_FORMAT;
+    }
+    d->type = h[4];
+    d->width = get_u32(h + 5);
+    d->height = get_u32(h + 9);
+    d->depth = get_u32(h + 13);
+    d->num_mips = get_u32(h + 17);
+    d->fmt = h[21];
+    d->storage_flags = get_u32(h + 22);
+    const size_t n = get_u32(h + 26);
+    if (payload_bytes) *payload_bytes = n;
+    int rc = HKBCN_OK;
+    if (payload) {
+        const size_t want = n < capacity ? n : capacity;
+        if (fread(payload, 1, want, f) != want) { set_err("%s is truncated", path); rc = HKBCN_ERR_BAD_FORMAT; }
+    }
+    fclose(f);
+    return rc;
+}
+
+int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (n_jobs == 0) return HKBCN_OK;
+    if (!jobs) { set_err("null jobs"); return HKBCN_ERR_BAD_ARG; }
+    const size_t nd = g_devs.size();
+    // plan as hkbcn_compress_batch does (pixel count x per-format weight; a mip chain adds a third everywhere alike)
+    std::vector<hkbcn_job> plain(n_jobs);
+    for (size_t i = 0; i < n_jobs; i++) {
+        plain[i] = hkbcn_job{jobs[i].fmt, jobs[i].width, jobs[i].height, jobs[i].flags, nullptr, nullptr, 0};
+        jobs[i].status = HKBCN_OK;
+    }
+    std::vector<int> assign(n_jobs);
+    plan_batch(plain.data(), n_jobs, (int)nd, assign.data());
+    std::vector<std::vector<size_t>> bins(nd);
+    for (size_t i = 0; i < n_jobs; i++) bins[(size_t)assign[i]].push_back(i);
+
+    // encoded chains queue up for one writer thread, so a GPU never waits for the file system
+    struct Done { size_t idx; std::vector<uint8_t> own; const void* data; size_t bytes; uint32_t mips; };
+    std::mutex qmu;
+    std::condition_variable qcv;
+    std::deque<Done> queue;
+    size_t workers_left = nd;
+    std::vector<int> first_err(nd + 1, 0);
+    std::vector<std::string> err_msg(nd + 1);
+
+    std::thread writer([&]() {
+        for (;;) {
+            Done d;
+            {
+                std::unique_lock<std::mutex> lk(qmu);
+                qcv.wait(lk, [&] { return !queue.empty() || workers_left == 0; });
+                if (queue.empty()) return;
+                d = std::move(queue.front());
+                queue.pop_front();
+            }
+            hkbcn_import_job& j = jobs[d.idx];
+            hkbcn_texture_desc desc{HKBCN_TEXTURE_2D, j.width, j.height, 1, d.mips, j.fmt,
+                                    (j.mip.no_alpha ? (uint32_t)HKBCN_STORAGE_NO_ALPHA : 0u) | (j.mip.alpha_premultiplied ? (uint32_t)HKBCN_STORAGE_ALPHA_PREMULTIPLIED : 0u)};
+            const int wrc = hkbcn_write_texture(j.out_path, &desc, d.data, d.bytes);
+            if (wrc) {
+                j.status = wrc;
+                if (!first_err[nd]) { first_err[nd] = wrc; err_msg[nd] = t_err; }
+            }
+        }
+    });
+    std::vector<std::thread> th;
+    for (size_t dv = 0; dv < nd; dv++) {
+        th.emplace_back([&, dv]() {
+            for (size_t idx : bins[dv]) {
+                hkbcn_import_job& j = jobs[idx];
+                const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
+                const size_t bytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips);
+                Done d{idx, {}, nullptr, bytes, mips};
+                void* out = j.dst;
+                if (!out) {
+                    d.own.resize(bytes);
+                    out = d.own.data();
+                }
+                j.status = import_host_on(g_devs[dv], j.fmt, j.src_level0, out, j.width, j.height, mips, &j.mip, j.flags);
+                if (j.status) {
+                    if (!first_err[dv]) { first_err[dv] = j.status; err_msg[dv] = t_err; }
+                    continue;
+                }
+                if (!j.out_path) continue;
+                d.data = out;
+                {
+                    std::lock_guard<std::mutex> lk(qmu);
+                    queue.push_back(std::move(d));
+                }
+                qcv.notify_one();
+            }
+            {
+                std::lock_guard<std::mutex> lk(qmu);
+                workers_left--;
+            }
+            qcv.notify_one();
+        });
+    }
+    for (auto& t : th) t.join();
+    writer.join();
+    for (size_t d = 0; d <= nd; d++)
         if (first_err[d]) { set_err("%s", err_msg[d].c_str()); return first_err[d]; }
     return HKBCN_OK;
 }

@@ -30,6 +30,7 @@ EXPORTS = [
     "hkbcn_compress_dev", "hkbcn_decompress_dev", "hkbcn_compress_chain_dev", "hkbcn_compress_chain",
     "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
     "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
+    "hkbcn_texture_header", "hkbcn_write_texture", "hkbcn_read_texture", "hkbcn_import_batch",
 ]
 
 
@@ -44,6 +45,16 @@ class MipConfig(C.Structure):
 class Job(C.Structure):
     _fields_ = [("fmt", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("flags", C.c_uint32),
                 ("src", C.c_void_p), ("dst", C.c_void_p), ("status", C.c_int)]
+
+
+class TextureDesc(C.Structure):
+    _fields_ = [("type", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("depth", C.c_uint32), ("num_mips", C.c_uint32),
+                ("fmt", C.c_int), ("storage_flags", C.c_uint32)]
+
+
+class ImportJob(C.Structure):
+    _fields_ = [("fmt", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("generate_mips", C.c_int), ("mip", MipConfig),
+                ("flags", C.c_uint32), ("src_level0", C.c_void_p), ("out_path", C.c_char_p), ("dst", C.c_void_p), ("status", C.c_int)]
 
 
 _lib = None
@@ -82,6 +93,10 @@ def lib():
         L.hkbcn_import_chain.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32]
         L.hkbcn_launch_count.restype = C.c_uint64
         L.hkbcn_alloc_pinned.restype = C.c_void_p
+        L.hkbcn_texture_header.argtypes = [C.POINTER(TextureDesc), C.c_uint32, C.c_void_p]
+        L.hkbcn_write_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
+        L.hkbcn_read_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.hkbcn_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t]
         L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
         L.hkbcn_free_pinned.argtypes = [C.c_void_p]
         _lib = L
@@ -195,3 +210,49 @@ def generate_mips(fmt, level0, width, height, mips, cfg=None, flags=0):
     dst = np.zeros(lib().hkbcn_chain_src_bytes(fmt, width, height, mips, flags), np.uint8)
     check(lib().hkbcn_generate_mips(fmt, _ptr(level0), _ptr(dst), width, height, mips, C.byref(cfg) if cfg else None, flags))
     return dst
+
+
+def texture_header(type_, width, height, depth, mips, fmt, storage_flags, payload_bytes):
+    """the 30 header bytes of a .texture file (host only)"""
+    d = TextureDesc(type_, width, height, depth, mips, fmt, storage_flags)
+    out = (C.c_uint8 * 30)()
+    check(lib().hkbcn_texture_header(C.byref(d), payload_bytes, out))
+    return bytes(out)
+
+
+def write_texture(path, type_, width, height, depth, mips, fmt, storage_flags, payload):
+    payload = np.ascontiguousarray(payload)
+    d = TextureDesc(type_, width, height, depth, mips, fmt, storage_flags)
+    check(lib().hkbcn_write_texture(os.fsencode(path), C.byref(d), _ptr(payload), C.c_size_t(payload.nbytes)))
+
+
+def read_texture(path):
+    """-> (TextureDesc, payload ndarray)"""
+    d = TextureDesc()
+    n = C.c_size_t(0)
+    check(lib().hkbcn_read_texture(os.fsencode(path), C.byref(d), None, C.c_size_t(0), C.byref(n)))
+    payload = np.zeros(n.value, np.uint8)
+    check(lib().hkbcn_read_texture(os.fsencode(path), C.byref(d), _ptr(payload), C.c_size_t(n.value), C.byref(n)))
+    return d, payload
+
+
+def import_batch(jobs):
+    """jobs: list of dicts {fmt, level0, width, height, mips(bool), cfg(MipConfig or None), flags, out_path or None}
+    -> list of compressed chains (ndarray)"""
+    arr = (ImportJob * len(jobs))()
+    keep, outs = [], []
+    for i, j in enumerate(jobs):
+        src = np.ascontiguousarray(j["level0"])
+        mips = lib().hkbcn_calc_num_mips(j["width"], j["height"]) if j.get("mips") else 1
+        dst = np.zeros(lib().hkbcn_chain_bytes(j["fmt"], j["width"], j["height"], 1, mips), np.uint8)
+        keep.append(src)
+        outs.append(dst)
+        cfg = j.get("cfg") or MipConfig()
+        path = os.fsencode(j["out_path"]) if j.get("out_path") else None
+        arr[i] = ImportJob(j["fmt"], j["width"], j["height"], 1 if j.get("mips") else 0, cfg, j.get("flags", 0),
+                           src.ctypes.data, path, dst.ctypes.data, 0)
+    check(lib().hkbcn_import_batch(arr, C.c_size_t(len(jobs))))
+    for i in range(len(jobs)):
+        if arr[i].status:
+            raise HkbcnError(f"import job {i} failed with status {arr[i].status}")
+    return outs

@@ -174,6 +174,48 @@ HKBCN_API int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs);
  * of the GPU job i would be sent to.  Greedy longest-processing-time by pixel count x per-format cost weight; deterministic. */
 HKBCN_API int hkbcn_plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job);
 
+/* ---- .texture files and the importer batch -----------
+ * File layout written by the importers: AssetUtils::CreateTexture (Hork/Resources/Resource_Texture.cpp:104-109) =
+ * MakeResourceMagic(RESOURCE_TEXTURE = 4, Version = 1) (ResourceBase.h:72-75: 'H' 'k' type version) followed by
+ * ImageStorage::Write (Hork/Image/Image.cpp:833-844): u8 type, u32 width, u32 height, u32 depth / slice count,
+ * u32 mip count, u8 format, u32 flags, u32 payload size, payload.  All integers little-endian
+ * (Core/BinaryStream.h:408-412).  30 header bytes.  These three entry points are host-only (no device needed). */
+#define HKBCN_TEXTURE_HEADER_BYTES 30
+#define HKBCN_TEXTURE_2D 2            /* TEXTURE_TYPE (Image.h:40-51) */
+#define HKBCN_TEXTURE_CUBE 5
+#define HKBCN_STORAGE_NO_ALPHA 1      /* IMAGE_STORAGE_FLAGS (Image.h:221-226) */
+#define HKBCN_STORAGE_ALPHA_PREMULTIPLIED 2
+typedef struct hkbcn_texture_desc {
+    int      type;          /* TEXTURE_TYPE */
+    uint32_t width, height;
+    uint32_t depth;         /* depth or slice count: 1 for 2D, 6 for a cube */
+    uint32_t num_mips;
+    int      fmt;           /* TEXTURE_FORMAT = enum hkbcn_format */
+    uint32_t storage_flags; /* IMAGE_STORAGE_FLAGS */
+} hkbcn_texture_desc;
+HKBCN_API int hkbcn_texture_header(const hkbcn_texture_desc* desc, uint32_t payload_bytes, void* dst30);
+HKBCN_API int hkbcn_write_texture(const char* path, const hkbcn_texture_desc* desc, const void* payload, size_t payload_bytes);
+/* payload may be NULL (header only); *payload_bytes receives the stored size, at most `capacity` bytes are copied */
+HKBCN_API int hkbcn_read_texture(const char* path, hkbcn_texture_desc* desc, void* payload, size_t capacity, size_t* payload_bytes);
+
+/* One texture of an import batch: what one run of Tools/TextureImporter does (Main.cpp:58-253 -> CreateImage, Image.cpp:1700-1803),
+ * from level 0 already in memory to the .texture file.  File decoding (stb_image / tinyexr / webp) stays with the caller.
+ * generate_mips: 0 = level 0 only (no -mip_* flag given), 1 = full chain with `mip` (zeroes = the importer's defaults). */
+typedef struct hkbcn_import_job {
+    int              fmt;
+    uint32_t         width, height;   /* multiples of 4; powers of two when generate_mips (Image.cpp:415-416) */
+    int              generate_mips;
+    hkbcn_mip_config mip;             /* no_alpha / alpha_premultiplied are also stored as the file's IMAGE_STORAGE_FLAGS */
+    uint32_t         flags;           /* HKBCN_FLAG_* for the source texels */
+    const void*      src_level0;      /* host */
+    const char*      out_path;        /* .texture file to write; NULL = keep the chain in `dst` only */
+    void*            dst;             /* optional host buffer for the compressed chain (hkbcn_chain_bytes), may be NULL */
+    int              status;          /* out */
+} hkbcn_import_job;
+/* Jobs are sharded over the selected GPUs as in hkbcn_compress_batch (whole textures, no collective); each GPU's worker runs
+ * upload -> mip cascade -> encode -> download, and the files are written by a separate thread behind it. */
+HKBCN_API int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs);
+
 /* ---- instrumentation --------------------------------------------------------
  * Number of kernels this library launched since init (bench.py's gpu_launches). */
 HKBCN_API uint64_t hkbcn_launch_count(void);

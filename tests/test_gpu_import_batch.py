@@ -1,0 +1,76 @@
+"""Row f2: hkbcn_import_batch = what one TextureImporter run per texture does (Tools/TextureImporter/Main.cpp:58-253 ->
+CreateImage, Hork/Image/Image.cpp:1700-1803 -> AssetUtils::CreateTexture), as one sharded batch.  The files must be the
+bytes the reference's writer would produce around the chain (oracle restatement in test_texture_file_cpu.py), the
+chain must be hkbcn_import_chain's, and where the whole pipeline is deterministic integer work (BC4 / BC5: linear uint8
+cascade, bit-exact encoders) the file must equal the one built from the reference's own stbir + rgbcx chain."""
+import numpy as np
+import pytest
+
+import hkbcn
+import refshim
+import synth
+from test_gpu_mips import ref_cascade
+from test_texture_file_cpu import oracle_texture_file
+
+pytestmark = pytest.mark.gpu
+BC1S, BC3, BC4, BC5, BC7 = 55, 58, 60, 62, 66
+
+
+def _jobs(tmp_path):
+    tri_wrap = hkbcn.MipConfig(3, 2, 0, 0)  # normal / roughness maps are mipped with the triangle filter (Image.cpp:2359, :2463)
+    return [
+        dict(fmt=BC4, level0=synth.roughness_r8(512, 512, 2).reshape(512, 512, 1), width=512, height=512, mips=True, cfg=tri_wrap,
+             out_path=str(tmp_path / "rough.texture")),
+        dict(fmt=BC5, level0=synth.normals_rg8(256, 128, 3).reshape(128, 256, 2), width=256, height=128, mips=True, cfg=tri_wrap,
+             out_path=str(tmp_path / "normal.texture")),
+        dict(fmt=BC1S, level0=synth.albedo_rgba8(256, 256, 0xB2000001, "opaque").reshape(256, 256, 4), width=256, height=256, mips=True,
+             cfg=None, out_path=str(tmp_path / "albedo.texture")),
+        dict(fmt=BC7, level0=synth.albedo_rgba8(128, 128, 0xB2000004, "opaque").reshape(128, 128, 4), width=128, height=128, mips=False,
+             cfg=None, out_path=str(tmp_path / "albedo7.texture")),
+        dict(fmt=BC3, level0=synth.albedo_rgba8(64, 64, 0xB2000005, "mask").reshape(64, 64, 4), width=64, height=64, mips=False,
+             cfg=hkbcn.MipConfig(0, 0, 0, 1), out_path=str(tmp_path / "decal.texture")),
+        dict(fmt=BC4, level0=synth.roughness_r8(64, 64, 9).reshape(64, 64, 1), width=64, height=64, mips=False, cfg=None, out_path=None),
+    ]
+
+
+def test_batch_writes_the_importers_files(tmp_path):
+    jobs = _jobs(tmp_path)
+    chains = hkbcn.import_batch(jobs)
+    assert len(chains) == len(jobs)
+    for j, chain in zip(jobs, chains):
+        w, h, fmt = j["width"], j["height"], j["fmt"]
+        mips = hkbcn.lib().hkbcn_calc_num_mips(w, h) if j["mips"] else 1
+        # the chain is the single-texture entry point's, byte for byte
+        assert np.array_equal(chain, hkbcn.import_chain(fmt, j["level0"], w, h, mips, j["cfg"]))
+        if j["out_path"] is None:
+            continue
+        cfg = j["cfg"] or hkbcn.MipConfig()
+        flags = (1 if cfg.no_alpha else 0) | (2 if cfg.alpha_premultiplied else 0)
+        raw = open(j["out_path"], "rb").read()
+        assert raw == oracle_texture_file(2, w, h, 1, mips, fmt, flags, chain.tobytes())
+        d, payload = hkbcn.read_texture(j["out_path"])
+        assert (d.type, d.width, d.height, d.depth, d.num_mips, d.fmt, d.storage_flags) == (2, w, h, 1, mips, fmt, flags)
+        assert payload.nbytes == hkbcn.lib().hkbcn_chain_bytes(fmt, w, h, 1, mips)
+
+
+@pytest.mark.parametrize("which", [0, 1])
+def test_bc4_bc5_files_equal_the_reference_pipeline(tmp_path, which):
+    """stbir cascade (triangle, wrap) + rgbcx encode_bc4_hq / bc5_hq of every level, wrapped by the reference writer"""
+    j = _jobs(tmp_path)[which]
+    w, h, fmt = j["width"], j["height"], j["fmt"]
+    mips = hkbcn.lib().hkbcn_calc_num_mips(w, h)
+    hkbcn.import_batch([j])
+    levels = ref_cascade(j["level0"], mips, -1, False, edge=3, filt=2)
+    ref_chain = np.concatenate([refshim.compress(fmt, lv, lv.shape[1], lv.shape[0]) for lv in levels])
+    raw = np.frombuffer(open(j["out_path"], "rb").read(), np.uint8)
+    want = np.frombuffer(oracle_texture_file(2, w, h, 1, mips, fmt, 0, ref_chain.tobytes()), np.uint8)
+    assert raw.size == want.size
+    assert np.array_equal(raw[:30], want[:30])
+    # level 0 never passes through the resampler: byte-identical.  Mips: the cascade's contract is +-1 LSB, so blocks may
+    # differ where a texel did; report how many and bound it.
+    bb = 8 if fmt == BC4 else 16
+    n0 = (w // 4) * (h // 4) * bb
+    assert np.array_equal(raw[30:30 + n0], want[30:30 + n0])
+    diff_blocks = np.any((raw[30:] != want[30:]).reshape(-1, bb), axis=1)
+    print(f"fmt {fmt}: {diff_blocks.sum()} of {diff_blocks.size} blocks differ from the reference pipeline's file")
+    assert diff_blocks.mean() < 0.02
