@@ -53,6 +53,14 @@ struct Device {
     uint32_t*    sched = nullptr;
     std::atomic<uint32_t> sched_seq{0};
     static constexpr uint32_t SCHED_SLOTS = 256;
+    // hkbcn_import_batch: two pipeline slots, each with its own stream, device buffers and pinned staging, so the upload of
+    // texture i + 1 and the download of texture i - 1 overlap the kernels of texture i
+    struct Slot {
+        cudaStream_t st = nullptr;
+        void *d_src = nullptr, *d_dst = nullptr, *h_src = nullptr, *h_dst = nullptr;
+        size_t dsc = 0, ddc = 0, hsc = 0, hdc = 0;
+    } slots[2];
+    std::mutex   batch_mu;
 };
 
 std::mutex            g_mu;
@@ -129,6 +137,22 @@ int grow(void** p, size_t* cap, size_t need)
     CK(cudaMalloc(p, want));
     *cap = want;
     return HKBCN_OK;
+}
+
+int grow_pinned(void** p, size_t* cap, size_t need)
+{
+    if (*cap >= need) return HKBCN_OK;
+    if (*p) { cudaFreeHost(*p); *p = nullptr; *cap = 0; }
+    size_t want = std::max(need, (size_t)1 << 20);
+    CK(cudaHostAlloc(p, want, cudaHostAllocPortable));
+    *cap = want;
+    return HKBCN_OK;
+}
+bool is_pinned(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
 }
 
 // Append one surface to a launch descriptor.
@@ -288,6 +312,13 @@ void hkbcn_shutdown(void)
         if (D->lut_srgb) cudaFree(D->lut_srgb);
         if (D->lut_lin) cudaFree(D->lut_lin);
         if (D->sched) cudaFree(D->sched);
+        for (auto& sl : D->slots) {
+            if (sl.d_src) cudaFree(sl.d_src);
+            if (sl.d_dst) cudaFree(sl.d_dst);
+            if (sl.h_src) cudaFreeHost(sl.h_src);
+            if (sl.h_dst) cudaFreeHost(sl.h_dst);
+            if (sl.st) cudaStreamDestroy(sl.st);
+        }
         for (auto& kv : D->taps) { cudaFree(kv.second.idx); cudaFree(kv.second.w); }
         D->taps.clear();
         if (D->stream) cudaStreamDestroy(D->stream);
@@ -761,29 +792,79 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
     std::vector<std::thread> th;
     for (size_t dv = 0; dv < nd; dv++) {
         th.emplace_back([&, dv]() {
-            for (size_t idx : bins[dv]) {
-                hkbcn_import_job& j = jobs[idx];
-                const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
-                const size_t bytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips);
-                Done d{idx, {}, nullptr, bytes, mips};
-                void* out = j.dst;
-                if (!out) {
-                    d.own.resize(bytes);
-                    out = d.own.data();
-                }
-                j.status = import_host_on(g_devs[dv], j.fmt, j.src_level0, out, j.width, j.height, mips, &j.mip, j.flags);
-                if (j.status) {
-                    if (!first_err[dv]) { first_err[dv] = j.status; err_msg[dv] = t_err; }
-                    continue;
-                }
-                if (!j.out_path) continue;
-                d.data = out;
+            Device* D = g_devs[dv];
+            std::lock_guard<std::mutex> blk(D->batch_mu);
+            auto fail = [&](hkbcn_import_job& j, int rc) {
+                j.status = rc;
+                if (!first_err[dv]) { first_err[dv] = rc; err_msg[dv] = t_err; }
+            };
+            struct InFlight { long idx = -1; Done d; void* out = nullptr; bool staged = false; } fl[2];
+            // wait for a slot's texture, move its chain out of the staging buffer and queue the file
+            auto retire = [&](int s) {
+                InFlight& f = fl[s];
+                if (f.idx < 0) return;
+                hkbcn_import_job& j = jobs[(size_t)f.idx];
+                const cudaError_t e = cudaStreamSynchronize(D->slots[s].st);
+                f.idx = -1;
+                if (e != cudaSuccess) { set_err("import batch: %s", cudaGetErrorString(e)); fail(j, HKBCN_ERR_CUDA); return; }
+                if (f.staged) memcpy(f.out, D->slots[s].h_dst, f.d.bytes);
+                if (!j.out_path) return;
+                f.d.data = f.out;
                 {
                     std::lock_guard<std::mutex> lk(qmu);
-                    queue.push_back(std::move(d));
+                    queue.push_back(std::move(f.d));
                 }
                 qcv.notify_one();
+            };
+            auto submit = [&](int s, size_t idx) -> int {
+                hkbcn_import_job& j = jobs[idx];
+                Device::Slot& S = D->slots[s];
+                int rc;
+                const int codec = codec_of(j.fmt);
+                if (codec < 0) { set_err("bad format %d", j.fmt); return HKBCN_ERR_BAD_FORMAT; }
+                if ((j.width & 3) || (j.height & 3) || !j.width || !j.height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+                if (!j.src_level0) { set_err("null source"); return HKBCN_ERR_BAD_ARG; }
+                const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
+                const size_t sbytes = chain_src_bytes(codec, j.flags, j.width, j.height, mips);
+                const size_t l0 = (size_t)j.width * j.height * src_bpp(codec, j.flags);
+                const size_t dbytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips);
+                CK(cudaSetDevice(D->id));
+                if (!S.st) CK(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking));
+                if ((rc = grow(&S.d_src, &S.dsc, sbytes)) != HKBCN_OK) return rc;
+                if ((rc = grow(&S.d_dst, &S.ddc, dbytes)) != HKBCN_OK) return rc;
+                InFlight& f = fl[s];
+                f.d = Done{idx, {}, nullptr, dbytes, mips};
+                f.out = j.dst;
+                if (!f.out) {
+                    f.d.own.resize(dbytes);
+                    f.out = f.d.own.data();
+                }
+                const void* hsrc = j.src_level0;
+                if (!is_pinned(hsrc)) { // pageable memory: stage through pinned so that the copy engine, not this thread, feeds the GPU
+                    if ((rc = grow_pinned(&S.h_src, &S.hsc, l0)) != HKBCN_OK) return rc;
+                    memcpy(S.h_src, hsrc, l0);
+                    hsrc = S.h_src;
+                }
+                f.staged = !is_pinned(f.out);
+                if (f.staged && (rc = grow_pinned(&S.h_dst, &S.hdc, dbytes)) != HKBCN_OK) return rc;
+                CK(cudaMemcpyAsync(S.d_src, hsrc, l0, cudaMemcpyHostToDevice, S.st)); // level 0 only crosses PCIe
+                if (mips > 1 && (rc = generate_mips_on(D, j.fmt, S.d_src, j.width, j.height, mips, &j.mip, j.flags, S.st)) != HKBCN_OK) return rc;
+                EncodeParams P;
+                if ((rc = build_chain(P, codec, j.flags, S.d_src, S.d_dst, j.width, j.height, mips)) != HKBCN_OK) return rc;
+                if ((rc = launch_encode(D, j.fmt, codec, P, S.st)) != HKBCN_OK) return rc;
+                CK(cudaMemcpyAsync(f.staged ? S.h_dst : f.out, S.d_dst, dbytes, cudaMemcpyDeviceToHost, S.st));
+                f.idx = (long)idx;
+                return HKBCN_OK;
+            };
+            int s = 0;
+            for (size_t idx : bins[dv]) {
+                retire(s); // the slot's previous texture (two submissions ago)
+                const int rc = submit(s, idx);
+                if (rc) fail(jobs[idx], rc);
+                s ^= 1;
             }
+            retire(s);
+            retire(s ^ 1);
             {
                 std::lock_guard<std::mutex> lk(qmu);
                 workers_left--;

@@ -1,0 +1,315 @@
+// TextureImporterBatch.cpp -- hk_texture_import: the reference's Tools/TextureImporter (Main.cpp:58-253) as a batch driver
+// over the C ABI (include/hkbcn.h), SURVEY.md 8f row f2.
+//
+// Same flags and meaning as the reference tool for the part of it that is on this path:
+//     -s <file> -o <file> -format <name> [-no_alpha] [-alpha_premult] [-mip_edge_mode <m>] [-mip_filter <f>]
+// and, new, `-batch <manifest>`: a text file with one such flag set per line (`#` comments), imported as ONE sharded batch
+// (hkbcn_import_batch: every texture whole on one GPU, no collective) instead of one process per texture.
+// Giving either -mip_* flag turns mip generation on, as in the reference (Main.cpp:124-143); -format takes the
+// TexFormat[] names of Hork/Image/Image.cpp:105-118.
+//
+// Out of scope (stay on the CPU in the reference): file decoding through stb_image / tinyexr / webp and
+// the -resample pre-pass.  Sources are raw containers that need no decoder: binary PGM / PPM (P5 / P6, 8 bit), PFM
+// (Pf / PF), or `gen:<kind>:<width>:<height>:<seed>` procedural images (kind: albedo, mask, rough, normal, sky).
+// Channel mapping follows CreateImage (Image.cpp:1700-1716): BC1/2/3/7 take RGBA8 (alpha 255 when the file has none), BC4
+// the first channel, BC5 the first two, BC6H RGBA32F.
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <chrono>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include "../../include/hkbcn.h"
+
+namespace {
+
+struct Args {
+    std::string src, out, format;
+    bool no_alpha = false, alpha_premult = false, mips = false;
+    int edge = 0, filter = 0;
+};
+
+struct Pixels {
+    uint32_t w = 0, h = 0;
+    int ch = 0;      // channels in `u8` / `f32`
+    bool is_float = false;
+    std::vector<uint8_t> u8;
+    std::vector<float> f32;
+};
+
+const struct { const char* name; int fmt; } kFormats[] = {
+    {"BC1_UNORM", HKBCN_BC1_UNORM}, {"BC1_UNORM_SRGB", HKBCN_BC1_UNORM_SRGB}, {"BC2_UNORM", HKBCN_BC2_UNORM},
+    {"BC2_UNORM_SRGB", HKBCN_BC2_UNORM_SRGB}, {"BC3_UNORM", HKBCN_BC3_UNORM}, {"BC3_UNORM_SRGB", HKBCN_BC3_UNORM_SRGB},
+    {"BC4_UNORM", HKBCN_BC4_UNORM}, {"BC5_UNORM", HKBCN_BC5_UNORM}, {"BC6H_UFLOAT", HKBCN_BC6H_UFLOAT},
+    {"BC6H_SFLOAT", HKBCN_BC6H_SFLOAT}, {"BC7_UNORM", HKBCN_BC7_UNORM}, {"BC7_UNORM_SRGB", HKBCN_BC7_UNORM_SRGB}};
+
+int find_format(const std::string& n)
+{
+    for (auto& f : kFormats)
+        if (n == f.name) return f.fmt;
+    return -1;
+}
+// GetResampleEdgeMode / GetResampleFilter of the reference tool: names -> IMAGE_RESAMPLE_EDGE_MODE / _FILTER (Image.h:330-347)
+int edge_mode(const std::string& s) { return s == "clamp" ? 1 : s == "reflect" ? 2 : s == "wrap" ? 3 : s == "zero" ? 4 : 0; }
+int filter_of(const std::string& s) { return s == "box" ? 1 : s == "triangle" ? 2 : s == "cubicspline" ? 3 : s == "catmullrom" ? 4 : s == "mitchell" ? 5 : 0; }
+
+bool parse_flags(const std::vector<std::string>& t, Args& a, std::string& err)
+{
+    for (size_t i = 0; i < t.size(); i++) {
+        auto need = [&](int n) { return i + (size_t)n < t.size(); };
+        if (t[i] == "-s" && need(1)) a.src = t[++i];
+        else if (t[i] == "-o" && need(1)) a.out = t[++i];
+        else if (t[i] == "-format" && need(1)) a.format = t[++i];
+        else if (t[i] == "-no_alpha") a.no_alpha = true;
+        else if (t[i] == "-alpha_premult") a.alpha_premult = true;
+        else if (t[i] == "-mip_edge_mode" && need(1)) { a.edge = edge_mode(t[++i]); a.mips = true; }
+        else if (t[i] == "-mip_filter" && need(1)) { a.filter = filter_of(t[++i]); a.mips = true; }
+        else { err = "unknown or incomplete flag '" + t[i] + "'"; return false; }
+    }
+    if (a.out.empty()) { err = "Output file is not specified. Use -o <filename>"; return false; }
+    if (a.src.empty()) { err = "Source file is not specified. Use -s <filename>"; return false; }
+    if (find_format(a.format) < 0) { err = "unknown -format '" + a.format + "'"; return false; }
+    return true;
+}
+
+// ---- sources ----------------------------------------------------------------------------------------------------------
+uint32_t lcg(uint32_t& s) { s = s * 1664525u + 1013904223u; return s >> 8; }
+
+bool generate(const std::string& spec, Pixels& p, std::string& err)
+{
+    // gen:<kind>:<w>:<h>:<seed> -- smooth gradients + value noise, enough to exercise every encoder mode
+    std::vector<std::string> f;
+    std::stringstream ss(spec);
+    for (std::string x; std::getline(ss, x, ':');) f.push_back(x);
+    if (f.size() != 5) { err = "expected gen:<kind>:<w>:<h>:<seed>"; return false; }
+    p.w = (uint32_t)atoi(f[2].c_str());
+    p.h = (uint32_t)atoi(f[3].c_str());
+    uint32_t seed = (uint32_t)strtoul(f[4].c_str(), nullptr, 0) * 2654435761u + 12345u;
+    if (!p.w || !p.h) { err = "bad size in " + spec; return false; }
+    const std::string& kind = f[1];
+    const size_t n = (size_t)p.w * p.h;
+    if (kind == "sky") {
+        p.is_float = true;
+        p.ch = 4;
+        p.f32.resize(n * 4);
+        for (uint32_t y = 0; y < p.h; y++)
+            for (uint32_t x = 0; x < p.w; x++) {
+                const float v = (float)y / p.h, u = (float)x / p.w;
+                const float sun = expf(-60.0f * ((u - 0.7f) * (u - 0.7f) + (v - 0.3f) * (v - 0.3f))) * 40.0f;
+                float* o = &p.f32[((size_t)y * p.w + x) * 4];
+                o[0] = 0.2f + 0.5f * v + sun + (lcg(seed) & 255) / 4096.0f;
+                o[1] = 0.3f + 0.4f * v + sun * 0.9f;
+                o[2] = 0.9f - 0.5f * v + sun * 0.6f;
+                o[3] = 1.0f;
+            }
+        return true;
+    }
+    p.ch = kind == "rough" ? 1 : kind == "normal" ? 2 : 4;
+    if (kind != "rough" && kind != "normal" && kind != "albedo" && kind != "mask") { err = "unknown kind '" + kind + "'"; return false; }
+    p.u8.resize(n * (size_t)p.ch);
+    for (uint32_t y = 0; y < p.h; y++)
+        for (uint32_t x = 0; x < p.w; x++) {
+            uint8_t* o = &p.u8[((size_t)y * p.w + x) * (size_t)p.ch];
+            const float u = (float)x / p.w, v = (float)y / p.h;
+            const int nz = (int)(lcg(seed) & 15);
+            if (p.ch == 1) o[0] = (uint8_t)(128 + 100 * sinf(20 * u) * cosf(14 * v) + nz);
+            else if (p.ch == 2) { o[0] = (uint8_t)(128 + 90 * sinf(31 * u + 3 * v)); o[1] = (uint8_t)(128 + 90 * cosf(27 * v - 2 * u)); }
+            else {
+                o[0] = (uint8_t)(40 + 180 * u + nz);
+                o[1] = (uint8_t)(60 + 150 * v + nz);
+                o[2] = (uint8_t)(128 + 100 * sinf(25 * (u + v)));
+                o[3] = kind == "mask" ? (uint8_t)((((x >> 4) ^ (y >> 4)) & 1) ? 255 : (16 * ((x + y) & 15))) : 255;
+            }
+        }
+    return true;
+}
+
+bool read_pnm(const std::string& path, Pixels& p, std::string& err)
+{
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) { err = "Failed to load " + path; return false; }
+    char magic[3] = {0, 0, 0};
+    auto token = [&](std::string& out) {
+        out.clear();
+        int c;
+        for (;;) {
+            c = fgetc(f);
+            if (c == '#') { while (c != '\n' && c != EOF) c = fgetc(f); continue; }
+            if (c == EOF || !isspace(c)) break;
+        }
+        while (c != EOF && !isspace(c)) { out.push_back((char)c); c = fgetc(f); }
+        return !out.empty();
+    };
+    std::string t;
+    bool ok = fread(magic, 1, 2, f) == 2;
+    const std::string m(magic);
+    if (ok && (m == "P5" || m == "P6")) {
+        std::string a, b, c;
+        ok = token(a) && token(b) && token(c);
+        p.w = (uint32_t)atoi(a.c_str());
+        p.h = (uint32_t)atoi(b.c_str());
+        p.ch = m == "P5" ? 1 : 3;
+        ok = ok && atoi(c.c_str()) == 255 && p.w && p.h;
+        if (ok) {
+            p.u8.resize((size_t)p.w * p.h * (size_t)p.ch);
+            ok = fread(p.u8.data(), 1, p.u8.size(), f) == p.u8.size();
+        }
+    } else if (ok && (m == "Pf" || m == "PF")) {
+        std::string a, b, c;
+        ok = token(a) && token(b) && token(c);
+        p.w = (uint32_t)atoi(a.c_str());
+        p.h = (uint32_t)atoi(b.c_str());
+        p.ch = m == "Pf" ? 1 : 3;
+        p.is_float = true;
+        const double scale = atof(c.c_str());
+        ok = ok && scale < 0 && p.w && p.h; // little-endian files only
+        if (ok) {
+            std::vector<float> rows((size_t)p.w * p.h * (size_t)p.ch);
+            ok = fread(rows.data(), 4, rows.size(), f) == rows.size();
+            p.f32.resize(rows.size());
+            const size_t rb = (size_t)p.w * (size_t)p.ch;
+            for (uint32_t y = 0; y < p.h && ok; y++) // PFM stores the bottom row first
+                memcpy(&p.f32[(size_t)y * rb], &rows[(size_t)(p.h - 1 - y) * rb], rb * 4);
+        }
+    } else ok = false;
+    fclose(f);
+    if (!ok) err = "Failed to load " + path + " (binary P5 / P6 with maxval 255, or little-endian Pf / PF expected)";
+    return ok;
+}
+
+// source texels for `fmt` (hkbcn_src_texel_bytes): RGBA8 / R8 / RG8 / RGBA32F
+// (pinned host memory: the batch then uploads straight from it with the copy engine)
+bool to_source(const Pixels& p, int fmt, uint8_t*& out, std::string& err)
+{
+    const size_t n = (size_t)p.w * p.h;
+    const int bpp = hkbcn_src_texel_bytes(fmt, 0);
+    out = (uint8_t*)hkbcn_alloc_pinned(n * (size_t)bpp);
+    if (!out) { err = hkbcn_last_error(); return false; }
+    if (bpp == 16) {
+        if (!p.is_float) { err = "BC6H needs a float source (PFM or gen:sky)"; return false; }
+        float* o = (float*)out;
+        for (size_t i = 0; i < n; i++)
+            for (int c = 0; c < 4; c++) o[i * 4 + c] = c < p.ch ? p.f32[i * (size_t)p.ch + c] : (c == 3 ? 1.0f : (p.ch == 1 ? p.f32[i] : 0.0f));
+        return true;
+    }
+    if (p.is_float) { err = "an 8-bit format needs an 8-bit source"; return false; }
+    const int oc = bpp; // 1, 2 or 4 channels of one byte
+    for (size_t i = 0; i < n; i++)
+        for (int c = 0; c < oc; c++) {
+            uint8_t v;
+            if (c < p.ch) v = p.u8[i * (size_t)p.ch + c];
+            else if (c == 3) v = 255;
+            else v = p.ch == 1 ? p.u8[i] : 0; // grey -> RGB
+            out[i * (size_t)oc + c] = v;
+        }
+    return true;
+}
+
+std::vector<std::string> split_ws(const std::string& line)
+{
+    std::vector<std::string> t;
+    std::stringstream ss(line);
+    for (std::string x; ss >> x;) t.push_back(x);
+    return t;
+}
+
+const char* kHelp = R"(hk_texture_import -- BCn texture import on the GPU (libhkbcn)
+    -h                      -- Help
+    -s <filename>           -- Source: binary PGM/PPM (P5/P6), PFM (Pf/PF) or gen:<albedo|mask|rough|normal|sky>:<w>:<h>:<seed>
+    -o <filename>           -- Output .texture file
+    -no_alpha               -- Don't aware about alpha channel or ignore it
+    -alpha_premult          -- Set this flag if your texture has premultiplied alpha
+    -format <name>          -- Output texture format: BC1_UNORM[_SRGB] BC2_.. BC3_.. BC4_UNORM BC5_UNORM BC6H_UFLOAT BC6H_SFLOAT BC7_UNORM[_SRGB]
+    -mip_edge_mode <mode>   -- clamp | reflect | wrap | zero          (giving either -mip_* flag generates the mip chain)
+    -mip_filter <filter>    -- box | triangle | cubicspline | catmullrom | mitchell
+    -batch <manifest>       -- one flag set per line; all lines are imported as one batch sharded over the GPUs
+    -gpus <mask>            -- bit mask of the CUDA devices to use (default: all)
+)";
+
+} // namespace
+
+int main(int argc, char** argv)
+{
+    std::vector<std::string> argvv(argv + 1, argv + argc);
+    std::vector<Args> all;
+    uint32_t mask = 0;
+    std::vector<std::string> single;
+    for (size_t i = 0; i < argvv.size(); i++) {
+        if (argvv[i] == "-h") { fputs(kHelp, stdout); return 0; }
+        if (argvv[i] == "-gpus" && i + 1 < argvv.size()) { mask = (uint32_t)strtoul(argvv[++i].c_str(), nullptr, 0); continue; }
+        if (argvv[i] == "-batch" && i + 1 < argvv.size()) {
+            std::ifstream mf(argvv[++i]);
+            if (!mf) { fprintf(stderr, "Failed to open manifest %s\n", argvv[i].c_str()); return -1; }
+            int ln = 0;
+            for (std::string line; std::getline(mf, line);) {
+                ln++;
+                const size_t hash = line.find('#');
+                if (hash != std::string::npos) line.resize(hash);
+                const auto t = split_ws(line);
+                if (t.empty()) continue;
+                Args a;
+                std::string err;
+                if (!parse_flags(t, a, err)) { fprintf(stderr, "%s:%d: %s\n", argvv[i].c_str(), ln, err.c_str()); return -1; }
+                all.push_back(a);
+            }
+            continue;
+        }
+        single.push_back(argvv[i]);
+    }
+    if (!single.empty()) {
+        Args a;
+        std::string err;
+        if (!parse_flags(single, a, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        all.push_back(a);
+    }
+    if (all.empty()) { fputs(kHelp, stdout); return -1; }
+    if (hkbcn_init(mask) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+
+    std::vector<uint8_t*> sources(all.size(), nullptr);
+    std::vector<hkbcn_import_job> jobs(all.size());
+    double mpix = 0;
+    for (size_t i = 0; i < all.size(); i++) {
+        const Args& a = all[i];
+        Pixels p;
+        std::string err;
+        printf("Loading %s...\n", a.src.c_str());
+        const bool ok = a.src.rfind("gen:", 0) == 0 ? generate(a.src, p, err) : read_pnm(a.src, p, err);
+        const int fmt = find_format(a.format);
+        if (!ok || !to_source(p, fmt, sources[i], err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        // CalcNumMips / ImageStorage (Image.cpp:203-204, :415-416)
+        if ((p.w & 3) || (p.h & 3)) { fprintf(stderr, "%s: width and height must be multiples of the block size 4\n", a.src.c_str()); return -1; }
+        if (a.mips && ((p.w & (p.w - 1)) || (p.h & (p.h - 1)))) {
+            fprintf(stderr, "%s: width and height must be powers of two for compressed mipmapped textures\n", a.src.c_str());
+            return -1;
+        }
+        hkbcn_import_job& j = jobs[i];
+        memset(&j, 0, sizeof(j));
+        j.fmt = fmt;
+        j.width = p.w;
+        j.height = p.h;
+        j.generate_mips = a.mips ? 1 : 0;
+        j.mip.edge_mode = a.edge;
+        j.mip.filter = a.filter;
+        j.mip.no_alpha = a.no_alpha ? 1 : 0;
+        j.mip.alpha_premultiplied = a.alpha_premult ? 1 : 0;
+        j.src_level0 = sources[i];
+        j.out_path = a.out.c_str();
+        mpix += (double)p.w * p.h * (a.mips ? 4.0 / 3.0 : 1.0) / 1e6;
+    }
+    for (auto& a : all) printf("Importing texture %s...\n", a.out.c_str());
+    const auto t0 = std::chrono::steady_clock::now();
+    const int rc = hkbcn_import_batch(jobs.data(), jobs.size());
+    const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (rc != HKBCN_OK) { fprintf(stderr, "import failed: %s\n", hkbcn_last_error()); return -1; }
+    printf("%zu texture(s), %.1f Mpix in %.3f s on %d GPU(s): %.1f Mpix/s including upload, download and file writes\n", jobs.size(), mpix,
+           s, hkbcn_device_count(), mpix / s);
+    for (uint8_t* q : sources) hkbcn_free_pinned(q);
+    hkbcn_shutdown();
+    return 0;
+}

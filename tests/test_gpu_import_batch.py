@@ -74,3 +74,48 @@ def test_bc4_bc5_files_equal_the_reference_pipeline(tmp_path, which):
     diff_blocks = np.any((raw[30:] != want[30:]).reshape(-1, bb), axis=1)
     print(f"fmt {fmt}: {diff_blocks.sum()} of {diff_blocks.size} blocks differ from the reference pipeline's file")
     assert diff_blocks.mean() < 0.02
+
+
+def _write_pnm(path, img):
+    h, w, c = img.shape
+    with open(path, "wb") as f:
+        f.write((b"P5" if c == 1 else b"P6") + f"\n# test\n{w} {h}\n255\n".encode())
+        f.write(np.ascontiguousarray(img).tobytes())
+
+
+def test_importer_tool_batch_manifest(tmp_path):
+    """hk_texture_import -batch: the reference tool's flags per line; files equal the library calls' results"""
+    import os
+    import subprocess
+    tool = os.path.join(os.path.dirname(hkbcn.LIB_PATH), "hk_texture_import")
+    assert os.path.exists(tool), "hk_texture_import not built (python __graft_entry__.py build)"
+    rough = synth.roughness_r8(256, 256, 2).reshape(256, 256, 1)
+    albedo = synth.albedo_rgba8(128, 64, 0xB2000001, "opaque").reshape(64, 128, 4)
+    _write_pnm(tmp_path / "rough.pgm", rough)
+    _write_pnm(tmp_path / "albedo.ppm", albedo[:, :, :3])
+    manifest = tmp_path / "batch.txt"
+    manifest.write_text(
+        f"# roughness: mipped with the triangle filter\n"
+        f"-s {tmp_path}/rough.pgm -o {tmp_path}/rough.texture -format BC4_UNORM -mip_filter triangle -mip_edge_mode wrap\n"
+        f"-s {tmp_path}/albedo.ppm -o {tmp_path}/albedo.texture -format BC1_UNORM_SRGB -no_alpha -mip_filter mitchell\n"
+        f"-s {tmp_path}/albedo.ppm -o {tmp_path}/albedo7.texture -format BC7_UNORM   # no mips\n"
+        f"-s gen:sky:64:64:3 -o {tmp_path}/sky.texture -format BC6H_UFLOAT\n")
+    r = subprocess.run([tool, "-batch", str(manifest)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    rgba = np.concatenate([albedo[:, :, :3], np.full((64, 128, 1), 255, np.uint8)], axis=2)
+    d, p = hkbcn.read_texture(str(tmp_path / "rough.texture"))
+    m4 = hkbcn.lib().hkbcn_calc_num_mips(256, 256)
+    assert (d.fmt, d.width, d.height, d.num_mips, d.storage_flags) == (BC4, 256, 256, m4, 0)
+    assert np.array_equal(p, hkbcn.import_chain(BC4, rough, 256, 256, m4, hkbcn.MipConfig(3, 2, 0, 0)))
+    d, p = hkbcn.read_texture(str(tmp_path / "albedo.texture"))
+    m1 = hkbcn.lib().hkbcn_calc_num_mips(128, 64)
+    assert (d.fmt, d.width, d.height, d.num_mips, d.storage_flags) == (BC1S, 128, 64, m1, 1)
+    assert np.array_equal(p, hkbcn.import_chain(BC1S, rgba, 128, 64, m1, hkbcn.MipConfig(0, 5, 1, 0)))
+    d, p = hkbcn.read_texture(str(tmp_path / "albedo7.texture"))
+    assert (d.fmt, d.num_mips) == (BC7, 1)
+    assert np.array_equal(p, hkbcn.compress(BC7, rgba, 128, 64))
+    d, p = hkbcn.read_texture(str(tmp_path / "sky.texture"))
+    assert (d.fmt, d.width, d.num_mips, p.nbytes) == (64, 64, 1, 16 * 16 * 16)
+    # the reference tool's error behaviour: a missing output name is an error before any work
+    r = subprocess.run([tool, "-s", "gen:albedo:64:64:1", "-format", "BC7_UNORM"], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "Output file is not specified" in r.stderr
