@@ -679,6 +679,188 @@ int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
     return HKBCN_OK;
 }
 
+// ---- normal maps and roughness (row f4) -------------------------------------------------------------------------------
+int hkbcn_pack_texel_bytes(int variant)
+{
+    if (variant == NP_RGBA_BC1 || variant == NP_RGBA_BC3) return 4;
+    if (variant >= NP_RG_BC5 && variant <= NP_PARABOLOID_BC5) return 2;
+    return -1;
+}
+
+#define DEV_OR_RETURN(D, device)                                                                   \
+    {                                                                                              \
+        const int rc_ = ensure_init();                                                             \
+        if (rc_) return rc_;                                                                       \
+    }                                                                                              \
+    Device* D = dev_at(device);                                                                    \
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+
+int hkbcn_pack_normals_dev(int device, int variant, const float* d_n, void* d_dst, size_t count, void* stream)
+{
+    DEV_OR_RETURN(D, device)
+    if (hkbcn_pack_texel_bytes(variant) < 0) { set_err("bad normal-map packing %d", variant); return HKBCN_ERR_BAD_ARG; }
+    if (count == 0) return HKBCN_OK;
+    CK(cudaSetDevice(D->id));
+    CK(launch_pack_normals(variant, d_n, (uint8_t*)d_dst, count, (cudaStream_t)stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+int hkbcn_unpack_normals_dev(int device, int variant, const void* d_src, float* d_n, size_t count, void* stream)
+{
+    DEV_OR_RETURN(D, device)
+    if (hkbcn_pack_texel_bytes(variant) < 0) { set_err("bad normal-map packing %d", variant); return HKBCN_ERR_BAD_ARG; }
+    if (count == 0) return HKBCN_OK;
+    CK(cudaSetDevice(D->id));
+    CK(launch_unpack_normals(variant, (const uint8_t*)d_src, d_n, count, (cudaStream_t)stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+int hkbcn_normalize_vectors_dev(int device, float* d_v, size_t count, void* stream)
+{
+    DEV_OR_RETURN(D, device)
+    if (count == 0) return HKBCN_OK;
+    CK(cudaSetDevice(D->id));
+    CK(launch_normalize_vectors(d_v, count, (cudaStream_t)stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+size_t hkbcn_bake_scratch_bytes(uint32_t width, uint32_t height)
+{
+    // two ping-pong images of averaged normals: level 1 and level 2 sizes
+    return 12 * ((size_t)mip_dim(width, 1) * mip_dim(height, 1) + (size_t)mip_dim(width, 2) * mip_dim(height, 2));
+}
+
+static int bake_roughness_on(Device* D, const float* d_n, uint8_t* d_rough, void* d_scratch, uint32_t w, uint32_t h, uint32_t mips, int bake,
+                             int filter, int edge, cudaStream_t st)
+{
+    if (bake != HKBCN_ROUGHNESS_BAKE_VMF && bake != HKBCN_ROUGHNESS_BAKE_TOKSVIG) { set_err("bad roughness bake %d", bake); return HKBCN_ERR_BAD_ARG; }
+    if (!filter) filter = 2; // NormalMapResampleFilter = triangle (Image.cpp:2359)
+    if (!edge) edge = 3;
+    if (edge < 1 || edge > 4 || filter < 1 || filter > 5) { set_err("bad edge mode %d / filter %d", edge, filter); return HKBCN_ERR_BAD_ARG; }
+    if (mips == 0 || mips > HKBCN_MAX_LEVELS || !w || !h) { set_err("bad chain %u x %u, %u mips", w, h, mips); return HKBCN_ERR_BAD_ARG; }
+    uint8_t* a = (uint8_t*)d_scratch;
+    uint8_t* b = a + 12 * (size_t)mip_dim(w, 1) * mip_dim(h, 1);
+    const uint8_t* src = (const uint8_t*)d_n;
+    uint8_t* rough = d_rough + (size_t)w * h;
+    for (uint32_t i = 1; i < mips; i++) {
+        const uint32_t iw = mip_dim(w, i - 1), ih = mip_dim(h, i - 1), ow = mip_dim(w, i), oh = mip_dim(h, i);
+        uint8_t* dst = (i & 1) ? a : b;
+        Device::Taps tx, ty;
+        int rc;
+        if ((rc = get_taps(D, (int)iw, (int)ow, filter, edge, tx)) != HKBCN_OK) return rc;
+        if ((rc = get_taps(D, (int)ih, (int)oh, filter, edge, ty)) != HKBCN_OK) return rc;
+        ResizeParams P;
+        P.src = src; P.dst = dst;
+        P.ix = tx.idx; P.wx = tx.w; P.iy = ty.idx; P.wy = ty.w;
+        P.lut = D->lut_lin;
+        P.in_w = (int)iw; P.in_h = (int)ih; P.out_w = (int)ow; P.out_h = (int)oh; P.Tx = tx.T; P.Ty = ty.T;
+        P.alpha = -1; P.weight = 0; P.srgb = 0;
+        CK(launch_mip_resize(P, 3, true, st));
+        CK(launch_roughness_bake(bake, (const float*)dst, rough, (size_t)ow * oh, st));
+        g_launches.fetch_add(2, std::memory_order_relaxed);
+        src = dst;
+        rough += (size_t)ow * oh;
+    }
+    return HKBCN_OK;
+}
+
+int hkbcn_bake_roughness_dev(int device, const float* d_n, uint8_t* d_rough, void* d_scratch, uint32_t w, uint32_t h, uint32_t mips, int bake,
+                             int filter, int edge, void* stream)
+{
+    DEV_OR_RETURN(D, device)
+    CK(cudaSetDevice(D->id));
+    return bake_roughness_on(D, d_n, d_rough, d_scratch, w, h, mips, bake, filter, edge, (cudaStream_t)stream);
+}
+
+// host-pointer forms: device 0's scratch buffers, synchronous
+static int with_scratch(Device* D, size_t in_bytes, size_t out_bytes)
+{
+    int rc;
+    CK(cudaSetDevice(D->id));
+    if ((rc = grow(&D->d_src, &D->src_cap, in_bytes)) != HKBCN_OK) return rc;
+    return grow(&D->d_dst, &D->dst_cap, out_bytes);
+}
+
+int hkbcn_pack_normals(int variant, const float* n, void* dst, size_t count)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int tb = hkbcn_pack_texel_bytes(variant);
+    if (tb < 0) { set_err("bad normal-map packing %d", variant); return HKBCN_ERR_BAD_ARG; }
+    if (count == 0) return HKBCN_OK;
+    if (!n || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    if ((rc = with_scratch(D, count * 12, count * (size_t)tb)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, n, count * 12, cudaMemcpyHostToDevice, D->stream));
+    CK(launch_pack_normals(variant, (const float*)D->d_src, (uint8_t*)D->d_dst, count, D->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CK(cudaMemcpyAsync(dst, D->d_dst, count * (size_t)tb, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_unpack_normals(int variant, const void* src, float* n, size_t count)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int tb = hkbcn_pack_texel_bytes(variant);
+    if (tb < 0) { set_err("bad normal-map packing %d", variant); return HKBCN_ERR_BAD_ARG; }
+    if (count == 0) return HKBCN_OK;
+    if (!n || !src) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    if ((rc = with_scratch(D, count * (size_t)tb, count * 12)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src, count * (size_t)tb, cudaMemcpyHostToDevice, D->stream));
+    CK(launch_unpack_normals(variant, (const uint8_t*)D->d_src, (float*)D->d_dst, count, D->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CK(cudaMemcpyAsync(n, D->d_dst, count * 12, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_normalize_vectors(float* v, size_t count)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (count == 0) return HKBCN_OK;
+    if (!v) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    if ((rc = with_scratch(D, count * 12, 0)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, v, count * 12, cudaMemcpyHostToDevice, D->stream));
+    CK(launch_normalize_vectors((float*)D->d_src, count, D->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CK(cudaMemcpyAsync(v, D->d_src, count * 12, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_bake_roughness(const float* n, uint8_t* rough, uint32_t w, uint32_t h, uint32_t mips, int bake, int filter, int edge)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (!n || !rough) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    if (mips == 0 || mips > HKBCN_MAX_LEVELS || !w || !h) { set_err("bad chain %u x %u, %u mips", w, h, mips); return HKBCN_ERR_BAD_ARG; }
+    size_t rbytes = 0;
+    for (uint32_t i = 0; i < mips; i++) rbytes += (size_t)mip_dim(w, i) * mip_dim(h, i);
+    const size_t nbytes = (size_t)w * h * 12, sbytes = hkbcn_bake_scratch_bytes(w, h);
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    // d_src: normals followed by the scratch; d_dst: the roughness chain
+    if ((rc = with_scratch(D, nbytes + sbytes + 256, rbytes)) != HKBCN_OK) return rc;
+    uint8_t* scratch = (uint8_t*)D->d_src + ((nbytes + 255) & ~(size_t)255);
+    CK(cudaMemcpyAsync(D->d_src, n, nbytes, cudaMemcpyHostToDevice, D->stream));
+    CK(cudaMemcpyAsync(D->d_dst, rough, rbytes, cudaMemcpyHostToDevice, D->stream));
+    if ((rc = bake_roughness_on(D, (const float*)D->d_src, (uint8_t*)D->d_dst, scratch, w, h, mips, bake, filter, edge, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(rough, D->d_dst, rbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
 // ---- .texture files (row f2) ------------------------------------------------------------------------------------------
 static void put_u32(uint8_t* p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
 static uint32_t get_u32(const uint8_t* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }

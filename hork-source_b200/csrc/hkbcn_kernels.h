@@ -54,6 +54,13 @@ struct ResizeParams {
 };
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
 
+// ---- normal-map packers and roughness bake (normal_pack.cu) ------------------
+enum { NP_RGBA_BC1 = 0, NP_RG_BC5 = 1, NP_SPHEREMAP_BC5 = 2, NP_STEREOGRAPHIC_BC5 = 3, NP_PARABOLOID_BC5 = 4, NP_RGBA_BC3 = 5 };
+cudaError_t launch_pack_normals(int variant, const float* d_normals, uint8_t* d_dst, size_t count, cudaStream_t st);
+cudaError_t launch_unpack_normals(int variant, const uint8_t* d_src, float* d_normals, size_t count, cudaStream_t st);
+cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st);
+cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t* d_rough, size_t count, cudaStream_t st);
+
 } // namespace hkbcn
 
 #include <vector>

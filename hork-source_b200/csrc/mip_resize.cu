@@ -203,10 +203,32 @@ __global__ void __launch_bounds__(256) mip_resize_f32_kernel(const ResizeParams 
     ((float4*)P.dst)[(size_t)oy * P.out_w + ox] = acc;
 }
 
+// RGB32F (Float3 normals, 4-byte aligned): the averaged-normal cascade of the roughness bake (Image.cpp:2530-2542)
+__global__ void __launch_bounds__(256) mip_resize_f32x3_kernel(const ResizeParams P)
+{
+    const int ox = blockIdx.x * 32 + (threadIdx.x & 31), oy = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (ox >= P.out_w || oy >= P.out_h) return;
+    float ax = 0, ay = 0, az = 0;
+    for (int ky = 0; ky < P.Ty; ky++) {
+        const float wy = P.wy[oy * P.Ty + ky];
+        const float* row = (const float*)P.src + (size_t)P.iy[oy * P.Ty + ky] * P.in_w * 3;
+        float hx = 0, hy = 0, hz = 0;
+        for (int kx = 0; kx < P.Tx; kx++) {
+            const float wx = P.wx[ox * P.Tx + kx];
+            const float* v = row + (size_t)P.ix[ox * P.Tx + kx] * 3;
+            hx += v[0] * wx; hy += v[1] * wx; hz += v[2] * wx;
+        }
+        ax += hx * wy; ay += hy * wy; az += hz * wy;
+    }
+    float* d = (float*)P.dst + ((size_t)oy * P.out_w + ox) * 3;
+    d[0] = ax; d[1] = ay; d[2] = az;
+}
+
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream)
 {
     const dim3 grid((unsigned)(P.out_w + 31) / 32, (unsigned)(P.out_h + 7) / 8);
-    if (f32) mip_resize_f32_kernel<<<grid, 256, 0, stream>>>(P);
+    if (f32 && channels == 3) mip_resize_f32x3_kernel<<<grid, 256, 0, stream>>>(P);
+    else if (f32) mip_resize_f32_kernel<<<grid, 256, 0, stream>>>(P);
     else if (channels == 1) mip_resize_u8_kernel<1><<<grid, 256, 0, stream>>>(P);
     else if (channels == 2) mip_resize_u8_kernel<2><<<grid, 256, 0, stream>>>(P);
     else if (channels == 4) mip_resize_u8_kernel<4><<<grid, 256, 0, stream>>>(P);

@@ -1,0 +1,210 @@
+// normal_pack.cu -- normal-map packers / unpackers and the roughness anti-aliasing bake on the device (sm_100a),
+// the element-wise float work between load and the BC5 / BC4 / BC1 / BC3 encoders of the
+// PBRImporter path, so the normal + roughness pipeline (BASELINE.json configs[1]) stays resident in HBM.
+//
+// Replaces (reference, scalar CPU loops):
+//   PackNormals{RGBA_BC1, RG_BC5, Spheremap_BC5, Stereographic_BC5, Paraboloid_BC5, RGBA_BC3}_Compatible
+//                                  Hork/Image/ImageEncoders.cpp:693-796
+//   UnpackNormal*_Compatible       Hork/Image/ImageEncoders.cpp:798-878
+//   NormalizeVectors               Hork/Image/Image.cpp:2251-2260  (v * 2 - 1, then TVector3::NormalizeSelf, VectorMath.h:888-899)
+//   the vMF / Toksvig roughness update of CreateNormalAndRoughness, Hork/Image/Image.cpp:2526-2580
+//   (== Tools/PBRImporter/Main.cpp:616-680)
+//
+// Arithmetic: the reference is plain IEEE single precision without contraction (Math::Round = std::round, half away from
+// zero, Core/BaseMath.h:681-685; Math::Saturate = min(max(v, 0), 1), :794-798; Math::RSqrt = the 0x5f3759df bit trick with
+// one Newton step, :949-962).  The library is built with --fmad=false and CUDA's sqrtf / division are correctly rounded
+// by default, so every packer is bit-exact; the Toksvig branch calls sqrt() on floats, where the reference may run in
+// double depending on the overload it resolves to -- contract +-1 LSB there.
+// HBM-bound streaming kernels: 12 B/texel in, 2 or 4 B/texel out (packers), one thread per texel, 32-bit accesses (Float3
+// arrays are only 4-byte aligned).
+#include <stdint.h>
+#include "hkbcn_kernels.h"
+
+namespace hkbcn {
+
+namespace {
+
+__device__ __forceinline__ float saturate_ref(float v) { return fminf(fmaxf(v, 0.0f), 1.0f); }
+__device__ __forceinline__ uint8_t unorm8(float v) { return (uint8_t)roundf(saturate_ref(v) * 255.0f); }
+__device__ __forceinline__ float sqrt_ref(float v) { return v > 0.0f ? sqrtf(v) : 0.0f; } // Math::Sqrt, Core/BaseMath.h:936-940
+__device__ __forceinline__ float rsqrt_ref(float value)
+{
+    const float x2 = value * 0.5f;
+    float f = __uint_as_float(0x5f3759dfu - (__float_as_uint(value) >> 1));
+    f *= 1.5f - x2 * f * f;
+    return f;
+}
+
+template <int VARIANT>
+__global__ void __launch_bounds__(256) pack_normals_kernel(const float* __restrict__ n, uint8_t* __restrict__ dst, size_t count)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    const float x = n[3 * i], y = n[3 * i + 1], z = n[3 * i + 2];
+    if (VARIANT == NP_RGBA_BC1) {
+        *(uchar4*)(dst + 4 * i) = make_uchar4(unorm8(x * 0.5f + 0.5f), unorm8(y * 0.5f + 0.5f), unorm8(z * 0.5f + 0.5f), 255);
+    } else if (VARIANT == NP_RGBA_BC3) {
+        *(uchar4*)(dst + 4 * i) = make_uchar4(255, unorm8(y * 0.5f + 0.5f), unorm8(z * 0.5f + 0.5f), unorm8(x * 0.5f + 0.5f));
+    } else {
+        float u, v;
+        if (VARIANT == NP_RG_BC5) {
+            u = x * 0.5f + 0.5f;
+            v = y * 0.5f + 0.5f;
+        } else if (VARIANT == NP_SPHEREMAP_BC5) {
+            const float denom = 1.0f / sqrt_ref(z * 8.0f + 8.0f);
+            u = x * denom + 0.5f;
+            v = y * denom + 0.5f;
+        } else if (VARIANT == NP_STEREOGRAPHIC_BC5) {
+            u = x / (1.0f + z) * 0.5f + 0.5f;
+            v = y / (1.0f + z) * 0.5f + 0.5f;
+        } else { // paraboloid
+            const float a = (x * x) + (y * y), b = z, c = -1.0f;
+            const float discriminant = b * b - 4.0f * a * c;
+            const float t = (-b + sqrtf(discriminant)) / (2.0f * a);
+            u = (x * t) * 0.5f + 0.5f;
+            v = (y * t) * 0.5f + 0.5f;
+        }
+        *(uchar2*)(dst + 2 * i) = make_uchar2(unorm8(u), unorm8(v));
+    }
+}
+
+template <int VARIANT>
+__global__ void __launch_bounds__(256) unpack_normals_kernel(const uint8_t* __restrict__ src, float* __restrict__ n, size_t count)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    float x, y, z;
+    if (VARIANT == NP_RGBA_BC1 || VARIANT == NP_RGBA_BC3) {
+        const uchar4 d = *(const uchar4*)(src + 4 * i);
+        if (VARIANT == NP_RGBA_BC1) {
+            x = (d.x / 255.0f) * 2.0f - 1.0f;
+            y = (d.y / 255.0f) * 2.0f - 1.0f;
+            z = (d.z / 255.0f) * 2.0f - 1.0f;
+        } else {
+            x = d.w / 255.0f * 2.0f - 1.0f;
+            y = d.y / 255.0f * 2.0f - 1.0f;
+            z = d.z / 255.0f * 2.0f - 1.0f;
+        }
+    } else {
+        const uchar2 d = *(const uchar2*)(src + 2 * i);
+        if (VARIANT == NP_RG_BC5) {
+            x = (d.x / 255.0f) * 2.0f - 1.0f;
+            y = (d.y / 255.0f) * 2.0f - 1.0f;
+            z = sqrt_ref(1.0f - (x * x + y * y));
+        } else if (VARIANT == NP_SPHEREMAP_BC5) {
+            const float px = (d.x / 255.0f) * 4.0f - 2.0f, py = (d.y / 255.0f) * 4.0f - 2.0f;
+            const float f = px * px + py * py;
+            const float s = sqrt_ref(1.0f - f / 4.0f);
+            x = px * s;
+            y = py * s;
+            z = 1.0f - f / 2.0f;
+        } else if (VARIANT == NP_STEREOGRAPHIC_BC5) {
+            x = (d.x / 255.0f) * 2.0f - 1.0f;
+            y = (d.y / 255.0f) * 2.0f - 1.0f;
+            const float denom = 2.0f / (1 + saturate_ref(x * x + y * y));
+            x *= denom;
+            y *= denom;
+            z = denom - 1.0f;
+        } else { // paraboloid
+            x = (d.x / 255.0f) * 2.0f - 1.0f;
+            y = (d.y / 255.0f) * 2.0f - 1.0f;
+            z = 1.0f - saturate_ref(x * x + y * y);
+        }
+    }
+    n[3 * i] = x;
+    n[3 * i + 1] = y;
+    n[3 * i + 2] = z;
+}
+
+__global__ void __launch_bounds__(256) normalize_vectors_kernel(float* __restrict__ v, size_t count)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    float x = v[3 * i] * 2.0f - 1.0f, y = v[3 * i + 1] * 2.0f - 1.0f, z = v[3 * i + 2] * 2.0f - 1.0f;
+    const float len = sqrtf(x * x + y * y + z * z);
+    if (len != 0.0f) {
+        const float inv = 1.0f / len;
+        x *= inv;
+        y *= inv;
+        z *= inv;
+    }
+    v[3 * i] = x;
+    v[3 * i + 1] = y;
+    v[3 * i + 2] = z;
+}
+
+// one mip level: roughness[i] updated from the length of the averaged normal (Image.cpp:2546-2578)
+template <int BAKE>
+__global__ void __launch_bounds__(256) roughness_bake_kernel(const float* __restrict__ avg, uint8_t* __restrict__ rough, size_t count)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    const float x = avg[3 * i], y = avg[3 * i + 1], z = avg[3 * i + 2];
+    const float r2 = x * x + y * y + z * z;
+    if (!(r2 > 1e-8f && r2 < 1.0f)) return;
+    if (BAKE == 1) { // vMF
+        const float variance = 2.0f * rsqrt_ref(r2) * (1.0f - r2) / (3.0f - r2);
+        const float rv = rough[i] / 255.0f;
+        rough[i] = unorm8(sqrt_ref(rv * rv + variance));
+    } else { // Toksvig
+        const float r = sqrtf(r2);
+        const uint8_t q = rough[i] < 1 ? 1 : rough[i];
+        const float rr = q / 255.0f;
+        const float specPower = 2.0f / (rr * rr) - 2.0f;
+        const float ft = r / (specPower + r * (1.0f - specPower)); // Math::Lerp(specPower, 1, r) = a + frac * (b - a)
+        rough[i] = unorm8(sqrtf(2.0f / (ft * specPower + 2.0f)));
+    }
+}
+
+} // namespace
+
+cudaError_t launch_pack_normals(int variant, const float* d_normals, uint8_t* d_dst, size_t count, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    const unsigned g = (unsigned)((count + 255) / 256);
+    switch (variant) {
+    case NP_RGBA_BC1: pack_normals_kernel<NP_RGBA_BC1><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    case NP_RG_BC5: pack_normals_kernel<NP_RG_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    case NP_SPHEREMAP_BC5: pack_normals_kernel<NP_SPHEREMAP_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    case NP_STEREOGRAPHIC_BC5: pack_normals_kernel<NP_STEREOGRAPHIC_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    case NP_PARABOLOID_BC5: pack_normals_kernel<NP_PARABOLOID_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    case NP_RGBA_BC3: pack_normals_kernel<NP_RGBA_BC3><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_unpack_normals(int variant, const uint8_t* d_src, float* d_normals, size_t count, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    const unsigned g = (unsigned)((count + 255) / 256);
+    switch (variant) {
+    case NP_RGBA_BC1: unpack_normals_kernel<NP_RGBA_BC1><<<g, 256, 0, st>>>(d_src, d_normals, count); break;
+    case NP_RG_BC5: unpack_normals_kernel<NP_RG_BC5><<<g, 256, 0, st>>>(d_src, d_normals, count); break;
+    case NP_SPHEREMAP_BC5: unpack_normals_kernel<NP_SPHEREMAP_BC5><<<g, 256, 0, st>>>(d_src, d_normals, count); break;
+    case NP_STEREOGRAPHIC_BC5: unpack_normals_kernel<NP_STEREOGRAPHIC_BC5><<<g, 256, 0, st>>>(d_src, d_normals, count); break;
+    case NP_PARABOLOID_BC5: unpack_normals_kernel<NP_PARABOLOID_BC5><<<g, 256, 0, st>>>(d_src, d_normals, count); break;
+    case NP_RGBA_BC3: unpack_normals_kernel<NP_RGBA_BC3><<<g, 256, 0, st>>>(d_src, d_normals, count); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    normalize_vectors_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(d_v, count);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t* d_rough, size_t count, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    const unsigned g = (unsigned)((count + 255) / 256);
+    if (bake == 1) roughness_bake_kernel<1><<<g, 256, 0, st>>>(d_avg_normals, d_rough, count);
+    else if (bake == 2) roughness_bake_kernel<2><<<g, 256, 0, st>>>(d_avg_normals, d_rough, count);
+    else return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+} // namespace hkbcn

@@ -31,6 +31,8 @@ EXPORTS = [
     "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
     "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
     "hkbcn_texture_header", "hkbcn_write_texture", "hkbcn_read_texture", "hkbcn_import_batch",
+    "hkbcn_pack_texel_bytes", "hkbcn_pack_normals", "hkbcn_unpack_normals", "hkbcn_normalize_vectors", "hkbcn_bake_roughness",
+    "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
 ]
 
 
@@ -97,6 +99,16 @@ def lib():
         L.hkbcn_write_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_read_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.hkbcn_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t]
+        L.hkbcn_pack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.hkbcn_unpack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.hkbcn_normalize_vectors.argtypes = [C.c_void_p, C.c_size_t]
+        L.hkbcn_bake_roughness.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int]
+        L.hkbcn_pack_normals_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.hkbcn_unpack_normals_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.hkbcn_normalize_vectors_dev.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.hkbcn_bake_scratch_bytes.restype = C.c_size_t
+        L.hkbcn_bake_scratch_bytes.argtypes = [C.c_uint32, C.c_uint32]
+        L.hkbcn_bake_roughness_dev.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
         L.hkbcn_free_pinned.argtypes = [C.c_void_p]
         _lib = L
@@ -256,3 +268,32 @@ def import_batch(jobs):
         if arr[i].status:
             raise HkbcnError(f"import job {i} failed with status {arr[i].status}")
     return outs
+
+
+def pack_normals(variant, normals):
+    """PackNormals*_Compatible over Float3 normals (n, 3) -> uint8 bytes"""
+    n = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+    out = np.zeros(n.shape[0] * lib().hkbcn_pack_texel_bytes(variant), np.uint8)
+    check(lib().hkbcn_pack_normals(variant, _ptr(n), _ptr(out), C.c_size_t(n.shape[0])))
+    return out
+
+
+def unpack_normals(variant, packed, count):
+    p = np.ascontiguousarray(packed, np.uint8)
+    out = np.zeros((count, 3), np.float32)
+    check(lib().hkbcn_unpack_normals(variant, _ptr(p), _ptr(out), C.c_size_t(count)))
+    return out
+
+
+def normalize_vectors(v):
+    out = np.array(v, np.float32).reshape(-1, 3).copy()
+    check(lib().hkbcn_normalize_vectors(_ptr(out), C.c_size_t(out.shape[0])))
+    return out
+
+
+def bake_roughness(normals, rough_chain, width, height, mips, bake, filt=0, edge=0):
+    """roughness chain (uint8, levels back to back) updated in a copy and returned"""
+    n = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+    r = np.array(rough_chain, np.uint8).ravel().copy()
+    check(lib().hkbcn_bake_roughness(_ptr(n), _ptr(r), width, height, mips, bake, filt, edge))
+    return r

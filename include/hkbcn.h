@@ -216,6 +216,43 @@ typedef struct hkbcn_import_job {
  * upload -> mip cascade -> encode -> download, and the files are written by a separate thread behind it. */
 HKBCN_API int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs);
 
+/* ---- normal maps and roughness anti-aliasing ----------
+ * The element-wise work of the PBRImporter path between load and the BC5 / BC4 / BC1 / BC3 encoders:
+ *   hkbcn_pack_normals    PackNormals*_Compatible (Hork/Image/ImageEncoders.cpp:693-796): Float3 normals -> RG8 / RGBA8
+ *   hkbcn_unpack_normals  UnpackNormal*_Compatible (:798-878) applied to `count` texels
+ *   hkbcn_normalize_vectors  NormalizeVectors (Hork/Image/Image.cpp:2251-2260): v = v * 2 - 1, then normalise
+ *   hkbcn_bake_roughness  the vMF / Toksvig update of the roughness mips from the averaged normals
+ *                         (CreateNormalAndRoughness, Image.cpp:2526-2580 == Tools/PBRImporter/Main.cpp:616-680)
+ * Packers, unpackers and the normalisation are bit-exact with the reference; the bake is within +-1 LSB. */
+enum hkbcn_normal_pack {
+    HKBCN_NORMALS_RGBA_BC1 = 0,          /* NORMAL_MAP_PACK_RGBA_BC1_COMPATIBLE: x y z 255 */
+    HKBCN_NORMALS_RG_BC5 = 1,            /* x y */
+    HKBCN_NORMALS_SPHEREMAP_BC5 = 2,
+    HKBCN_NORMALS_STEREOGRAPHIC_BC5 = 3,
+    HKBCN_NORMALS_PARABOLOID_BC5 = 4,
+    HKBCN_NORMALS_RGBA_BC3 = 5           /* 255 y z x */
+};
+#define HKBCN_ROUGHNESS_BAKE_VMF 1
+#define HKBCN_ROUGHNESS_BAKE_TOKSVIG 2
+HKBCN_API int hkbcn_pack_texel_bytes(int variant); /* 2 or 4; <0 on a bad variant */
+/* host pointers; normals are tightly packed Float3 (12 bytes per texel) */
+HKBCN_API int hkbcn_pack_normals(int variant, const float* normals_xyz, void* dst, size_t count);
+HKBCN_API int hkbcn_unpack_normals(int variant, const void* src, float* normals_xyz, size_t count);
+HKBCN_API int hkbcn_normalize_vectors(float* xyz, size_t count);
+/* roughness_chain: the R8 mip chain (levels back to back, as hkbcn_generate_mips lays out BC4's source) of a width x height
+ * roughness map; normals_xyz: the normalised normal map of the same size.  Level i >= 1 is updated from the normals averaged
+ * down level by level with `filter` / `edge_mode` (hkbcn_mip_config values; 0 = the importers' triangle / wrap). */
+HKBCN_API int hkbcn_bake_roughness(const float* normals_xyz, uint8_t* roughness_chain, uint32_t width, uint32_t height,
+                                   uint32_t num_mips, int bake, int filter, int edge_mode);
+/* device pointers, asynchronous on `stream`; d_scratch: hkbcn_bake_scratch_bytes() bytes for the averaged normals */
+HKBCN_API int hkbcn_pack_normals_dev(int device, int variant, const float* d_normals_xyz, void* d_dst, size_t count, void* stream);
+HKBCN_API int hkbcn_unpack_normals_dev(int device, int variant, const void* d_src, float* d_normals_xyz, size_t count, void* stream);
+HKBCN_API int hkbcn_normalize_vectors_dev(int device, float* d_xyz, size_t count, void* stream);
+HKBCN_API size_t hkbcn_bake_scratch_bytes(uint32_t width, uint32_t height);
+HKBCN_API int hkbcn_bake_roughness_dev(int device, const float* d_normals_xyz, uint8_t* d_roughness_chain, void* d_scratch,
+                                       uint32_t width, uint32_t height, uint32_t num_mips, int bake, int filter, int edge_mode,
+                                       void* stream);
+
 /* ---- instrumentation --------------------------------------------------------
  * Number of kernels this library launched since init (bench.py's gpu_launches). */
 HKBCN_API uint64_t hkbcn_launch_count(void);

@@ -18,6 +18,10 @@ def lib():
         L.oracle_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.oracle_decompress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_int]
         L.oracle_encode_bc4_fast.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.oracle_pack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.oracle_unpack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
+        L.oracle_normalize_vectors.argtypes = [C.c_void_p, C.c_size_t]
+        L.oracle_bake_roughness_level.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         _lib = L
     return _lib
 
@@ -48,3 +52,30 @@ def encode_bc4_fast(src, n):
     for i in range(n):
         lib().oracle_encode_bc4_fast(src.ctypes.data + 16 * i, 1, dst.ctypes.data + 8 * i)
     return dst
+
+
+def pack_normals(variant, normals):
+    n = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+    out = np.zeros(n.shape[0] * (4 if variant in (0, 5) else 2), np.uint8)
+    assert lib().oracle_pack_normals(variant, n.ctypes.data, out.ctypes.data, n.shape[0]) == 0
+    return out
+
+
+def unpack_normals(variant, packed, count):
+    p = np.ascontiguousarray(packed, np.uint8)
+    out = np.zeros((count, 3), np.float32)
+    assert lib().oracle_unpack_normals(variant, p.ctypes.data, out.ctypes.data, count) == 0
+    return out
+
+
+def normalize_vectors(v):
+    out = np.array(v, np.float32).reshape(-1, 3).copy()
+    lib().oracle_normalize_vectors(out.ctypes.data, out.shape[0])
+    return out
+
+
+def bake_roughness_level(bake, avg_normals, rough):
+    a = np.ascontiguousarray(avg_normals, np.float32).reshape(-1, 3)
+    r = np.array(rough, np.uint8).ravel().copy()
+    lib().oracle_bake_roughness_level(bake, a.ctypes.data, r.ctypes.data, r.size)
+    return r

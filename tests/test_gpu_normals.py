@@ -1,0 +1,92 @@
+"""Row f4 parity: normal-map packers / unpackers, NormalizeVectors and the roughness bake on the device against the C
+restatement of the reference loops (oracle/oracle_pack.c; ImageEncoders.cpp:693-878, Image.cpp:2251-2260, :2526-2580).
+Packers, unpackers and normalisation: bit-exact.  Bake: the averaged normals come from the device cascade (within 1e-6 of
+stbir, tests/test_gpu_mips.py), so a roughness value may land on the other side of a rounding boundary: +-1 LSB."""
+import numpy as np
+import pytest
+
+import hkbcn
+import oracle_c
+import refshim
+import synth
+
+pytestmark = pytest.mark.gpu
+VARIANTS = [0, 1, 2, 3, 4, 5]
+
+
+def _normals(n, seed, hemisphere=True):
+    rng = np.random.default_rng(seed)
+    v = rng.normal(size=(n, 3)).astype(np.float32)
+    if hemisphere:
+        v[:, 2] = np.abs(v[:, 2])
+    v /= np.linalg.norm(v, axis=1, keepdims=True).astype(np.float32)
+    # edge cases the reference loops meet: axis-aligned, straight up, grazing, un-normalised, zero
+    edge = np.array([[0, 0, 1], [1, 0, 0], [0, 1, 0], [-1, 0, 0], [0, -1, 0], [0, 0, -1], [0.6, 0.8, 0], [0, 0, 0], [2, -3, 0.5],
+                     [1e-20, 0, 1], [-0.0, 0.0, 1]], np.float32)
+    return np.concatenate([edge, v]).astype(np.float32)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_packers_bit_exact(variant):
+    n = _normals(100000, 11 + variant)
+    with np.errstate(all="ignore"):
+        want = oracle_c.pack_normals(variant, n)
+    got = hkbcn.pack_normals(variant, n)
+    assert got.size == want.size
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, f"variant {variant}: {bad.size} bytes differ, first at texel {bad[0] // (got.size // n.shape[0])}"
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_unpackers_bit_exact(variant):
+    tb = 4 if variant in (0, 5) else 2
+    rng = np.random.default_rng(variant)
+    packed = np.concatenate([np.arange(256 * tb, dtype=np.uint32).astype(np.uint8), rng.integers(0, 256, 50000 * tb, dtype=np.uint8)])
+    if tb == 2:  # all 65536 byte pairs
+        a, b = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8))
+        packed = np.concatenate([packed, np.stack([a.ravel(), b.ravel()], 1).ravel()])
+    count = packed.size // tb
+    want = oracle_c.unpack_normals(variant, packed, count)
+    got = hkbcn.unpack_normals(variant, packed, count)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_normalize_vectors_bit_exact():
+    rng = np.random.default_rng(3)
+    v = rng.random((200000, 3), dtype=np.float32)
+    v[:5] = [[0.5, 0.5, 0.5], [1, 1, 1], [0, 0, 0], [0.5, 0.5, 1.0], [0.25, 0.75, 0.5]]  # the first one normalises a zero vector
+    want = oracle_c.normalize_vectors(v)
+    got = hkbcn.normalize_vectors(v)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("bake", [1, 2])
+@pytest.mark.parametrize("size", [(256, 256), (128, 64)])
+def test_roughness_bake_matches_reference_cascade(bake, size):
+    """CreateNormalAndRoughness: average the normals down with stbir (triangle, wrap), update each roughness mip"""
+    w, h = size
+    mips = hkbcn.lib().hkbcn_calc_num_mips(w, h)
+    # a bumpy normal map: decoded from the synthetic RG8 normals and normalised as the importer does
+    rg = synth.normals_rg8(w, h, 3).reshape(h, w, 2).astype(np.float32) / 255.0
+    n01 = np.concatenate([rg, np.full((h, w, 1), 0.85, np.float32)], axis=2)
+    rng = np.random.default_rng(1)
+    n01 = np.clip(n01 + rng.normal(scale=0.15, size=n01.shape).astype(np.float32), 0, 1).astype(np.float32)
+    normals = oracle_c.normalize_vectors(n01.reshape(-1, 3)).reshape(h, w, 3)
+    rough0 = synth.roughness_r8(w, h, 2).reshape(h, w, 1)
+    chain = hkbcn.generate_mips(60, rough0, w, h, mips, hkbcn.MipConfig(3, 2, 0, 0))  # CreateRoughnessMap: triangle, wrap
+    got = hkbcn.bake_roughness(normals, chain, w, h, mips, bake, 2, 3)
+    want = chain.copy()
+    avg, off = normals, w * h
+    changed = 0
+    for i in range(1, mips):
+        lw, lh = max(w >> i, 4), max(h >> i, 4)
+        avg = refshim.stbir_resize(avg, lw, lh, alpha_channel=-1, flags=0, edge=3, filt=2, space=0)
+        new = oracle_c.bake_roughness_level(bake, avg, want[off:off + lw * lh])
+        changed += int(np.sum(new != want[off:off + lw * lh]))
+        want[off:off + lw * lh] = new
+        off += lw * lh
+    assert off == chain.size and changed > 0.5 * (chain.size - w * h), "the bake must actually change the mips"
+    assert np.array_equal(got[: w * h], chain[: w * h])  # level 0 is never touched
+    d = np.abs(got.astype(int) - want.astype(int))
+    print(f"bake {bake} {w}x{h}: {np.mean(d != 0):.5f} of values differ, max {d.max()} LSB")
+    assert d.max() <= 1 and np.mean(d != 0) < 0.01

@@ -1,0 +1,46 @@
+"""Row f4, CPU side: the C restatement of the packers (oracle/oracle_pack.c) against hand-computed known answers and
+round trips, so the checker the GPU tests lean on is itself checked.  (The reference has no tests or vectors for these
+functions: parity of the restatement is by construction, statement by statement.)"""
+import numpy as np
+
+import oracle_c
+
+
+def test_known_answers():
+    # Math::Round(Math::Saturate(v * 0.5 + 0.5) * 255): 0 -> 127.5 -> 128 (half away from zero), 1 -> 255, -1 -> 0
+    up = np.array([[0, 0, 1]], np.float32)
+    assert oracle_c.pack_normals(0, up).tolist() == [128, 128, 255, 255]
+    assert oracle_c.pack_normals(5, up).tolist() == [255, 128, 255, 128]
+    assert oracle_c.pack_normals(1, up).tolist() == [128, 128]
+    assert oracle_c.pack_normals(1, np.array([[1, -1, 0]], np.float32)).tolist() == [255, 0]
+    # spheremap: denom = 1 / sqrt(8 z + 8); z = 1 -> 0.25; x = 0.6 -> 0.65 * 255 = 165.75 -> 166
+    assert oracle_c.pack_normals(2, np.array([[0.6, 0.0, 1.0]], np.float32)).tolist() == [166, 128]
+    # stereographic: x / (1 + z) * 0.5 + 0.5 with z = 0: x = 0.6 -> 0.8 * 255 = 204
+    assert oracle_c.pack_normals(3, np.array([[0.6, 0.8, 0.0]], np.float32)).tolist() == [204, 230]  # 0.9 * 255 = 229.5 -> 230
+    # out-of-range components saturate
+    assert oracle_c.pack_normals(0, np.array([[3, -3, 0.2]], np.float32)).tolist() == [255, 0, 153, 255]
+    # NormalizeVectors: v * 2 - 1, normalise; the zero vector stays zero
+    out = oracle_c.normalize_vectors(np.array([[0.5, 0.5, 1.0], [0.5, 0.5, 0.5], [1.0, 0.5, 0.5]], np.float32))
+    assert out.tolist() == [[0, 0, 1], [0, 0, 0], [1, 0, 0]]
+
+
+def test_round_trips_are_within_quantisation():
+    rng = np.random.default_rng(2)
+    v = rng.normal(size=(20000, 3)).astype(np.float32)
+    v[:, 2] = np.abs(v[:, 2]) + 0.05
+    v /= np.linalg.norm(v, axis=1, keepdims=True).astype(np.float32)
+    for variant, tol in ((0, 0.005), (1, 0.03), (2, 0.02), (3, 0.02), (5, 0.005)):
+        back = oracle_c.unpack_normals(variant, oracle_c.pack_normals(variant, v), v.shape[0])
+        back /= np.maximum(np.linalg.norm(back, axis=1, keepdims=True), 1e-6)
+        err = np.linalg.norm(back - v, axis=1)
+        assert np.percentile(err, 99) < tol * 4 and np.median(err) < tol, (variant, float(np.median(err)))
+
+
+def test_bake_raises_roughness_where_normals_disagree():
+    # a shortened averaged normal (|n| < 1) means variance below the texel: roughness goes up, never down
+    avg = np.array([[0, 0, 1.0], [0, 0, 0.9], [0, 0, 0.5], [0, 0, 0.0]], np.float32)
+    rough = np.array([100, 100, 100, 100], np.uint8)
+    for bake in (1, 2):
+        out = oracle_c.bake_roughness_level(bake, avg, rough)
+        assert out[0] == 100 and out[3] == 100      # r2 == 1 and r2 <= 1e-8 are left alone
+        assert out[1] > 100 and out[2] > out[1]
