@@ -861,6 +861,76 @@ int hkbcn_bake_roughness(const float* n, uint8_t* rough, uint32_t w, uint32_t h,
     return HKBCN_OK;
 }
 
+// ---- environment probes (row f3) --------------------------------------------------------------------------------------
+size_t hkbcn_envprobe_texels(int max_lod) { return (max_lod < 1 || max_lod > 12) ? 0 : envprobe_texels(max_lod); }
+
+static int probe_args_ok(uint32_t src_size, int max_lod)
+{
+    if (src_size < 1 || src_size > 8192) { set_err("bad source cube size %u", src_size); return HKBCN_ERR_BAD_ARG; }
+    if (max_lod < 1 || max_lod > 12) { set_err("max_lod %d out of range 1..12 (roughness of level L is L / max_lod)", max_lod); return HKBCN_ERR_BAD_ARG; }
+    return HKBCN_OK;
+}
+
+int hkbcn_envprobe_prefilter_dev(int device, const float* d_cube, uint32_t src_size, int max_lod, float* d_dst, void* stream)
+{
+    DEV_OR_RETURN(D, device)
+    int rc = probe_args_ok(src_size, max_lod);
+    if (rc) return rc;
+    CK(cudaSetDevice(D->id));
+    CK(launch_envprobe_prefilter(d_cube, (int)src_size, max_lod, d_dst, (cudaStream_t)stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+int hkbcn_irradiance_dev(int device, const float* d_cube, uint32_t src_size, uint32_t out_size, float* d_dst, void* stream)
+{
+    DEV_OR_RETURN(D, device)
+    int rc = probe_args_ok(src_size, 1);
+    if (rc) return rc;
+    if (out_size < 1 || out_size > 1024) { set_err("bad irradiance size %u", out_size); return HKBCN_ERR_BAD_ARG; }
+    CK(cudaSetDevice(D->id));
+    CK(launch_irradiance(d_cube, (int)src_size, (int)out_size, d_dst, (cudaStream_t)stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+int hkbcn_envprobe_prefilter(const float* cube, uint32_t src_size, int max_lod, float* dst)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if ((rc = probe_args_ok(src_size, max_lod)) != HKBCN_OK) return rc;
+    if (!cube || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    const size_t in = (size_t)6 * src_size * src_size * 16, out = (size_t)envprobe_texels(max_lod) * 16;
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    if ((rc = with_scratch(D, in, out)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, cube, in, cudaMemcpyHostToDevice, D->stream));
+    CK(launch_envprobe_prefilter((const float*)D->d_src, (int)src_size, max_lod, (float*)D->d_dst, D->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CK(cudaMemcpyAsync(dst, D->d_dst, out, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_irradiance(const float* cube, uint32_t src_size, uint32_t out_size, float* dst)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if ((rc = probe_args_ok(src_size, 1)) != HKBCN_OK) return rc;
+    if (out_size < 1 || out_size > 1024) { set_err("bad irradiance size %u", out_size); return HKBCN_ERR_BAD_ARG; }
+    if (!cube || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    const size_t in = (size_t)6 * src_size * src_size * 16, out = (size_t)6 * out_size * out_size * 16;
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    if ((rc = with_scratch(D, in, out)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, cube, in, cudaMemcpyHostToDevice, D->stream));
+    CK(launch_irradiance((const float*)D->d_src, (int)src_size, (int)out_size, (float*)D->d_dst, D->stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CK(cudaMemcpyAsync(dst, D->d_dst, out, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
 // ---- .texture files (row f2) ------------------------------------------------------------------------------------------
 static void put_u32(uint8_t* p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
 static uint32_t get_u32(const uint8_t* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }

@@ -54,6 +54,11 @@ struct ResizeParams {
 };
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
 
+// ---- environment probes (envprobe.cu) ----------------------------------------
+uint32_t envprobe_texels(int max_lod); // 6 * sum of (2^max_lod >> lod)^2
+cudaError_t launch_envprobe_prefilter(const float* d_cube, int src_size, int max_lod, float* d_dst, cudaStream_t st);
+cudaError_t launch_irradiance(const float* d_cube, int src_size, int out_size, float* d_dst, cudaStream_t st);
+
 // ---- normal-map packers and roughness bake (normal_pack.cu) ------------------
 enum { NP_RGBA_BC1 = 0, NP_RG_BC5 = 1, NP_SPHEREMAP_BC5 = 2, NP_STEREOGRAPHIC_BC5 = 3, NP_PARABOLOID_BC5 = 4, NP_RGBA_BC3 = 5 };
 cudaError_t launch_pack_normals(int variant, const float* d_normals, uint8_t* d_dst, size_t count, cudaStream_t st);

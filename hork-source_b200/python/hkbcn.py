@@ -31,6 +31,7 @@ EXPORTS = [
     "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
     "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
     "hkbcn_texture_header", "hkbcn_write_texture", "hkbcn_read_texture", "hkbcn_import_batch",
+    "hkbcn_envprobe_texels", "hkbcn_envprobe_prefilter", "hkbcn_irradiance", "hkbcn_envprobe_prefilter_dev", "hkbcn_irradiance_dev",
     "hkbcn_pack_texel_bytes", "hkbcn_pack_normals", "hkbcn_unpack_normals", "hkbcn_normalize_vectors", "hkbcn_bake_roughness",
     "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
 ]
@@ -99,6 +100,12 @@ def lib():
         L.hkbcn_write_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_read_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.hkbcn_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t]
+        L.hkbcn_envprobe_texels.restype = C.c_size_t
+        L.hkbcn_envprobe_texels.argtypes = [C.c_int]
+        L.hkbcn_envprobe_prefilter.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+        L.hkbcn_irradiance.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.hkbcn_envprobe_prefilter_dev.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+        L.hkbcn_irradiance_dev.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         L.hkbcn_pack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.hkbcn_unpack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.hkbcn_normalize_vectors.argtypes = [C.c_void_p, C.c_size_t]
@@ -297,3 +304,23 @@ def bake_roughness(normals, rough_chain, width, height, mips, bake, filt=0, edge
     r = np.array(rough_chain, np.uint8).ravel().copy()
     check(lib().hkbcn_bake_roughness(_ptr(n), _ptr(r), width, height, mips, bake, filt, edge))
     return r
+
+
+def envprobe_prefilter(cube, src_size, max_lod):
+    """cube: (6, n, n, 4) float32 -> list of levels [(6, s, s, 4)] with s = 2^max_lod >> level"""
+    c = np.ascontiguousarray(cube, np.float32)
+    out = np.zeros(lib().hkbcn_envprobe_texels(max_lod) * 4, np.float32)
+    check(lib().hkbcn_envprobe_prefilter(_ptr(c), src_size, max_lod, _ptr(out)))
+    levels, off = [], 0
+    for lod in range(max_lod + 1):
+        s = (1 << max_lod) >> lod
+        levels.append(out[off:off + 6 * s * s * 4].reshape(6, s, s, 4))
+        off += 6 * s * s * 4
+    return levels
+
+
+def irradiance(cube, src_size, out_size):
+    c = np.ascontiguousarray(cube, np.float32)
+    out = np.zeros((6, out_size, out_size, 4), np.float32)
+    check(lib().hkbcn_irradiance(_ptr(c), src_size, out_size, _ptr(out)))
+    return out

@@ -253,6 +253,21 @@ HKBCN_API int hkbcn_bake_roughness_dev(int device, const float* d_normals_xyz, u
                                        uint32_t width, uint32_t height, uint32_t num_mips, int bake, int filter, int edge_mode,
                                        void* stream);
 
+/* ---- environment probes: GGX-prefiltered reflection chain and irradiance cube ----
+ * The reference computes these by rendering into layered cubemaps through OpenGL (EnvProbeGenerator::Generate,
+ * Hork/RenderUtils/EnvProbeGenerator.cpp:182-240 with envprobegen.frag; IrradianceGenerator::Generate,
+ * IrradianceGenerator.cpp:160-200 with irradiancegen.frag).  Here the shader arithmetic runs as CUDA kernels on plain buffers.
+ * cube: six RGBA32F faces of src_size x src_size, face-major (+X -X +Y -Y +Z -Z), rows top to bottom, linear HDR.
+ * Prefilter output: levels back to back, level L = six faces of (2^max_lod >> L)^2 RGBA32F texels, roughness L / max_lod
+ * (hkbcn_envprobe_texels() texels in all; alpha = 1).  The reference uses max_lod = 7 (128^2 .. 1^2).
+ * Irradiance output: six faces of out_size^2 (the reference uses 32).  Every level >= 4 texels wide can go straight into
+ * hkbcn_compress(HKBCN_BC6H_UFLOAT, ...) face by face. */
+HKBCN_API size_t hkbcn_envprobe_texels(int max_lod);
+HKBCN_API int hkbcn_envprobe_prefilter(const float* cube_rgba32f, uint32_t src_size, int max_lod, float* dst_rgba32f);
+HKBCN_API int hkbcn_irradiance(const float* cube_rgba32f, uint32_t src_size, uint32_t out_size, float* dst_rgba32f);
+HKBCN_API int hkbcn_envprobe_prefilter_dev(int device, const float* d_cube, uint32_t src_size, int max_lod, float* d_dst, void* stream);
+HKBCN_API int hkbcn_irradiance_dev(int device, const float* d_cube, uint32_t src_size, uint32_t out_size, float* d_dst, void* stream);
+
 /* ---- instrumentation --------------------------------------------------------
  * Number of kernels this library launched since init (bench.py's gpu_launches). */
 HKBCN_API uint64_t hkbcn_launch_count(void);

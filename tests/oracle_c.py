@@ -18,6 +18,9 @@ def lib():
         L.oracle_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
         L.oracle_decompress.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_size_t, C.c_int]
         L.oracle_encode_bc4_fast.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.oracle_envprobe_prefilter.restype = C.c_size_t
+        L.oracle_envprobe_prefilter.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.oracle_irradiance.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.oracle_pack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.oracle_unpack_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t]
         L.oracle_normalize_vectors.argtypes = [C.c_void_p, C.c_size_t]
@@ -79,3 +82,23 @@ def bake_roughness_level(bake, avg_normals, rough):
     r = np.array(rough, np.uint8).ravel().copy()
     lib().oracle_bake_roughness_level(bake, a.ctypes.data, r.ctypes.data, r.size)
     return r
+
+
+def envprobe_prefilter(cube, src_size, max_lod):
+    c = np.ascontiguousarray(cube, np.float32)
+    n = sum(6 * ((1 << max_lod) >> l) ** 2 for l in range(max_lod + 1))
+    out = np.zeros(n * 4, np.float32)
+    assert lib().oracle_envprobe_prefilter(c.ctypes.data, src_size, max_lod, out.ctypes.data) == n
+    levels, off = [], 0
+    for lod in range(max_lod + 1):
+        s = (1 << max_lod) >> lod
+        levels.append(out[off:off + 6 * s * s * 4].reshape(6, s, s, 4))
+        off += 6 * s * s * 4
+    return levels
+
+
+def irradiance(cube, src_size, out_size):
+    c = np.ascontiguousarray(cube, np.float32)
+    out = np.zeros((6, out_size, out_size, 4), np.float32)
+    lib().oracle_irradiance(c.ctypes.data, src_size, out_size, out.ctypes.data)
+    return out

@@ -7,7 +7,7 @@ name=$1; shift
 out=../../build/variants; mkdir -p $out/$name
 FL="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-fvisibility=hidden --fmad=false"
 objs=""
-for s in hkbcn_api bc45_encode bc123_encode bc7_encode bc6h_encode bcn_decode mip_resize normal_pack; do
+for s in hkbcn_api bc45_encode bc123_encode bc7_encode bc6h_encode bcn_decode mip_resize normal_pack envprobe; do
   case " ${VARIANT_SRCS:-bcn_decode} " in
     *" $s "*) nvcc $FL "$@" -c $s.cu -o $out/$name/$s.o & objs="$objs $out/$name/$s.o";;
     *) objs="$objs build/$s.o";;
