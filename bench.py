@@ -381,6 +381,7 @@ def run_gpu(args):
         if world == 1:
             out["decode"] = decode_sweep(torch, hkbcn, L, d_dst, stream, flush, hbm)
             out["encode_other_formats"] = encode_others(torch, hkbcn, L, stream, flush)
+            out["next_rows"] = next_rows(torch, hkbcn, L, stream, flush, hbm)
             v, dt, cores, sample = time_reference(levels, 1, 0)
             out["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample}
             # the CPU side of the import cascade: the reference's stbir_resize is single-threaded as shipped
@@ -499,6 +500,55 @@ def encode_others(torch, hkbcn, L, stream, flush):
             0, fmt, d_src.data_ptr(), d_dst.data_ptr(), n, n, 0, C.c_void_p(stream.cuda_stream))), 3, 1)
         out[name] = {"Mpix/s": round(n * n / ms / 1e3, 1), "ms": round(ms, 3)}
         del d_src, d_dst
+    return out
+
+
+def next_rows(torch, hkbcn, L, stream, flush, hbm):
+    """SURVEY.md 8f rows f4 and f3, device-resident: the normal-map packers / roughness bake (HBM-bound streaming kernels,
+    algorithmic bytes = Float3 in + packed texels out) and the environment-probe kernels (gather-bound; samples/s), with the
+    C restatement of the probe shader timed on one host core on a small level beside it."""
+    import time as _t
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import cubesynth
+    import oracle_c
+    out = {}
+    n = 4096
+    cs = C.c_void_p(stream.cuda_stream)
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    nrm = torch.rand((n * n, 3), dtype=torch.float32, device="cuda", generator=gen)
+    hkbcn.check(L.hkbcn_normalize_vectors_dev(0, nrm.data_ptr(), n * n, cs))
+    packed = torch.empty(n * n * 2, dtype=torch.uint8, device="cuda")
+    ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_pack_normals_dev(0, 1, nrm.data_ptr(), packed.data_ptr(), n * n, cs)), 5, 3)
+    gbs = n * n * 14 / (ms * 1e-3) / 1e9
+    out["pack_normals_rg_bc5_4096"] = {"us": round(ms * 1e3, 1), "GB/s": round(gbs, 1), "frac": round(gbs / hbm, 4), "Gpix/s": round(n * n / ms / 1e6, 2)}
+    ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_normalize_vectors_dev(0, nrm.data_ptr(), n * n, cs)), 5, 3)
+    gbs = n * n * 24 / (ms * 1e-3) / 1e9
+    out["normalize_vectors_4096"] = {"us": round(ms * 1e3, 1), "GB/s": round(gbs, 1), "frac": round(gbs / hbm, 4)}
+    mips = L.hkbcn_calc_num_mips(n, n)
+    rough = torch.randint(0, 256, (L.hkbcn_chain_src_bytes(60, n, n, mips, 0),), dtype=torch.uint8, device="cuda", generator=gen)
+    scratch = torch.empty(L.hkbcn_bake_scratch_bytes(n, n), dtype=torch.uint8, device="cuda")
+    ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_bake_roughness_dev(
+        0, nrm.data_ptr(), rough.data_ptr(), scratch.data_ptr(), n, n, mips, 1, 2, 3, cs)), 3, 2)
+    out["bake_roughness_vmf_4096_chain"] = {"ms": round(ms, 3), "Mpix/s": round(n * n / ms / 1e3, 1)}
+    del nrm, packed, rough, scratch
+    # environment probe: 6 x 512^2 source, the reference's maxLod 7 (128^2 .. 1^2) and 32^2 irradiance
+    src, max_lod = 512, 7
+    cube = torch.from_numpy(cubesynth.sky_cube(src, 1)).cuda()
+    texels = L.hkbcn_envprobe_texels(max_lod)
+    dst = torch.empty(texels * 4, dtype=torch.float32, device="cuda")
+    ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_envprobe_prefilter_dev(0, cube.data_ptr(), src, max_lod, dst.data_ptr(), cs)), 3, 2)
+    out["envprobe_prefilter_512_lod7"] = {"ms": round(ms, 3), "Gsamples/s": round(texels * 1024 / ms / 1e6, 2), "texels": int(texels)}
+    irr = torch.empty(6 * 32 * 32 * 4, dtype=torch.float32, device="cuda")
+    ms_i = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_irradiance_dev(0, cube.data_ptr(), src, 32, irr.data_ptr(), cs)), 3, 2)
+    out["irradiance_512_to_32"] = {"ms": round(ms_i, 3), "Gsamples/s": round(6 * 32 * 32 * 252 * 63 / ms_i / 1e6, 2)}
+    # the same shader arithmetic on one host core (oracle port), bounded: a 64^2 source and maxLod 3 (8^2 .. 1^2)
+    small = cubesynth.sky_cube(64, 1)
+    t0 = _t.perf_counter()
+    oracle_c.envprobe_prefilter(small, 64, 3)
+    dt = _t.perf_counter() - t0
+    cpu_rate = 6 * (64 + 16 + 4 + 1) * 1024 / dt / 1e9
+    out["envprobe_prefilter_cpu_port"] = {"Gsamples/s": round(cpu_rate, 5), "cores": 1, "sample": "64^2 source, maxLod 3 (510 texels x 1024 samples)",
+                                          "kind": "port"}
     return out
 
 

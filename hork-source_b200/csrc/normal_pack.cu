@@ -15,8 +15,8 @@
 // one Newton step, :949-962).  The library is built with --fmad=false and CUDA's sqrtf / division are correctly rounded
 // by default, so every packer is bit-exact; the Toksvig branch calls sqrt() on floats, where the reference may run in
 // double depending on the overload it resolves to -- contract +-1 LSB there.
-// HBM-bound streaming kernels: 12 B/texel in, 2 or 4 B/texel out (packers), one thread per texel, 32-bit accesses (Float3
-// arrays are only 4-byte aligned).
+// HBM-bound streaming kernels: 12 B/texel in, 2 or 4 B/texel out (packers).  The packers take four texels per thread with
+// 16-byte loads when the buffers are 16-byte aligned (Float3 arrays themselves only promise 4).
 #include <stdint.h>
 #include "hkbcn_kernels.h"
 
@@ -35,36 +35,63 @@ __device__ __forceinline__ float rsqrt_ref(float value)
     return f;
 }
 
+// one texel: the packed bytes in the low 16 (BC5 variants) or all 32 bits
 template <int VARIANT>
+__device__ __forceinline__ uint32_t pack_one(float x, float y, float z)
+{
+    if (VARIANT == NP_RGBA_BC1)
+        return (uint32_t)unorm8(x * 0.5f + 0.5f) | ((uint32_t)unorm8(y * 0.5f + 0.5f) << 8) | ((uint32_t)unorm8(z * 0.5f + 0.5f) << 16) | 0xFF000000u;
+    if (VARIANT == NP_RGBA_BC3)
+        return 255u | ((uint32_t)unorm8(y * 0.5f + 0.5f) << 8) | ((uint32_t)unorm8(z * 0.5f + 0.5f) << 16) | ((uint32_t)unorm8(x * 0.5f + 0.5f) << 24);
+    float u, v;
+    if (VARIANT == NP_RG_BC5) {
+        u = x * 0.5f + 0.5f;
+        v = y * 0.5f + 0.5f;
+    } else if (VARIANT == NP_SPHEREMAP_BC5) {
+        const float denom = 1.0f / sqrt_ref(z * 8.0f + 8.0f);
+        u = x * denom + 0.5f;
+        v = y * denom + 0.5f;
+    } else if (VARIANT == NP_STEREOGRAPHIC_BC5) {
+        u = x / (1.0f + z) * 0.5f + 0.5f;
+        v = y / (1.0f + z) * 0.5f + 0.5f;
+    } else { // paraboloid
+        const float a = (x * x) + (y * y), b = z, c = -1.0f;
+        const float discriminant = b * b - 4.0f * a * c;
+        const float t = (-b + sqrtf(discriminant)) / (2.0f * a);
+        u = (x * t) * 0.5f + 0.5f;
+        v = (y * t) * 0.5f + 0.5f;
+    }
+    return (uint32_t)unorm8(u) | ((uint32_t)unorm8(v) << 8);
+}
+
+// Four texels per thread: three 16-byte loads cover their 48 bytes of Float3 (a warp reads 1.5 KB contiguous), one 8- or
+// 16-byte store takes the result.  VEC needs 16-byte aligned pointers; the tail and unaligned calls go one texel at a time.
+template <int VARIANT, bool VEC>
 __global__ void __launch_bounds__(256) pack_normals_kernel(const float* __restrict__ n, uint8_t* __restrict__ dst, size_t count)
 {
-    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= count) return;
-    const float x = n[3 * i], y = n[3 * i + 1], z = n[3 * i + 2];
-    if (VARIANT == NP_RGBA_BC1) {
-        *(uchar4*)(dst + 4 * i) = make_uchar4(unorm8(x * 0.5f + 0.5f), unorm8(y * 0.5f + 0.5f), unorm8(z * 0.5f + 0.5f), 255);
-    } else if (VARIANT == NP_RGBA_BC3) {
-        *(uchar4*)(dst + 4 * i) = make_uchar4(255, unorm8(y * 0.5f + 0.5f), unorm8(z * 0.5f + 0.5f), unorm8(x * 0.5f + 0.5f));
-    } else {
-        float u, v;
-        if (VARIANT == NP_RG_BC5) {
-            u = x * 0.5f + 0.5f;
-            v = y * 0.5f + 0.5f;
-        } else if (VARIANT == NP_SPHEREMAP_BC5) {
-            const float denom = 1.0f / sqrt_ref(z * 8.0f + 8.0f);
-            u = x * denom + 0.5f;
-            v = y * denom + 0.5f;
-        } else if (VARIANT == NP_STEREOGRAPHIC_BC5) {
-            u = x / (1.0f + z) * 0.5f + 0.5f;
-            v = y / (1.0f + z) * 0.5f + 0.5f;
-        } else { // paraboloid
-            const float a = (x * x) + (y * y), b = z, c = -1.0f;
-            const float discriminant = b * b - 4.0f * a * c;
-            const float t = (-b + sqrtf(discriminant)) / (2.0f * a);
-            u = (x * t) * 0.5f + 0.5f;
-            v = (y * t) * 0.5f + 0.5f;
+    constexpr bool WIDE = VARIANT == NP_RGBA_BC1 || VARIANT == NP_RGBA_BC3;
+    const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (VEC) {
+        const size_t i = t * 4;
+        if (i + 4 <= count) {
+            const float4* p = (const float4*)(n + 3 * i);
+            const float4 a = __ldcs(p), b = __ldcs(p + 1), c = __ldcs(p + 2);
+            const uint32_t q0 = pack_one<VARIANT>(a.x, a.y, a.z), q1 = pack_one<VARIANT>(a.w, b.x, b.y), q2 = pack_one<VARIANT>(b.z, b.w, c.x),
+                           q3 = pack_one<VARIANT>(c.y, c.z, c.w);
+            if (WIDE) __stcs((uint4*)(dst + 4 * i), make_uint4(q0, q1, q2, q3));
+            else __stcs((uint2*)(dst + 2 * i), make_uint2(q0 | (q1 << 16), q2 | (q3 << 16)));
+            return;
         }
-        *(uchar2*)(dst + 2 * i) = make_uchar2(unorm8(u), unorm8(v));
+        for (size_t k = i; k < count; k++) { // the last, partial group
+            const uint32_t q = pack_one<VARIANT>(n[3 * k], n[3 * k + 1], n[3 * k + 2]);
+            if (WIDE) *(uint32_t*)(dst + 4 * k) = q;
+            else *(uint16_t*)(dst + 2 * k) = (uint16_t)q;
+        }
+    } else {
+        if (t >= count) return;
+        const uint32_t q = pack_one<VARIANT>(n[3 * t], n[3 * t + 1], n[3 * t + 2]);
+        if (WIDE) *(uint32_t*)(dst + 4 * t) = q;
+        else *(uint16_t*)(dst + 2 * t) = (uint16_t)q;
     }
 }
 
@@ -158,17 +185,24 @@ __global__ void __launch_bounds__(256) roughness_bake_kernel(const float* __rest
 
 } // namespace
 
+template <int VARIANT>
+static void launch_pack_t(const float* d_normals, uint8_t* d_dst, size_t count, cudaStream_t st)
+{
+    const bool vec = !((size_t)d_normals & 15) && !((size_t)d_dst & 15);
+    if (vec) pack_normals_kernel<VARIANT, true><<<(unsigned)(((count + 3) / 4 + 255) / 256), 256, 0, st>>>(d_normals, d_dst, count);
+    else pack_normals_kernel<VARIANT, false><<<(unsigned)((count + 255) / 256), 256, 0, st>>>(d_normals, d_dst, count);
+}
+
 cudaError_t launch_pack_normals(int variant, const float* d_normals, uint8_t* d_dst, size_t count, cudaStream_t st)
 {
     if (count == 0) return cudaSuccess;
-    const unsigned g = (unsigned)((count + 255) / 256);
     switch (variant) {
-    case NP_RGBA_BC1: pack_normals_kernel<NP_RGBA_BC1><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
-    case NP_RG_BC5: pack_normals_kernel<NP_RG_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
-    case NP_SPHEREMAP_BC5: pack_normals_kernel<NP_SPHEREMAP_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
-    case NP_STEREOGRAPHIC_BC5: pack_normals_kernel<NP_STEREOGRAPHIC_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
-    case NP_PARABOLOID_BC5: pack_normals_kernel<NP_PARABOLOID_BC5><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
-    case NP_RGBA_BC3: pack_normals_kernel<NP_RGBA_BC3><<<g, 256, 0, st>>>(d_normals, d_dst, count); break;
+    case NP_RGBA_BC1: launch_pack_t<NP_RGBA_BC1>(d_normals, d_dst, count, st); break;
+    case NP_RG_BC5: launch_pack_t<NP_RG_BC5>(d_normals, d_dst, count, st); break;
+    case NP_SPHEREMAP_BC5: launch_pack_t<NP_SPHEREMAP_BC5>(d_normals, d_dst, count, st); break;
+    case NP_STEREOGRAPHIC_BC5: launch_pack_t<NP_STEREOGRAPHIC_BC5>(d_normals, d_dst, count, st); break;
+    case NP_PARABOLOID_BC5: launch_pack_t<NP_PARABOLOID_BC5>(d_normals, d_dst, count, st); break;
+    case NP_RGBA_BC3: launch_pack_t<NP_RGBA_BC3>(d_normals, d_dst, count, st); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

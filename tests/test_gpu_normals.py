@@ -90,3 +90,26 @@ def test_roughness_bake_matches_reference_cascade(bake, size):
     d = np.abs(got.astype(int) - want.astype(int))
     print(f"bake {bake} {w}x{h}: {np.mean(d != 0):.5f} of values differ, max {d.max()} LSB")
     assert d.max() <= 1 and np.mean(d != 0) < 0.01
+
+
+def test_packers_device_pointers_unaligned_and_tails():
+    """the _dev entry point on the caller's stream: 16-byte aligned buffers take the four-texel path, others the scalar one"""
+    import ctypes as C
+    import torch
+    L = hkbcn.lib()
+    hkbcn.init()
+    n = _normals(1001, 5)
+    want = {v: oracle_c.pack_normals(v, n) for v in VARIANTS}
+    buf = torch.zeros(n.size + 8, dtype=torch.float32, device="cuda")
+    out = torch.zeros(n.shape[0] * 4 + 64, dtype=torch.uint8, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for off_in, off_out in ((0, 0), (1, 0), (0, 2), (3, 6)):  # float / byte offsets
+        buf[off_in:off_in + n.size] = torch.from_numpy(n.ravel()).cuda()
+        for v in VARIANTS:
+            tb = L.hkbcn_pack_texel_bytes(v)
+            out.zero_()
+            hkbcn.check(L.hkbcn_pack_normals_dev(0, v, buf.data_ptr() + 4 * off_in, out.data_ptr() + off_out * tb, n.shape[0], st))
+            torch.cuda.synchronize()
+            got = out[off_out * tb: off_out * tb + n.shape[0] * tb].cpu().numpy()
+            assert np.array_equal(got, want[v]), (v, off_in, off_out)
+            assert int(out[off_out * tb + n.shape[0] * tb:].max()) == 0  # nothing written past the end
