@@ -28,11 +28,17 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
 {
     constexpr int BPP = F16SRC ? 8 : 16;
     constexpr int ROWB = BC6_TB * 4 * BPP;
-    __shared__ __align__(128) uint8_t stage[4 * ROWB];
+    // The staged texels and the integer-domain copy of the tile share one buffer: every thread converts its block into
+    // registers, a barrier retires the stage, then the integers are written over it.  30 KB per CTA instead of 42 KB, so
+    // seven CTAs (14 warps) fit an SM instead of five -- with 65,536 blocks = 2048 warp-tiles per 1024^2 surface that is the
+    // difference between one round of tiles and two, the second of them three-quarters empty.
+    constexpr int BUFB = 4 * ROWB > 48 * BC6_NT * 4 ? 4 * ROWB : 48 * BC6_NT * 4;
+    __shared__ __align__(128) uint8_t buf[BUFB];
     __shared__ __align__(16) bc6h::Layout L6;
     __shared__ float tf[48 * BC6_NT];
-    __shared__ int ti[48 * BC6_NT];
     __shared__ __align__(8) uint64_t bar;
+    uint8_t* const stage = buf;
+    int* const ti = (int*)buf;
 
     {
         const uint32_t* src = (const uint32_t*)&g_bc6h_enc_layout;
@@ -57,6 +63,7 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
         stage_tile<BPP, BC6_TB, BC6_NT>(L, b0, nb, stage, &bar, phase);
         __syncthreads();
         const uint32_t k = threadIdx.x;
+        int q[48];
         if (k < nb) {
 #pragma unroll
             for (int r = 0; r < 4; r++)
@@ -77,13 +84,18 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
                     for (int c = 0; c < 3; c++) {
                         const int i = 3 * (4 * r + x) + c;
                         tf[i * BC6_NT + k] = v[c];
-                        ti[i * BC6_NT + k] = bc6h::f16_to_int(bc6h::half_from_float_bits(__float_as_uint(v[c])), isSigned != 0);
+                        q[i] = bc6h::f16_to_int(bc6h::half_from_float_bits(__float_as_uint(v[c])), isSigned != 0);
                     }
                 }
+        }
+        __syncthreads(); // every thread has read its texels: the stage becomes the integer copy
+        if (k < nb) {
+#pragma unroll
+            for (int i = 0; i < 48; i++) ti[i * BC6_NT + k] = q[i];
             const uint4 out = bc6h::encode_block(blk, L6, isSigned != 0);
             *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }
-        __syncthreads(); // stage is reused by the next tile
+        __syncthreads(); // the buffer is staged into again by the next tile
     }
 }
 
@@ -94,7 +106,10 @@ cudaError_t launch_bc6h_encode(bool is_signed, bool src_f16, const EncodeParams&
     if (P.totalTiles == 0) return cudaSuccess;
     // one tile per CTA iteration; tiles differ a lot in cost (the search exits early on exact fits), so the grid is
     // sized to the tile count up to a few resident CTAs per SM and the remainder strides
-    const uint32_t g = (uint32_t)sm_count * 4;
+#ifndef BC6E_CTAS_PER_SM
+#define BC6E_CTAS_PER_SM 7
+#endif
+    const uint32_t g = (uint32_t)sm_count * BC6E_CTAS_PER_SM;
     const int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
     if (src_f16)
         bc6h_encode_kernel<true><<<grid, BC6_NT, 0, stream>>>(P, is_signed ? 1u : 0u);

@@ -202,7 +202,7 @@ template <int N> __device__ __forceinline__ float nearest_entry(int r, int g, in
 }
 
 // MapColorsQuantized (bc6h_enc.h:3127-3158): total error of the texels in `mask` against the palette of `e`
-template <int N> __device__ __forceinline__ float map_colors_quantized(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned)
+template <int N> __device__ __forceinline__ float map_colors_quantized_body(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned)
 {
     int pal[N][3];
     palette_quantized<N>(e, prec, isSigned, pal);
@@ -214,6 +214,36 @@ template <int N> __device__ __forceinline__ float map_colors_quantized(const Blo
         tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
     }
     return tot;
+}
+// The search calls this from 36 sites per mode class (three channels x {A, B, alternating} x one / two regions x 3- / 4-bit
+// indices); inlined everywhere it made the kernel 51 K instructions (palette generation alone 28 K) -- far beyond the
+// instruction cache once more than two warps per scheduler run at different points of the search.  One real function per
+// index width instead; the arguments are scalars so nothing goes through local memory.
+#ifndef BC6H_NOINLINE_MAP
+#define BC6H_NOINLINE_MAP 1
+#endif
+template <int N>
+__device__ __noinline__ float map_colors_quantized_fn(const int* ip, int stride, uint32_t mask, int a0, int a1, int a2, int b0, int b1, int b2,
+                                                      uint32_t prec_packed, bool isSigned)
+{
+    Block blk;
+    blk.f = nullptr;
+    blk.ip = ip;
+    blk.stride = stride;
+    Ep e;
+    e.A[0] = a0; e.A[1] = a1; e.A[2] = a2;
+    e.B[0] = b0; e.B[1] = b1; e.B[2] = b2;
+    const uint8_t prec[3] = {(uint8_t)prec_packed, (uint8_t)(prec_packed >> 8), (uint8_t)(prec_packed >> 16)};
+    return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned);
+}
+template <int N> __device__ __forceinline__ float map_colors_quantized(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned)
+{
+#if BC6H_NOINLINE_MAP
+    return map_colors_quantized_fn<N>(blk.ip, blk.stride, mask, e.A[0], e.A[1], e.A[2], e.B[0], e.B[1], e.B[2],
+                                      (uint32_t)prec[0] | ((uint32_t)prec[1] << 8) | ((uint32_t)prec[2] << 16), isSigned);
+#else
+    return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned);
+#endif
 }
 
 // PerturbOne (bc6h_enc.h:3160-3219): logarithmic search on one component of one endpoint.  Returns the best error,
