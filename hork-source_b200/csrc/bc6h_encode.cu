@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
     __shared__ __align__(16) bc6h::Layout L6;
     __shared__ float tf[48 * BC6_NT];
     __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t nextTile;
     uint8_t* const stage = buf;
     int* const ti = (int*)buf;
 
@@ -56,7 +57,8 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
     blk.ip = ti + threadIdx.x;
     blk.stride = BC6_NT;
 
-    for (uint32_t tile = blockIdx.x; tile < P.totalTiles; tile += gridDim.x) {
+    uint32_t tile = blockIdx.x;
+    while (tile < P.totalTiles) {
         const Level& L = P.lv[find_level(P, tile)];
         const uint32_t b0 = (tile - L.tileBase) * BC6_TB;
         const uint32_t nb = min((uint32_t)BC6_TB, L.nblocks - b0);
@@ -95,7 +97,18 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
             const uint4 out = bc6h::encode_block(blk, L6, isSigned != 0);
             *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }
+        // tiles are claimed from the launch's counter, not strided: the search exits early on exact fits, so a tile's
+        // cost varies by an order of magnitude with content
+        if (threadIdx.x == 0) nextTile = gridDim.x + atomicAdd(P.sched, 1u);
         __syncthreads(); // the buffer is staged into again by the next tile
+        tile = nextTile;
+    }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(P.sched + 1, 1u) == gridDim.x - 1u) {
+            P.sched[0] = 0;
+            P.sched[1] = 0;
+        }
     }
 }
 
@@ -104,8 +117,7 @@ uint32_t bc6h_tile_blocks() { return BC6_TB; }
 cudaError_t launch_bc6h_encode(bool is_signed, bool src_f16, const EncodeParams& P, int sm_count, cudaStream_t stream)
 {
     if (P.totalTiles == 0) return cudaSuccess;
-    // one tile per CTA iteration; tiles differ a lot in cost (the search exits early on exact fits), so the grid is
-    // sized to the tile count up to a few resident CTAs per SM and the remainder strides
+    // one tile per CTA iteration; the grid is one resident wave (or the tile count if smaller) and CTAs claim further tiles
 #ifndef BC6E_CTAS_PER_SM
 #define BC6E_CTAS_PER_SM 7
 #endif

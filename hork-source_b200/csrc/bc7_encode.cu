@@ -5,10 +5,11 @@
 // compressionParams.bc7_params[4] (:59-63; ThirdParty/bc7enc_rdo/bc7enc.cpp:2402-2438).
 // See bc7_block.cuh for the per-block algorithm and the parity contract.
 //
-// Kernel shape: persistent 128-thread CTAs.  A CTA stages a tile of 256 consecutive blocks (16 KB of RGBA8)
+// Kernel shape: persistent 128-thread CTAs, one resident wave, tiles claimed from a per-launch counter (tile cost
+// varies several-fold with content).  A CTA stages a tile of 128 consecutive blocks (8 KB of RGBA8)
 // into shared memory with TMA bulk copies, sorts the tile's blocks into opaque ones and ones with alpha
 // (the two classes run different mode sets, bc7enc.cpp:2428-2437; sorted so that at most one warp per tile
-// holds both), and every thread then encodes one block at a time from a transposed copy of its 16 texels.
+// holds both), and every thread then encodes one block from a transposed copy of its 16 texels.
 // Algorithmic HBM bytes: 5 B/px; the kernel is ALU-bound by about three orders of magnitude.
 #include "hkbcn_common.cuh"
 #include "hkbcn_kernels.h"
@@ -19,18 +20,34 @@ namespace hkbcn {
 
 __device__ bc7::Tables g_bc7_tables;
 
-constexpr int BC7_NT = 128;
-constexpr int BC7_TB = 256;
+#ifndef BC7_DYNAMIC
+#define BC7_DYNAMIC 1
+#endif
+#ifndef BC7_TILE_BLOCKS
+#define BC7_TILE_BLOCKS 512
+#endif
+#ifndef BC7_PHASE_SYNC
+#define BC7_PHASE_SYNC 1
+#endif
+#ifndef BC7_THREADS
+#define BC7_THREADS 512
+#endif
+constexpr int BC7_NT = BC7_THREADS;
+constexpr int BC7_OCC = 512 / BC7_NT; // 128 registers per thread
+constexpr int BC7_TB = BC7_TILE_BLOCKS;
+constexpr size_t BC7_SMEM = 4 * BC7_TB * 16 + 64 * BC7_NT + sizeof(bc7::Tables); // stage, transposed texels, tables
 
-__global__ void __launch_bounds__(BC7_NT, 4) bc7_encode_kernel(const __grid_constant__ EncodeParams P)
+__global__ void __launch_bounds__(BC7_NT, BC7_OCC) bc7_encode_kernel(const __grid_constant__ EncodeParams P)
 {
     constexpr int ROWB = BC7_TB * 16;
-    __shared__ __align__(128) uint8_t stage[4 * ROWB];
-    __shared__ __align__(16) bc7::Tables T;
-    __shared__ __align__(16) uint32_t tpx[16 * BC7_NT];
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* const stage = smem;                                   // 4 * ROWB
+    uint32_t* const tpx = (uint32_t*)(smem + 4 * ROWB);            // 16 * BC7_NT words
+    bc7::Tables& T = *(bc7::Tables*)(smem + 4 * ROWB + 64 * BC7_NT);
     __shared__ __align__(8) uint64_t bar;
-    __shared__ uint8_t order[BC7_TB];
+    __shared__ uint16_t order[BC7_TB];
     __shared__ uint32_t count[2];
+    __shared__ uint32_t nextTile;
 
     {
         const uint32_t* src = (const uint32_t*)&g_bc7_tables;
@@ -47,7 +64,8 @@ __global__ void __launch_bounds__(BC7_NT, 4) bc7_encode_kernel(const __grid_cons
     blk.px = tpx + threadIdx.x;
     blk.stride = BC7_NT;
 
-    for (uint32_t tile = blockIdx.x; tile < P.totalTiles; tile += gridDim.x) {
+    uint32_t tile = blockIdx.x;
+    while (tile < P.totalTiles) {
         const Level& L = P.lv[find_level(P, tile)];
         const uint32_t b0 = (tile - L.tileBase) * BC7_TB;
         const uint32_t nb = min((uint32_t)BC7_TB, L.nblocks - b0);
@@ -75,9 +93,29 @@ __global__ void __launch_bounds__(BC7_NT, 4) bc7_encode_kernel(const __grid_cons
         __syncthreads();
 #pragma unroll
         for (int q = 0; q < BC7_TB / BC7_NT; q++)
-            if (cls[q] < 2) order[slot[q] + (cls[q] ? count[0] : 0)] = (uint8_t)(threadIdx.x + q * BC7_NT);
+            if (cls[q] < 2) order[slot[q] + (cls[q] ? count[0] : 0)] = (uint16_t)(threadIdx.x + q * BC7_NT);
         __syncthreads();
 
+#if BC7_PHASE_SYNC
+#pragma unroll 1
+        for (uint32_t base = 0; base < nb; base += BC7_NT) {
+            const uint32_t item = base + threadIdx.x;
+            const int c = item < nb ? (item >= count[0] ? 1 : 0) : 2;
+            const uint32_t k = c < 2 ? order[item] : 0;
+            if (c < 2) {
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const uint4 v = *(const uint4*)(stage + r * ROWB + k * 16);
+                    tpx[(4 * r + 0) * BC7_NT + threadIdx.x] = v.x;
+                    tpx[(4 * r + 1) * BC7_NT + threadIdx.x] = v.y;
+                    tpx[(4 * r + 2) * BC7_NT + threadIdx.x] = v.z;
+                    tpx[(4 * r + 3) * BC7_NT + threadIdx.x] = v.w;
+                }
+            }
+            const uint4 out = bc7::encode_phased(blk, T, c);
+            if (c < 2) *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
+        }
+#else
 #pragma unroll 1
         for (uint32_t item = threadIdx.x; item < nb; item += BC7_NT) {
             const uint32_t k = order[item];
@@ -92,7 +130,18 @@ __global__ void __launch_bounds__(BC7_NT, 4) bc7_encode_kernel(const __grid_cons
             const uint4 out = (item >= count[0]) ? bc7::encode_alpha(blk, T) : bc7::encode_opaque(blk, T);
             *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }
+#endif
+        // tile cost varies several-fold with content (opaque vs alpha, flat vs busy), so tiles are claimed, not strided
+        if (threadIdx.x == 0) nextTile = BC7_DYNAMIC ? gridDim.x + atomicAdd(P.sched, 1u) : tile + gridDim.x;
         __syncthreads(); // stage / order are reused by the next tile
+        tile = nextTile;
+    }
+    if (BC7_DYNAMIC && threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(P.sched + 1, 1u) == gridDim.x - 1u) {
+            P.sched[0] = 0;
+            P.sched[1] = 0;
+        }
     }
 }
 
@@ -101,9 +150,15 @@ uint32_t bc7_tile_blocks() { return BC7_TB; }
 cudaError_t launch_bc7_encode(const EncodeParams& P, int sm_count, cudaStream_t stream)
 {
     if (P.totalTiles == 0) return cudaSuccess;
-    const uint32_t g = (uint32_t)sm_count * 4;
+    const uint32_t g = (uint32_t)sm_count * BC7_OCC;
     const int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
-    bc7_encode_kernel<<<grid, BC7_NT, 0, stream>>>(P);
+    static bool once = false; // same value every time, so a race only repeats the call
+    if (!once) {
+        cudaError_t e = cudaFuncSetAttribute(bc7_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BC7_SMEM);
+        if (e != cudaSuccess) return e;
+        once = true;
+    }
+    bc7_encode_kernel<<<grid, BC7_NT, BC7_SMEM, stream>>>(P);
     return cudaGetLastError();
 }
 

@@ -1168,5 +1168,57 @@ __device__ __forceinline__ uint4 encode_alpha(const Block& blk, const Tables& T)
     return out;
 }
 
+// encode_opaque / encode_alpha with the CTA's warps re-aligned between the stages of the search.  The encoder is ~200 KB of
+// SASS against a 32 KB L1.5 instruction cache, so warps at different stages each stream their own instructions from L2;
+// warps inside the same stage share the fetches.  cls: 0 opaque, 1 alpha, 2 no block (takes part in the barriers only).
+// Every thread of the CTA must call this the same number of times.
+__device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T, int cls)
+{
+    uint4 out = make_uint4(0, 0, 0, 0);
+    uint64_t best = 0;
+    if (cls < 2) {
+        Sub r6[1];
+        uint64_t s6;
+        if (cls == 0)
+            color_cell_compression<6, false>(blk, 0, T, r6, s6);
+        else
+            color_cell_compression<6, true>(blk, 0, T, r6, s6);
+        out = pack_mode6(r6[0], s6);
+        best = weighted(r6[0].err);
+    }
+    __syncthreads();
+    uint32_t part = 0;
+    if (best > 0) {
+        if (cls == 1) {
+            Sub r5[1];
+            uint64_t s5, as5;
+            color_cell_compression<5, false>(blk, 0, T, r5, s5);
+            int alo, ahi;
+            const uint32_t aerr = mode5_alpha(blk, T, alo, ahi, as5);
+            const uint64_t e5 = weighted((uint64_t)r5[0].err + aerr);
+            if (e5 < best) {
+                best = e5;
+                out = pack_mode5(r5[0], s5, alo, ahi, as5);
+            }
+            if (best > 0) part = estimate_partition<true>(blk);
+        } else {
+            part = estimate_partition<false>(blk);
+        }
+    }
+    __syncthreads();
+    if (best > 0) {
+        Sub r[2];
+        uint64_t s;
+        if (cls == 1) {
+            color_cell_compression<7, true>(blk, kShape2[part], T, r, s);
+            if (weighted((uint64_t)r[0].err + r[1].err) < best) out = pack_mode17<7>(part, r, s);
+        } else {
+            color_cell_compression<1, false>(blk, kShape2[part], T, r, s);
+            if (weighted((uint64_t)r[0].err + r[1].err) < best) out = pack_mode17<1>(part, r, s);
+        }
+    }
+    return out;
+}
+
 } // namespace bc7
 } // namespace hkbcn

@@ -173,9 +173,11 @@ void add_level(EncodeParams& P, int codec, uint32_t flags, const void* src, void
     P.totalTiles += (L.nblocks + tb - 1) / tb;
 }
 
-int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P, cudaStream_t st)
+int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStream_t st)
 {
-    if (P.totalTiles == 0) return HKBCN_OK;
+    if (P0.totalTiles == 0) return HKBCN_OK;
+    EncodeParams P = P0;
+    P.sched = D->sched + 8 * (D->sched_seq.fetch_add(1, std::memory_order_relaxed) % Device::SCHED_SLOTS); // one 32-byte sector each
     cudaError_t e = cudaSuccess;
     switch (codec) {
     case C_BC4: e = launch_bc45_encode(1, P, D->sm_count, st); break;

@@ -33,6 +33,7 @@ struct EncodeParams {
     uint32_t totalTiles;
     uint32_t flags;
     uint32_t pad;
+    uint32_t* sched; // {next tile, finished CTAs} of this launch (persistent encoders); both zero between launches
 };
 
 // ---- mbarrier / bulk-copy (TMA 1-D) wrappers --------------------------------
