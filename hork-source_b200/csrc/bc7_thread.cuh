@@ -1172,6 +1172,7 @@ __device__ __forceinline__ uint4 encode_alpha(const Block& blk, const Tables& T)
 // SASS against a 32 KB L1.5 instruction cache, so warps at different stages each stream their own instructions from L2;
 // warps inside the same stage share the fetches.  cls: 0 opaque, 1 alpha, 2 no block (takes part in the barriers only).
 // Every thread of the CTA must call this the same number of times.
+#ifdef __CUDACC__
 __device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T, int cls)
 {
     uint4 out = make_uint4(0, 0, 0, 0);
@@ -1219,6 +1220,7 @@ __device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T
     }
     return out;
 }
+#endif
 
 } // namespace bc7
 } // namespace hkbcn
