@@ -382,6 +382,7 @@ def run_gpu(args):
             out["decode"] = decode_sweep(torch, hkbcn, L, d_dst, stream, flush, hbm)
             out["encode_other_formats"] = encode_others(torch, hkbcn, L, stream, flush)
             out["next_rows"] = next_rows(torch, hkbcn, L, stream, flush, hbm)
+            out["cube_bc6h"] = cube_bc6h(torch, hkbcn, L, stream, flush)
             v, dt, cores, sample = time_reference(levels, 1, 0)
             out["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample}
             # the CPU side of the import cascade: the reference's stbir_resize is single-threaded as shipped
@@ -500,6 +501,42 @@ def encode_others(torch, hkbcn, L, stream, flush):
             0, fmt, d_src.data_ptr(), d_dst.data_ptr(), n, n, 0, C.c_void_p(stream.cuda_stream))), 3, 1)
         out[name] = {"Mpix/s": round(n * n / ms / 1e3, 1), "ms": round(ms, 3)}
         del d_src, d_dst
+    return out
+
+
+def cube_bc6h(torch, hkbcn, L, stream, flush, size=1024):
+    """BASELINE.json configs[3]: a 6 x 1024^2 RGBA32F sky cube -> GGX-prefiltered chain (max_lod 10, roughness L/10, 1024^2 ..
+    1^2, the envprobegen.frag arithmetic) -> BC6H_UFLOAT of every level >= 4^2 of every face in ONE launch
+    (hkbcn_compress_slices_dev, ImageStorage order).  Device-resident; the reference's own encoder (CompressBC6h, all host
+    threads) is timed beside it on one 128^2 face level of the same chain."""
+    import time as _t
+    import synth
+    import refshim
+    cs = C.c_void_p(stream.cuda_stream)
+    max_lod = int(np.log2(size))
+    mips = max_lod - 1  # 1024 .. 4
+    cube = torch.from_numpy(np.stack([synth.sky_rgba32f(size, size, 0xB2000006, f) for f in range(6)])).cuda()
+    texels = L.hkbcn_envprobe_texels(max_lod)
+    chain = torch.empty(texels * 4, dtype=torch.float32, device="cuda")
+    ms_pre = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_envprobe_prefilter_dev(0, cube.data_ptr(), size, max_lod, chain.data_ptr(), cs)), 2, 1)
+    px = sum(6 * (size >> i) ** 2 for i in range(mips))
+    dst = torch.empty(L.hkbcn_chain_bytes(64, size, size, 6, mips), dtype=torch.uint8, device="cuda")
+    ms_enc = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_compress_slices_dev(0, 64, chain.data_ptr(), dst.data_ptr(), size, size, 6, mips, 0, cs)), 2, 1)
+    out = {"workload": f"6 x {size}^2 RGBA32F sky cube, GGX-prefiltered chain of {mips} levels ({px} px), BC6H_UFLOAT, one launch",
+           "prefilter_ms": round(ms_pre, 2), "prefilter_Gsamples/s": round(texels * 1024 / ms_pre / 1e6, 1),
+           "encode_ms": round(ms_enc, 1), "encode_Mpix/s": round(px / ms_enc / 1e3, 2),
+           "api": "hkbcn_envprobe_prefilter_dev + hkbcn_compress_slices_dev"}
+    if refshim.have_ref():
+        # bounded CPU sample: face 0 of the 128^2 level of the same prefiltered chain (16384 px), reference CompressBC6h
+        lvl = max_lod - 7
+        off = sum(6 * (size >> i) ** 2 for i in range(lvl)) * 4
+        n = size >> lvl
+        face = chain[off:off + n * n * 4].cpu().numpy()
+        t0 = _t.perf_counter()
+        refshim.compress(64, face, n, n, refshim.hw_threads())
+        dt = _t.perf_counter() - t0
+        out["cpu_reference"] = {"Mpix/s": round(n * n / dt / 1e6, 5), "cores": refshim.hw_threads(), "kind": "reference",
+                                "sample": f"face 0 of the {n}^2 level ({n * n} px), CompressBC6h on all host threads"}
     return out
 
 

@@ -196,15 +196,20 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
 // level i of a chain: max(w>>i,4) x max(h>>i,4) texels (compressed dims clamp to >= 4, Image.cpp:412-416)
 inline uint32_t mip_dim(uint32_t d, uint32_t i) { uint32_t v = d >> i; return v < 4 ? 4 : v; }
 
-int build_chain(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips)
+int build_chain(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips,
+                uint32_t slices = 1)
 {
+    // ImageStorage keeps all slices of a level together (Image.cpp:498-574): `slices` tightly packed w x h surfaces are one
+    // w x (slices*h) surface whose row-major block order is slice 0's blocks, then slice 1's, ... -- no block straddles two
+    // slices because h is a multiple of 4 -- so a sliced level needs no Level entry of its own.
+    if (slices == 0 || (uint64_t)mip_dim(h, 0) * slices > 0x40000000ull) { set_err("slice count %u out of range", slices); return HKBCN_ERR_BAD_ARG; }
     if (mips == 0 || mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range 1..%d", mips, HKBCN_MAX_LEVELS); return HKBCN_ERR_BAD_ARG; }
     memset(&P, 0, sizeof(P));
     P.flags = flags;
     const uint8_t* s = (const uint8_t*)src;
     uint8_t* d = (uint8_t*)dst;
     for (uint32_t i = 0; i < mips; i++) {
-        uint32_t lw = mip_dim(w, i), lh = mip_dim(h, i);
+        uint32_t lw = mip_dim(w, i), lh = mip_dim(h, i) * slices;
         add_level(P, codec, flags, s, d, lw, lh);
         s += (size_t)lw * lh * src_bpp(codec, flags);
         d += (size_t)(lw / 4) * (lh / 4) * blk_bytes(codec);
@@ -212,20 +217,21 @@ int build_chain(EncodeParams& P, int codec, uint32_t flags, const void* src, voi
     return HKBCN_OK;
 }
 
-size_t chain_src_bytes(int codec, uint32_t flags, uint32_t w, uint32_t h, uint32_t mips)
+size_t chain_src_bytes(int codec, uint32_t flags, uint32_t w, uint32_t h, uint32_t mips, uint32_t slices = 1)
 {
     size_t n = 0;
-    for (uint32_t i = 0; i < mips; i++) n += (size_t)mip_dim(w, i) * mip_dim(h, i) * src_bpp(codec, flags);
+    for (uint32_t i = 0; i < mips; i++) n += (size_t)mip_dim(w, i) * mip_dim(h, i) * src_bpp(codec, flags) * slices;
     return n;
 }
 
-int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags)
+int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags,
+                     uint32_t slices = 1)
 {
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
     if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
-    const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips);
-    const size_t dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
+    const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips, slices);
+    const size_t dbytes = hkbcn_chain_bytes(fmt, w, h, slices, mips);
     if (dbytes == 0) return HKBCN_OK;
     std::lock_guard<std::mutex> lk(D->mu);
     CK(cudaSetDevice(D->id));
@@ -234,7 +240,7 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
     if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
     CK(cudaMemcpyAsync(D->d_src, src, sbytes, cudaMemcpyHostToDevice, D->stream));
     EncodeParams P;
-    if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, w, h, mips)) != HKBCN_OK) return rc;
+    if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, w, h, mips, slices)) != HKBCN_OK) return rc;
     if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
     CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
     CK(cudaStreamSynchronize(D->stream));
@@ -557,6 +563,41 @@ int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, void* d_dst
     EncodeParams P;
     if ((rc = build_chain(P, codec, flags, d_src, d_dst, width, height, num_mips)) != HKBCN_OK) return rc;
     return launch_encode(D, fmt, codec, P, (cudaStream_t)stream);
+}
+
+// Sliced storage (cube faces, array layers) in one launch: CubemapImporter's per-face CompressBC6h loop (Image.cpp:2033-2035)
+// and every mip level of every face, src and dst both in ImageStorage order (all slices of level 0, then of level 1, ...).
+int hkbcn_compress_slices_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t slices,
+                              uint32_t num_mips, uint32_t flags, void* stream)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = dev_at(device);
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if ((width & 3) || (height & 3)) { set_err("sliced surfaces must be multiples of 4 texels (Image.cpp:412-413)"); return HKBCN_ERR_BAD_ARG; }
+    if (width == 0 || height == 0) return HKBCN_OK;
+    CK(cudaSetDevice(D->id));
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, flags, d_src, d_dst, width, height, num_mips, slices)) != HKBCN_OK) return rc;
+    return launch_encode(D, fmt, codec, P, (cudaStream_t)stream);
+}
+
+int hkbcn_compress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips,
+                          uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if ((width & 3) || (height & 3)) { set_err("sliced surfaces must be multiples of 4 texels (Image.cpp:412-413)"); return HKBCN_ERR_BAD_ARG; }
+    if (slices == 0) { set_err("slice count 0"); return HKBCN_ERR_BAD_ARG; }
+    return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags, slices);
+}
+
+size_t hkbcn_slices_src_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips, uint32_t flags)
+{
+    const int codec = codec_of(fmt);
+    return codec < 0 ? 0 : chain_src_bytes(codec, flags, width, height, num_mips, slices);
 }
 
 int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, size_t dst_row_stride,

@@ -126,6 +126,16 @@ HKBCN_API int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, v
 HKBCN_API int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height,
                                    uint32_t num_mips, uint32_t flags);
 
+/* Sliced storage (TEXTURE_CUBE faces, array layers) with its mip levels in ONE launch.  Replaces LoadSkyboxImages' per-face
+ * loop `CompressBC6h(face.data, subres.data, w, h, false)` (Image.cpp:2033-2035) and the per-slice / per-mip loops of
+ * CreateImage (Image.cpp:1753-1803).  src and dst are both in ImageStorage order (Image.cpp:498-574): all `slices` surfaces
+ * of level 0, then all of level 1, ...; level i is max(w>>i,4) x max(h>>i,4); width and height multiples of 4. */
+HKBCN_API size_t hkbcn_slices_src_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips, uint32_t flags);
+HKBCN_API int hkbcn_compress_slices_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                        uint32_t slices, uint32_t num_mips, uint32_t flags, void* stream);
+HKBCN_API int hkbcn_compress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices,
+                                    uint32_t num_mips, uint32_t flags);
+
 /* ---- device-side mip cascade ------------------------------------------------
  * The importers build every mip level on the CPU from the previous one with stbir_resize and compress it
  * (Image.cpp:1755-1803 for BC1-5/BC7, :1852-1899 for BC6H; ImageMipmapConfig, Image.h:361-371).  These entry points do the

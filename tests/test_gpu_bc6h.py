@@ -141,3 +141,48 @@ def test_bc6h_structurally_valid():
     mode = got.reshape(-1, 16)[:, 0] & 0x1F
     assert not np.isin(mode, [0x13, 0x17, 0x1B, 0x1F]).any()
     assert np.array_equal(hkbcn.decompress(BC6U, got, n, n), refshim.decompress(BC6U, got, n, n))
+
+
+def cube_levels(size, mips, seed, fn):
+    """ImageStorage order (Image.cpp:498-574): the six faces of level 0, then the six faces of level 1, ..."""
+    return [[fn(lw, lh, seed, f) for f in range(6)] for lw, lh in synth.mip_dims(size, size, mips)]
+
+
+def test_bc6h_cube_slices_one_launch():
+    """Config 4 (CubemapImporter): six RGBA32F faces and their mip levels through hkbcn_compress_slices in ONE launch equal
+    the reference's per-face CompressBC6h loop (Image.cpp:2033-2035) -- each (level, face) subresource byte-identical to the
+    zero-init reference build of that face, at its ImageStorage offset."""
+    size, mips = 32, 4  # 32, 16, 8, 4
+    lv = cube_levels(size, mips, 0xB2000006, synth.sky_rgba32f)
+    src = np.concatenate([f.ravel() for faces in lv for f in faces])
+    n0 = hkbcn.lib().hkbcn_launch_count()
+    got = hkbcn.compress_slices(BC6U, src, size, size, 6, mips)
+    assert hkbcn.lib().hkbcn_launch_count() == n0 + 1
+    assert got.size == hkbcn.lib().hkbcn_chain_bytes(BC6U, size, size, 6, mips)
+    off = 0
+    for (lw, lh), faces in zip(synth.mip_dims(size, size, mips), lv):
+        for f, img in enumerate(faces):
+            want = refshim.compress(BC6U, img, lw, lh, lib=refshim.ref0())
+            assert np.array_equal(got[off:off + want.size], want), f"level {lw}x{lh} face {f} differs"
+            off += want.size
+    assert off == got.size
+
+
+def test_slices_integer_formats_bit_exact():
+    """the same sliced layout for the deterministic encoders (texture arrays / cube faces in CreateImage, Image.cpp:1753-1803)"""
+    size, mips, slices = 64, 5, 6
+    cases = ((hkbcn.BC1_UNORM, lambda w, h, s, f: synth.albedo_rgba8(w, h, s + f)),
+             (hkbcn.BC4_UNORM, lambda w, h, s, f: synth.roughness_r8(w, h, s + f)),
+             (hkbcn.BC5_UNORM, lambda w, h, s, f: synth.normals_rg8(w, h, s + f)),
+             (hkbcn.BC7_UNORM, lambda w, h, s, f: synth.albedo_rgba8(w, h, s + f, "mask")))
+    for fmt, gen in cases:
+        lv = cube_levels(size, mips, 0xB2000010, gen)
+        src = np.concatenate([np.asarray(f).ravel() for faces in lv for f in faces])
+        got = hkbcn.compress_slices(fmt, src, size, size, slices, mips)
+        off = 0
+        for (lw, lh), faces in zip(synth.mip_dims(size, size, mips), lv):
+            for f, img in enumerate(faces):
+                want = refshim.compress(fmt, img, lw, lh)
+                assert np.array_equal(got[off:off + want.size], want), f"fmt {fmt} level {lw}x{lh} slice {f} differs"
+                off += want.size
+        assert off == got.size
