@@ -631,11 +631,19 @@ __device__ __forceinline__ uint4 emit_block(const Layout& L, int mode, uint32_t 
 
 // Refine (bc6h_enc.h:3420-3465) for one (mode, shape): `unq` = the shape's unquantised endpoints from the rough fit.
 // Updates best_err / out when this candidate wins.
+// Refine (bc6h_enc.h:3420-3465) for a GROUP of modes that share endpoint precision and transform (modes 3-5 are all
+// 11-bit base, modes 7-9 all 8-bit base; they differ only in how the delta bits are split over R, G, B).  Everything up to
+// the fit test -- QuantizeEndPts, AssignIndices, SwapIndices, the forward transform, OptimizeEndPoints and the second
+// AssignIndices -- reads only prec[0] and the transform flag, so it is computed once per (group, shape) and each mode of the
+// group then applies its own EndPointsFit and emission.  The reference visits candidates mode-major, rank-minor and keeps
+// the first one reaching the minimum (strict <); here a candidate carries its visiting order `ord = mode * 8 + rank` and
+// ties go to the lower ord, which selects the same candidate whatever the evaluation order.
 template <int N, int NR>
-__device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mode, bool isSigned, uint32_t shapeIdx, const Ep unq[NR], float& best_err,
-                                       uint4& out)
+__device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mode0, int nmodes, int rank, bool isSigned, uint32_t shapeIdx,
+                                       const Ep unq[NR], float& best_err, int& best_ord, uint4& out)
 {
-    const Mode& M = kModes[mode];
+    const Mode& M = kModes[mode0];
+    const bool transformed = M.transformed != 0;
     const uint32_t shape = NR == 2 ? kShape2[shapeIdx] : 0u;
     const int fix1 = NR == 2 ? kAnchor2[shapeIdx] : 0;
     const uint8_t* prec = M.prec[0];
@@ -652,9 +660,13 @@ __device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mo
         }
     assign_indices<N, NR>(blk, shape, org, prec, isSigned, org_idx, org_err);
     swap_indices<N, NR>(shape, fix1, org, org_idx);
-    if (M.transformed) transform_forward<NR>(org);
-    if (!endpoints_fit<NR>(M, isSigned, org)) return;
-    if (M.transformed) transform_inverse<NR>(org, prec, isSigned);
+    if (transformed) transform_forward<NR>(org);
+    uint32_t fits = 0;
+#pragma unroll 1
+    for (int m = 0; m < nmodes; m++)
+        if (endpoints_fit<NR>(kModes[mode0 + m], isSigned, org)) fits |= 1u << m;
+    if (!fits) return;
+    if (transformed) transform_inverse<NR>(org, prec, isSigned);
     // OptimizeEndPoints (:3271-3293): region 0 over g_aPartitionTable[0] (every texel), region 1 over its own texels
     optimize_one<N>(blk, 0xFFFFu, prec, isSigned, org_err[0], org[0], opt[0]);
     if (NR == 2) optimize_one<N>(blk, shape, prec, isSigned, org_err[NR - 1], org[NR - 1], opt[NR - 1]);
@@ -666,17 +678,29 @@ __device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mo
         org_tot += org_err[p];
         opt_tot += opt_err[p];
     }
-    if (M.transformed) transform_forward<NR>(opt);
+    if (transformed) transform_forward<NR>(opt);
+    bool org_fwd = false; // the reference re-applies the forward transform to the (inverse-transformed) original before emitting it
+#pragma unroll 1
+    for (int m = 0; m < nmodes; m++) {
+        if (!(fits >> m & 1u)) continue;
+        const int mode = mode0 + m;
+        const int ord = mode * 8 + rank;
 #ifdef BC6H_DEBUG
-    printf("MY  refine mode %d shape %d org %.1f opt %.1f best %.1f fit %d\n", mode, (int)shapeIdx, org_tot, opt_tot, best_err, (int)endpoints_fit<NR>(M, isSigned, opt));
+        printf("MY  refine mode %d shape %d org %.1f opt %.1f best %.1f fit %d\n", mode, (int)shapeIdx, org_tot, opt_tot, best_err, (int)endpoints_fit<NR>(kModes[mode], isSigned, opt));
 #endif
-    if (endpoints_fit<NR>(M, isSigned, opt) && opt_tot < org_tot && opt_tot < best_err) {
-        best_err = opt_tot;
-        out = emit_block<N, NR>(L, mode, shapeIdx, fix1, opt, opt_idx);
-    } else if (org_tot < best_err) {
-        if (M.transformed) transform_forward<NR>(org);
-        best_err = org_tot;
-        out = emit_block<N, NR>(L, mode, shapeIdx, fix1, org, org_idx);
+        if (endpoints_fit<NR>(kModes[mode], isSigned, opt) && opt_tot < org_tot && (opt_tot < best_err || (opt_tot == best_err && ord < best_ord))) {
+            best_err = opt_tot;
+            best_ord = ord;
+            out = emit_block<N, NR>(L, mode, shapeIdx, fix1, opt, opt_idx);
+        } else if (org_tot < best_err || (org_tot == best_err && ord < best_ord)) {
+            if (transformed && !org_fwd) {
+                transform_forward<NR>(org);
+                org_fwd = true;
+            }
+            best_err = org_tot;
+            best_ord = ord;
+            out = emit_block<N, NR>(L, mode, shapeIdx, fix1, org, org_idx);
+        }
     }
 }
 
@@ -717,17 +741,25 @@ __device__ __forceinline__ uint4 encode_block(const Block& blk, const Layout& L,
         rough_region<8>(blk, ~kShape2[order[i]] & 0xFFFFu, isSigned, unq8[i][0]);
         rough_region<8>(blk, kShape2[order[i]], isSigned, unq8[i][1]);
     }
-    // mode-major, rank-minor, as the reference visits them (:2916-2950): the first candidate reaching the minimum wins
+    // The reference visits mode-major, rank-minor (:2916-2950) and the first candidate reaching the minimum wins.  Modes of
+    // equal endpoint precision are refined together (see refine); a zero error ends the search once no unvisited candidate
+    // precedes the holder in the reference's order.
+    int best_ord = 0x7FFFFFFF;
+    int mode = 0;
 #pragma unroll 1
-    for (int mode = 0; mode < 10 && best_err > 0.0f; mode++)
+    for (int g = 0; g < 6 && best_err > 0.0f; g++) {
+        const int nm = (g == 2 || g == 4) ? 3 : 1; // {1} {2} {3,4,5} {6} {7,8,9} {10}
 #pragma unroll 1
-        for (int i = 0; i < 8 && best_err > 0.0f; i++) refine<8, 2>(blk, L, mode, isSigned, order[i], unq8[i], best_err, out);
+        for (int i = 0; i < 8 && (best_err > 0.0f || best_ord > mode * 8 + i); i++)
+            refine<8, 2>(blk, L, mode, nm, i, isSigned, order[i], unq8[i], best_err, best_ord, out);
+        mode += nm;
+    }
     // ---- one-region family (modes 11-14): a single shape
     if (best_err > 0.0f) {
         Ep unq1[1];
         rough_region<16>(blk, 0xFFFFu, isSigned, unq1[0]);
 #pragma unroll 1
-        for (int mode = 10; mode < 14 && best_err > 0.0f; mode++) refine<16, 1>(blk, L, mode, isSigned, 0, unq1, best_err, out);
+        for (int mode1 = 10; mode1 < 14 && best_err > 0.0f; mode1++) refine<16, 1>(blk, L, mode1, 1, 0, isSigned, 0, unq1, best_err, best_ord, out);
     }
     return out;
 }
