@@ -11,6 +11,7 @@
 // (the two classes run different mode sets, bc7enc.cpp:2428-2437; sorted so that at most one warp per tile
 // holds both), and every thread then encodes one block from a transposed copy of its 16 texels.
 // Algorithmic HBM bytes: 5 B/px; the kernel is ALU-bound by about three orders of magnitude.
+#include <atomic>
 #include "hkbcn_common.cuh"
 #include "hkbcn_kernels.h"
 #include "bc7_thread.cuh"
@@ -152,11 +153,16 @@ cudaError_t launch_bc7_encode(const EncodeParams& P, int sm_count, cudaStream_t 
     if (P.totalTiles == 0) return cudaSuccess;
     const uint32_t g = (uint32_t)sm_count * BC7_OCC;
     const int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
-    static bool once = false; // same value every time, so a race only repeats the call
-    if (!once) {
+    // function attributes live in the device's context: once per DEVICE, not per process (a second GPU launching with the
+    // first one's flag set fails with "invalid argument").  Same value every time, so a race only repeats the call.
+    static std::atomic<uint64_t> done{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
         cudaError_t e = cudaFuncSetAttribute(bc7_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BC7_SMEM);
         if (e != cudaSuccess) return e;
-        once = true;
+        done.fetch_or(bit, std::memory_order_release);
     }
     bc7_encode_kernel<<<grid, BC7_NT, BC7_SMEM, stream>>>(P);
     return cudaGetLastError();

@@ -11,6 +11,7 @@
 // threads of a warp hold 32 horizontally adjacent blocks, so each of the 4 row stores of a
 // warp is one contiguous run (32 x 16 B = 512 B for RGBA8) written with 128-bit stores --
 // no shared-memory transpose needed.  BC4 packs 4 blocks per thread to reach 128-bit stores.
+#include <atomic>
 #include "hkbcn_common.cuh"
 #include "hkbcn_kernels.h"
 #include "bcn_tables.cuh"
@@ -985,13 +986,16 @@ template <bool F32, bool SIGNED>
 static cudaError_t launch_bc6h_lean(const DecodeParams& P, int sm_count, uint32_t nTiles, bool rows, cudaStream_t stream)
 {
     constexpr int stage = 4 * D7_NT * (F32 ? 48 : 24);
-    static bool attr_set[2] = {false, false};
+    static std::atomic<uint64_t> attr_set[2]; // bit per device: function attributes live in the device's context
     static int occ[2] = {0, 0};
-    if (!attr_set[rows]) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(attr_set[rows].load(std::memory_order_acquire) & bit)) {
         cudaError_t e = rows ? cudaFuncSetAttribute(decode_bc6h_lean_kernel<F32, SIGNED, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage)
                              : cudaFuncSetAttribute(decode_bc6h_lean_kernel<F32, SIGNED, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, stage);
         if (e != cudaSuccess) return e;
-        attr_set[rows] = true; // per process; attributes are per device context but the value never changes
+        attr_set[rows].fetch_or(bit, std::memory_order_release);
     }
     if (rows) {
         const uint32_t grid = resident_grid(decode_bc6h_lean_kernel<F32, SIGNED, true>, stage, sm_count, nTiles, &occ[1]);

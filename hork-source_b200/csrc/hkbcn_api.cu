@@ -361,11 +361,112 @@ size_t hkbcn_chain_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slic
     return n;
 }
 
+// ---- one large surface over several GPUs: horizontal bands of whole block rows -------------------------
+// Blocks are independent and a band of block rows [r0, r1) of a tightly packed level is one contiguous range of the source
+// (texel rows 4*r0 .. 4*r1) and of the destination (blocks r0*nbx .. r1*nbx), so GPU d takes band d of EVERY level, encodes
+// its pieces in one launch and copies each piece to its final offset of the caller's buffer ("host gather").  No exchange.
+int hkbcn_plan_bands(uint32_t height, uint32_t num_mips, int n_gpus, int device, uint32_t* row0, uint32_t* row1)
+{
+    if (n_gpus <= 0 || device < 0 || device >= n_gpus || !row0 || !row1) { set_err("bad arguments"); return HKBCN_ERR_BAD_ARG; }
+    for (uint32_t i = 0; i < num_mips; i++) {
+        const uint64_t nby = mip_dim(height, i) / 4;
+        row0[i] = (uint32_t)(nby * (uint64_t)device / (uint64_t)n_gpus);
+        row1[i] = (uint32_t)(nby * (uint64_t)(device + 1) / (uint64_t)n_gpus);
+    }
+    return HKBCN_OK;
+}
+
+static int compress_bands_on(Device* D, int d, int nd, int fmt, int codec, const uint8_t* src, uint8_t* dst, uint32_t w, uint32_t h,
+                             uint32_t mips, uint32_t flags)
+{
+    uint32_t r0[HKBCN_MAX_LEVELS], r1[HKBCN_MAX_LEVELS];
+    int rc = hkbcn_plan_bands(h, mips, nd, d, r0, r1);
+    if (rc) return rc;
+    const uint32_t bpp = src_bpp(codec, flags), bb = blk_bytes(codec);
+    size_t sbytes = 0, dbytes = 0;
+    for (uint32_t i = 0; i < mips; i++) {
+        const size_t rows = r1[i] - r0[i];
+        sbytes += rows * 4 * mip_dim(w, i) * bpp;
+        dbytes += rows * (mip_dim(w, i) / 4) * bb;
+    }
+    if (dbytes == 0) return HKBCN_OK;
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    EncodeParams P;
+    memset(&P, 0, sizeof(P));
+    P.flags = flags;
+    size_t so = 0, dof = 0, ls = 0, ld = 0; // offsets in the device staging / in the caller's chain
+    for (uint32_t i = 0; i < mips; i++) {
+        const uint32_t lw = mip_dim(w, i), lh = mip_dim(h, i);
+        const size_t rows = r1[i] - r0[i];
+        if (rows) {
+            const size_t sb = rows * 4 * lw * bpp, db = rows * (lw / 4) * bb;
+            CK(cudaMemcpyAsync((uint8_t*)D->d_src + so, src + ls + (size_t)r0[i] * 4 * lw * bpp, sb, cudaMemcpyHostToDevice, D->stream));
+            add_level(P, codec, flags, (uint8_t*)D->d_src + so, (uint8_t*)D->d_dst + dof, lw, (uint32_t)rows * 4);
+            so += sb;
+            dof += db;
+        }
+        ls += (size_t)lw * lh * bpp;
+        ld += (size_t)(lw / 4) * (lh / 4) * bb;
+    }
+    if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
+    dof = 0;
+    ld = 0;
+    for (uint32_t i = 0; i < mips; i++) {
+        const uint32_t lw = mip_dim(w, i), lh = mip_dim(h, i);
+        const size_t rows = r1[i] - r0[i];
+        if (rows) {
+            const size_t db = rows * (lw / 4) * bb;
+            CK(cudaMemcpyAsync(dst + ld + (size_t)r0[i] * (lw / 4) * bb, (uint8_t*)D->d_dst + dof, db, cudaMemcpyDeviceToHost, D->stream));
+            dof += db;
+        }
+        ld += (size_t)(lw / 4) * (lh / 4) * bb;
+    }
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_compress_chain_multi(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags,
+                               int n_gpus)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if ((width & 3) || (height & 3) || !width || !height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+    if (num_mips == 0 || num_mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range 1..%d", num_mips, HKBCN_MAX_LEVELS); return HKBCN_ERR_BAD_ARG; }
+    if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    const int avail = (int)g_devs.size();
+    // n_gpus > 0: that many of the selected GPUs; 0: all of them; < 0: -n_gpus bands dealt round-robin over the selected GPUs
+    // (more bands than devices -- lets a one-GPU box run the banded path)
+    if (n_gpus < -64) { set_err("at most 64 bands"); return HKBCN_ERR_BAD_ARG; }
+    const int nd = n_gpus < 0 ? -n_gpus : (n_gpus == 0 || n_gpus > avail ? avail : n_gpus);
+    if (nd == 1) return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags);
+    std::vector<std::thread> th;
+    std::vector<int> err(nd, 0);
+    std::vector<std::string> msg(nd);
+    for (int d = 0; d < nd; d++)
+        th.emplace_back([&, d]() {
+            err[d] = compress_bands_on(g_devs[(size_t)d % (size_t)avail], d, nd, fmt, codec, (const uint8_t*)src, (uint8_t*)dst, width, height, num_mips, flags);
+            if (err[d]) msg[d] = t_err;
+        });
+    for (auto& t : th) t.join();
+    for (int d = 0; d < nd; d++)
+        if (err[d]) { set_err("%s", msg[d].c_str()); return err[d]; }
+    return HKBCN_OK;
+}
+
+// a surface this large is worth splitting over the selected GPUs (each has its own PCIe link and its own SMs)
+static bool worth_banding(uint32_t w, uint32_t h) { return g_devs.size() > 1 && (uint64_t)w * h >= (4u << 20); }
+
 int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t flags)
 {
     int rc = ensure_init();
     if (rc) return rc;
     if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK; // reference: zero blocks, nothing written
+    if (!(width & 3) && worth_banding(width, height)) return hkbcn_compress_chain_multi(fmt, src, dst, width, height & ~3u, 1, flags, 0);
     return compress_host_on(g_devs[0], fmt, src, dst, width & ~3u, height & ~3u, 1, flags) ;
 }
 
@@ -374,6 +475,7 @@ int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, ui
     int rc = ensure_init();
     if (rc) return rc;
     if ((width & 3) || (height & 3)) { set_err("chain dims must be multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+    if (worth_banding(width, height)) return hkbcn_compress_chain_multi(fmt, src, dst, width, height, num_mips, flags, 0);
     return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags);
 }
 

@@ -28,7 +28,7 @@ EXPORTS = [
     "hkbcn_block_bytes", "hkbcn_src_texel_bytes", "hkbcn_dst_texel_bytes", "hkbcn_calc_num_mips", "hkbcn_chain_bytes",
     "hkbcn_compress", "hkbcn_decompress", "hkbcn_encode_blocks", "hkbcn_decode_blocks",
     "hkbcn_compress_dev", "hkbcn_decompress_dev", "hkbcn_compress_chain_dev", "hkbcn_compress_chain",
-    "hkbcn_slices_src_bytes", "hkbcn_compress_slices_dev", "hkbcn_compress_slices",
+    "hkbcn_slices_src_bytes", "hkbcn_compress_slices_dev", "hkbcn_compress_slices", "hkbcn_compress_chain_multi", "hkbcn_plan_bands",
     "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
     "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
     "hkbcn_texture_header", "hkbcn_write_texture", "hkbcn_read_texture", "hkbcn_import_batch",
@@ -90,6 +90,8 @@ def lib():
         L.hkbcn_slices_src_bytes.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
         L.hkbcn_compress_slices_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         L.hkbcn_compress_slices.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_compress_chain_multi.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
+        L.hkbcn_plan_bands.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.hkbcn_compress_batch.argtypes = [C.POINTER(Job), C.c_size_t]
         L.hkbcn_plan_batch.argtypes = [C.POINTER(Job), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
         L.hkbcn_mip_taps.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
@@ -167,6 +169,20 @@ def compress_slices(fmt, src, width, height, slices, mips, flags=0):
     dst = np.zeros(lib().hkbcn_chain_bytes(fmt, width, height, slices, mips), np.uint8)
     check(lib().hkbcn_compress_slices(fmt, _ptr(src), _ptr(dst), width, height, slices, mips, flags))
     return dst
+
+
+def compress_chain_multi(fmt, src, width, height, mips, n_gpus=0, flags=0):
+    """One chain over several GPUs in bands of block rows; n_gpus < 0 = that many bands over the selected GPUs."""
+    src = np.ascontiguousarray(src)
+    dst = np.zeros(lib().hkbcn_chain_bytes(fmt, width, height, 1, mips), np.uint8)
+    check(lib().hkbcn_compress_chain_multi(fmt, _ptr(src), _ptr(dst), width, height, mips, flags, n_gpus))
+    return dst
+
+
+def plan_bands(height, mips, n_gpus, device):
+    r0, r1 = (C.c_uint32 * mips)(), (C.c_uint32 * mips)()
+    check(lib().hkbcn_plan_bands(height, mips, n_gpus, device, r0, r1))
+    return list(r0), list(r1)
 
 
 def encode_blocks(fmt, src, n, flags=0):

@@ -136,6 +136,15 @@ HKBCN_API int hkbcn_compress_slices_dev(int device, int fmt, const void* d_src, 
 HKBCN_API int hkbcn_compress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices,
                                     uint32_t num_mips, uint32_t flags);
 
+/* One large surface (or pre-built chain) over several GPUs: GPU d encodes band d -- whole block rows -- of every level and
+ * copies it to its final offset in dst; no exchange between GPUs.  n_gpus: 0 = all GPUs selected by
+ * hkbcn_init, n > 0 = the first n of them, n < 0 = -n bands dealt round-robin over them.  hkbcn_compress and
+ * hkbcn_compress_chain take this path by themselves for surfaces of 4 Mpix and more when several GPUs are selected.
+ * hkbcn_plan_bands (host only): block-row range [row0[i], row1[i]) of level i that `device` of `n_gpus` encodes. */
+HKBCN_API int hkbcn_compress_chain_multi(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                                         uint32_t flags, int n_gpus);
+HKBCN_API int hkbcn_plan_bands(uint32_t height, uint32_t num_mips, int n_gpus, int device, uint32_t* row0, uint32_t* row1);
+
 /* ---- device-side mip cascade ------------------------------------------------
  * The importers build every mip level on the CPU from the previous one with stbir_resize and compress it
  * (Image.cpp:1755-1803 for BC1-5/BC7, :1852-1899 for BC6H; ImageMipmapConfig, Image.h:361-371).  These entry points do the

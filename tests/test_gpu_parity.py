@@ -263,3 +263,18 @@ def test_batch_api_matches_single():
     outs = hkbcn.compress_batch(jobs)
     for (fmt, src, w, h, _), o in zip(jobs, outs):
         assert np.array_equal(o, refshim.compress(fmt, src, w, h))
+
+
+@pytest.mark.parametrize("n_gpus", [0, -3, -7])
+def test_banded_chain_equals_single_device(n_gpus):
+    """one surface split over GPUs in bands of whole block rows.  n_gpus = 0 uses every GPU on the box; negative
+    counts deal that many bands over the GPUs there are, so the banded path also runs on a one-GPU box.  Bands of a level that
+    has fewer block rows than bands are empty for some devices (the 4^2 and 8^2 levels here)."""
+    w, h = 128, 64
+    mips = hkbcn.lib().hkbcn_calc_num_mips(w, h)
+    for fmt, gen in ((BC1, lambda lw, lh: synth.albedo_rgba8(lw, lh, 21)), (BC5, lambda lw, lh: synth.normals_rg8(lw, lh, 22)),
+                     (BC7, lambda lw, lh: synth.albedo_rgba8(lw, lh, 23, "mask"))):
+        src = np.concatenate([np.asarray(gen(lw, lh)).ravel() for lw, lh in synth.mip_dims(w, h, mips)])
+        want = hkbcn.compress_chain(fmt, src, w, h, mips)
+        got = hkbcn.compress_chain_multi(fmt, src, w, h, mips, n_gpus)
+        assert np.array_equal(got, want), f"fmt {fmt}, n_gpus {n_gpus}"

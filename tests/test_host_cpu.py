@@ -82,3 +82,18 @@ def test_lean_decoders_match_reference_on_host(tmp_path):
     subprocess.run(["g++", "-O2", "-std=c++17", "-DWITH_BC7", "-o", exe, os.path.join(ROOT, "tools", "decode_host_check.cpp"), "-ldl"], check=True)
     out = subprocess.run([exe, refshim.REF_PATH, "60000"], capture_output=True, text=True, check=True).stdout.strip().splitlines()[-1]
     assert out.endswith(", 0 differ") and int(out.split()[0]) > 500000, out
+
+
+def test_plan_bands_tiles_every_level():
+    """hkbcn_plan_bands (host only): the bands of n GPUs partition the block rows of every level, in order, without overlap"""
+    import hkbcn
+    for height, mips in ((4096, 11), (64, 5), (4, 1), (1000, 6)):
+        for n in (1, 2, 3, 8):
+            edges = [hkbcn.plan_bands(height, mips, n, d) for d in range(n)]
+            for lvl in range(mips):
+                nby = max(height >> lvl, 4) // 4
+                assert edges[0][0][lvl] == 0 and edges[-1][1][lvl] == nby
+                for d in range(1, n):
+                    assert edges[d][0][lvl] == edges[d - 1][1][lvl]
+                sizes = [e[1][lvl] - e[0][lvl] for e in edges]
+                assert max(sizes) - min(sizes) <= 1
