@@ -219,6 +219,232 @@ std::vector<std::string> split_ws(const std::string& line)
     return t;
 }
 
+// ---- CubemapImporter (Tools/CubemapImporter/Main.cpp:58-145 -> LoadSkyboxImages, Image.cpp:1918-2040) -------------------
+//     -cubemap -s <six face files: +X -X +Y -Y +Z -Z> -o <file> -format BC6H_UFLOAT | BC1_UNORM_SRGB [-hdri_scale v] [-hdri_pow v]
+// The six faces are compressed in ONE launch (hkbcn_compress_slices, ImageStorage order) and written as a TEXTURE_CUBE
+// storage of six slices, one mip, IMAGE_STORAGE_NO_ALPHA (Image.cpp:2002-2011).  The reference's uncompressed skybox
+// formats (SRGBA8 / SBGRA8 / R11G11B10F) are not block compression and stay out; faces whose size is not a multiple of 4
+// would need its Mitchell / clamp pre-resample (Image.cpp:1960-1982), which is the CPU -resample pre-pass left out above.
+int run_cubemap(const std::vector<std::string>& t, uint32_t mask)
+{
+    std::string faces[6], out, format = "BC6H_UFLOAT";
+    float scale = 1.0f, pw = 1.0f;
+    int nf = 0;
+    for (size_t i = 0; i < t.size(); i++) {
+        if (t[i] == "-cubemap") continue;
+        if (t[i] == "-s" && i + 6 < t.size()) { for (nf = 0; nf < 6; nf++) faces[nf] = t[++i]; }
+        else if (t[i] == "-o" && i + 1 < t.size()) out = t[++i];
+        else if (t[i] == "-format" && i + 1 < t.size()) format = t[++i];
+        else if (t[i] == "-hdri_scale" && i + 1 < t.size()) scale = (float)atof(t[++i].c_str());
+        else if (t[i] == "-hdri_pow" && i + 1 < t.size()) pw = (float)atof(t[++i].c_str());
+        else { fprintf(stderr, "unknown or incomplete flag '%s'\n", t[i].c_str()); return -1; }
+    }
+    if (out.empty()) { fprintf(stderr, "Output file is not specified. Use -o <filename>\n"); return -1; }
+    if (nf != 6) { fprintf(stderr, "Source files not specified. Use -s <cubemap faces>\n"); return -1; }
+    const int fmt = find_format(format);
+    if (fmt != HKBCN_BC6H_UFLOAT && fmt != HKBCN_BC1_UNORM_SRGB) { fprintf(stderr, "Unexpected texture format %s\n", format.c_str()); return -1; }
+    if (hkbcn_init(mask) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+    const bool hdri = fmt == HKBCN_BC6H_UFLOAT;
+    uint32_t w = 0;
+    uint8_t* packed = nullptr;
+    size_t face_bytes = 0;
+    for (int f = 0; f < 6; f++) {
+        Pixels p;
+        std::string err;
+        printf("Loading %s...\n", faces[f].c_str());
+        const bool ok = faces[f].rfind("gen:", 0) == 0 ? generate(faces[f], p, err) : read_pnm(faces[f], p, err);
+        if (!ok) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        if (f == 0) w = p.w;
+        if (p.w != w || p.w != p.h) { fprintf(stderr, "LoadSkyboxImages: Invalid image size\n"); return -1; }
+        if (w & 3) { fprintf(stderr, "face size %u is not a multiple of the block size 4 (pre-resample is not part of this tool)\n", w); return -1; }
+        if (hdri && p.is_float && (scale != 1.0f || pw != 1.0f)) // Image.cpp:1984-2000
+            for (size_t j = 0; j < p.f32.size(); j += (size_t)p.ch)
+                for (int c = 0; c < 3 && c < p.ch; c++) p.f32[j + (size_t)c] = powf(p.f32[j + (size_t)c] * scale, pw);
+        uint8_t* one = nullptr;
+        if (!to_source(p, fmt, one, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        if (f == 0) {
+            face_bytes = (size_t)w * w * (size_t)hkbcn_src_texel_bytes(fmt, 0);
+            packed = (uint8_t*)hkbcn_alloc_pinned(6 * face_bytes);
+            if (!packed) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        }
+        memcpy(packed + (size_t)f * face_bytes, one, face_bytes);
+        hkbcn_free_pinned(one);
+    }
+    const size_t nbytes = hkbcn_chain_bytes(fmt, w, w, 6, 1);
+    std::vector<uint8_t> blocks(nbytes);
+    printf("Importing texture %s...\n", out.c_str());
+    const auto t0 = std::chrono::steady_clock::now();
+    if (hkbcn_compress_slices(fmt, packed, blocks.data(), w, w, 6, 1, 0) != HKBCN_OK) { fprintf(stderr, "import failed: %s\n", hkbcn_last_error()); return -1; }
+    hkbcn_texture_desc d;
+    memset(&d, 0, sizeof(d));
+    d.type = HKBCN_TEXTURE_CUBE;
+    d.width = d.height = w;
+    d.depth = 6;
+    d.num_mips = 1;
+    d.fmt = fmt;
+    d.storage_flags = HKBCN_STORAGE_NO_ALPHA;
+    if (hkbcn_write_texture(out.c_str(), &d, blocks.data(), nbytes) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+    const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    printf("cubemap 6 x %u^2, %.1f Mpix in %.3f s: %.2f Mpix/s including upload, download and the file write\n", w, 6.0 * w * w / 1e6, s,
+           6.0 * w * w / 1e6 / s);
+    hkbcn_free_pinned(packed);
+    hkbcn_shutdown();
+    return 0;
+}
+
+// ---- PBRImporter (Tools/PBRImporter/Main.cpp:284-755) -----------------------------------------------------------------
+//     -pbr_preset ORMX_BC1|ORMX_BC3|ORMX_BC7 <out> [-occlusion f ch] [-roughness f ch] [-metallic f ch]
+//     [-displacement_to_alpha f ch | -emission_to_alpha f ch] [-normal <src> <dst>] [-a vMF|Toksvig] [-dx_normal]
+//     [-normal_pack <type>] [-mip_edge_mode m] [-mip_filter f]
+// ORMX: the four maps are gathered into one RGBA8 image (CreateORMX, Main.cpp:86-190: defaults 255 255 0 255), its mips are
+// generated as an RGBA8_UNORM storage with IMAGE_STORAGE_NO_ALPHA (:596-613), the roughness channel of every level >= 1 is
+// updated from the triangle-filtered normals (:616-680), the chain is compressed and written (:683-735).  Normal map:
+// v*2-1 + normalise (:197-206), CreateNormalMap (Image.cpp:2262-2346): pack level 0, mip the PACKED texels (triangle filter,
+// NO_ALPHA), compress every level.  Every step is a libhkbcn call; what stays out is what stays on the CPU in the reference:
+// file decoding, -resample, and the uncompressed presets (ORMX, -no_compress_normals), which are not block compression.
+struct MapArg { std::string file; int ch = 0; };
+
+bool load_rgba8(const std::string& src, Pixels& p, std::vector<uint8_t>& rgba, std::string& err)
+{
+    if (!(src.rfind("gen:", 0) == 0 ? generate(src, p, err) : read_pnm(src, p, err))) return false;
+    if (p.is_float) { err = src + ": an 8-bit source is expected"; return false; }
+    const size_t n = (size_t)p.w * p.h;
+    rgba.resize(n * 4);
+    for (size_t i = 0; i < n; i++)
+        for (int c = 0; c < 4; c++) rgba[i * 4 + (size_t)c] = c < p.ch ? p.u8[i * (size_t)p.ch + (size_t)c] : (c == 3 ? 255 : (p.ch == 1 ? p.u8[i] : 0));
+    return true;
+}
+
+int run_pbr(const std::vector<std::string>& t, uint32_t mask)
+{
+    MapArg maps[4]; // occlusion, roughness, metallic, displacement / emission
+    maps[0].ch = 1; maps[1].ch = 1; maps[2].ch = 0; maps[3].ch = 0; // the reference's default channel indices
+    std::string preset, out_pbr, normal_src, normal_dst;
+    int bake = 0, pack = HKBCN_NORMALS_RGBA_BC1, edge = 0, filter = 0;
+    bool mips = false, dx = false;
+    for (size_t i = 0; i < t.size(); i++) {
+        auto need = [&](int n) { return i + (size_t)n < t.size(); };
+        int which = t[i] == "-occlusion" ? 0 : t[i] == "-roughness" ? 1 : t[i] == "-metallic" ? 2 : (t[i] == "-displacement_to_alpha" || t[i] == "-emission_to_alpha") ? 3 : -1;
+        if (which >= 0 && need(2)) {
+            maps[which].file = t[++i];
+            maps[which].ch = atoi(t[++i].c_str());
+            if (maps[which].ch < 0 || maps[which].ch >= 4) { fprintf(stderr, "Invalid channel index %d\n", maps[which].ch); return -1; }
+        } else if (t[i] == "-pbr_preset" && need(2)) { preset = t[++i]; out_pbr = t[++i]; }
+        else if (t[i] == "-normal" && need(2)) { normal_src = t[++i]; normal_dst = t[++i]; }
+        else if (t[i] == "-a" && need(1)) { ++i; bake = (t[i] == "vMF" || t[i] == "vmf") ? HKBCN_ROUGHNESS_BAKE_VMF : (t[i] == "Toksvig" || t[i] == "toksvig") ? HKBCN_ROUGHNESS_BAKE_TOKSVIG : 0; }
+        else if (t[i] == "-dx_normal") dx = true;
+        else if (t[i] == "-normal_pack" && need(1)) {
+            static const char* names[6] = {"RGBA_BC1_COMPATIBLE", "RG_BC5_COMPATIBLE", "SPHEREMAP_BC5_COMPATIBLE", "STEREOGRAPHIC_BC5_COMPATIBLE",
+                                           "PARABOLOID_BC5_COMPATIBLE", "RGBA_BC3_COMPATIBLE"};
+            ++i;
+            pack = HKBCN_NORMALS_RGBA_BC1; // GetNormalMapPack falls back to RGBA_BC1_COMPATIBLE on an unknown name
+            for (int k = 0; k < 6; k++)
+                if (t[i] == names[k]) pack = k;
+        } else if (t[i] == "-mip_edge_mode" && need(1)) { edge = edge_mode(t[++i]); mips = true; }
+        else if (t[i] == "-mip_filter" && need(1)) { filter = filter_of(t[++i]); mips = true; }
+        else { fprintf(stderr, "unknown or incomplete flag '%s'\n", t[i].c_str()); return -1; }
+    }
+    int fmt = -1;
+    if (!preset.empty()) {
+        fmt = preset == "ORMX_BC1" ? HKBCN_BC1_UNORM : preset == "ORMX_BC3" ? HKBCN_BC3_UNORM : preset == "ORMX_BC7" ? HKBCN_BC7_UNORM : -1;
+        if (fmt < 0) { fprintf(stderr, "Unknown PBR preset: %s (the uncompressed ORMX preset is not block compression)\n", preset.c_str()); return -1; }
+    }
+    if (preset.empty() && normal_src.empty()) { fputs("nothing to do: give -pbr_preset and / or -normal\n", stderr); return -1; }
+    if (hkbcn_init(mask) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+    auto check_dims = [&](uint32_t w, uint32_t h, const char* what) {
+        if ((w & 3) || (h & 3) || (mips && ((w & (w - 1)) || (h & (h - 1))))) {
+            fprintf(stderr, "%s: %u x %u must be a multiple of 4%s (resampling is not part of this tool)\n", what, w, h, mips ? " and a power of two" : "");
+            return false;
+        }
+        return true;
+    };
+    std::string err;
+    // ---- normal map source: Float3 in [0, 1] -> v * 2 - 1, normalised
+    std::vector<float> normals;
+    uint32_t nw = 0, nh = 0;
+    if (!normal_src.empty()) {
+        Pixels p;
+        printf("Loading %s...\n", normal_src.c_str());
+        if (!(normal_src.rfind("gen:", 0) == 0 ? generate(normal_src, p, err) : read_pnm(normal_src, p, err))) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        if (p.ch < 2) { fprintf(stderr, "%s: a normal map needs at least two channels\n", normal_src.c_str()); return -1; }
+        nw = p.w; nh = p.h;
+        if (!check_dims(nw, nh, normal_src.c_str())) return -1;
+        const size_t n = (size_t)nw * nh;
+        normals.resize(n * 3);
+        for (size_t i = 0; i < n; i++)
+            for (int c = 0; c < 3; c++) {
+                float v = c < p.ch ? (p.is_float ? p.f32[i * (size_t)p.ch + (size_t)c] : p.u8[i * (size_t)p.ch + (size_t)c] / 255.0f) : 1.0f;
+                if (dx && c == 1) v = 1.0f - v; // RawImage::InvertGreen
+                normals[i * 3 + (size_t)c] = v;
+            }
+        if (hkbcn_normalize_vectors(normals.data(), n) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    double mpix = 0;
+    // ---- ORMX
+    if (fmt >= 0) {
+        std::vector<uint8_t> ormx;
+        uint32_t w = 0, h = 0;
+        bool any = false;
+        for (int k = 0; k < 4; k++) {
+            if (maps[k].file.empty()) continue;
+            Pixels p;
+            std::vector<uint8_t> rgba;
+            printf("Loading %s...\n", maps[k].file.c_str());
+            if (!load_rgba8(maps[k].file, p, rgba, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+            if (!any) {
+                w = p.w; h = p.h; any = true;
+                ormx.resize((size_t)w * h * 4);
+                for (size_t i = 0; i < (size_t)w * h; i++) { ormx[i * 4] = 255; ormx[i * 4 + 1] = 255; ormx[i * 4 + 2] = 0; ormx[i * 4 + 3] = 255; } // Clear({1, 1, 0, 1})
+            } else if (p.w != w || p.h != h) {
+                fputs("The source images have different sizes. Use the -resample option to configure resampling parameters.\n", stderr);
+                return -1;
+            }
+            for (size_t i = 0; i < (size_t)w * h; i++) ormx[i * 4 + (size_t)k] = rgba[i * 4 + (size_t)maps[k].ch];
+        }
+        if (!any) { fputs("-pbr_preset needs at least one source map\n", stderr); return -1; }
+        if (!check_dims(w, h, "ORMX")) return -1;
+        if (bake && !normals.empty() && (w != nw || h != nh)) { fputs("Can't apply antialiasing. ORMX and NormalMap must be the same size.\n", stderr); return -1; }
+        const uint32_t nm = mips ? hkbcn_calc_num_mips(w, h) : 1;
+        hkbcn_mip_config cfg = {edge, filter, 1, 0};
+        std::vector<uint8_t> chain(hkbcn_chain_src_bytes(HKBCN_BC7_UNORM, w, h, nm, 0));
+        if (nm > 1) {
+            if (hkbcn_generate_mips(HKBCN_BC7_UNORM, ormx.data(), chain.data(), w, h, nm, &cfg, 0) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        } else memcpy(chain.data(), ormx.data(), ormx.size());
+        if (bake && !normals.empty() && nm > 1) {
+            std::vector<uint8_t> rough(chain.size() / 4); // roughness = second channel of every level
+            for (size_t i = 0; i < rough.size(); i++) rough[i] = chain[i * 4 + 1];
+            if (hkbcn_bake_roughness(normals.data(), rough.data(), w, h, nm, bake, 2 /* triangle */, edge) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+            for (size_t i = 0; i < rough.size(); i++) chain[i * 4 + 1] = rough[i];
+        }
+        std::vector<uint8_t> blocks(hkbcn_chain_bytes(fmt, w, h, 1, nm));
+        printf("Importing texture %s...\n", out_pbr.c_str());
+        if (hkbcn_compress_chain(fmt, chain.data(), blocks.data(), w, h, nm, 0) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        hkbcn_texture_desc d = {HKBCN_TEXTURE_2D, w, h, 1, nm, fmt, HKBCN_STORAGE_NO_ALPHA};
+        if (hkbcn_write_texture(out_pbr.c_str(), &d, blocks.data(), blocks.size()) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        mpix += (double)chain.size() / 4e6;
+    }
+    // ---- normal map
+    if (!normals.empty()) {
+        const int nfmt = pack == HKBCN_NORMALS_RGBA_BC1 ? HKBCN_BC1_UNORM : pack == HKBCN_NORMALS_RGBA_BC3 ? HKBCN_BC3_UNORM : HKBCN_BC5_UNORM;
+        const size_t n = (size_t)nw * nh;
+        std::vector<uint8_t> packed(n * (size_t)hkbcn_pack_texel_bytes(pack));
+        if (hkbcn_pack_normals(pack, normals.data(), packed.data(), n) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        const uint32_t nm = mips ? hkbcn_calc_num_mips(nw, nh) : 1;
+        hkbcn_mip_config cfg = {edge, 2 /* IMAGE_RESAMPLE_FILTER_TRIANGLE, Main.cpp:748 */, 1, 0};
+        std::vector<uint8_t> blocks(hkbcn_chain_bytes(nfmt, nw, nh, 1, nm));
+        printf("Importing texture %s...\n", normal_dst.c_str());
+        if (hkbcn_import_chain(nfmt, packed.data(), blocks.data(), nw, nh, nm, &cfg, 0) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        hkbcn_texture_desc d = {HKBCN_TEXTURE_2D, nw, nh, 1, nm, nfmt, HKBCN_STORAGE_NO_ALPHA};
+        if (hkbcn_write_texture(normal_dst.c_str(), &d, blocks.data(), blocks.size()) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        mpix += (double)n * (mips ? 4.0 / 3.0 : 1.0) / 1e6;
+    }
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    printf("PBR import: %.1f Mpix in %.3f s (%.1f Mpix/s including transfers and file writes)\n", mpix, sec, mpix / sec);
+    hkbcn_shutdown();
+    return 0;
+}
+
 const char* kHelp = R"(hk_texture_import -- BCn texture import on the GPU (libhkbcn)
     -h                      -- Help
     -s <filename>           -- Source: binary PGM/PPM (P5/P6), PFM (Pf/PF) or gen:<albedo|mask|rough|normal|sky>:<w>:<h>:<seed>
@@ -230,6 +456,11 @@ const char* kHelp = R"(hk_texture_import -- BCn texture import on the GPU (libhk
     -mip_filter <filter>    -- box | triangle | cubicspline | catmullrom | mitchell
     -batch <manifest>       -- one flag set per line; all lines are imported as one batch sharded over the GPUs
     -gpus <mask>            -- bit mask of the CUDA devices to use (default: all)
+    -pbr_preset / -normal   -- PBRImporter mode: -pbr_preset ORMX_BC1|ORMX_BC3|ORMX_BC7 <out> [-occlusion f ch] [-roughness f ch] [-metallic f ch]
+                               [-displacement_to_alpha f ch | -emission_to_alpha f ch] [-normal <src> <dst>] [-a vMF|Toksvig] [-dx_normal]
+                               [-normal_pack <type>] [-mip_edge_mode m] [-mip_filter f]
+    -cubemap                -- CubemapImporter mode: -s <six faces +X -X +Y -Y +Z -Z> -o <file> -format BC6H_UFLOAT | BC1_UNORM_SRGB
+                               [-hdri_scale <v>] [-hdri_pow <v>]   (result = pow(color * hdri_scale, hdri_pow))
 )";
 
 } // namespace
@@ -243,6 +474,22 @@ int main(int argc, char** argv)
     for (size_t i = 0; i < argvv.size(); i++) {
         if (argvv[i] == "-h") { fputs(kHelp, stdout); return 0; }
         if (argvv[i] == "-gpus" && i + 1 < argvv.size()) { mask = (uint32_t)strtoul(argvv[++i].c_str(), nullptr, 0); continue; }
+        if (argvv[i] == "-pbr_preset" || argvv[i] == "-normal") {
+            std::vector<std::string> rest;
+            for (size_t k = 0; k < argvv.size(); k++) {
+                if (argvv[k] == "-gpus" && k + 1 < argvv.size()) { mask = (uint32_t)strtoul(argvv[++k].c_str(), nullptr, 0); continue; }
+                rest.push_back(argvv[k]);
+            }
+            return run_pbr(rest, mask);
+        }
+        if (argvv[i] == "-cubemap") {
+            std::vector<std::string> rest;
+            for (size_t k = 0; k < argvv.size(); k++) {
+                if (argvv[k] == "-gpus" && k + 1 < argvv.size()) { mask = (uint32_t)strtoul(argvv[++k].c_str(), nullptr, 0); continue; }
+                rest.push_back(argvv[k]);
+            }
+            return run_cubemap(rest, mask);
+        }
         if (argvv[i] == "-batch" && i + 1 < argvv.size()) {
             std::ifstream mf(argvv[++i]);
             if (!mf) { fprintf(stderr, "Failed to open manifest %s\n", argvv[i].c_str()); return -1; }

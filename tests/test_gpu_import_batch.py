@@ -119,3 +119,109 @@ def test_importer_tool_batch_manifest(tmp_path):
     # the reference tool's error behaviour: a missing output name is an error before any work
     r = subprocess.run([tool, "-s", "gen:albedo:64:64:1", "-format", "BC7_UNORM"], capture_output=True, text=True, timeout=60)
     assert r.returncode != 0 and "Output file is not specified" in r.stderr
+
+
+def _write_pfm(path, rgb):
+    """little-endian colour PFM, bottom row first"""
+    h, w, _ = rgb.shape
+    with open(path, "wb") as f:
+        f.write(f"PF\n{w} {h}\n-1.0\n".encode())
+        f.write(np.ascontiguousarray(rgb[::-1].astype("<f4")).tobytes())
+
+
+def test_importer_tool_cubemap_mode(tmp_path):
+    """hk_texture_import -cubemap = Tools/CubemapImporter (Main.cpp:58-145 -> LoadSkyboxImages, Image.cpp:1918-2040): six faces ->
+    TEXTURE_CUBE storage, six slices, one mip, IMAGE_STORAGE_NO_ALPHA; each face's blocks are the reference's CompressBC6h /
+    CompressBC1 of that face (BC6H against the zero-init build, see test_gpu_bc6h.py), -hdri_scale / -hdri_pow applied first."""
+    import os
+    import subprocess
+    tool = os.path.join(os.path.dirname(hkbcn.LIB_PATH), "hk_texture_import")
+    n, scale, pw = 32, 0.5, 1.25
+    faces = [synth.sky_rgba32f(n, n, 0xB2000006, f).reshape(n, n, 4) for f in range(6)]
+    names = []
+    for f, img in enumerate(faces):
+        names.append(str(tmp_path / f"face{f}.pfm"))
+        _write_pfm(names[-1], img[:, :, :3])
+    out = str(tmp_path / "sky.texture")
+    r = subprocess.run([tool, "-cubemap", "-s", *names, "-o", out, "-format", "BC6H_UFLOAT", "-hdri_scale", str(scale), "-hdri_pow", str(pw)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    d, payload = hkbcn.read_texture(out)
+    assert (d.type, d.width, d.height, d.depth, d.num_mips, d.fmt, d.storage_flags) == (5, n, n, 6, 1, 64, 1)
+    want = []
+    for img in faces:
+        adj = img.copy()
+        adj[:, :, :3] = np.power(adj[:, :, :3] * np.float32(scale), np.float32(pw)).astype(np.float32)
+        want.append(refshim.compress(64, adj, n, n, lib=refshim.ref0()))
+    want = np.concatenate(want)
+    same = (payload.reshape(-1, 16) == want.reshape(-1, 16)).all(axis=1)
+    # powf on the host vs numpy's float32 power may differ in the last bit of a few texels; the blocks must still agree
+    # wherever the inputs do -- demand at least 98 % identical blocks and equal size
+    assert payload.nbytes == want.nbytes and same.mean() >= 0.98, f"{100 * same.mean():.2f}% identical"
+    # LDR skybox: BC1_UNORM_SRGB from 8-bit faces, bit-exact
+    names8 = []
+    faces8 = [synth.albedo_rgba8(n, n, 40 + f, "opaque").reshape(n, n, 4) for f in range(6)]
+    for f, img in enumerate(faces8):
+        names8.append(str(tmp_path / f"face{f}.ppm"))
+        _write_pnm(names8[-1], img[:, :, :3])
+    out8 = str(tmp_path / "sky8.texture")
+    r = subprocess.run([tool, "-cubemap", "-s", *names8, "-o", out8, "-format", "BC1_UNORM_SRGB"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    d, payload = hkbcn.read_texture(out8)
+    assert (d.type, d.depth, d.fmt, d.storage_flags) == (5, 6, BC1S, 1)
+    want8 = np.concatenate([refshim.compress(BC1S, img, n, n) for img in faces8])
+    raw = open(out8, "rb").read()
+    assert raw == oracle_texture_file(5, n, n, 6, 1, BC1S, 1, want8.tobytes())
+    # reference error behaviour
+    r = subprocess.run([tool, "-cubemap", "-s", *names8[:3], "-o", out8], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0
+
+
+def test_importer_tool_pbr_mode(tmp_path):
+    """hk_texture_import -pbr_preset ... -normal ... = Tools/PBRImporter (Main.cpp:284-755): ORMX gather (defaults 255 255 0 255),
+    RGBA8 mips with NO_ALPHA, vMF roughness update from the triangle-filtered normals, BC7 chain; normal map normalised, packed
+    RG_BC5, the packed texels mipped with the triangle filter, BC5 chain.  Level 0 of both files is checked against the
+    reference's own encoders on the gathered / packed image, the whole files against the library calls the tool composes
+    (each of which has its own oracle test: test_gpu_mips, test_gpu_normals)."""
+    import os
+    import subprocess
+    tool = os.path.join(os.path.dirname(hkbcn.LIB_PATH), "hk_texture_import")
+    n = 64
+    occl = synth.roughness_r8(n, n, 11).reshape(n, n, 1)
+    rough_src = synth.albedo_rgba8(n, n, 12, "opaque").reshape(n, n, 4)[:, :, :3]  # roughness taken from channel 2 of an RGB file
+    nrm8 = np.concatenate([synth.normals_rg8(n, n, 13).reshape(n, n, 2), np.full((n, n, 1), 255, np.uint8)], axis=2)
+    _write_pnm(tmp_path / "occl.pgm", occl)
+    _write_pnm(tmp_path / "rough.ppm", rough_src)
+    _write_pnm(tmp_path / "normal.ppm", nrm8)
+    out, nout = str(tmp_path / "orm.texture"), str(tmp_path / "normal.texture")
+    r = subprocess.run([tool, "-occlusion", str(tmp_path / "occl.pgm"), "0", "-roughness", str(tmp_path / "rough.ppm"), "2",
+                        "-pbr_preset", "ORMX_BC7", out, "-normal", str(tmp_path / "normal.ppm"), nout, "-a", "vMF",
+                        "-normal_pack", "RG_BC5_COMPATIBLE", "-mip_edge_mode", "wrap", "-mip_filter", "mitchell"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    mips = hkbcn.lib().hkbcn_calc_num_mips(n, n)
+    # what the tool composes
+    ormx = np.empty((n, n, 4), np.uint8)
+    ormx[:, :, 0] = occl[:, :, 0]
+    ormx[:, :, 1] = rough_src[:, :, 2]
+    ormx[:, :, 2] = 0
+    ormx[:, :, 3] = 255
+    normals = hkbcn.normalize_vectors((nrm8.astype(np.float32) / np.float32(255.0)).reshape(-1, 3))
+    chain = hkbcn.generate_mips(BC7, ormx, n, n, mips, hkbcn.MipConfig(3, 5, 1, 0)).copy()
+    rough = hkbcn.bake_roughness(normals, chain[1::4], n, n, mips, 1, 2, 3)
+    assert not np.array_equal(rough, chain[1::4]), "the bake changed nothing: test content too flat"
+    chain[1::4] = rough
+    d, payload = hkbcn.read_texture(out)
+    assert (d.type, d.width, d.height, d.depth, d.num_mips, d.fmt, d.storage_flags) == (2, n, n, 1, mips, BC7, 1)
+    assert np.array_equal(payload, hkbcn.compress_chain(BC7, chain, n, n, mips))
+    assert np.array_equal(payload[: n * n], refshim.compress(BC7, ormx, n, n)), "ORMX level 0 differs from the reference's CompressBC7"
+    packed = hkbcn.pack_normals(1, normals)
+    d, payload = hkbcn.read_texture(nout)
+    assert (d.type, d.width, d.num_mips, d.fmt, d.storage_flags) == (2, n, mips, BC5, 1)
+    assert np.array_equal(payload, hkbcn.import_chain(BC5, packed, n, n, mips, hkbcn.MipConfig(3, 2, 1, 0)))
+    assert np.array_equal(payload[: n * n], refshim.compress(BC5, packed, n, n)), "normal level 0 differs from the reference's CompressBC5"
+    # reference error behaviour: antialiasing needs equal sizes
+    _write_pnm(tmp_path / "occl32.pgm", synth.roughness_r8(32, 32, 11).reshape(32, 32, 1))
+    r = subprocess.run([tool, "-occlusion", str(tmp_path / "occl32.pgm"), "0", "-pbr_preset", "ORMX_BC1", out, "-normal", str(tmp_path / "normal.ppm"),
+                        nout, "-a", "vMF", "-mip_filter", "mitchell"], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "must be the same size" in r.stderr
