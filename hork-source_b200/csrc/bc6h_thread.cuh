@@ -208,8 +208,8 @@ template <int N> __device__ __forceinline__ float map_colors_quantized_body(cons
     palette_quantized<N>(e, prec, isSigned, pal);
     float tot = 0.0f;
 #pragma unroll 1
-    for (int i = 0; i < 16; i++) {
-        if (!((mask >> i) & 1)) continue;
+    for (uint32_t tm = mask & 0xFFFFu; tm; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
+        const int i = __ffs((int)tm) - 1;
         int idx;
         tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
     }
@@ -433,8 +433,8 @@ __device__ __forceinline__ void optimize_rgb4(const Block& blk, uint32_t mask, f
         Y[c] = -FLT_MAX;
     }
 #pragma unroll 1
-    for (int i = 0; i < 16; i++) {
-        if (!((mask >> i) & 1)) continue;
+    for (uint32_t tm = mask & 0xFFFFu; tm; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
+        const int i = __ffs((int)tm) - 1;
 #pragma unroll
         for (int c = 0; c < 3; c++) {
             const float v = blk.hdr(i, c);
@@ -450,8 +450,8 @@ __device__ __forceinline__ void optimize_rgb4(const Block& blk, uint32_t mask, f
     const float Mid[3] = {(X[0] + Y[0]) * 0.5f, (X[1] + Y[1]) * 0.5f, (X[2] + Y[2]) * 0.5f};
     float fDir[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll 1
-    for (int i = 0; i < 16; i++) {
-        if (!((mask >> i) & 1)) continue;
+    for (uint32_t tm = mask & 0xFFFFu; tm; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
+        const int i = __ffs((int)tm) - 1;
         const float pr = (blk.hdr(i, 0) - Mid[0]) * Dir[0], pg = (blk.hdr(i, 1) - Mid[1]) * Dir[1], pb = (blk.hdr(i, 2) - Mid[2]) * Dir[2];
         float f;
         f = pr + pg + pb; fDir[0] += f * f;
@@ -489,8 +489,8 @@ __device__ __forceinline__ void optimize_rgb4(const Block& blk, uint32_t mask, f
         Dir[2] *= fScale;
         float d2X = 0.0f, d2Y = 0.0f, dX[3] = {0.0f, 0.0f, 0.0f}, dY[3] = {0.0f, 0.0f, 0.0f};
 #pragma unroll 1
-        for (int i = 0; i < 16; i++) {
-            if (!((mask >> i) & 1)) continue;
+        for (uint32_t tm = mask & 0xFFFFu; tm; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
+            const int i = __ffs((int)tm) - 1;
             const float p0 = blk.hdr(i, 0), p1 = blk.hdr(i, 1), p2 = blk.hdr(i, 2);
             const float fDot = (p0 - X[0]) * Dir[0] + (p1 - X[1]) * Dir[1] + (p2 - X[2]) * Dir[2];
             int s;
@@ -563,8 +563,8 @@ template <int N> __device__ __forceinline__ float rough_region(const Block& blk,
     }
     float tot = 0.0f;
 #pragma unroll 1
-    for (int i = 0; i < 16; i++) {
-        if (!((mask >> i) & 1)) continue;
+    for (uint32_t tm = mask & 0xFFFFu; tm; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
+        const int i = __ffs((int)tm) - 1;
         int idx;
         tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
     }
