@@ -20,11 +20,14 @@ namespace hkbcn {
 
 __device__ bc6h::Layout g_bc6h_enc_layout;
 
+#ifndef BC6E_CTAS_PER_SM
+#define BC6E_CTAS_PER_SM 7 // resident CTAs per SM the register budget is held to (and the grid is sized by)
+#endif
 constexpr int BC6_NT = 64;
 constexpr int BC6_TB = 64;
 
 template <bool F16SRC>
-__global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_constant__ EncodeParams P, const uint32_t isSigned)
+__global__ void __launch_bounds__(BC6_NT, BC6E_CTAS_PER_SM) bc6h_encode_kernel(const __grid_constant__ EncodeParams P, const uint32_t isSigned)
 {
     constexpr int BPP = F16SRC ? 8 : 16;
     constexpr int ROWB = BC6_TB * 4 * BPP;
@@ -118,9 +121,6 @@ cudaError_t launch_bc6h_encode(bool is_signed, bool src_f16, const EncodeParams&
 {
     if (P.totalTiles == 0) return cudaSuccess;
     // one tile per CTA iteration; the grid is one resident wave (or the tile count if smaller) and CTAs claim further tiles
-#ifndef BC6E_CTAS_PER_SM
-#define BC6E_CTAS_PER_SM 7
-#endif
     const uint32_t g = (uint32_t)sm_count * BC6E_CTAS_PER_SM;
     const int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
     if (src_f16)
