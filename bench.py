@@ -90,6 +90,16 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.t0 = self.t1 = self.tw = None
+
+    def warm(self):
+        self.tw = time.perf_counter()
+
+    def begin(self):
+        self.t0 = time.perf_counter()
+
+    def end(self):
+        self.t1 = time.perf_counter()
 
     def start(self):
         try:
@@ -101,7 +111,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
     def stop(self):
         if self.proc:
@@ -112,7 +122,14 @@ class ClockSampler:
                 self.proc.kill()
         sm, mx, reasons = [], 0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        # nvidia-smi needs 0.1 - 0.5 s to come up (longer on an 8-GPU box), so it is started before the warm-up and the rows
+        # are cut to the timed region by arrival time; a region too short for two rows falls back to warm-up + timed rows
+        # (the same kernel under the same load) and says so
+        rows = [r for t, r in self.rows if self.t0 is None or (self.t0 <= t <= (self.t1 or t))]
+        window = "timed region"
+        if len(rows) < 2:
+            rows, window = [r for t, r in self.rows if self.tw is None or (self.tw <= t <= (self.t1 or t))], "warm-up + timed region"
+        for r in rows:
             try:
                 sm.append(float(r[0]))
                 mx = max(mx, float(r[1]))
@@ -121,7 +138,8 @@ class ClockSampler:
             for n, v in zip(names, r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm),
+                "window": window}
 
 
 def peaks():
@@ -268,6 +286,9 @@ def run_gpu(args):
 
     L = hkbcn.lib()
     hkbcn.init(1 << local)  # library device 0 == cuda:local
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # long before the timed region: nvidia-smi takes a while to come up
     levels = make_chain_gpu(rank_seed(rank))
     mips, px = len(levels), chain_pixels(levels)
     src_np = np.concatenate([l.ravel() for l in levels])
@@ -283,15 +304,14 @@ def run_gpu(args):
     def step():
         hkbcn.check(L.hkbcn_compress_chain_dev(0, BC7, d_src.data_ptr(), d_dst.data_ptr(), SIZE, SIZE, mips, 0, C.c_void_p(stream.cuda_stream)))
 
+    sampler.warm()
     for i in range(max(args.warmup, 3)):
         step()
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     launches0 = L.hkbcn_launch_count()
     evs = []
     barrier()
+    sampler.begin()
     for i in range(args.steps):
         flush.fill_(i & 255)  # evict the input from the 126 MB L2 (untimed)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -300,6 +320,7 @@ def run_gpu(args):
         e1.record(stream)
         evs.append((e0, e1))
     barrier()
+    sampler.end()
     launches = L.hkbcn_launch_count() - launches0
     value, ms_step = whole_job_value(ranks, px, sum(a.elapsed_time(b) for a, b in evs) / args.steps)
     clocks = sampler.stop() if rank == 0 else None
