@@ -123,7 +123,10 @@ template <int CH>
 __global__ void __launch_bounds__(256) mip_resize_u8_kernel(const ResizeParams P)
 {
     __shared__ float lut[256];
+    __shared__ float alut[256]; // alpha decode i / 255.0f: the same IEEE division, once per CTA instead of once per tap (it was
+                                // half of the kernel's instructions)
     lut[threadIdx.x] = P.lut[threadIdx.x];
+    alut[threadIdx.x] = (float)threadIdx.x / 255.0f;
     __syncthreads();
     const int ox = blockIdx.x * 32 + (threadIdx.x & 31), oy = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (ox >= P.out_w || oy >= P.out_h) return;
@@ -140,15 +143,16 @@ __global__ void __launch_bounds__(256) mip_resize_u8_kernel(const ResizeParams P
             const float wx = P.wx[ox * P.Tx + kx];
             const uint8_t* t = row + (size_t)P.ix[ox * P.Tx + kx] * CH;
             float v[CH];
+            int q[CH];
             if constexpr (CH == 4) {
-                const uchar4 q = *(const uchar4*)t;
-                v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+                const uchar4 q4 = *(const uchar4*)t;
+                q[0] = q4.x; q[1] = q4.y; q[2] = q4.z; q[3] = q4.w;
             } else {
 #pragma unroll
-                for (int c = 0; c < CH; c++) v[c] = t[c];
+                for (int c = 0; c < CH; c++) q[c] = t[c];
             }
 #pragma unroll
-            for (int c = 0; c < CH; c++) v[c] = (c == P.alpha) ? v[c] / 255.0f : lut[(int)v[c]];
+            for (int c = 0; c < CH; c++) v[c] = ((c == P.alpha) ? alut : lut)[q[c]];
             if (P.weight) {
                 // alpha weighting (:1375-1400): the epsilon keeps the colour of fully transparent texels
                 float a = 0;
