@@ -151,43 +151,53 @@ def peaks():
 
 
 # ----------------------------------------------------------------------------- reference arm (CPU)
-def ref_sample(levels):
-    """bounded sample of the workload for CPU timing: mip levels 1.. (2048^2 and below, 5,592,400 px = 25% of the chain)"""
-    return levels[1:]
+REF_BUDGET_S = 200.0  # the whole `--impl reference --steps K --warmup W` run should end within a few minutes
 
 
-def time_reference(levels, steps, warmup):
+def time_reference(levels, steps, warmup, keep_blocks=False):
     """the reference's own bc7enc_compress_block (oracle/_ref, unmodified sources) over all host threads,
-    contiguous block ranges per thread (the decomposition CompressBC6h uses, ImageEncoders.cpp:426-486)"""
+    contiguous block ranges per thread (the decomposition CompressBC6h uses, ImageEncoders.cpp:426-486).
+    A step is the WHOLE chain (level 0 included) whenever steps + warmup of it fit REF_BUDGET_S on this host -- probed on
+    mip levels 1.. (25 % of the pixels) -- else that 25 % sample.  Returns (Mpix/s, s per step, threads, sample text, blocks)."""
     import refshim
     if not refshim.have_ref():
         raise SystemExit("oracle/_ref/libhkref.so missing: run `python __graft_entry__.py build` where /root/reference exists")
     cores = refshim.hw_threads()
-    sample = ref_sample(levels)
-    px = chain_pixels(sample)
 
-    def one():
-        for l in sample:
-            refshim.compress(BC7, l, l.shape[1], l.shape[0], cores)
+    def one(sample):
+        return [refshim.compress(BC7, l, l.shape[1], l.shape[0], cores) for l in sample]
+    t0 = time.perf_counter()
+    one(levels[1:])  # probe (doubles as a warm-up: page faults, thread start-up)
+    probe = time.perf_counter() - t0
+    whole = probe * chain_pixels(levels) / chain_pixels(levels[1:]) * (steps + warmup) <= REF_BUDGET_S
+    sample = levels if whole else levels[1:]
+    px = chain_pixels(sample)
     for _ in range(warmup):
-        one()
+        one(sample)
+    blocks = None
     t0 = time.perf_counter()
     for _ in range(steps):
-        one()
+        blocks = one(sample)
     dt = (time.perf_counter() - t0) / steps
-    return px / dt / 1e6, dt, cores, f"mip levels 1..{len(levels) - 1} of the chain ({px} px of {chain_pixels(levels)})"
+    text = (f"the whole chain, levels 0..{len(levels) - 1} ({px} px)" if whole else
+            f"mip levels 1..{len(levels) - 1} of the chain ({px} px of {chain_pixels(levels)}; the whole chain would not fit {REF_BUDGET_S:.0f} s on {cores} threads)")
+    return px / dt / 1e6, dt, cores, text, (blocks if keep_blocks and whole else None)
+
+
+def cpu_baseline_dict(v, cores, sample):
+    return {"value": v, "unit": "Mpix/s", "cores": cores, "per_thread": v / cores, "kind": "reference", "sample": sample}
 
 
 def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     levels = make_chain_ref(SEED)
-    v, dt, cores, sample = time_reference(levels, max(1, args.steps), args.warmup)
+    v, dt, cores, sample, _ = time_reference(levels, max(1, args.steps), args.warmup)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic",
         "config": workload_config(levels, args.gpus),
-        "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample},
+        "cpu_baseline": cpu_baseline_dict(v, cores, sample),
         "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -291,6 +301,16 @@ def run_gpu(args):
         sampler.start()  # long before the timed region: nvidia-smi takes a while to come up
     levels = make_chain_gpu(rank_seed(rank))
     mips, px = len(levels), chain_pixels(levels)
+    chain_identity = None
+    if rank == 0:
+        # the reference arm encodes the chain the reference's own stbir builds; this arm's chain comes from the device cascade.
+        # They must be the same bytes or the two arms do not run the same workload.
+        import refshim
+        if refshim.have_ref():
+            ref_levels = make_chain_ref(rank_seed(rank))
+            chain_identity = all(np.array_equal(a, b) for a, b in zip(levels, ref_levels))
+            if not chain_identity:
+                raise SystemExit("bench.py: the device mip cascade's chain differs from the reference's stbir chain")
     src_np = np.concatenate([l.ravel() for l in levels])
     dst_bytes = L.hkbcn_chain_bytes(BC7, SIZE, SIZE, 1, mips)
     assert dst_bytes == px  # 16 B per 16 px
@@ -350,6 +370,24 @@ def run_gpu(args):
         raise SystemExit("bench.py: host-pointer and device-pointer encodes differ")
     e2e_value = world * px / e2e_s / 1e6
 
+    # ---- the same call on PAGEABLE host memory: what the drop-in caller hands over (Image.cpp passes HeapBlob memory)
+    pg_dst = np.zeros(dst_bytes, np.uint8)
+
+    def pageable_step():
+        hkbcn.check(L.hkbcn_compress_chain(BC7, src_np.ctypes.data_as(C.c_void_p), pg_dst.ctypes.data_as(C.c_void_p), SIZE, SIZE, mips, 0))
+    for _ in range(2):
+        pageable_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        pageable_step()
+    torch.cuda.synchronize()
+    pg_s = max_over_ranks(time.perf_counter() - t0) / e2e_steps
+    barrier()
+    if not np.array_equal(pg_dst, host_out):
+        raise SystemExit("bench.py: pageable and pinned host-pointer encodes differ")
+    pg_value = world * px / pg_s / 1e6
+
     # ---- the importers' whole cascade through the C ABI: level 0 in (host), mips generated on the device, chain encoded,
     # compressed chain out (host).  Only level 0 crosses PCIe.  Same bytes out as the pre-built chain (the cascade is
     # bit-identical to stbir for linear formats).
@@ -380,34 +418,43 @@ def run_gpu(args):
 
     if rank == 0:
         hbm, which = peaks()
-        achieved = 5.0 * px / (ms_step * 1e-3) / 1e9  # algorithmic bytes: 4 B/px read + 1 B/px written
+        hbm_achieved = 5.0 * px / (ms_step * 1e-3) / 1e9  # algorithmic bytes: 4 B/px read + 1 B/px written
         out = {
             "metric": METRIC, "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32+f32", "data": "synthetic",
             "config": workload_config(levels, world),
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "h2d_bytes_per_step": int(src_np.nbytes), "d2h_bytes_per_step": int(dst_bytes),
                     "ms_per_step": e2e_s * 1e3, "api": "hkbcn_compress_chain (host pointers, pinned)"},
+            "e2e_pageable": {"value": pg_value, "unit": "Mpix/s", "ms_per_step": pg_s * 1e3,
+                             "api": "hkbcn_compress_chain on malloc'd (pageable) buffers -- what Image.cpp's HeapBlob memory is to the runtime"},
             "import_chain": {"value": import_value, "unit": "Mpix/s", "ms_per_step": imp_s * 1e3, "h2d_bytes_per_step": l0_bytes,
                              "d2h_bytes_per_step": int(dst_bytes), "api": "hkbcn_import_chain (level 0 in, device mip cascade + encode, chain out)"},
             "batch": {"value": batch_value, "unit": "Mpix/s", "textures_per_gpu": batch["n"], "mix": batch["mix"], "s": batch_s,
                       "h2d_bytes": batch["h2d"], "d2h_bytes": batch["d2h"],
                       "api": "hkbcn_import_batch (pinned level 0 in, compressed chains out, mips on the device)"},
             "gpu_launches": int(launches), "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "bc7_encode_kernel", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                         "traffic": ncu_traffic(px), "peak_source": which,
-                         "note": "BC7 encode is ALU-bound by ~3 orders of magnitude (north_star: evidence is SM ALU-pipe utilisation, see 'alu'); "
-                                 "the HBM-bound kernels of this path are the decoders, see 'decode'"},
-            "alu": alu_model(px // 16, ms_step, clocks),
+            "roofline": roofline_block(px, ms_step, clocks, hbm, which, hbm_achieved),
+            "chain_equals_stbir_chain": chain_identity,
         }
         if world == 1:
+            import refshim
             out["decode"] = decode_sweep(torch, hkbcn, L, d_dst, stream, flush, hbm)
             out["encode_other_formats"] = encode_others(torch, hkbcn, L, stream, flush)
             out["next_rows"] = next_rows(torch, hkbcn, L, stream, flush, hbm)
             out["cube_bc6h"] = cube_bc6h(torch, hkbcn, L, stream, flush)
-            v, dt, cores, sample = time_reference(levels, 1, 0)
-            out["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "reference", "sample": sample}
+            # (ii) of BASELINE.md 3: the reference's per-block encoder over all host threads, on the whole chain, once; its
+            # blocks are kept and compared with the GPU's
+            v, dt, cores, sample, ref_blocks = time_reference(levels, 1, 0, keep_blocks=True)
+            out["cpu_baseline"] = cpu_baseline_dict(v, cores, sample)
+            out["parity"] = parity_block(levels, host_out, ref_blocks)
+            # (i) as shipped: CompressBC7 is a single-threaded loop (ImageEncoders.cpp:524-557); bounded: the 1024^2 level
+            lv = levels[2]
+            t0 = time.perf_counter()
+            refshim.compress(BC7, lv, lv.shape[1], lv.shape[0], 1)
+            dt1 = time.perf_counter() - t0
+            out["cpu_as_shipped"] = {"value": lv.shape[0] * lv.shape[1] / dt1 / 1e6, "unit": "Mpix/s", "cores": 1, "kind": "reference",
+                                     "sample": f"CompressBC7 (one thread, as the reference ships it) on the {lv.shape[1]}^2 level"}
             # the CPU side of the import cascade: the reference's stbir_resize is single-threaded as shipped
-            import refshim
             t0 = time.perf_counter()
             cur = levels[0]
             while cur.shape[0] > 4:
@@ -507,7 +554,10 @@ def decode_sweep(torch, hkbcn, L, bc7_blocks, stream, flush, hbm):
 
 
 def encode_others(torch, hkbcn, L, stream, flush):
-    """the other encoders of the path on BASELINE.json's configs (level 0 only), device-resident, Mpix/s"""
+    """the other encoders of the path on BASELINE.json's configs (level 0 only), device-resident, Mpix/s -- each with the
+    reference's own encoder over all host threads beside it (whole surface; BC6H: a 256^2 crop, the reference needs ~15 s
+    per Mpix on 16 threads) and, for the bit-exact encoders, the count of blocks identical to the reference's"""
+    import refshim
     import synth
     out = {}
     for name, fmt, n, img in (("BC1_2048", 54, 2048, lambda: synth.albedo_rgba8(2048, 2048, 0xB2000001)),
@@ -515,12 +565,31 @@ def encode_others(torch, hkbcn, L, stream, flush):
                               ("BC4_4096", 60, 4096, lambda: synth.roughness_r8(4096, 4096, 0xB2000002)),
                               ("BC5_4096", 62, 4096, lambda: synth.normals_rg8(4096, 4096, 0xB2000003)),
                               ("BC7_alpha_2048", 66, 2048, lambda: synth.albedo_rgba8(2048, 2048, 0xB2000005, "mask")),
-                              ("BC6H_1024", 64, 1024, lambda: synth.sky_rgba32f(1024, 1024, 0xB2000006, 0))):
-        d_src = torch.from_numpy(np.ascontiguousarray(img()).view(np.uint8).ravel()).cuda()
-        d_dst = torch.empty((n // 4) ** 2 * hkbcn.block_bytes(fmt), dtype=torch.uint8, device="cuda")
+                              ("BC6H_1024", 64, 1024, lambda: synth.sky_rgba32f(1024, 1024, 0xB2000006, 0)),
+                              ("BC6H_512", 64, 512, lambda: synth.sky_rgba32f(512, 512, 0xB2000006, 0))):
+        src = np.ascontiguousarray(img())
+        d_src = torch.from_numpy(src.view(np.uint8).ravel()).cuda()
+        bb = hkbcn.block_bytes(fmt)
+        d_dst = torch.empty((n // 4) ** 2 * bb, dtype=torch.uint8, device="cuda")
         ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_compress_dev(
             0, fmt, d_src.data_ptr(), d_dst.data_ptr(), n, n, 0, C.c_void_p(stream.cuda_stream))), 3, 1)
         out[name] = {"Mpix/s": round(n * n / ms / 1e3, 1), "ms": round(ms, 3)}
+        if refshim.have_ref() and name != "BC6H_512":
+            cores = refshim.hw_threads()
+            if fmt == 64:
+                m = 256
+                crop = np.ascontiguousarray(src.reshape(n, n, 4)[256:256 + m, 512:512 + m])
+                t0 = time.perf_counter()
+                refshim.compress(fmt, crop, m, m, cores)
+                dt = time.perf_counter() - t0
+                out[name]["cpu_reference"] = {"Mpix/s": round(m * m / dt / 1e6, 4), "cores": cores, "sample": f"{m}^2 crop of the face"}
+            else:
+                t0 = time.perf_counter()
+                want = refshim.compress(fmt, src, n, n, cores)
+                dt = time.perf_counter() - t0
+                same = (d_dst.cpu().numpy().reshape(-1, bb) == want.reshape(-1, bb)).all(axis=1)
+                out[name]["cpu_reference"] = {"Mpix/s": round(n * n / dt / 1e6, 2), "cores": cores, "sample": "the whole surface"}
+                out[name]["identical_blocks"] = [int(same.sum()), int(same.size)]
         del d_src, d_dst
     return out
 
@@ -618,22 +687,69 @@ def _profile_json():
         return {}
 
 
-def ncu_traffic(px):
-    """dram bytes per launch of bc7_encode_kernel: bytes per pixel from the committed `ncu --set full` capture
-    (profiles/bc7_encode_ncu.json, taken on a 2048^2 surface) x the pixels of one launch; null without a capture"""
-    per_px = _profile_json().get("dram_bytes_per_px")
-    return per_px * px if per_px else None
+def kernel_source_hash():
+    """sha256 over the sources that make up bc7_encode_kernel: the committed ncu figures are valid for exactly this code"""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("bc7_thread.cuh", "bc7_encode.cu", "hkbcn_common.cuh", "bc7_host_tables.h"):
+        with open(os.path.join(ROOT, "hork-source_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
-def alu_model(blocks, ms_step, clocks):
-    """issue-slot utilisation: warp instructions per 4x4 block (counted by ncu, profiles/bc7_encode_ncu.json) x blocks
-    / (SMs x 4 schedulers x clock x time).  null until the profile exists."""
-    ipb = _profile_json().get("warp_inst_per_block")
-    if not ipb or not clocks or not clocks.get("sm_mhz"):
-        return None
+def roofline_block(px, ms_step, clocks, hbm, which, hbm_achieved):
+    """The governing roofline of bc7_encode_kernel is the SM issue rate, not HBM: achieved = warp instructions per second =
+    (warp instructions per 4x4 block, counted by ncu on this very source, profiles/bc7_encode_ncu.json) x blocks / CUDA-event
+    time of the step; peak = 148 SMs x 4 schedulers x the SM clock sampled during the timed region.  The instruction count is
+    only valid for the source it was captured on: the profile carries a hash of the kernel sources, and a mismatch yields
+    frac null + stale_profile instead of a silently stale fraction.  The HBM figures stay beside it."""
+    prof = _profile_json()
+    blocks = px // 16
+    out = {"bound": "alu-issue", "kernel": "bc7_encode_kernel", "unit": "G warp-inst/s", "achieved": None, "peak": None, "frac": None,
+           "hbm": {"achieved": hbm_achieved, "peak": hbm, "unit": "GB/s", "frac": hbm_achieved / hbm, "peak_source": which,
+                   "algorithmic_bytes": 5 * px, "traffic": None},
+           "hbm_frac": hbm_achieved / hbm, "traffic": None}
+    stale = prof.get("source_hash") != kernel_source_hash()
+    out["stale_profile"] = bool(stale)
+    ipb = prof.get("warp_inst_per_block")
+    if stale or not ipb or not clocks or not clocks.get("sm_mhz"):
+        return out
     peak = 148 * 4 * clocks["sm_mhz"] * 1e6
     rate = ipb * blocks / (ms_step * 1e-3)
-    return {"warp_inst_per_block": ipb, "issue_rate_ginst_s": rate / 1e9, "issue_peak_ginst_s": peak / 1e9, "issue_frac": rate / peak}
+    traffic = prof["dram_bytes_per_px"] * px if prof.get("dram_bytes_per_px") else None
+    out.update({"achieved": rate / 1e9, "peak": peak / 1e9, "frac": rate / peak, "warp_inst_per_block": ipb,
+                "lanes_active": prof.get("lanes_active"), "pipe_alu_pct": prof.get("pipe_alu_pct"), "pipe_fmaheavy_pct": prof.get("pipe_fmaheavy_pct"),
+                "issue_slots_busy_pct_ncu": prof.get("issue_slots_busy_pct"), "profile": prof.get("summary"), "traffic": traffic})
+    out["hbm"]["traffic"] = traffic
+    return out
+
+
+def parity_block(levels, gpu_chain, ref_blocks):
+    """in-run identity and PSNR: the GPU's blocks of the timed workload against the blocks the reference arm's encoder just
+    produced for the same chain, both decoded with the REFERENCE decoder (bc7decomp) against the uncompressed source"""
+    import refshim
+    if ref_blocks is None:
+        return None
+    ref_chain = np.concatenate(ref_blocks)
+    g = np.asarray(gpu_chain)
+    same = (g.reshape(-1, 16) == ref_chain.reshape(-1, 16)).all(axis=1)
+
+    def chain_psnr(chain):
+        se, n, off = 0.0, 0, 0
+        for l in levels:
+            h, w, _ = l.shape
+            nb = (w // 4) * (h // 4) * 16
+            dec = refshim.decompress(BC7, chain[off:off + nb], w, h)
+            d = dec.astype(np.int32) - l.ravel().astype(np.int32)
+            se += float((d.astype(np.int64) ** 2).sum())
+            n += d.size
+            off += nb
+        mse = se / n
+        return 99.0 if mse == 0 else float(10 * np.log10(255.0 ** 2 / mse))
+    pr = chain_psnr(ref_chain)
+    pg = pr if same.all() else chain_psnr(g)
+    return {"identical_blocks": int(same.sum()), "of": int(same.size), "psnr_gpu": round(pg, 4), "psnr_ref": round(pr, 4),
+            "psnr": "RGBA, whole chain, decoded with the reference's bc7decomp"}
 
 
 def main():

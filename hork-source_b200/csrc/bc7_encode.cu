@@ -3,13 +3,14 @@
 // Replaces TextureBlockCompression::CompressBC7 (Hork/Image/ImageEncoders.cpp:524-557) ->
 // Encode_BC7(.., BC7_ENCODE_MAX_LEVEL = 4) (:207-212) -> bc7enc_compress_block with
 // compressionParams.bc7_params[4] (:59-63; ThirdParty/bc7enc_rdo/bc7enc.cpp:2402-2438).
-// See bc7_block.cuh for the per-block algorithm and the parity contract.
+// See bc7_thread.cuh for the per-block algorithm and the parity contract.
 //
-// Kernel shape: persistent 128-thread CTAs, one resident wave, tiles claimed from a per-launch counter (tile cost
-// varies several-fold with content).  A CTA stages a tile of 128 consecutive blocks (8 KB of RGBA8)
-// into shared memory with TMA bulk copies, sorts the tile's blocks into opaque ones and ones with alpha
-// (the two classes run different mode sets, bc7enc.cpp:2428-2437; sorted so that at most one warp per tile
-// holds both), and every thread then encodes one block from a transposed copy of its 16 texels.
+// Kernel shape: persistent 512-thread CTAs, one per SM (128 registers per thread), tiles claimed from the launch's counter
+// (tile cost varies several-fold with content).  A CTA stages a tile of 512 consecutive blocks (32 KB of RGBA8) into
+// shared memory with TMA bulk copies, sorts the tile's blocks into opaque ones and ones with alpha (the two classes run
+// different mode sets, bc7enc.cpp:2428-2437; sorted so that at most one warp per tile holds both), and every thread then
+// encodes one block from a transposed copy of its 16 texels; the warps of a CTA are re-aligned between search stages so
+// that they fetch the same instructions.
 // Algorithmic HBM bytes: 5 B/px; the kernel is ALU-bound by about three orders of magnitude.
 #include <atomic>
 #include "hkbcn_common.cuh"

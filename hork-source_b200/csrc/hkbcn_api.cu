@@ -21,6 +21,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <unistd.h>
 
 using namespace hkbcn;
 
@@ -48,11 +49,15 @@ struct Device {
     struct Taps { int* idx; float* w; int T; };
     std::map<uint64_t, Taps> taps;
     std::mutex   taps_mu;
-    // tile counters of the persistent decode kernels: a ring of zeroed word pairs, one pair per launch (a kernel leaves its
-    // pair zeroed again), so launches in flight on different streams never share one
-    uint32_t*    sched = nullptr;
-    std::atomic<uint32_t> sched_seq{0};
-    static constexpr uint32_t SCHED_SLOTS = 256;
+    // tile counters of the persistent kernels: one zeroed {next tile, finished CTAs} pair PER STREAM.  Launches on one stream
+    // run one after another and a kernel leaves its pair zeroed again, so two kernels never share a live pair however many
+    // launches are outstanding; streams get their pair on first use (chunks of SCHED_CHUNK pairs, never moved or freed
+    // before shutdown because kernels in flight hold pointers into them).
+    static constexpr uint32_t SCHED_CHUNK = 64;
+    std::vector<uint32_t*> sched_chunks;
+    std::map<cudaStream_t, uint32_t*> sched_of_stream;
+    uint32_t     sched_used = 0;
+    std::mutex   sched_mu;
     // hkbcn_import_batch: two pipeline slots, each with its own stream, device buffers and pinned staging, so the upload of
     // texture i + 1 and the download of texture i - 1 overlap the kernels of texture i
     struct Slot {
@@ -64,7 +69,7 @@ struct Device {
 };
 
 std::mutex            g_mu;
-bool                  g_init = false;
+std::atomic<bool>     g_init{false}; // published (release) only after g_devs is complete; readers load with acquire
 std::vector<Device*>  g_devs;      // selected devices
 std::atomic<uint64_t> g_launches{0};
 
@@ -123,8 +128,29 @@ uint32_t tile_blocks(int codec)
 
 int ensure_init()
 {
-    if (g_init) return HKBCN_OK;
+    if (g_init.load(std::memory_order_acquire)) return HKBCN_OK;
     return hkbcn_init(0);
+}
+
+// the stream's own {next tile, finished CTAs} pair (see Device::sched_of_stream); nullptr + error text on failure
+uint32_t* sched_slot(Device* D, cudaStream_t st)
+{
+    std::lock_guard<std::mutex> lk(D->sched_mu);
+    auto it = D->sched_of_stream.find(st);
+    if (it != D->sched_of_stream.end()) return it->second;
+    if (D->sched_used % Device::SCHED_CHUNK == 0) {
+        uint32_t* c = nullptr;
+        // cudaMalloc / cudaMemset act on the CURRENT device: callers have done cudaSetDevice(D->id)
+        if (cudaMalloc((void**)&c, Device::SCHED_CHUNK * 32) != cudaSuccess || cudaMemset(c, 0, Device::SCHED_CHUNK * 32) != cudaSuccess) {
+            set_err("cannot allocate tile counters for a new stream: %s", cudaGetErrorString(cudaGetLastError()));
+            return nullptr;
+        }
+        D->sched_chunks.push_back(c);
+    }
+    uint32_t* p = D->sched_chunks.back() + 8 * (D->sched_used % Device::SCHED_CHUNK); // one 32-byte sector each
+    D->sched_used++;
+    D->sched_of_stream[st] = p;
+    return p;
 }
 
 Device* dev_at(int i) { return (i >= 0 && i < (int)g_devs.size()) ? g_devs[i] : nullptr; }
@@ -156,7 +182,9 @@ bool is_pinned(const void* p)
 }
 
 // Append one surface to a launch descriptor.
-void add_level(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h)
+// src_w: texels per source row when it differs from w (a surface whose Width is not a multiple of 4: the reference
+// truncates the block count, numBlocksX = Width / 4, but keeps rowStride = Width * bpp, ImageEncoders.cpp:224-226)
+void add_level(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t src_w = 0)
 {
     Level& L = P.lv[P.nLevels++];
     const uint32_t bpp = src_bpp(codec, flags);
@@ -165,7 +193,7 @@ void add_level(EncodeParams& P, int codec, uint32_t flags, const void* src, void
     L.dst = (uint8_t*)dst;
     L.nbx = w / 4;
     L.nblocks = (w / 4) * (h / 4);
-    L.rowStride = w * bpp;
+    L.rowStride = (src_w ? src_w : w) * bpp;
     L.tileBase = P.totalTiles;
     // TMA bulk path: base 16-B aligned and every block-row segment a multiple of 16 B
     L.bulkOk = (((size_t)src & 15) == 0 && ((L.nbx * 4 * bpp) & 15) == 0 && (L.rowStride & 15) == 0) ? 1u : 0u;
@@ -173,11 +201,20 @@ void add_level(EncodeParams& P, int codec, uint32_t flags, const void* src, void
     P.totalTiles += (L.nblocks + tb - 1) / tb;
 }
 
+// the encoders store whole blocks (8 / 16 bytes at once): the destination of a *_dev call must be block-aligned.  Sources
+// may sit at any address (unaligned ones take the plain-load staging path instead of the bulk copy).
+int check_dev_ptrs(int codec, const void* d_src, const void* d_dst)
+{
+    if (!d_src || !d_dst) { set_err("null device pointer"); return HKBCN_ERR_BAD_ARG; }
+    if ((size_t)d_dst % (size_t)blk_bytes(codec)) { set_err("d_dst must be %d-byte aligned (one block)", blk_bytes(codec)); return HKBCN_ERR_BAD_ARG; }
+    return HKBCN_OK;
+}
+
 int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStream_t st)
 {
     if (P0.totalTiles == 0) return HKBCN_OK;
     EncodeParams P = P0;
-    P.sched = D->sched + 8 * (D->sched_seq.fetch_add(1, std::memory_order_relaxed) % Device::SCHED_SLOTS); // one 32-byte sector each
+    if (!(P.sched = sched_slot(D, st))) return HKBCN_ERR_CUDA;
     cudaError_t e = cudaSuccess;
     switch (codec) {
     case C_BC4: e = launch_bc45_encode(1, P, D->sm_count, st); break;
@@ -195,6 +232,21 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
 
 // level i of a chain: max(w>>i,4) x max(h>>i,4) texels (compressed dims clamp to >= 4, Image.cpp:412-416)
 inline uint32_t mip_dim(uint32_t d, uint32_t i) { uint32_t v = d >> i; return v < 4 ? 4 : v; }
+
+// What ImageStorage::Reset accepts for block-compressed storage (Image.cpp:412-431): dimensions that are multiples of the
+// block size; powers of two when the storage is mipmapped (else level i = dim >> i stops being a whole number of blocks and
+// the reference refuses to load the result); at most CalcNumMips levels (the reference wants 1 or exactly that many -- a
+// prefix of a valid chain is accepted here because every level of it is still whole blocks).
+int check_chain_dims(uint32_t w, uint32_t h, uint32_t mips)
+{
+    if (!w || !h || (w & 3) || (h & 3)) { set_err("chain dims must be non-zero multiples of 4 (Image.cpp:412-413)"); return HKBCN_ERR_BAD_ARG; }
+    if (mips == 0 || mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range 1..%d", mips, HKBCN_MAX_LEVELS); return HKBCN_ERR_BAD_ARG; }
+    if (mips > 1) {
+        if ((w & (w - 1)) || (h & (h - 1))) { set_err("mipmapped compressed storage needs power-of-two dimensions (Image.cpp:415-416), got %u x %u", w, h); return HKBCN_ERR_BAD_ARG; }
+        if (mips > hkbcn_calc_num_mips(w, h)) { set_err("num_mips %u exceeds CalcNumMips(%u, %u) = %u", mips, w, h, hkbcn_calc_num_mips(w, h)); return HKBCN_ERR_BAD_ARG; }
+    }
+    return HKBCN_OK;
+}
 
 int build_chain(EncodeParams& P, int codec, uint32_t flags, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips,
                 uint32_t slices = 1)
@@ -230,7 +282,10 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
     if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
-    const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips, slices);
+    // Width % 4 != 0 (single surfaces only): rows keep their full length, the last Width % 4 texels of each are never read
+    const bool ragged = (w & 3) != 0;
+    if (ragged && (mips != 1 || slices != 1)) { set_err("chains and sliced storage need widths that are multiples of 4 (Image.cpp:412-413)"); return HKBCN_ERR_BAD_ARG; }
+    const size_t sbytes = ragged ? (size_t)w * h * src_bpp(codec, flags) : chain_src_bytes(codec, flags, w, h, mips, slices);
     const size_t dbytes = hkbcn_chain_bytes(fmt, w, h, slices, mips);
     if (dbytes == 0) return HKBCN_OK;
     std::lock_guard<std::mutex> lk(D->mu);
@@ -240,7 +295,11 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
     if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
     CK(cudaMemcpyAsync(D->d_src, src, sbytes, cudaMemcpyHostToDevice, D->stream));
     EncodeParams P;
-    if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, w, h, mips, slices)) != HKBCN_OK) return rc;
+    if (ragged) {
+        memset(&P, 0, sizeof(P));
+        P.flags = flags;
+        add_level(P, codec, flags, D->d_src, D->d_dst, w & ~3u, h, w);
+    } else if ((rc = build_chain(P, codec, flags, D->d_src, D->d_dst, w, h, mips, slices)) != HKBCN_OK) return rc;
     if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
     CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
     CK(cudaStreamSynchronize(D->stream));
@@ -255,88 +314,107 @@ extern "C" {
 const char* hkbcn_last_error(void) { return t_err; }
 const char* hkbcn_version(void) { return "hkbcn 0.1 (sm_100a)"; }
 
+static void destroy_device(Device* D)
+{
+    cudaSetDevice(D->id);
+    if (D->d_src) cudaFree(D->d_src);
+    if (D->d_dst) cudaFree(D->d_dst);
+    if (D->lut_srgb) cudaFree(D->lut_srgb);
+    if (D->lut_lin) cudaFree(D->lut_lin);
+    for (uint32_t* c : D->sched_chunks) cudaFree(c);
+    for (auto& sl : D->slots) {
+        if (sl.d_src) cudaFree(sl.d_src);
+        if (sl.d_dst) cudaFree(sl.d_dst);
+        if (sl.h_src) cudaFreeHost(sl.h_src);
+        if (sl.h_dst) cudaFreeHost(sl.h_dst);
+        if (sl.st) cudaStreamDestroy(sl.st);
+    }
+    for (auto& kv : D->taps) { cudaFree(kv.second.idx); cudaFree(kv.second.w); }
+    D->taps.clear();
+    if (D->stream) cudaStreamDestroy(D->stream);
+    delete D;
+}
+
+// one device's state; on failure everything built so far is released and *out stays null
+static int create_device(int i, const cudaDeviceProp& prop, Device** out)
+{
+    Device* D = new Device();
+    D->id = i;
+    D->sm_count = prop.multiProcessorCount;
+    struct Guard { Device* d; ~Guard() { if (d) destroy_device(d); } } guard{D};
+    CK(cudaSetDevice(i));
+    CK(cudaStreamCreateWithFlags(&D->stream, cudaStreamNonBlocking));
+    // a12: lookup tables consumed by the encoders / BC6H decoder
+    CK(decode_upload_tables());
+    CK(bc1_upload_tables());
+    cudaError_t te = bc7_upload_tables();
+    if (te != cudaSuccess && te != cudaErrorNotSupported) { set_err("bc7 table upload: %s", cudaGetErrorString(te)); return HKBCN_ERR_CUDA; }
+    CK(bc6h_upload_tables());
+    // stbir's uint8 decode: sRGB -> linear (stb_image_resize.h:634-640, tabulated there) and v / 255
+    float srgb[256], lin[256];
+    for (int v = 0; v < 256; v++) {
+        const double f = v / 255.0;
+        srgb[v] = (float)(f <= 0.04045 ? f / 12.92 : pow((f + 0.055) / 1.055, 2.4));
+        lin[v] = (float)v / 255.0f;
+    }
+    CK(cudaMalloc((void**)&D->lut_srgb, sizeof(srgb)));
+    CK(cudaMalloc((void**)&D->lut_lin, sizeof(lin)));
+    CK(cudaMemcpy(D->lut_srgb, srgb, sizeof(srgb), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(D->lut_lin, lin, sizeof(lin), cudaMemcpyHostToDevice));
+    guard.d = nullptr;
+    *out = D;
+    return HKBCN_OK;
+}
+
 int hkbcn_init(uint32_t device_mask)
 {
     std::lock_guard<std::mutex> lk(g_mu);
-    if (g_init) return HKBCN_OK;
+    if (g_init.load(std::memory_order_acquire)) return HKBCN_OK;
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) {
         set_err("no CUDA device available (%s); this library has no CPU fallback", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
         return HKBCN_ERR_NO_DEVICE;
     }
-    for (int i = 0; i < n; i++) {
+    // the list is built aside and published together with g_init only when every selected device came up: a failure half way
+    // leaves no half-built state behind, and a later call starts from scratch instead of appending the same GPUs again
+    std::vector<Device*> devs;
+    int rc = HKBCN_OK;
+    for (int i = 0; i < n && rc == HKBCN_OK; i++) {
         if (device_mask && !(device_mask & (1u << i))) continue;
         cudaDeviceProp prop;
-        CK(cudaGetDeviceProperties(&prop, i));
+        if (cudaGetDeviceProperties(&prop, i) != cudaSuccess) { set_err("cudaGetDeviceProperties(%d) failed", i); rc = HKBCN_ERR_CUDA; break; }
         if (prop.major != 10) {
             set_err("device %d (%s, sm_%d%d) is not sm_100; kernels are built for sm_100a only", i, prop.name, prop.major, prop.minor);
             continue;
         }
-        CK(cudaSetDevice(i));
-        Device* D = new Device();
-        D->id = i;
-        D->sm_count = prop.multiProcessorCount;
-        CK(cudaStreamCreateWithFlags(&D->stream, cudaStreamNonBlocking));
-        // a12: lookup tables consumed by the encoders / BC6H decoder
-        CK(decode_upload_tables());
-        CK(bc1_upload_tables());
-        cudaError_t te = bc7_upload_tables();
-        if (te != cudaSuccess && te != cudaErrorNotSupported) { set_err("bc7 table upload: %s", cudaGetErrorString(te)); return HKBCN_ERR_CUDA; }
-        CK(bc6h_upload_tables());
-        {
-            // stbir's uint8 decode: sRGB -> linear (stb_image_resize.h:634-640, tabulated there) and v / 255
-            float srgb[256], lin[256];
-            for (int v = 0; v < 256; v++) {
-                const double f = v / 255.0;
-                srgb[v] = (float)(f <= 0.04045 ? f / 12.92 : pow((f + 0.055) / 1.055, 2.4));
-                lin[v] = (float)v / 255.0f;
-            }
-            CK(cudaMalloc((void**)&D->lut_srgb, sizeof(srgb)));
-            CK(cudaMalloc((void**)&D->lut_lin, sizeof(lin)));
-            CK(cudaMemcpy(D->lut_srgb, srgb, sizeof(srgb), cudaMemcpyHostToDevice));
-            CK(cudaMemcpy(D->lut_lin, lin, sizeof(lin), cudaMemcpyHostToDevice));
-        }
-        CK(cudaMalloc((void**)&D->sched, Device::SCHED_SLOTS * 32));
-        CK(cudaMemset(D->sched, 0, Device::SCHED_SLOTS * 32));
-        g_devs.push_back(D);
+        Device* D = nullptr;
+        rc = create_device(i, prop, &D);
+        if (rc == HKBCN_OK) devs.push_back(D);
     }
-    if (g_devs.empty()) {
+    if (rc == HKBCN_OK && devs.empty()) {
         if (!t_err[0]) set_err("no sm_100 device selected by mask 0x%x", device_mask);
-        return HKBCN_ERR_NO_DEVICE;
+        rc = HKBCN_ERR_NO_DEVICE;
     }
-    CK(cudaSetDevice(g_devs[0]->id));
-    g_init = true;
+    if (rc != HKBCN_OK) {
+        for (Device* D : devs) destroy_device(D);
+        return rc;
+    }
+    CK(cudaSetDevice(devs[0]->id));
+    g_devs = std::move(devs);
+    g_init.store(true, std::memory_order_release);
     return HKBCN_OK;
 }
 
 void hkbcn_shutdown(void)
 {
     std::lock_guard<std::mutex> lk(g_mu);
-    for (Device* D : g_devs) {
-        cudaSetDevice(D->id);
-        if (D->d_src) cudaFree(D->d_src);
-        if (D->d_dst) cudaFree(D->d_dst);
-        if (D->lut_srgb) cudaFree(D->lut_srgb);
-        if (D->lut_lin) cudaFree(D->lut_lin);
-        if (D->sched) cudaFree(D->sched);
-        for (auto& sl : D->slots) {
-            if (sl.d_src) cudaFree(sl.d_src);
-            if (sl.d_dst) cudaFree(sl.d_dst);
-            if (sl.h_src) cudaFreeHost(sl.h_src);
-            if (sl.h_dst) cudaFreeHost(sl.h_dst);
-            if (sl.st) cudaStreamDestroy(sl.st);
-        }
-        for (auto& kv : D->taps) { cudaFree(kv.second.idx); cudaFree(kv.second.w); }
-        D->taps.clear();
-        if (D->stream) cudaStreamDestroy(D->stream);
-        delete D;
-    }
+    g_init.store(false, std::memory_order_release);
+    for (Device* D : g_devs) destroy_device(D);
     g_devs.clear();
-    g_init = false;
 }
 
-int hkbcn_device_count(void) { return (int)g_devs.size(); }
+int hkbcn_device_count(void) { return g_init.load(std::memory_order_acquire) ? (int)g_devs.size() : 0; }
 uint64_t hkbcn_launch_count(void) { return g_launches.load(); }
 
 int hkbcn_block_bytes(int fmt) { int c = codec_of(fmt); return c < 0 ? HKBCN_ERR_BAD_FORMAT : blk_bytes(c); }
@@ -435,8 +513,7 @@ int hkbcn_compress_chain_multi(int fmt, const void* src, void* dst, uint32_t wid
     if (rc) return rc;
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
-    if ((width & 3) || (height & 3) || !width || !height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
-    if (num_mips == 0 || num_mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range 1..%d", num_mips, HKBCN_MAX_LEVELS); return HKBCN_ERR_BAD_ARG; }
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
     if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
     const int avail = (int)g_devs.size();
     // n_gpus > 0: that many of the selected GPUs; 0: all of them; < 0: -n_gpus bands dealt round-robin over the selected GPUs
@@ -467,14 +544,14 @@ int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width, uint32_t
     if (rc) return rc;
     if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK; // reference: zero blocks, nothing written
     if (!(width & 3) && worth_banding(width, height)) return hkbcn_compress_chain_multi(fmt, src, dst, width, height & ~3u, 1, flags, 0);
-    return compress_host_on(g_devs[0], fmt, src, dst, width & ~3u, height & ~3u, 1, flags) ;
+    return compress_host_on(g_devs[0], fmt, src, dst, width, height & ~3u, 1, flags);
 }
 
 int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags)
 {
     int rc = ensure_init();
     if (rc) return rc;
-    if ((width & 3) || (height & 3)) { set_err("chain dims must be multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
     if (worth_banding(width, height)) return hkbcn_compress_chain_multi(fmt, src, dst, width, height, num_mips, flags, 0);
     return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags);
 }
@@ -506,7 +583,7 @@ static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint3
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
     if (codec == C_BC6H && (flags & HKBCN_FLAG_SRC_F16)) { set_err("mip cascade of RGBA16F sources is not supported (the importers resample RGBA32F)"); return HKBCN_ERR_UNSUPPORTED; }
-    if (mips == 0 || mips > HKBCN_MAX_LEVELS) { set_err("num_mips %u out of range", mips); return HKBCN_ERR_BAD_ARG; }
+    { const int rc = check_chain_dims(w, h, mips); if (rc) return rc; }
     const int edge = cfg && cfg->edge_mode ? cfg->edge_mode : 3, filter = cfg && cfg->filter ? cfg->filter : 5;
     if (edge < 1 || edge > 4 || filter < 1 || filter > 5) { set_err("bad edge mode %d / filter %d", edge, filter); return HKBCN_ERR_BAD_ARG; }
     const uint32_t bpp = src_bpp(codec, flags);
@@ -610,7 +687,7 @@ static int import_host_on(Device* D, int fmt, const void* src_level0, void* dst,
     int rc;
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
-    if ((width & 3) || (height & 3) || !width || !height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
     if (!src_level0 || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
     const size_t sbytes = chain_src_bytes(codec, flags, width, height, num_mips);
     const size_t l0 = (size_t)width * height * src_bpp(codec, flags);
@@ -648,7 +725,22 @@ int hkbcn_encode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, ui
 
 int hkbcn_compress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t flags, void* stream)
 {
-    return hkbcn_compress_chain_dev(device, fmt, d_src, d_dst, width & ~3u, height & ~3u, 1, flags, stream);
+    if (!(width & 3)) return hkbcn_compress_chain_dev(device, fmt, d_src, d_dst, width, height & ~3u, 1, flags, stream);
+    // Width % 4 != 0: numBlocksX = Width / 4 with rowStride = Width * bpp (ImageEncoders.cpp:224-226)
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = dev_at(device);
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK;
+    if ((rc = check_dev_ptrs(codec, d_src, d_dst)) != HKBCN_OK) return rc;
+    CK(cudaSetDevice(D->id));
+    EncodeParams P;
+    memset(&P, 0, sizeof(P));
+    P.flags = flags;
+    add_level(P, codec, flags, d_src, d_dst, width & ~3u, height & ~3u, width);
+    return launch_encode(D, fmt, codec, P, (cudaStream_t)stream);
 }
 
 int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t num_mips,
@@ -661,6 +753,8 @@ int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, void* d_dst
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
     if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK;
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
+    if ((rc = check_dev_ptrs(codec, d_src, d_dst)) != HKBCN_OK) return rc;
     CK(cudaSetDevice(D->id));
     EncodeParams P;
     if ((rc = build_chain(P, codec, flags, d_src, d_dst, width, height, num_mips)) != HKBCN_OK) return rc;
@@ -678,8 +772,9 @@ int hkbcn_compress_slices_dev(int device, int fmt, const void* d_src, void* d_ds
     if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
-    if ((width & 3) || (height & 3)) { set_err("sliced surfaces must be multiples of 4 texels (Image.cpp:412-413)"); return HKBCN_ERR_BAD_ARG; }
     if (width == 0 || height == 0) return HKBCN_OK;
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
+    if ((rc = check_dev_ptrs(codec, d_src, d_dst)) != HKBCN_OK) return rc;
     CK(cudaSetDevice(D->id));
     EncodeParams P;
     if ((rc = build_chain(P, codec, flags, d_src, d_dst, width, height, num_mips, slices)) != HKBCN_OK) return rc;
@@ -691,7 +786,7 @@ int hkbcn_compress_slices(int fmt, const void* src, void* dst, uint32_t width, u
 {
     int rc = ensure_init();
     if (rc) return rc;
-    if ((width & 3) || (height & 3)) { set_err("sliced surfaces must be multiples of 4 texels (Image.cpp:412-413)"); return HKBCN_ERR_BAD_ARG; }
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
     if (slices == 0) { set_err("slice count 0"); return HKBCN_ERR_BAD_ARG; }
     return compress_host_on(g_devs[0], fmt, src, dst, width, height, num_mips, flags, slices);
 }
@@ -720,9 +815,12 @@ int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, ui
     P.codec = codec;
     P.is_signed = fmt == HKBCN_BC6H_SFLOAT;
     P.f32out = (flags & HKBCN_FLAG_DST_F32) != 0;
-    P.sched = D->sched + 8 * (D->sched_seq.fetch_add(1, std::memory_order_relaxed) % Device::SCHED_SLOTS); // one 32-byte sector each
     if (P.nblocks == 0) return HKBCN_OK;
+    // the decoders load whole blocks (8 / 16 bytes) and store texel rows; the block stream must be block-aligned
+    if ((size_t)d_src % (size_t)blk_bytes(codec)) { set_err("d_src must be %d-byte aligned (one block)", blk_bytes(codec)); return HKBCN_ERR_BAD_ARG; }
+    if ((size_t)d_dst % (size_t)(codec == C_BC6H ? 2 : 1) || (codec == C_BC6H && P.f32out && ((size_t)d_dst & 3))) { set_err("d_dst is not aligned to its component type"); return HKBCN_ERR_BAD_ARG; }
     CK(cudaSetDevice(D->id));
+    if (!(P.sched = sched_slot(D, (cudaStream_t)stream))) return HKBCN_ERR_CUDA;
     cudaError_t e = launch_decode(P, D->sm_count, (cudaStream_t)stream);
     if (e != cudaSuccess) { set_err("decode launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -813,7 +911,7 @@ int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
             for (size_t idx : bins[d]) {
                 hkbcn_job& j = jobs[idx];
                 if (j.width / 4 == 0 || j.height / 4 == 0) { j.status = HKBCN_OK; continue; }
-                j.status = compress_host_on(g_devs[d], j.fmt, j.src, j.dst, j.width & ~3u, j.height & ~3u, 1, j.flags);
+                j.status = compress_host_on(g_devs[d], j.fmt, j.src, j.dst, j.width, j.height & ~3u, 1, j.flags);
                 if (j.status && !first_err[d]) { first_err[d] = j.status; err_msg[d] = t_err; }
             }
         });
@@ -1077,6 +1175,7 @@ int hkbcn_irradiance(const float* cube, uint32_t src_size, uint32_t out_size, fl
 }
 
 // ---- .texture files (row f2) ------------------------------------------------------------------------------------------
+static std::atomic<uint32_t> g_tmp_seq{0};
 static void put_u32(uint8_t* p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
 static uint32_t get_u32(const uint8_t* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }
 
@@ -1103,10 +1202,14 @@ int hkbcn_write_texture(const char* path, const hkbcn_texture_desc* d, const voi
     if (payload_bytes > 0xFFFFFFFFull) { set_err("payload of %zu bytes does not fit the format's u32 size field", payload_bytes); return HKBCN_ERR_BAD_ARG; }
     uint8_t h[HKBCN_TEXTURE_HEADER_BYTES];
     hkbcn_texture_header(d, (uint32_t)payload_bytes, h);
-    FILE* f = fopen(path, "wb");
-    if (!f) { set_err("cannot open %s for writing", path); return HKBCN_ERR_BAD_ARG; }
+    // written beside the target and renamed into place: a reader (or a re-run with HKBCN_FLAG_SKIP_EXISTING after a crash)
+    // never sees a half-written texture (checkpoint / resume of the batch driver)
+    const std::string tmp = std::string(path) + ".tmp." + std::to_string((long)getpid()) + "." + std::to_string(g_tmp_seq.fetch_add(1));
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) { set_err("cannot open %s for writing", tmp.c_str()); return HKBCN_ERR_BAD_ARG; }
     const bool ok = fwrite(h, 1, sizeof(h), f) == sizeof(h) && (payload_bytes == 0 || fwrite(payload, 1, payload_bytes, f) == payload_bytes);
-    if (fclose(f) != 0 || !ok) { set_err("short write to %s", path); return HKBCN_ERR_BAD_ARG; }
+    if (fclose(f) != 0 || !ok) { remove(tmp.c_str()); set_err("short write to %s", tmp.c_str()); return HKBCN_ERR_BAD_ARG; }
+    if (rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); set_err("cannot rename %s to %s", tmp.c_str(), path); return HKBCN_ERR_BAD_ARG; }
     return HKBCN_OK;
 }
 
@@ -1137,6 +1240,23 @@ int hkbcn_read_texture(const char* path, hkbcn_texture_desc* d, void* payload, s
     }
     fclose(f);
     return rc;
+}
+
+// re-run of an interrupted batch: the output is there, is a texture resource of the job's shape and holds its whole payload
+static bool complete_texture_exists(const hkbcn_import_job& j)
+{
+    hkbcn_texture_desc d;
+    size_t n = 0;
+    if (hkbcn_read_texture(j.out_path, &d, nullptr, 0, &n) != HKBCN_OK) return false;
+    const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
+    if (d.width != j.width || d.height != j.height || d.fmt != j.fmt || d.num_mips != mips) return false;
+    if (n != hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips)) return false;
+    FILE* f = fopen(j.out_path, "rb");
+    if (!f) return false;
+    fseek(f, 0, SEEK_END);
+    const long sz = ftell(f);
+    fclose(f);
+    return sz == (long)(HKBCN_TEXTURE_HEADER_BYTES + n);
 }
 
 int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
@@ -1219,9 +1339,9 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                 int rc;
                 const int codec = codec_of(j.fmt);
                 if (codec < 0) { set_err("bad format %d", j.fmt); return HKBCN_ERR_BAD_FORMAT; }
-                if ((j.width & 3) || (j.height & 3) || !j.width || !j.height) { set_err("chain dims must be non-zero multiples of 4"); return HKBCN_ERR_BAD_ARG; }
-                if (!j.src_level0) { set_err("null source"); return HKBCN_ERR_BAD_ARG; }
                 const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
+                if ((rc = check_chain_dims(j.width, j.height, mips)) != HKBCN_OK) return rc;
+                if (!j.src_level0) { set_err("null source"); return HKBCN_ERR_BAD_ARG; }
                 const size_t sbytes = chain_src_bytes(codec, j.flags, j.width, j.height, mips);
                 const size_t l0 = (size_t)j.width * j.height * src_bpp(codec, j.flags);
                 const size_t dbytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips);
@@ -1255,6 +1375,10 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
             };
             int s = 0;
             for (size_t idx : bins[dv]) {
+                if ((jobs[idx].flags & HKBCN_FLAG_SKIP_EXISTING) && jobs[idx].out_path && !jobs[idx].dst && complete_texture_exists(jobs[idx])) {
+                    jobs[idx].status = HKBCN_SKIPPED;
+                    continue;
+                }
                 retire(s); // the slot's previous texture (two submissions ago)
                 const int rc = submit(s, idx);
                 if (rc) fail(jobs[idx], rc);

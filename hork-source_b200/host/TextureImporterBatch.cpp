@@ -456,6 +456,7 @@ const char* kHelp = R"(hk_texture_import -- BCn texture import on the GPU (libhk
     -mip_filter <filter>    -- box | triangle | cubicspline | catmullrom | mitchell
     -batch <manifest>       -- one flag set per line; all lines are imported as one batch sharded over the GPUs
     -gpus <mask>            -- bit mask of the CUDA devices to use (default: all)
+    -skip_existing          -- leave textures alone whose output file is already complete (re-run of an interrupted batch)
     -pbr_preset / -normal   -- PBRImporter mode: -pbr_preset ORMX_BC1|ORMX_BC3|ORMX_BC7 <out> [-occlusion f ch] [-roughness f ch] [-metallic f ch]
                                [-displacement_to_alpha f ch | -emission_to_alpha f ch] [-normal <src> <dst>] [-a vMF|Toksvig] [-dx_normal]
                                [-normal_pack <type>] [-mip_edge_mode m] [-mip_filter f]
@@ -470,9 +471,11 @@ int main(int argc, char** argv)
     std::vector<std::string> argvv(argv + 1, argv + argc);
     std::vector<Args> all;
     uint32_t mask = 0;
+    bool skip_existing = false;
     std::vector<std::string> single;
     for (size_t i = 0; i < argvv.size(); i++) {
         if (argvv[i] == "-h") { fputs(kHelp, stdout); return 0; }
+        if (argvv[i] == "-skip_existing") { skip_existing = true; continue; }
         if (argvv[i] == "-gpus" && i + 1 < argvv.size()) { mask = (uint32_t)strtoul(argvv[++i].c_str(), nullptr, 0); continue; }
         if (argvv[i] == "-pbr_preset" || argvv[i] == "-normal") {
             std::vector<std::string> rest;
@@ -547,6 +550,7 @@ int main(int argc, char** argv)
         j.mip.alpha_premultiplied = a.alpha_premult ? 1 : 0;
         j.src_level0 = sources[i];
         j.out_path = a.out.c_str();
+        if (skip_existing) j.flags |= HKBCN_FLAG_SKIP_EXISTING;
         mpix += (double)p.w * p.h * (a.mips ? 4.0 / 3.0 : 1.0) / 1e6;
     }
     for (auto& a : all) printf("Importing texture %s...\n", a.out.c_str());
@@ -554,6 +558,9 @@ int main(int argc, char** argv)
     const int rc = hkbcn_import_batch(jobs.data(), jobs.size());
     const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (rc != HKBCN_OK) { fprintf(stderr, "import failed: %s\n", hkbcn_last_error()); return -1; }
+    size_t skipped = 0;
+    for (auto& j : jobs) skipped += j.status == HKBCN_SKIPPED;
+    if (skipped) printf("%zu texture(s) already complete, skipped\n", skipped);
     printf("%zu texture(s), %.1f Mpix in %.3f s on %d GPU(s): %.1f Mpix/s including upload, download and file writes\n", jobs.size(), mpix,
            s, hkbcn_device_count(), mpix / s);
     for (uint8_t* q : sources) hkbcn_free_pinned(q);

@@ -10,7 +10,14 @@
  * Layout conventions (identical to the reference, ImageEncoders.cpp:215-557):
  *   source surface  : tightly packed row-major texels, rowStride = Width * bpp
  *   compressed      : tightly packed blocks, row-major block order
- *   Width/4, Height/4 truncate; callers guarantee multiples of 4 (Image.cpp:412-413)
+ *   Width/4, Height/4 truncate (ImageEncoders.cpp:224-226): the single-surface calls (hkbcn_compress, _compress_dev,
+ *   _compress_batch) accept any Width / Height, keep rowStride = Width * bpp and skip the Width % 4 texels at the end of
+ *   each row and the Height % 4 rows at the bottom, exactly as the reference does.  Chains and sliced storage
+ *   (ImageStorage, Image.cpp:412-431) need multiples of 4 -- powers of two when mipmapped -- and return HKBCN_ERR_BAD_ARG
+ *   otherwise.
+ *   Device pointers (*_dev): compressed-block pointers (d_dst of the encoders, d_src of the decoders) must be aligned to
+ *   the block size (8 or 16 bytes); texel pointers may sit at any address of their component type.  Violations return
+ *   HKBCN_ERR_BAD_ARG instead of faulting.  Work on one stream runs in order; different streams may run concurrently.
  */
 #ifndef HKBCN_H
 #define HKBCN_H
@@ -53,14 +60,18 @@ typedef enum hkbcn_status {
     HKBCN_ERR_NO_DEVICE   = -3, /* no CUDA device, or device is not sm_100 */
     HKBCN_ERR_CUDA        = -4, /* a CUDA runtime call failed; see hkbcn_last_error() */
     HKBCN_ERR_NOT_INIT    = -5,
-    HKBCN_ERR_UNSUPPORTED = -6
+    HKBCN_ERR_UNSUPPORTED = -6,
+    HKBCN_SKIPPED         =  1  /* hkbcn_import_job.status only: the output file already existed (HKBCN_FLAG_SKIP_EXISTING) */
 } hkbcn_status;
 
 /* flags for hkbcn_compress* */
 enum {
     HKBCN_FLAG_NONE        = 0,
     HKBCN_FLAG_SRC_F16     = 1u << 0, /* BC6H: source texels are RGBA16F (Encode_BC6h_f16, ImageEncoders.cpp:187) */
-    HKBCN_FLAG_FAST        = 1u << 1  /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:171-185) */
+    HKBCN_FLAG_FAST        = 1u << 1, /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:171-185) */
+    HKBCN_FLAG_SKIP_EXISTING = 1u << 16 /* hkbcn_import_batch: leave a job alone (status HKBCN_SKIPPED) when its out_path already holds a
+                                           complete .texture of the job's format, size and mip count -- re-running an interrupted
+                                           batch only does what is missing (files are written to a temporary name and renamed) */
 };
 /* flags for hkbcn_decompress* */
 enum {

@@ -89,7 +89,9 @@ def test_roughness_bake_matches_reference_cascade(bake, size):
     assert np.array_equal(got[: w * h], chain[: w * h])  # level 0 is never touched
     d = np.abs(got.astype(int) - want.astype(int))
     print(f"bake {bake} {w}x{h}: {np.mean(d != 0):.5f} of values differ, max {d.max()} LSB")
-    assert d.max() <= 1 and np.mean(d != 0) < 0.01
+    # SURVEY.md 8f allows +-1 LSB for the bake (RSqrt / sqrt); the device code repeats the reference arithmetic operation for
+    # operation and what is measured is identity -- hold it to that
+    assert d.max() == 0
 
 
 def test_packers_device_pointers_unaligned_and_tails():

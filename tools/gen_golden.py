@@ -40,7 +40,8 @@ out["bc7_src"] = img7
 out["bc7_ref_enc"] = refshim.compress(BC7, img7, 64, 64, 0)
 hdr = synth.sky_rgba32f(32, 32, 0xB2000006)
 out["bc6h_src"] = hdr
-out["bc6h_ref_enc"] = refshim.compress(BC6U, hdr, 32, 32, 0)
+out["bc6h_ref_enc"] = refshim.compress(BC6U, hdr, 32, 32, 0)  # as shipped (moves with stack leftovers: PSNR oracle only)
+out["bc6h_ref0_enc"] = refshim.compress(BC6U, hdr, 32, 32, 0, lib=refshim.ref0())  # zero-init build: the bit-exact oracle
 os.makedirs(os.path.join(ROOT, "tests", "golden"), exist_ok=True)
 np.savez_compressed(os.path.join(ROOT, "tests", "golden", "bcn_golden.npz"), **out)
 print("wrote", {k: v.shape for k, v in out.items()})
