@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
         __syncthreads();
         const uint32_t k = threadIdx.x;
         int q[48];
+        bool nan_in = false;
         if (k < nb) {
 #pragma unroll
             for (int r = 0; r < 4; r++)
@@ -90,6 +91,7 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
                     for (int c = 0; c < 3; c++) {
                         const int i = 3 * (4 * r + x) + c;
                         tf[i * BC6_NT + k] = v[c];
+                        nan_in = nan_in || v[c] != v[c];
                         q[i] = bc6h::f16_to_int(bc6h::half_from_float_bits(__float_as_uint(v[c])), isSigned != 0);
                     }
                 }
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(BC6_NT) bc6h_encode_kernel(const __grid_consta
         if (k < nb) {
 #pragma unroll
             for (int i = 0; i < 48; i++) ti[i * BC6_NT + k] = q[i];
+            blk.nan_sign = nan_in ? 0u : 0x80000000u;
             const uint4 out = bc6h::encode_block(blk, L6, isSigned != 0);
             *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }

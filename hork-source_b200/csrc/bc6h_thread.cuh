@@ -57,6 +57,13 @@ struct Block {
     const float* f;
     const int*   ip;
     int          stride;
+    // Sign of a NaN that the endpoint fit produces.  The reference runs on x86, where an invalid operation (Inf - Inf, Inf * 0:
+    // any block holding +-Inf texels gets there in OptimizeRGB) yields the NEGATIVE default NaN and a NaN operand is passed
+    // on with its own sign; the GPU always yields +NaN (0x7FFFFFFF).  The sign decides what F16ToINT makes of the fitted
+    // endpoint (unsigned: sign set -> 0, clear -> clamp to F16MAX), so it is restored where the fit is converted: negative
+    // unless the block's own texels hold a NaN (numpy / C NAN are positive and propagate as such).  Blocks that mix Inf and
+    // NaN texels may still differ from the reference; finite input never reaches this.
+    uint32_t     nan_sign = 0x80000000u;
     __device__ __forceinline__ float hdr(int i, int c) const { return f[(3 * i + c) * stride]; }
     __device__ __forceinline__ int px(int i, int c) const { return ip[(3 * i + c) * stride]; }
 };
@@ -528,6 +535,17 @@ __device__ __forceinline__ void optimize_rgb4(const Block& blk, uint32_t mask, f
     }
 }
 
+// bit pattern of a fitted endpoint component as the reference's x86 build would hold it (see Block::nan_sign)
+__device__ __forceinline__ uint32_t fit_bits(float v, const Block& blk)
+{
+#ifdef HKBCN_HOST_EMU
+    (void)blk;
+    return __float_as_uint(v); // the host check runs on x86 itself
+#else
+    return v != v ? (0x7FC00000u | blk.nan_sign) : __float_as_uint(v);
+#endif
+}
+
 // Unquantised endpoints + rough error of one region (the body of RoughMSE's loop, bc6h_enc.h:3580-3632).
 // N = palette size of the family (8: two regions, 16: one region).
 template <int N> __device__ __forceinline__ float rough_region(const Block& blk, uint32_t mask, bool isSigned, Ep& e)
@@ -548,8 +566,8 @@ template <int N> __device__ __forceinline__ float rough_region(const Block& blk,
     optimize_rgb4(blk, mask, X, Y);
 #pragma unroll
     for (int c = 0; c < 3; c++) {
-        const int a = f16_to_int(half_from_float_bits(__float_as_uint(X[c])), isSigned);
-        const int b = f16_to_int(half_from_float_bits(__float_as_uint(Y[c])), isSigned);
+        const int a = f16_to_int(half_from_float_bits(fit_bits(X[c], blk)), isSigned);
+        const int b = f16_to_int(half_from_float_bits(fit_bits(Y[c], blk)), isSigned);
         e.A[c] = min(F16MAX, max(isSigned ? -F16MAX : 0, a));
         e.B[c] = min(F16MAX, max(isSigned ? -F16MAX : 0, b));
     }
