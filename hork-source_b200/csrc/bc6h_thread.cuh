@@ -209,13 +209,18 @@ template <int N> __device__ __forceinline__ float nearest_entry(int r, int g, in
 }
 
 // MapColorsQuantized (bc6h_enc.h:3127-3158): total error of the texels in `mask` against the palette of `e`
-template <int N> __device__ __forceinline__ float map_colors_quantized_body(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned)
+// `limit`: the caller only asks whether the total is below it (PerturbOne's `err < min_err`).  Every texel adds a
+// non-negative error and a float sum of non-negative terms never decreases, so once the running total has reached the limit
+// the answer is known and the remaining texels are skipped; the value returned then is some total >= limit, which the caller
+// rejects exactly as it would the full sum.  The lanes of a warp run the same step of the same mode's search, so the wide
+// steps of the logarithmic search -- whose trials are hopeless after a texel or two -- end early for the whole warp.
+template <int N> __device__ __forceinline__ float map_colors_quantized_body(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned, float limit)
 {
     int pal[N][3];
     palette_quantized<N>(e, prec, isSigned, pal);
     float tot = 0.0f;
 #pragma unroll 1
-    for (uint32_t tm = mask & 0xFFFFu; tm; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
+    for (uint32_t tm = mask & 0xFFFFu; tm && tot < limit; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
         const int i = __ffs((int)tm) - 1;
         int idx;
         tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
@@ -231,7 +236,7 @@ template <int N> __device__ __forceinline__ float map_colors_quantized_body(cons
 #endif
 template <int N>
 __device__ __noinline__ float map_colors_quantized_fn(const int* ip, int stride, uint32_t mask, int a0, int a1, int a2, int b0, int b1, int b2,
-                                                      uint32_t prec_packed, bool isSigned)
+                                                      uint32_t prec_packed, bool isSigned, float limit)
 {
     Block blk;
     blk.f = nullptr;
@@ -241,15 +246,15 @@ __device__ __noinline__ float map_colors_quantized_fn(const int* ip, int stride,
     e.A[0] = a0; e.A[1] = a1; e.A[2] = a2;
     e.B[0] = b0; e.B[1] = b1; e.B[2] = b2;
     const uint8_t prec[3] = {(uint8_t)prec_packed, (uint8_t)(prec_packed >> 8), (uint8_t)(prec_packed >> 16)};
-    return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned);
+    return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned, limit);
 }
-template <int N> __device__ __forceinline__ float map_colors_quantized(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned)
+template <int N> __device__ __forceinline__ float map_colors_quantized(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned, float limit)
 {
 #if BC6H_NOINLINE_MAP
     return map_colors_quantized_fn<N>(blk.ip, blk.stride, mask, e.A[0], e.A[1], e.A[2], e.B[0], e.B[1], e.B[2],
-                                      (uint32_t)prec[0] | ((uint32_t)prec[1] << 8) | ((uint32_t)prec[2] << 16), isSigned);
+                                      (uint32_t)prec[0] | ((uint32_t)prec[1] << 8) | ((uint32_t)prec[2] << 16), isSigned, limit);
 #else
-    return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned);
+    return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned, limit);
 #endif
 }
 
@@ -276,7 +281,7 @@ __device__ __forceinline__ float perturb_one(const Block& blk, uint32_t mask, co
                 tmp.B[CH] = out.B[CH] + sign * step;
                 if (tmp.B[CH] < 0 || tmp.B[CH] >= (1 << uPrec)) continue;
             }
-            const float err = map_colors_quantized<N>(blk, mask, tmp, prec, isSigned);
+            const float err = map_colors_quantized<N>(blk, mask, tmp, prec, isSigned, min_err);
             if (err < min_err) {
                 improved = true;
                 min_err = err;
