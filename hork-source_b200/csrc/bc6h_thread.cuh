@@ -52,11 +52,12 @@ __device__ const Mode kModes[14] = {
     {0x0b, 0, 1, 4, {{12, 12, 12}, {8, 8, 8}, {0, 0, 0}, {0, 0, 0}}},  {0x0f, 0, 1, 4, {{16, 16, 16}, {4, 4, 4}, {0, 0, 0}, {0, 0, 0}}},
 };
 
-// the thread's block: HDR texel i component c at f[(3 * i + c) * stride], its half-bit integer at ip[(3 * i + c) * stride]
+// one block's texels: HDR texel i component c at f[i * ts + c * cs], its half-bit integer at ip[i * ts + c * cs]
+// (thread-per-block layout: component-major, thread-minor, ts = 3 * stride, cs = stride; task-parallel kernel: ts = 4, cs = 1)
 struct Block {
     const float* f;
     const int*   ip;
-    int          stride;
+    int          ts, cs;
     // Sign of a NaN that the endpoint fit produces.  The reference runs on x86, where an invalid operation (Inf - Inf, Inf * 0:
     // any block holding +-Inf texels gets there in OptimizeRGB) yields the NEGATIVE default NaN and a NaN operand is passed
     // on with its own sign; the GPU always yields +NaN (0x7FFFFFFF).  The sign decides what F16ToINT makes of the fitted
@@ -64,8 +65,8 @@ struct Block {
     // unless the block's own texels hold a NaN (numpy / C NAN are positive and propagate as such).  Blocks that mix Inf and
     // NaN texels may still differ from the reference; finite input never reaches this.
     uint32_t     nan_sign = 0x80000000u;
-    __device__ __forceinline__ float hdr(int i, int c) const { return f[(3 * i + c) * stride]; }
-    __device__ __forceinline__ int px(int i, int c) const { return ip[(3 * i + c) * stride]; }
+    __device__ __forceinline__ float hdr(int i, int c) const { return f[i * ts + c * cs]; }
+    __device__ __forceinline__ int px(int i, int c) const { return ip[i * ts + c * cs]; }
 };
 
 struct Ep {
@@ -190,8 +191,17 @@ template <int N> __device__ __forceinline__ void palette_quantized(const Ep& e, 
 
 // Search shared by MapColors / MapColorsQuantized / AssignIndices (bc6h_enc.h:3137-3156, 3338-3357, 3514-3526): entry 0,
 // then entries in order while the error does not increase and is not yet zero; returns the error, idx = entry kept.
+#ifdef HKBCN_HOST_COUNT
+static long g_cnt[8]; static long g_hist[17]; static int g_cat = 0; // pair evaluations per category
+#define HK_COUNT(n) (g_cnt[g_cat] += (n))
+#define HK_CAT(c) (g_cat = (c))
+#else
+#define HK_COUNT(n)
+#define HK_CAT(c)
+#endif
 template <int N> __device__ __forceinline__ float nearest_entry(int r, int g, int b, const int pal[N][3], int& idx)
 {
+    HK_COUNT(N);
     float best = norm3(r, g, b, pal[0][0], pal[0][1], pal[0][2]);
     idx = 0;
     bool open = true;
@@ -220,11 +230,16 @@ template <int N> __device__ __forceinline__ float map_colors_quantized_body(cons
     palette_quantized<N>(e, prec, isSigned, pal);
     float tot = 0.0f;
 #pragma unroll 1
+    int ntex = 0;
     for (uint32_t tm = mask & 0xFFFFu; tm && tot < limit; tm &= tm - 1u) { // texels of the region in ascending order, one per trip
         const int i = __ffs((int)tm) - 1;
         int idx;
         tot += nearest_entry<N>(blk.px(i, 0), blk.px(i, 1), blk.px(i, 2), pal, idx);
+        ntex++;
     }
+#ifdef HKBCN_HOST_COUNT
+    g_hist[ntex]++;
+#endif
     return tot;
 }
 // The search calls this from 36 sites per mode class (three channels x {A, B, alternating} x one / two regions x 3- / 4-bit
@@ -235,13 +250,14 @@ template <int N> __device__ __forceinline__ float map_colors_quantized_body(cons
 #define BC6H_NOINLINE_MAP 1
 #endif
 template <int N>
-__device__ __noinline__ float map_colors_quantized_fn(const int* ip, int stride, uint32_t mask, int a0, int a1, int a2, int b0, int b1, int b2,
+__device__ __noinline__ float map_colors_quantized_fn(const int* ip, int ts, int cs, uint32_t mask, int a0, int a1, int a2, int b0, int b1, int b2,
                                                       uint32_t prec_packed, bool isSigned, float limit)
 {
     Block blk;
     blk.f = nullptr;
     blk.ip = ip;
-    blk.stride = stride;
+    blk.ts = ts;
+    blk.cs = cs;
     Ep e;
     e.A[0] = a0; e.A[1] = a1; e.A[2] = a2;
     e.B[0] = b0; e.B[1] = b1; e.B[2] = b2;
@@ -251,7 +267,7 @@ __device__ __noinline__ float map_colors_quantized_fn(const int* ip, int stride,
 template <int N> __device__ __forceinline__ float map_colors_quantized(const Block& blk, uint32_t mask, const Ep& e, const uint8_t prec[3], bool isSigned, float limit)
 {
 #if BC6H_NOINLINE_MAP
-    return map_colors_quantized_fn<N>(blk.ip, blk.stride, mask, e.A[0], e.A[1], e.A[2], e.B[0], e.B[1], e.B[2],
+    return map_colors_quantized_fn<N>(blk.ip, blk.ts, blk.cs, mask, e.A[0], e.A[1], e.A[2], e.B[0], e.B[1], e.B[2],
                                       (uint32_t)prec[0] | ((uint32_t)prec[1] << 8) | ((uint32_t)prec[2] << 16), isSigned, limit);
 #else
     return map_colors_quantized_body<N>(blk, mask, e, prec, isSigned, limit);
@@ -281,7 +297,12 @@ __device__ __forceinline__ float perturb_one(const Block& blk, uint32_t mask, co
                 tmp.B[CH] = out.B[CH] + sign * step;
                 if (tmp.B[CH] < 0 || tmp.B[CH] >= (1 << uPrec)) continue;
             }
+            HK_CAT(N == 8 ? 1 : 2);
             const float err = map_colors_quantized<N>(blk, mask, tmp, prec, isSigned, min_err);
+            HK_CAT(0);
+#ifdef HKBCN_HOST_COUNT
+            g_cnt[N == 8 ? 4 : 5]++;
+#endif
             if (err < min_err) {
                 improved = true;
                 min_err = err;
@@ -652,8 +673,6 @@ __device__ __forceinline__ uint4 emit_block(const Layout& L, int mode, uint32_t 
     return make_uint4((uint32_t)B.lo, (uint32_t)(B.lo >> 32), (uint32_t)B.hi, (uint32_t)(B.hi >> 32));
 }
 
-// Refine (bc6h_enc.h:3420-3465) for one (mode, shape): `unq` = the shape's unquantised endpoints from the rough fit.
-// Updates best_err / out when this candidate wins.
 // Refine (bc6h_enc.h:3420-3465) for a GROUP of modes that share endpoint precision and transform (modes 3-5 are all
 // 11-bit base, modes 7-9 all 8-bit base; they differ only in how the delta bits are split over R, G, B).  Everything up to
 // the fit test -- QuantizeEndPts, AssignIndices, SwapIndices, the forward transform, OptimizeEndPoints and the second
@@ -661,18 +680,21 @@ __device__ __forceinline__ uint4 emit_block(const Layout& L, int mode, uint32_t 
 // group then applies its own EndPointsFit and emission.  The reference visits candidates mode-major, rank-minor and keeps
 // the first one reaching the minimum (strict <); here a candidate carries its visiting order `ord = mode * 8 + rank` and
 // ties go to the lower ord, which selects the same candidate whatever the evaluation order.
+//
+// Three steps, so that the task-parallel kernel can run them as separate phases (bc6h_coop.cuh) while the thread-per-block
+// path (refine, below) runs them back to back:
+//   refine_setup   quantise, assign indices, fix-up swap, fit test of the group's modes -> org (absolute), indices, errors
+//   optimize_one   per region, from org to opt (OptimizeEndPoints)
+//   refine_finish  indices of opt, per-mode choice between opt and org, emission of the winner
 template <int N, int NR>
-__device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mode0, int nmodes, int rank, bool isSigned, uint32_t shapeIdx,
-                                       const Ep unq[NR], float& best_err, int& best_ord, uint4& out)
+__device__ __forceinline__ uint32_t refine_setup(const Block& blk, int mode0, int nmodes, bool isSigned, uint32_t shapeIdx, const Ep unq[NR], Ep org[NR],
+                                                 uint64_t& org_idx, float org_err[NR])
 {
     const Mode& M = kModes[mode0];
     const bool transformed = M.transformed != 0;
     const uint32_t shape = NR == 2 ? kShape2[shapeIdx] : 0u;
     const int fix1 = NR == 2 ? kAnchor2[shapeIdx] : 0;
     const uint8_t* prec = M.prec[0];
-    Ep org[NR], opt[NR];
-    float org_err[NR], opt_err[NR];
-    uint64_t org_idx, opt_idx;
     // QuantizeEndPts (:3359-3376)
 #pragma unroll
     for (int p = 0; p < NR; p++)
@@ -681,19 +703,33 @@ __device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mo
             org[p].A[c] = quantize(unq[p].A[c], prec[c], isSigned);
             org[p].B[c] = quantize(unq[p].B[c], prec[c], isSigned);
         }
+    HK_CAT(3);
     assign_indices<N, NR>(blk, shape, org, prec, isSigned, org_idx, org_err);
+    HK_CAT(0);
     swap_indices<N, NR>(shape, fix1, org, org_idx);
     if (transformed) transform_forward<NR>(org);
     uint32_t fits = 0;
 #pragma unroll 1
     for (int m = 0; m < nmodes; m++)
         if (endpoints_fit<NR>(kModes[mode0 + m], isSigned, org)) fits |= 1u << m;
-    if (!fits) return;
-    if (transformed) transform_inverse<NR>(org, prec, isSigned);
-    // OptimizeEndPoints (:3271-3293): region 0 over g_aPartitionTable[0] (every texel), region 1 over its own texels
-    optimize_one<N>(blk, 0xFFFFu, prec, isSigned, org_err[0], org[0], opt[0]);
-    if (NR == 2) optimize_one<N>(blk, shape, prec, isSigned, org_err[NR - 1], org[NR - 1], opt[NR - 1]);
+    if (fits && transformed) transform_inverse<NR>(org, prec, isSigned);
+    return fits;
+}
+
+template <int N, int NR>
+__device__ __forceinline__ void refine_finish(const Block& blk, const Layout& L, int mode0, int nmodes, uint32_t fits, int rank, bool isSigned, uint32_t shapeIdx,
+                                              Ep org[NR], uint64_t org_idx, const float org_err[NR], Ep opt[NR], float& best_err, int& best_ord, uint4& out)
+{
+    const Mode& M = kModes[mode0];
+    const bool transformed = M.transformed != 0;
+    const uint32_t shape = NR == 2 ? kShape2[shapeIdx] : 0u;
+    const int fix1 = NR == 2 ? kAnchor2[shapeIdx] : 0;
+    const uint8_t* prec = M.prec[0];
+    float opt_err[NR];
+    uint64_t opt_idx;
+    HK_CAT(3);
     assign_indices<N, NR>(blk, shape, opt, prec, isSigned, opt_idx, opt_err);
+    HK_CAT(0);
     swap_indices<N, NR>(shape, fix1, opt, opt_idx);
     float org_tot = 0.0f, opt_tot = 0.0f;
 #pragma unroll
@@ -708,9 +744,6 @@ __device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mo
         if (!(fits >> m & 1u)) continue;
         const int mode = mode0 + m;
         const int ord = mode * 8 + rank;
-#ifdef BC6H_DEBUG
-        printf("MY  refine mode %d shape %d org %.1f opt %.1f best %.1f fit %d\n", mode, (int)shapeIdx, org_tot, opt_tot, best_err, (int)endpoints_fit<NR>(kModes[mode], isSigned, opt));
-#endif
         if (endpoints_fit<NR>(kModes[mode], isSigned, opt) && opt_tot < org_tot && (opt_tot < best_err || (opt_tot == best_err && ord < best_ord))) {
             best_err = opt_tot;
             best_ord = ord;
@@ -725,6 +758,23 @@ __device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mo
             out = emit_block<N, NR>(L, mode, shapeIdx, fix1, org, org_idx);
         }
     }
+}
+
+template <int N, int NR>
+__device__ __forceinline__ void refine(const Block& blk, const Layout& L, int mode0, int nmodes, int rank, bool isSigned, uint32_t shapeIdx,
+                                       const Ep unq[NR], float& best_err, int& best_ord, uint4& out)
+{
+    const uint8_t* prec = kModes[mode0].prec[0];
+    const uint32_t shape = NR == 2 ? kShape2[shapeIdx] : 0u;
+    Ep org[NR], opt[NR];
+    float org_err[NR];
+    uint64_t org_idx;
+    const uint32_t fits = refine_setup<N, NR>(blk, mode0, nmodes, isSigned, shapeIdx, unq, org, org_idx, org_err);
+    if (!fits) return;
+    // OptimizeEndPoints (:3271-3293): region 0 over g_aPartitionTable[0] (every texel), region 1 over its own texels
+    optimize_one<N>(blk, 0xFFFFu, prec, isSigned, org_err[0], org[0], opt[0]);
+    if (NR == 2) optimize_one<N>(blk, shape, prec, isSigned, org_err[NR - 1], org[NR - 1], opt[NR - 1]);
+    refine_finish<N, NR>(blk, L, mode0, nmodes, fits, rank, isSigned, shapeIdx, org, org_idx, org_err, opt, best_err, best_ord, out);
 }
 
 // D3DX_BC6H::Encode (bc6h_enc.h:2910-2952)
