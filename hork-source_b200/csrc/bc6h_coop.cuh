@@ -140,16 +140,15 @@ __device__ __forceinline__ uint32_t coop_setup(const Block& blk, int block, int 
 //     until a perturbation no longer improves
 //   perturb(x): for step = 2^(prec-1) .. 1: try x - step, then x + step (skipping values outside [0, 2^prec)); a trial's error
 //     is the region's texels against the palette of the moved endpoints; x moves by the better improving step.
-// The channel is a template parameter: the optimise phase runs the R, G and B searches of all candidates as three passes
-// (the reference does R, G, B in sequence per region, each starting from the previous one's result, which the record carries
-// from pass to pass), so that every lane of the warp perturbs the same channel and the palettes can live in registers under
-// compile-time indices.  pal[c][j]: palette entry j of channel c as a float (the integers are < 2^16, so exact) -- the
-// committed endpoints' palette for the two channels at rest, the current trial's for channel CH.
-// ISB: the channel is B.  The error of a texel is (dR^2 + dG^2) + dB^2 in exactly this association; with m the moving channel
-// and c1 < c2 the two at rest, R and G give (m^2 + c1^2) + c2^2 (the inner sum commutes) and B gives (c1^2 + c2^2) + m^2 -- two
-// instantiations instead of three, the channel itself is a run-time value that only selects which texel component is read.
-template <int N, bool ISB, bool SIGNED> struct OptChan {
-    int          ch;      // 0, 1 (ISB false) or 2 (ISB true)
+// The optimise phase runs the R, G and B searches of all candidates as three passes (the reference does R, G, B in sequence per
+// region, each starting from the previous one's result, which the record carries from pass to pass), so that every lane of the
+// warp perturbs the same channel.
+// The channel is a run-time value, the same for every lane of a pass: it selects which texel component moves and how the three
+// squared differences are associated (see eval_texel) -- one instantiation of the pass loop per palette size instead of three.
+// (A compile-time channel saves two selects per palette entry, but the B-channel instantiation then spilled its state machine
+// under any register cap: 66 ms per 1024^2 face against 48 ms for this form.)
+template <int N, bool SIGNED> struct OptChan {
+    int          ch;      // 0, 1, 2 = R, G, B
     const float* tf;      // the block's texels in the encoder's integer domain as floats (exact), 4 per texel
     uint32_t     mask;    // texels of the region (region 0 of a two-region mode: all 16, bc6h_enc.h:3284)
     int          prec;    // endpoint precision (the same for R, G, B in every mode)
@@ -213,7 +212,7 @@ template <int N, bool ISB, bool SIGNED> struct OptChan {
             for (int j = 0; j < N; j++) pal1[j] = entry(u0 * 64 + 32, u1 - u0, j);
         }
         {
-            const int u0 = unq(ISB ? e.A[1] : e.A[2]), u1 = unq(ISB ? e.B[1] : e.B[2]);
+            const int u0 = unq(ch == 2 ? e.A[1] : e.A[2]), u1 = unq(ch == 2 ? e.B[1] : e.B[2]);
 #pragma unroll
             for (int j = 0; j < N; j++) pal2[j] = entry(u0 * 64 + 32, u1 - u0, j);
         }
@@ -305,14 +304,17 @@ template <int N, bool ISB, bool SIGNED> struct OptChan {
         const float t0 = tx.x, t1 = tx.y, t2 = tx.z;
 #endif
         const float tm_ = ch == 0 ? t0 : ch == 1 ? t1 : t2; // the moving channel's component, then the two at rest in R, G, B order
-        const float tc1 = ch == 0 ? t1 : t0, tc2 = ISB ? t1 : t2;
+        const float tc1 = ch == 0 ? t1 : t0, tc2 = ch == 2 ? t1 : t2;
         HK_COUNT(N);
         float best = 0.0f, prev = 0.0f;
         bool open = true;
 #pragma unroll
         for (int j = 0; j < N; j++) {
             const float dm = tm_ - entry(base, delta, j), d1 = tc1 - pal1[j], d2 = tc2 - pal2[j];
-            const float e = ISB ? (d1 * d1 + d2 * d2) + dm * dm : (dm * dm + d1 * d1) + d2 * d2;
+            // (dR^2 + dG^2) + dB^2 in exactly this association: with m the moving channel and c1 < c2 the two at rest, R and G
+            // give (c1^2 + m^2) + c2^2 (the inner sum commutes) and B gives (c1^2 + c2^2) + m^2
+            const float sm = dm * dm, s1 = d1 * d1, s2 = d2 * d2;
+            const float e = (s1 + (ch == 2 ? s2 : sm)) + (ch == 2 ? sm : s2);
             // nearest_entry without the index: stay on the entries while the error does not increase.  (Its `best > 0` stop
             // changes nothing here: from 0 the error can only stay 0 or close the scan.)  While the scan is open `best` is the
             // previous entry's error, so the test is written against that: the comparisons then depend on each other only

@@ -24,12 +24,11 @@ namespace hkbcn {
 __device__ bc6h::Layout g_bc6h_enc_layout;
 
 #ifndef BC6E_CTAS_PER_SM
-#define BC6E_CTAS_PER_SM 8  // resident one-warp CTAs per SM
+#define BC6E_CTAS_PER_SM 12 // resident one-warp CTAs per SM
 #endif
 #ifndef BC6E_MIN_CTAS
-#define BC6E_MIN_CTAS 8     // launch bound: 8 one-warp CTAs per SM leave ptxas 255 registers per thread.  Measured on a 1024^2
-                            // face: 255 registers / 8 warps 66 ms, 168 / 12 warps 80 ms, 128 / 16 warps 87 ms -- under a cap the
-                            // optimise passes spill their state machine, which costs more than the extra warps hide
+#define BC6E_MIN_CTAS 12    // launch bound: 12 one-warp CTAs per SM = 168 registers per thread.  Measured on a 1024^2 face:
+                            // 128 registers / 16 warps 57 ms, 168 / 12 warps 48 ms, 255 / 8 warps 55 ms
 #endif
 constexpr int BC6_NT = 32;
 constexpr int BC6_TB = bc6h::COOP_TB;
@@ -108,56 +107,60 @@ __device__ __noinline__ bool finish_fn(const int* tq, const bc6h::Layout* L, con
 
 // one pass (channel CH) of the optimise phase of one round: lanes pull (candidate, region) items and run OptChan to completion,
 // one texel per iteration
-template <int N, int NR, bool ISB, bool SIGNED>
-__device__ __noinline__ void optimise_pass(Bc6Smem& S, int nSurv, const int chArg)
+template <int N, int NR, bool SIGNED>
+__device__ __noinline__ void optimise_pass(Bc6Smem& S, int nSurv, const int CH)
 {
-    const int CH = ISB ? 2 : chArg;
     const uint32_t lane = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
     const int nItems = nSurv * NR;
-    bc6h::OptChan<N, ISB, SIGNED> M;
+    bc6h::OptChan<N, SIGNED> M;
     M.ch = CH;
     M.busy = false;
     M.in_trial = false;
     int next = 0, mine = -1;
 #pragma unroll 1
     for (;;) {
-        const bool idle = !M.busy;
-        if (idle && mine >= 0) { // the item just finished: channel CH of the region's endpoints and the region's error go back
-            bc6h::TaskRec& R = S.u.rec[NR == 2 ? mine >> 1 : mine];
-            const int p = NR == 2 ? mine & 1 : 0;
-            if (NR == 2) {
-                R.ep16[p][CH] = (int16_t)M.a;
-                R.ep16[p][3 + CH] = (int16_t)M.b;
-            } else {
-                R.ep32[CH] = M.a;
-                R.ep32[3 + CH] = M.b;
+        if (__any_sync(0xFFFFFFFFu, !M.busy)) { // some lane is between items (an item ends every few hundred iterations)
+            const bool idle = !M.busy;
+            if (idle && mine >= 0) { // the item just finished: channel CH of the region's endpoints and the region's error go back
+                bc6h::TaskRec& R = S.u.rec[NR == 2 ? mine >> 1 : mine];
+                const int p = NR == 2 ? mine & 1 : 0;
+                if (NR == 2) {
+                    R.ep16[p][CH] = (int16_t)M.a;
+                    R.ep16[p][3 + CH] = (int16_t)M.b;
+                } else {
+                    R.ep32[CH] = M.a;
+                    R.ep32[3 + CH] = M.b;
+                }
+                R.cur_err[p] = M.opt_err;
+                mine = -1;
             }
-            R.cur_err[p] = M.opt_err;
-            mine = -1;
-        }
-        const uint32_t m = __ballot_sync(0xFFFFFFFFu, idle);
-        if (m) {
-            const int my = next + __popc(m & lt);
-            next += __popc(m);
-            if (idle && my < nItems) {
-                const bc6h::TaskRec& R = S.u.rec[NR == 2 ? my >> 1 : my];
-                const int p = NR == 2 ? my & 1 : 0;
-                const int mode0 = (R.meta >> 8) & 15;
-                const uint32_t shapeIdx = (R.meta >> 20) & 31u;
-                bc6h::Ep e;
-                bc6h::rec_load_ep<NR>(R, p, e);
-                // OptimizeEndPoints (bc6h_enc.h:3271-3293): region 0 over g_aPartitionTable[0] = every texel, region 1 over its own
-                M.start(S.tf[R.meta & 15u], p ? kShape2[shapeIdx] : 0xFFFFu, bc6h::kModes[mode0].prec[0][0], e, R.cur_err[p]);
-                mine = my;
+            if (next < nItems) {
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, idle);
+                const int my = next + __popc(m & lt);
+                next += __popc(m);
+                if (idle && my < nItems) {
+                    const bc6h::TaskRec& R = S.u.rec[NR == 2 ? my >> 1 : my];
+                    const int p = NR == 2 ? my & 1 : 0;
+                    const int mode0 = (R.meta >> 8) & 15;
+                    const uint32_t shapeIdx = (R.meta >> 20) & 31u;
+                    bc6h::Ep e;
+                    bc6h::rec_load_ep<NR>(R, p, e);
+                    // OptimizeEndPoints (bc6h_enc.h:3271-3293): region 0 over g_aPartitionTable[0] = every texel, region 1 over its own
+                    M.start(S.tf[R.meta & 15u], p ? kShape2[shapeIdx] : 0xFFFFu, bc6h::kModes[mode0].prec[0][0], e, R.cur_err[p]);
+                    mine = my;
+                }
+            }
+            if (!__any_sync(0xFFFFFFFFu, M.busy)) {
+                if (next >= nItems && !__any_sync(0xFFFFFFFFu, mine >= 0)) break;
+                continue;
             }
         }
-        if (!__ballot_sync(0xFFFFFFFFu, M.busy)) {
-            if (next >= nItems && !__ballot_sync(0xFFFFFFFFu, mine >= 0)) break;
-            continue;
-        }
-        if (M.busy && !M.in_trial) M.advance();
-        if (M.busy && M.in_trial) M.eval_texel();
+        // a lane whose trial has ended moves to its next candidate; a second attempt when that one was out of range (about
+        // one candidate in three is: endpoints near 0 or 2^prec - 1 under the wide steps), so it does not sit out the evaluation
+#pragma unroll 1
+        for (int k = 0; k < 2 && M.busy && !M.in_trial; k++) M.advance();
+        if (M.in_trial) M.eval_texel();
     }
     __syncwarp(); // the next pass reads what this one wrote
 }
@@ -286,14 +289,10 @@ __global__ void __launch_bounds__(BC6_NT, BC6E_MIN_CTAS) bc6h_encode_kernel(cons
             }
             __syncwarp();
             // OptimizeOne's R, G, B searches as three passes over the round's candidates
-            if (round < 2) {
 #pragma unroll 1
-                for (int ch = 0; ch < 2; ch++) optimise_pass<8, 2, false, SIGNED>(S, nSurv, ch);
-                optimise_pass<8, 2, true, SIGNED>(S, nSurv, 2);
-            } else {
-#pragma unroll 1
-                for (int ch = 0; ch < 2; ch++) optimise_pass<16, 1, false, SIGNED>(S, nSurv, ch);
-                optimise_pass<16, 1, true, SIGNED>(S, nSurv, 2);
+            for (int ch = 0; ch < 3; ch++) {
+                if (round < 2) optimise_pass<8, 2, SIGNED>(S, nSurv, ch);
+                else optimise_pass<16, 1, SIGNED>(S, nSurv, ch);
             }
 #pragma unroll 1
             for (int s0 = 0; s0 < nSurv; s0 += BC6_NT) {

@@ -82,7 +82,7 @@ static uint4 encode_block_coop(const float* hdr4, const int* tq4, const bc6h::La
                     const uint32_t mask = round < 2 ? (p ? kShape2[shapeIdx] : 0xFFFFu) : 0xFFFFu;
 #define RUN(N, NR, CH, SG)                                                                                   \
     {                                                                                                        \
-        OptChan<N, CH == 2, SG> M;                                                                           \
+        OptChan<N, SG> M;                                                                           \
         M.ch = CH;                                                                                           \
         Ep e;                                                                                                \
         rec_load_ep<NR>(rec[t], p, e);                                                                       \
