@@ -133,6 +133,29 @@ __device__ __forceinline__ uint32_t coop_setup(const Block& blk, int block, int 
     return fits;
 }
 
+// ---- packed single precision (sm_100: add / sub / fma .f32x2, SASS FADD2 / FFMA2): two IEEE-rounded operations per issue slot.
+// Each half is rounded exactly as the scalar instruction rounds it, so results do not change; what changes is the issue count
+// of the palette scan, which is what bounds the optimise passes.  ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into one FFMA2
+// (a single rounding -- not what the reference computes) whatever the -fmad setting, so squares are taken as fma(d, d, z)
+// with z a +0.0 pair the compiler cannot see through (it comes from a kernel parameter): exact, and not contractible.
+#ifdef HKBCN_HOST_EMU
+struct f2 { float x, y; };
+static inline f2 f2_pack(float a, float b) { return f2{a, b}; }
+static inline f2 f2_sub(f2 a, f2 b) { return f2{a.x - b.x, a.y - b.y}; }
+static inline f2 f2_add(f2 a, f2 b) { return f2{a.x + b.x, a.y + b.y}; }
+static inline f2 f2_sq(f2 a, f2 z) { return f2{a.x * a.x + z.x, a.y * a.y + z.y}; } // z = +0: the product, rounded once
+static inline float f2_lo(f2 a) { return a.x; }
+static inline float f2_hi(f2 a) { return a.y; }
+#else
+typedef unsigned long long f2;
+__device__ __forceinline__ f2 f2_pack(float a, float b) { f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ f2 f2_sub(f2 a, f2 b) { f2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2 f2_add(f2 a, f2 b) { f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2 f2_sq(f2 a, f2 z) { f2 r; asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(a), "l"(z)); return r; }
+__device__ __forceinline__ float f2_lo(f2 a) { float x, y; asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(a)); return x; }
+__device__ __forceinline__ float f2_hi(f2 a) { float x, y; asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(a)); return y; }
+#endif
+
 // ---- optimise: one channel of OptimizeOne (bc6h_enc.h:3233-3267) for one region as a state machine -----------------------------
 // Control flow restated from optimize_channel / perturb_one (bc6h_thread.cuh):
 //     err0 = perturb(A[CH]) and err1 = perturb(B[CH]), both from the current endpoints           (phase 0, phase 1)
@@ -162,7 +185,9 @@ template <int N, bool SIGNED> struct OptChan {
     int          t;       // index of the current trial within the perturbation: step = 2^(prec-1-t/2), sign = t odd ? + : -
     bool         improved, trial_valid;
     float        min_err;
-    float        pal1[N], pal2[N]; // palettes of the channels at rest (committed endpoints), as floats: integers < 2^16, exact
+    f2           pal1[N / 2], pal2[N / 2]; // palettes of the channels at rest (committed endpoints), entries (2q, 2q + 1) as float
+                                           // pairs: integers < 2^16, exact
+    f2           zero2;                    // a +0.0 pair the compiler cannot fold (see f2_sq)
     int          base, delta;      // the trial's palette of channel ch: entry j = finish((base + delta * w_j) >> 6)
     float        tot;
     uint32_t     tm;
@@ -209,12 +234,12 @@ template <int N, bool SIGNED> struct OptChan {
             const int c1 = ch == 0 ? 1 : 0; // the two channels at rest, in R, G, B order
             const int u0 = unq(c1 ? e.A[1] : e.A[0]), u1 = unq(c1 ? e.B[1] : e.B[0]);
 #pragma unroll
-            for (int j = 0; j < N; j++) pal1[j] = entry(u0 * 64 + 32, u1 - u0, j);
+            for (int q = 0; q < N / 2; q++) pal1[q] = f2_pack(entry(u0 * 64 + 32, u1 - u0, 2 * q), entry(u0 * 64 + 32, u1 - u0, 2 * q + 1));
         }
         {
             const int u0 = unq(ch == 2 ? e.A[1] : e.A[2]), u1 = unq(ch == 2 ? e.B[1] : e.B[2]);
 #pragma unroll
-            for (int j = 0; j < N; j++) pal2[j] = entry(u0 * 64 + 32, u1 - u0, j);
+            for (int q = 0; q < N / 2; q++) pal2[q] = f2_pack(entry(u0 * 64 + 32, u1 - u0, 2 * q), entry(u0 * 64 + 32, u1 - u0, 2 * q + 1));
         }
         ua = unq(a);
         ub = unq(b);
@@ -306,25 +331,31 @@ template <int N, bool SIGNED> struct OptChan {
         const float tm_ = ch == 0 ? t0 : ch == 1 ? t1 : t2; // the moving channel's component, then the two at rest in R, G, B order
         const float tc1 = ch == 0 ? t1 : t0, tc2 = ch == 2 ? t1 : t2;
         HK_COUNT(N);
+        const f2 bm = f2_pack(tm_, tm_), b1 = f2_pack(tc1, tc1), b2 = f2_pack(tc2, tc2);
+        const bool chB = ch == 2; // the same for every lane of the pass: a uniform branch, not a select per entry
         float best = 0.0f, prev = 0.0f;
         bool open = true;
 #pragma unroll
-        for (int j = 0; j < N; j++) {
-            const float dm = tm_ - entry(base, delta, j), d1 = tc1 - pal1[j], d2 = tc2 - pal2[j];
+        for (int q = 0; q < N / 2; q++) {
+            const f2 dm = f2_sub(bm, f2_pack(entry(base, delta, 2 * q), entry(base, delta, 2 * q + 1)));
+            const f2 sm = f2_sq(dm, zero2), s1 = f2_sq(f2_sub(b1, pal1[q]), zero2), s2 = f2_sq(f2_sub(b2, pal2[q]), zero2);
             // (dR^2 + dG^2) + dB^2 in exactly this association: with m the moving channel and c1 < c2 the two at rest, R and G
             // give (c1^2 + m^2) + c2^2 (the inner sum commutes) and B gives (c1^2 + c2^2) + m^2
-            const float sm = dm * dm, s1 = d1 * d1, s2 = d2 * d2;
-            const float e = (s1 + (ch == 2 ? s2 : sm)) + (ch == 2 ? sm : s2);
-            // nearest_entry without the index: stay on the entries while the error does not increase.  (Its `best > 0` stop
-            // changes nothing here: from 0 the error can only stay 0 or close the scan.)  While the scan is open `best` is the
-            // previous entry's error, so the test is written against that: the comparisons then depend on each other only
-            // through the predicate, not through a chain of selects.
-            if (j == 0) best = e;
-            else {
-                open = open && e <= prev;
-                best = open ? e : best;
+            const f2 e2 = chB ? f2_add(f2_add(s1, s2), sm) : f2_add(f2_add(s1, sm), s2);
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const float e = h ? f2_hi(e2) : f2_lo(e2);
+                // nearest_entry without the index: stay on the entries while the error does not increase.  (Its `best > 0` stop
+                // changes nothing here: from 0 the error can only stay 0 or close the scan.)  While the scan is open `best` is
+                // the previous entry's error, so the test is written against that: the comparisons then depend on each other
+                // only through the predicate, not through a chain of selects.
+                if (q == 0 && h == 0) best = e;
+                else {
+                    open = open && e <= prev;
+                    best = open ? e : best;
+                }
+                prev = e;
             }
-            prev = e;
         }
         tot += best;
         if (tm == 0u || !(tot < min_err)) in_trial = false;

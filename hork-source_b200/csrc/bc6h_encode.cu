@@ -108,13 +108,14 @@ __device__ __noinline__ bool finish_fn(const int* tq, const bc6h::Layout* L, con
 // one pass (channel CH) of the optimise phase of one round: lanes pull (candidate, region) items and run OptChan to completion,
 // one texel per iteration
 template <int N, int NR, bool SIGNED>
-__device__ __noinline__ void optimise_pass(Bc6Smem& S, int nSurv, const int CH)
+__device__ __noinline__ void optimise_pass(Bc6Smem& S, int nSurv, const int CH, const unsigned long long zero2)
 {
     const uint32_t lane = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
     const int nItems = nSurv * NR;
     bc6h::OptChan<N, SIGNED> M;
     M.ch = CH;
+    M.zero2 = zero2;
     M.busy = false;
     M.in_trial = false;
     int next = 0, mine = -1;
@@ -173,6 +174,8 @@ __global__ void __launch_bounds__(BC6_NT, BC6E_MIN_CTAS) bc6h_encode_kernel(cons
     const uint32_t lane = threadIdx.x;
     const uint32_t lt = (1u << lane) - 1u;
     constexpr bool isSigned = SIGNED;
+    // a +0.0 pair from a kernel parameter (EncodeParams::pad is always 0): see f2_sq in bc6h_coop.cuh
+    const unsigned long long zero2 = ((unsigned long long)P.pad << 32) | P.pad;
     {
         const uint32_t* src = (const uint32_t*)&g_bc6h_enc_layout;
         uint32_t* dst = (uint32_t*)&S.L6;
@@ -291,8 +294,8 @@ __global__ void __launch_bounds__(BC6_NT, BC6E_MIN_CTAS) bc6h_encode_kernel(cons
             // OptimizeOne's R, G, B searches as three passes over the round's candidates
 #pragma unroll 1
             for (int ch = 0; ch < 3; ch++) {
-                if (round < 2) optimise_pass<8, 2, SIGNED>(S, nSurv, ch);
-                else optimise_pass<16, 1, SIGNED>(S, nSurv, ch);
+                if (round < 2) optimise_pass<8, 2, SIGNED>(S, nSurv, ch, zero2);
+                else optimise_pass<16, 1, SIGNED>(S, nSurv, ch, zero2);
             }
 #pragma unroll 1
             for (int s0 = 0; s0 < nSurv; s0 += BC6_NT) {

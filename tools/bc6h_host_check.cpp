@@ -84,6 +84,7 @@ static uint4 encode_block_coop(const float* hdr4, const int* tq4, const bc6h::La
     {                                                                                                        \
         OptChan<N, SG> M;                                                                           \
         M.ch = CH;                                                                                           \
+        M.zero2 = f2_pack(0.0f, 0.0f);                                                                       \
         Ep e;                                                                                                \
         rec_load_ep<NR>(rec[t], p, e);                                                                       \
         M.start(tf4, mask, prec, e, rec[t].cur_err[p]);                                                      \
