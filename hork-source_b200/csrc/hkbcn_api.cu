@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <unistd.h>
 
@@ -46,7 +47,7 @@ struct Device {
     // mip cascade: decode tables and tap tables (one pair per in/out size, filter and edge mode), built on first use
     float*       lut_srgb = nullptr;
     float*       lut_lin = nullptr;
-    struct Taps { int* idx; float* w; int T; };
+    struct Taps { int* idx; float* w; int T; int *first, *cnt, *map; int margin; int spanOk; int uniform; int first0; float u[8]; };
     std::map<uint64_t, Taps> taps;
     std::mutex   taps_mu;
     // tile counters of the persistent kernels: one zeroed {next tile, finished CTAs} pair PER STREAM.  Launches on one stream
@@ -564,17 +565,41 @@ static int get_taps(Device* D, int in_size, int out_size, int filter, int edge, 
     std::lock_guard<std::mutex> lk(D->taps_mu);
     auto it = D->taps.find(key);
     if (it != D->taps.end()) { out = it->second; return HKBCN_OK; }
-    std::vector<int> idx;
-    std::vector<float> w;
-    Device::Taps t{nullptr, nullptr, 0};
-    build_axis_taps(in_size, out_size, filter, edge, idx, w, t.T);
-    CK(cudaMalloc((void**)&t.idx, idx.size() * sizeof(int)));
-    CK(cudaMalloc((void**)&t.w, w.size() * sizeof(float)));
-    CK(cudaMemcpy(t.idx, idx.data(), idx.size() * sizeof(int), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(t.w, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice));
+    AxisTaps a;
+    build_axis_taps(in_size, out_size, filter, edge, a);
+    Device::Taps t{nullptr, nullptr, a.T, nullptr, nullptr, nullptr, a.margin, 1, a.uniform ? 1 : 0, a.first.empty() ? 0 : a.first[0], {0, 0, 0, 0, 0, 0, 0, 0}};
+    for (int k = 0; k < a.T && k < 8; k++) t.u[k] = a.w[(size_t)k];
+    // the separable tile kernel stages the inputs of 32 consecutive outputs (x) / 8 (y): at most 72 / 24 of them
+    for (int i = 0; i < out_size; i += 8) {
+        const int j32 = std::min(out_size, i + 32) - 1, j8 = std::min(out_size, i + 8) - 1;
+        if ((i % 32) == 0 && a.first[(size_t)j32] + a.cnt[(size_t)j32] - a.first[(size_t)i] > 72) t.spanOk = 0;
+        if (a.first[(size_t)j8] + a.cnt[(size_t)j8] - a.first[(size_t)i] > 24) t.spanOk = 0;
+    }
+    const size_t no = (size_t)out_size;
+    CK(cudaMalloc((void**)&t.idx, (a.idx.size() + 2 * no + a.map.size()) * sizeof(int)));
+    CK(cudaMalloc((void**)&t.w, a.w.size() * sizeof(float)));
+    t.first = t.idx + a.idx.size();
+    t.cnt = t.first + no;
+    t.map = t.cnt + no;
+    CK(cudaMemcpy(t.idx, a.idx.data(), a.idx.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.first, a.first.data(), no * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.cnt, a.cnt.data(), no * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.map, a.map.data(), a.map.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.w, a.w.data(), a.w.size() * sizeof(float), cudaMemcpyHostToDevice));
     D->taps[key] = t;
     out = t;
     return HKBCN_OK;
+}
+
+static void set_tile_taps(ResizeParams& P, const Device::Taps& tx, const Device::Taps& ty)
+{
+    P.firstx = tx.first; P.cntx = tx.cnt; P.mapx = tx.map; P.marginx = tx.margin;
+    P.firsty = ty.first; P.cnty = ty.cnt; P.mapy = ty.map; P.marginy = ty.margin;
+    P.tileOk = (tx.spanOk && ty.spanOk && !getenv("HKBCN_MIP_GATHER")) ? 1 : 0; // HKBCN_MIP_GATHER: the one-thread-per-texel kernels (A/B timing)
+    P.uniform = (tx.uniform && ty.uniform && !getenv("HKBCN_MIP_GENERAL")) ? 1 : 0;
+    P.x0 = tx.first0;
+    P.y0 = ty.first0;
+    for (int k = 0; k < 8; k++) { P.ux[k] = tx.u[k]; P.uy[k] = ty.u[k]; }
 }
 
 static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint32_t h, uint32_t mips, const hkbcn_mip_config* cfg,
@@ -608,6 +633,7 @@ static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint3
         P.alpha = has_alpha ? channels - 1 : -1;
         P.weight = (has_alpha && !(cfg && cfg->alpha_premultiplied)) ? 1 : 0;
         P.srgb = srgb ? 1 : 0;
+        set_tile_taps(P, tx, ty);
         cudaError_t e = launch_mip_resize(P, channels, f32, st);
         if (e != cudaSuccess) { set_err("mip resize launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
         g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -622,10 +648,11 @@ int hkbcn_mip_taps(int in_size, int out_size, int filter, int edge_mode, int* id
         set_err("bad arguments (downsampling only: out_size <= in_size)");
         return HKBCN_ERR_BAD_ARG;
     }
-    std::vector<int> i;
-    std::vector<float> w;
-    int T = 0;
-    build_axis_taps(in_size, out_size, filter, edge_mode, i, w, T);
+    AxisTaps a;
+    build_axis_taps(in_size, out_size, filter, edge_mode, a);
+    std::vector<int>& i = a.idx;
+    std::vector<float>& w = a.w;
+    const int T = a.T;
     *taps_per_output = T;
     if ((size_t)capacity < i.size()) { set_err("capacity %d < %zu", capacity, i.size()); return HKBCN_ERR_BAD_ARG; }
     if (idx) memcpy(idx, i.data(), i.size() * sizeof(int));
@@ -1001,6 +1028,7 @@ static int bake_roughness_on(Device* D, const float* d_n, uint8_t* d_rough, void
         P.lut = D->lut_lin;
         P.in_w = (int)iw; P.in_h = (int)ih; P.out_w = (int)ow; P.out_h = (int)oh; P.Tx = tx.T; P.Ty = ty.T;
         P.alpha = -1; P.weight = 0; P.srgb = 0;
+        set_tile_taps(P, tx, ty);
         CK(launch_mip_resize(P, 3, true, st));
         CK(launch_roughness_bake(bake, (const float*)dst, rough, (size_t)ow * oh, st));
         g_launches.fetch_add(2, std::memory_order_relaxed);

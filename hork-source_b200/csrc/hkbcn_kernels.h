@@ -51,6 +51,15 @@ struct ResizeParams {
     int            alpha;  // alpha channel index (decoded / encoded linearly) or -1
     int            weight; // 1: colour is weighted by alpha before filtering and un-weighted after (not premultiplied input)
     int            srgb;
+    // the same taps as runs of consecutive inputs (the separable tile kernel): output i reads the cnt[i] inputs
+    // first[i] .. first[i] + cnt[i] - 1 BEFORE edge mapping, input n lives at map[n + margin] (any texel where the weight is 0)
+    const int*     firstx; const int* cntx; const int* mapx; int marginx;
+    const int*     firsty; const int* cnty; const int* mapy; int marginy;
+    int            tileOk; // every 32 x 8 output tile needs at most 72 x 24 inputs: the tile kernel applies
+    // both axes are exact 2 : 1 reductions whose taps do not depend on the output (power-of-two chains: every output reads the
+    // Tx inputs 2 * i + x0 .. with the same weights ux[]): the register-blocked tile kernel applies
+    int            uniform, x0, y0;
+    float          ux[8], uy[8];
 };
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
 
@@ -70,5 +79,11 @@ cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t*
 
 #include <vector>
 namespace hkbcn {
-void build_axis_taps(int in_size, int out_size, int filter, int edge, std::vector<int>& idx, std::vector<float>& w, int& T);
+struct AxisTaps {
+    std::vector<int>   idx, first, cnt, map;
+    std::vector<float> w;
+    int                T = 0, margin = 0;
+    bool               uniform = false; // cnt[i] == T, first[i] == 2 * i + first[0], identical weights for every output
+};
+void build_axis_taps(int in_size, int out_size, int filter, int edge, AxisTaps& t);
 } // namespace hkbcn

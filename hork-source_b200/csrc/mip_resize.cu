@@ -66,8 +66,12 @@ int edge_index(int edge, int n, int max)
 } // namespace
 
 // Taps of one axis: output i reads idx[i*T + k] with weight w[i*T + k], k < T (padded with weight 0), ascending input order.
-void build_axis_taps(int in_size, int out_size, int filter, int edge, std::vector<int>& idx, std::vector<float>& w, int& T)
+// The contributors of an output are consecutive inputs first[i] .. first[i] + cnt[i] - 1 (before edge mapping; map[] maps them).
+void build_axis_taps(int in_size, int out_size, int filter, int edge, AxisTaps& t)
 {
+    std::vector<int>& idx = t.idx;
+    std::vector<float>& w = t.w;
+    int& T = t.T;
     const float scale = (float)out_size / (float)in_size, shift = 0.0f;
     const float support = filter_support(filter, scale);
     const float in_radius = support / scale;
@@ -98,11 +102,30 @@ void build_axis_taps(int in_size, int out_size, int filter, int edge, std::vecto
     }
     idx.assign((size_t)out_size * T, 0);
     w.assign((size_t)out_size * T, 0.0f);
+    t.margin = margin;
+    t.first.assign((size_t)out_size, 0);
+    t.cnt.assign((size_t)out_size, 0);
+    t.map.assign((size_t)(in_size + 2 * margin), 0);
+    for (int n = -margin; n < in_size + margin; n++) {
+        const int e = edge_index(edge, n, in_size);
+        t.map[(size_t)(n + margin)] = e < 0 ? 0 : e;
+    }
+    for (int i = 0; i < out_size; i++) {
+        t.first[(size_t)i] = per_out[(size_t)i].empty() ? 0 : per_out[(size_t)i][0].first;
+        t.cnt[(size_t)i] = (int)per_out[(size_t)i].size();
+    }
+    t.uniform = T <= 8 && in_size == 2 * out_size;
+    for (int i = 0; i < out_size && t.uniform; i++) {
+        if (t.cnt[(size_t)i] != T || t.first[(size_t)i] != 2 * i + t.first[0]) t.uniform = false;
+        for (int k = 0; k < T && t.uniform; k++)
+            if (per_out[(size_t)i][(size_t)k].second != per_out[0][(size_t)k].second) t.uniform = false;
+    }
     for (int i = 0; i < out_size; i++)
         for (size_t k = 0; k < per_out[(size_t)i].size(); k++) {
             const int e = edge_index(edge, per_out[(size_t)i][k].first, in_size);
             idx[(size_t)i * T + k] = e < 0 ? 0 : e;
             w[(size_t)i * T + k] = e < 0 ? 0.0f : per_out[(size_t)i][k].second; // a zero texel adds nothing
+            if (e < 0) t.uniform = false; // STBIR_EDGE_ZERO: the border outputs' weights differ
         }
 }
 
@@ -228,9 +251,321 @@ __global__ void __launch_bounds__(256) mip_resize_f32x3_kernel(const ResizeParam
     d[0] = ax; d[1] = ay; d[2] = az;
 }
 
+// ---- the separable form: stbir's own structure (horizontal pass per input row, then the vertical pass), per output tile ----
+// A CTA owns a 32 x 8 output tile.  It stages the (at most 72 x 24) input texels the tile's taps reach -- decoded once: table
+// lookup, alpha weighting -- in shared memory, filters every staged row horizontally to the tile's 32 columns, then filters
+// vertically.  Same products, same sums, same order as the gather kernels above (inputs ascending inside a row, rows
+// ascending, no contraction), so the results are bit-identical to them and to stbir; what changes is the count: a gather
+// thread evaluates Ty x Tx = 64 Mitchell taps and 64 decodes per output, here it is about 22 horizontal + 8 vertical taps
+// and 6 decodes.
+constexpr int MT_W = 32, MT_H = 8, MT_SX = 72, MT_SY = 24;
+
+template <int CH, bool F32>
+__global__ void __launch_bounds__(256) mip_resize_tile_kernel(const ResizeParams P)
+{
+    __shared__ __align__(16) float dec[MT_SY * MT_SX * CH];
+    __shared__ __align__(16) float hbuf[MT_SY * MT_W * CH];
+    __shared__ float s_wx[MT_W * 8], s_wy[MT_H * 8];
+    __shared__ int s_fx[MT_W], s_cx[MT_W], s_fy[MT_H], s_cy[MT_H];
+    __shared__ float lut[F32 ? 1 : 256], alut[F32 ? 1 : 256];
+    const int tid = threadIdx.x;
+    const int ox0 = blockIdx.x * MT_W, oy0 = blockIdx.y * MT_H;
+    const int tw = min(MT_W, P.out_w - ox0), th = min(MT_H, P.out_h - oy0);
+    if (!F32) {
+        lut[tid] = P.lut[tid];
+        alut[tid] = (float)tid / 255.0f; // alpha decode: the reference's IEEE division, once per CTA
+    }
+    if (tid < tw) {
+        s_fx[tid] = P.firstx[ox0 + tid];
+        s_cx[tid] = P.cntx[ox0 + tid];
+    }
+    if (tid >= 32 && tid < 32 + th) {
+        s_fy[tid - 32] = P.firsty[oy0 + tid - 32];
+        s_cy[tid - 32] = P.cnty[oy0 + tid - 32];
+    }
+    for (int i = tid; i < tw * P.Tx; i += 256) s_wx[i] = P.wx[(size_t)ox0 * P.Tx + i];
+    for (int i = tid; i < th * P.Ty; i += 256) s_wy[i] = P.wy[(size_t)oy0 * P.Ty + i];
+    __syncthreads();
+    const int nx_lo = s_fx[0], sx = s_fx[tw - 1] + s_cx[tw - 1] - nx_lo;
+    const int ny_lo = s_fy[0], sy = s_fy[th - 1] + s_cy[th - 1] - ny_lo;
+    // ---- stage + decode
+    for (int i = tid; i < sy * sx; i += 256) {
+        const int r = i / sx, c = i - r * sx;
+        const int iy = P.mapy[ny_lo + r + P.marginy], ix = P.mapx[nx_lo + c + P.marginx];
+        float v[CH];
+        if (F32) {
+            const float* t = (const float*)P.src + ((size_t)iy * P.in_w + ix) * CH;
+            if (CH == 4) {
+                const float4 q = *(const float4*)t;
+                v[0] = q.x; v[1] = q.y; v[2] = q.z; v[CH - 1] = q.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < CH; k++) v[k] = t[k];
+            }
+        } else {
+            const uint8_t* t = P.src + ((size_t)iy * P.in_w + ix) * CH;
+            int q[CH];
+            if (CH == 4) {
+                const uchar4 q4 = *(const uchar4*)t;
+                q[0] = q4.x; q[1] = q4.y; q[2] = q4.z; q[CH - 1] = q4.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < CH; k++) q[k] = t[k];
+            }
+#pragma unroll
+            for (int k = 0; k < CH; k++) v[k] = ((k == P.alpha) ? alut : lut)[q[k]];
+            if (P.weight) {
+                // alpha weighting (:1375-1400): the epsilon keeps the colour of fully transparent texels
+                float a = 0;
+#pragma unroll
+                for (int k = 0; k < CH; k++) if (k == P.alpha) a = v[k];
+                a += 1.0f / (1 << 20) / (1 << 20) / (1 << 20) / (1 << 20);
+#pragma unroll
+                for (int k = 0; k < CH; k++) v[k] = (k == P.alpha) ? a : v[k] * a;
+            }
+        }
+        float* d = dec + ((size_t)r * MT_SX + c) * CH;
+#pragma unroll
+        for (int k = 0; k < CH; k++) d[k] = v[k];
+    }
+    __syncthreads();
+    // ---- horizontal pass: every staged row to the tile's columns (inputs ascending)
+    for (int i = tid; i < sy * MT_W; i += 256) {
+        const int r = i >> 5, x = i & 31;
+        if (x >= tw) continue;
+        const float* row = dec + ((size_t)r * MT_SX + (s_fx[x] - nx_lo)) * CH;
+        const float* wx = s_wx + x * P.Tx;
+        float h[CH];
+#pragma unroll
+        for (int k = 0; k < CH; k++) h[k] = 0;
+        const int n = s_cx[x];
+        for (int kx = 0; kx < n; kx++) {
+            const float w = wx[kx];
+#pragma unroll
+            for (int k = 0; k < CH; k++) h[k] += row[kx * CH + k] * w;
+        }
+        float* d = hbuf + ((size_t)r * MT_W + x) * CH;
+#pragma unroll
+        for (int k = 0; k < CH; k++) d[k] = h[k];
+    }
+    __syncthreads();
+    // ---- vertical pass (rows ascending), un-weighting, encode
+    const int x = tid & 31, y = tid >> 5;
+    if (x >= tw || y >= th) return;
+    float acc[CH];
+#pragma unroll
+    for (int k = 0; k < CH; k++) acc[k] = 0;
+    {
+        const float* col = hbuf + ((size_t)(s_fy[y] - ny_lo) * MT_W + x) * CH;
+        const float* wy = s_wy + y * P.Ty;
+        const int n = s_cy[y];
+        for (int ky = 0; ky < n; ky++) {
+            const float w = wy[ky];
+#pragma unroll
+            for (int k = 0; k < CH; k++) acc[k] += col[(size_t)ky * MT_W * CH + k] * w;
+        }
+    }
+    const int ox = ox0 + x, oy = oy0 + y;
+    if (F32) {
+        float* d = (float*)P.dst + ((size_t)oy * P.out_w + ox) * CH;
+        if (CH == 4) *(float4*)d = make_float4(acc[0], acc[1], acc[2], acc[CH - 1]);
+        else {
+#pragma unroll
+            for (int k = 0; k < CH; k++) d[k] = acc[k];
+        }
+        return;
+    }
+    if (P.weight) {
+        float a = 0;
+#pragma unroll
+        for (int k = 0; k < CH; k++) if (k == P.alpha) a = acc[k];
+        const float r = a != 0 ? 1.0f / a : 0.0f;
+#pragma unroll
+        for (int k = 0; k < CH; k++) if (k != P.alpha) acc[k] *= r;
+    }
+    uint8_t o[CH];
+#pragma unroll
+    for (int k = 0; k < CH; k++) o[k] = (P.srgb && k != P.alpha) ? encode_srgb8(acc[k]) : encode_linear8(acc[k]);
+    uint8_t* d = P.dst + ((size_t)oy * P.out_w + ox) * CH;
+    if (CH == 4) *(uchar4*)d = make_uchar4(o[0], o[1], o[2], o[CH - 1]);
+    else {
+#pragma unroll
+        for (int k = 0; k < CH; k++) d[k] = o[k];
+    }
+}
+
+// ---- the same for the common case: both axes exact 2 : 1 with output-independent taps (every level of a power-of-two chain
+// under wrap / clamp / reflect).  The weights come as kernel parameters, the staged columns are dealt over eight shared-memory
+// lanes (column c at [c & 7][c >> 3]) so that a thread computing four adjacent outputs of a row reads its 6 + Tx inputs without
+// bank conflicts -- 14 loads for 4 outputs instead of 8 each -- and stores during the decode are conflict-free as well.
+template <int CH, bool F32>
+__global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizeParams P)
+{
+    constexpr int OCT = MT_SX / 8; // 9 slots per lane of columns
+    __shared__ __align__(16) float dec[MT_SY * MT_SX * CH];
+    __shared__ __align__(16) float hbuf[MT_SY * MT_W * CH];
+    __shared__ int s_mx[MT_SX], s_my[MT_SY];
+    __shared__ float lut[F32 ? 1 : 256], alut[F32 ? 1 : 256];
+    const int tid = threadIdx.x;
+    const int ox0 = blockIdx.x * MT_W, oy0 = blockIdx.y * MT_H;
+    const int tw = min(MT_W, P.out_w - ox0), th = min(MT_H, P.out_h - oy0);
+    const int nx_lo = 2 * ox0 + P.x0, sx = 2 * (tw - 1) + P.Tx;
+    const int ny_lo = 2 * oy0 + P.y0, sy = 2 * (th - 1) + P.Ty;
+    if (!F32) {
+        lut[tid] = P.lut[tid];
+        alut[tid] = (float)tid / 255.0f; // alpha decode: the reference's IEEE division, once per CTA
+    }
+    if (tid < sx) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
+    if (tid >= 128 && tid < 128 + sy) s_my[tid - 128] = P.mapy[ny_lo + tid - 128 + P.marginy];
+    __syncthreads();
+    // ---- stage + decode
+    const float inv_sx = 1.0f / (float)sx;
+    for (int i = tid; i < sy * sx; i += 256) {
+        const int r = (int)(((float)i + 0.5f) * inv_sx), c = i - r * sx; // i < 1728: the float quotient is exact enough to floor
+        float v[CH];
+        if (F32) {
+            const float* t = (const float*)P.src + ((size_t)s_my[r] * P.in_w + s_mx[c]) * CH;
+            if (CH == 4) {
+                const float4 q = *(const float4*)t;
+                v[0] = q.x; v[1] = q.y; v[2] = q.z; v[CH - 1] = q.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < CH; k++) v[k] = t[k];
+            }
+        } else {
+            const uint8_t* t = P.src + ((size_t)s_my[r] * P.in_w + s_mx[c]) * CH;
+            int q[CH];
+            if (CH == 4) {
+                const uchar4 q4 = *(const uchar4*)t;
+                q[0] = q4.x; q[1] = q4.y; q[2] = q4.z; q[CH - 1] = q4.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < CH; k++) q[k] = t[k];
+            }
+#pragma unroll
+            for (int k = 0; k < CH; k++) v[k] = ((k == P.alpha) ? alut : lut)[q[k]];
+            if (P.weight) {
+                // alpha weighting (:1375-1400): the epsilon keeps the colour of fully transparent texels
+                float a = 0;
+#pragma unroll
+                for (int k = 0; k < CH; k++) if (k == P.alpha) a = v[k];
+                a += 1.0f / (1 << 20) / (1 << 20) / (1 << 20) / (1 << 20);
+#pragma unroll
+                for (int k = 0; k < CH; k++) v[k] = (k == P.alpha) ? a : v[k] * a;
+            }
+        }
+        float* d = dec + ((size_t)r * MT_SX + (c & 7) * OCT + (c >> 3)) * CH;
+#pragma unroll
+        for (int k = 0; k < CH; k++) d[k] = v[k];
+    }
+    __syncthreads();
+    // ---- horizontal pass: thread = (staged row, group of four adjacent outputs); inputs ascending per output
+    if (tid < sy * 8) {
+        const int r = tid >> 3, g = tid & 7;
+        const float* row = dec + (size_t)r * MT_SX * CH;
+        float h[4][CH];
+#pragma unroll
+        for (int o = 0; o < 4; o++)
+#pragma unroll
+            for (int k = 0; k < CH; k++) h[o][k] = 0;
+        // input t of the group (column 8 g + t of the staged row) feeds output o as its tap t - 2 o
+#pragma unroll
+        for (int t = 0; t < 14; t++) {
+            if (t < 6 + P.Tx) {
+                float v[CH];
+                const float* s = row + ((size_t)(t & 7) * OCT + g + (t >> 3)) * CH;
+                if (CH == 4) {
+                    const float4 q = *(const float4*)s;
+                    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[CH - 1] = q.w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < CH; k++) v[k] = s[k];
+                }
+#pragma unroll
+                for (int o = 0; o < 4; o++) {
+                    const int kx = t - 2 * o;
+                    if (kx >= 0 && kx < 8 && kx < P.Tx) {
+#pragma unroll
+                        for (int k = 0; k < CH; k++) h[o][k] += v[k] * P.ux[kx];
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < 4; o++) {
+            float* d = hbuf + ((size_t)r * MT_W + 4 * g + o) * CH;
+#pragma unroll
+            for (int k = 0; k < CH; k++) d[k] = h[o][k];
+        }
+    }
+    __syncthreads();
+    // ---- vertical pass (rows ascending), un-weighting, encode
+    const int x = tid & 31, y = tid >> 5;
+    if (x >= tw || y >= th) return;
+    float acc[CH];
+#pragma unroll
+    for (int k = 0; k < CH; k++) acc[k] = 0;
+    {
+        const float* col = hbuf + ((size_t)(2 * y) * MT_W + x) * CH;
+#pragma unroll
+        for (int ky = 0; ky < 8; ky++) {
+            if (ky < P.Ty) {
+#pragma unroll
+                for (int k = 0; k < CH; k++) acc[k] += col[(size_t)ky * MT_W * CH + k] * P.uy[ky];
+            }
+        }
+    }
+    const int ox = ox0 + x, oy = oy0 + y;
+    if (F32) {
+        float* d = (float*)P.dst + ((size_t)oy * P.out_w + ox) * CH;
+        if (CH == 4) *(float4*)d = make_float4(acc[0], acc[1], acc[2], acc[CH - 1]);
+        else {
+#pragma unroll
+            for (int k = 0; k < CH; k++) d[k] = acc[k];
+        }
+        return;
+    }
+    if (P.weight) {
+        float a = 0;
+#pragma unroll
+        for (int k = 0; k < CH; k++) if (k == P.alpha) a = acc[k];
+        const float r = a != 0 ? 1.0f / a : 0.0f;
+#pragma unroll
+        for (int k = 0; k < CH; k++) if (k != P.alpha) acc[k] *= r;
+    }
+    uint8_t o[CH];
+#pragma unroll
+    for (int k = 0; k < CH; k++) o[k] = (P.srgb && k != P.alpha) ? encode_srgb8(acc[k]) : encode_linear8(acc[k]);
+    uint8_t* d = P.dst + ((size_t)oy * P.out_w + ox) * CH;
+    if (CH == 4) *(uchar4*)d = make_uchar4(o[0], o[1], o[2], o[CH - 1]);
+    else {
+#pragma unroll
+        for (int k = 0; k < CH; k++) d[k] = o[k];
+    }
+}
+
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream)
 {
+    if (P.uniform && P.tileOk) {
+        const dim3 grid2((unsigned)(P.out_w + 31) / 32, (unsigned)(P.out_h + 7) / 8);
+        if (f32 && channels == 3) mip_resize_tile2_kernel<3, true><<<grid2, 256, 0, stream>>>(P);
+        else if (f32 && channels == 4) mip_resize_tile2_kernel<4, true><<<grid2, 256, 0, stream>>>(P);
+        else if (!f32 && channels == 1) mip_resize_tile2_kernel<1, false><<<grid2, 256, 0, stream>>>(P);
+        else if (!f32 && channels == 2) mip_resize_tile2_kernel<2, false><<<grid2, 256, 0, stream>>>(P);
+        else if (!f32 && channels == 4) mip_resize_tile2_kernel<4, false><<<grid2, 256, 0, stream>>>(P);
+        else return cudaErrorInvalidValue;
+        return cudaGetLastError();
+    }
     const dim3 grid((unsigned)(P.out_w + 31) / 32, (unsigned)(P.out_h + 7) / 8);
+    if (P.tileOk && P.Tx <= 8 && P.Ty <= 8) {
+        if (f32 && channels == 3) mip_resize_tile_kernel<3, true><<<grid, 256, 0, stream>>>(P);
+        else if (f32 && channels == 4) mip_resize_tile_kernel<4, true><<<grid, 256, 0, stream>>>(P);
+        else if (!f32 && channels == 1) mip_resize_tile_kernel<1, false><<<grid, 256, 0, stream>>>(P);
+        else if (!f32 && channels == 2) mip_resize_tile_kernel<2, false><<<grid, 256, 0, stream>>>(P);
+        else if (!f32 && channels == 4) mip_resize_tile_kernel<4, false><<<grid, 256, 0, stream>>>(P);
+        else return cudaErrorInvalidValue;
+        return cudaGetLastError();
+    }
     if (f32 && channels == 3) mip_resize_f32x3_kernel<<<grid, 256, 0, stream>>>(P);
     else if (f32) mip_resize_f32_kernel<<<grid, 256, 0, stream>>>(P);
     else if (channels == 1) mip_resize_u8_kernel<1><<<grid, 256, 0, stream>>>(P);
