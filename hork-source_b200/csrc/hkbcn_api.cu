@@ -44,6 +44,13 @@ struct Device {
     void*        d_src = nullptr; size_t src_cap = 0;
     void*        d_dst = nullptr; size_t dst_cap = 0;
     std::mutex   mu; // serialises host-pointer calls that share the scratch buffers
+    // pageable callers (Image.cpp hands over HeapBlob memory): upload ring of two pinned pieces, a pinned copy of the output,
+    // a copy stream and events -- see compress_host_pipelined
+    cudaStream_t copy_stream = nullptr;
+    void*        h_in[2] = {nullptr, nullptr}; size_t h_in_cap[2] = {0, 0};
+    void*        h_out = nullptr; size_t h_out_cap = 0;
+    cudaEvent_t  ev_in[2] = {nullptr, nullptr};
+    cudaEvent_t  ev_piece[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     // mip cascade: decode tables and tap tables (one pair per in/out size, filter and edge mode), built on first use
     float*       lut_srgb = nullptr;
     float*       lut_lin = nullptr;
@@ -277,6 +284,79 @@ size_t chain_src_bytes(int codec, uint32_t flags, uint32_t w, uint32_t h, uint32
     return n;
 }
 
+// Host-pointer compress of a large PAGEABLE surface or chain.  The copy engine cannot read pageable memory: a plain
+// cudaMemcpyAsync from it is staged by the driver and serialises with everything else (27.6 ms for the 4096^2 BC7 chain
+// against 21.0 ms from pinned memory).  Here the chain is cut into pieces -- bands of block rows of level 0, then levels 1..
+// together -- and each piece is copied by this thread into one of two pinned buffers, uploaded on a copy stream and encoded
+// by its own launch as soon as it has arrived, so the staging copy of piece i + 1 runs under the kernel of piece i; outputs
+// come back through a pinned buffer the same way.  Same kernels, same bytes out.
+int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, uint8_t* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags)
+{
+    const uint32_t bpp = src_bpp(codec, flags), bb = blk_bytes(codec);
+    struct Piece { size_t soff, sbytes, doff, dbytes; uint32_t lvl0, lvl1, row0, rows; };
+    std::vector<Piece> pieces;
+    const uint32_t nby = h / 4;
+    const size_t l0 = (size_t)w * h * bpp;
+    int nb = (int)std::min<size_t>(6, std::max<size_t>(1, l0 / (12u << 20)));
+    if ((uint32_t)nb > nby) nb = (int)nby;
+    for (int b = 0; b < nb; b++) {
+        const uint32_t r0 = (uint32_t)((uint64_t)nby * b / nb), r1 = (uint32_t)((uint64_t)nby * (b + 1) / nb);
+        pieces.push_back({(size_t)r0 * 4 * w * bpp, (size_t)(r1 - r0) * 4 * w * bpp, (size_t)r0 * (w / 4) * bb, (size_t)(r1 - r0) * (w / 4) * bb, 0, 1, r0, r1 - r0});
+    }
+    if (mips > 1) {
+        const size_t s1 = chain_src_bytes(codec, flags, w, h, mips) - l0, d0 = (size_t)(w / 4) * nby * bb;
+        pieces.push_back({l0, s1, d0, hkbcn_chain_bytes(fmt, w, h, 1, mips) - d0, 1, mips, 0, 0});
+    }
+    if (pieces.size() > 8) { set_err("internal: too many pieces"); return HKBCN_ERR_BAD_ARG; }
+    const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips), dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
+    size_t maxp = 0;
+    for (auto& p : pieces) maxp = std::max(maxp, p.sbytes);
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    int rc;
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    for (int i = 0; i < 2; i++) {
+        if ((rc = grow_pinned(&D->h_in[i], &D->h_in_cap[i], maxp)) != HKBCN_OK) return rc;
+        if (!D->ev_in[i]) CK(cudaEventCreateWithFlags(&D->ev_in[i], cudaEventDisableTiming));
+    }
+    if ((rc = grow_pinned(&D->h_out, &D->h_out_cap, dbytes)) != HKBCN_OK) return rc;
+    if (!D->copy_stream) CK(cudaStreamCreateWithFlags(&D->copy_stream, cudaStreamNonBlocking));
+    for (size_t i = 0; i < pieces.size(); i++)
+        if (!D->ev_piece[i]) CK(cudaEventCreateWithFlags(&D->ev_piece[i], cudaEventDisableTiming));
+    for (size_t i = 0; i < pieces.size(); i++) {
+        const Piece& p = pieces[i];
+        const int slot = (int)(i & 1);
+        if (i >= 2) CK(cudaEventSynchronize(D->ev_in[slot])); // the slot's previous upload has left it
+        memcpy(D->h_in[slot], src + p.soff, p.sbytes);
+        CK(cudaMemcpyAsync((uint8_t*)D->d_src + p.soff, D->h_in[slot], p.sbytes, cudaMemcpyHostToDevice, D->copy_stream));
+        CK(cudaEventRecord(D->ev_in[slot], D->copy_stream));
+        CK(cudaStreamWaitEvent(D->stream, D->ev_in[slot], 0));
+        EncodeParams P;
+        memset(&P, 0, sizeof(P));
+        P.flags = flags;
+        if (p.lvl0 == 0) {
+            add_level(P, codec, flags, (uint8_t*)D->d_src + p.soff, (uint8_t*)D->d_dst + p.doff, w, p.rows * 4);
+        } else {
+            size_t so = l0, dof = p.doff;
+            for (uint32_t l = p.lvl0; l < p.lvl1; l++) {
+                const uint32_t lw = mip_dim(w, l), lh = mip_dim(h, l);
+                add_level(P, codec, flags, (uint8_t*)D->d_src + so, (uint8_t*)D->d_dst + dof, lw, lh);
+                so += (size_t)lw * lh * bpp;
+                dof += (size_t)(lw / 4) * (lh / 4) * bb;
+            }
+        }
+        if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
+        CK(cudaMemcpyAsync((uint8_t*)D->h_out + p.doff, (uint8_t*)D->d_dst + p.doff, p.dbytes, cudaMemcpyDeviceToHost, D->stream));
+        CK(cudaEventRecord(D->ev_piece[i], D->stream));
+    }
+    for (size_t i = 0; i < pieces.size(); i++) {
+        CK(cudaEventSynchronize(D->ev_piece[i]));
+        memcpy(dst + pieces[i].doff, (uint8_t*)D->h_out + pieces[i].doff, pieces[i].dbytes);
+    }
+    return HKBCN_OK;
+}
+
 int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags,
                      uint32_t slices = 1)
 {
@@ -289,6 +369,10 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
     const size_t sbytes = ragged ? (size_t)w * h * src_bpp(codec, flags) : chain_src_bytes(codec, flags, w, h, mips, slices);
     const size_t dbytes = hkbcn_chain_bytes(fmt, w, h, slices, mips);
     if (dbytes == 0) return HKBCN_OK;
+    if (!ragged && slices == 1 && sbytes >= (16u << 20) && !getenv("HKBCN_NO_PIPELINE")) {
+        CK(cudaSetDevice(D->id));
+        if (!is_pinned(src)) return compress_host_pipelined(D, fmt, codec, (const uint8_t*)src, (uint8_t*)dst, w, h, mips, flags);
+    }
     std::lock_guard<std::mutex> lk(D->mu);
     CK(cudaSetDevice(D->id));
     int rc;
@@ -322,6 +406,13 @@ static void destroy_device(Device* D)
     if (D->d_dst) cudaFree(D->d_dst);
     if (D->lut_srgb) cudaFree(D->lut_srgb);
     if (D->lut_lin) cudaFree(D->lut_lin);
+    for (int i = 0; i < 2; i++) {
+        if (D->h_in[i]) cudaFreeHost(D->h_in[i]);
+        if (D->ev_in[i]) cudaEventDestroy(D->ev_in[i]);
+    }
+    if (D->h_out) cudaFreeHost(D->h_out);
+    for (cudaEvent_t e : D->ev_piece) if (e) cudaEventDestroy(e);
+    if (D->copy_stream) cudaStreamDestroy(D->copy_stream);
     for (uint32_t* c : D->sched_chunks) cudaFree(c);
     for (auto& sl : D->slots) {
         if (sl.d_src) cudaFree(sl.d_src);
@@ -882,6 +973,71 @@ int hkbcn_decompress(int fmt, const void* src, void* dst, uint32_t width, uint32
     return HKBCN_OK;
 }
 
+// ---- whole storages: one launch per mip level, the level's slices as one tall surface ------------------------------------
+size_t hkbcn_decoded_chain_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips, uint32_t flags)
+{
+    const int codec = codec_of(fmt);
+    if (codec < 0) return 0;
+    size_t n = 0;
+    for (uint32_t i = 0; i < num_mips; i++) n += (size_t)mip_dim(width, i) * mip_dim(height, i) * slices * dst_bpp(codec, flags);
+    return n;
+}
+
+int hkbcn_decompress_slices_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t slices,
+                                uint32_t num_mips, uint32_t flags, void* stream)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (width == 0 || height == 0) return HKBCN_OK;
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
+    if (slices == 0 || (uint64_t)height * slices > 0x40000000ull) { set_err("slice count %u out of range", slices); return HKBCN_ERR_BAD_ARG; }
+    const uint8_t* s = (const uint8_t*)d_src;
+    uint8_t* d = (uint8_t*)d_dst;
+    for (uint32_t i = 0; i < num_mips; i++) {
+        const uint32_t lw = mip_dim(width, i), lh = mip_dim(height, i) * slices;
+        if ((rc = hkbcn_decompress_dev(device, fmt, s, d, lw, lh, (size_t)lw * dst_bpp(codec, flags), flags, stream)) != HKBCN_OK) return rc;
+        s += (size_t)(lw / 4) * (lh / 4) * blk_bytes(codec);
+        d += (size_t)lw * lh * dst_bpp(codec, flags);
+    }
+    return HKBCN_OK;
+}
+
+int hkbcn_decompress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips, uint32_t flags)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
+    const size_t sbytes = hkbcn_chain_bytes(fmt, width, height, slices, num_mips);
+    const size_t dbytes = hkbcn_decoded_chain_bytes(fmt, width, height, slices, num_mips, flags);
+    if (sbytes == 0) return HKBCN_OK;
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src, sbytes, cudaMemcpyHostToDevice, D->stream));
+    if ((rc = hkbcn_decompress_slices_dev(0, fmt, D->d_src, D->d_dst, width, height, slices, num_mips, flags, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_decompress_chain_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t num_mips,
+                               uint32_t flags, void* stream)
+{
+    return hkbcn_decompress_slices_dev(device, fmt, d_src, d_dst, width, height, 1, num_mips, flags, stream);
+}
+
+int hkbcn_decompress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags)
+{
+    return hkbcn_decompress_slices(fmt, src, dst, width, height, 1, num_mips, flags);
+}
+
 int hkbcn_decode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, size_t dst_row_stride, uint32_t flags)
 {
     if (n_blocks == 0) return HKBCN_OK;
@@ -941,6 +1097,86 @@ int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
                 j.status = compress_host_on(g_devs[d], j.fmt, j.src, j.dst, j.width, j.height & ~3u, 1, j.flags);
                 if (j.status && !first_err[d]) { first_err[d] = j.status; err_msg[d] = t_err; }
             }
+        });
+    }
+    for (auto& t : th) t.join();
+    for (size_t d = 0; d < nd; d++)
+        if (first_err[d]) { set_err("%s", err_msg[d].c_str()); return first_err[d]; }
+    return HKBCN_OK;
+}
+
+// independent surfaces decoded on the selected GPUs, whole surfaces per GPU (greedy by output bytes), results straight into
+// each job's dst; per GPU the uploads, launches and downloads of consecutive jobs are queued without a host sync in between
+int hkbcn_decompress_batch(hkbcn_job* jobs, size_t n_jobs)
+{
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (n_jobs == 0) return HKBCN_OK;
+    if (!jobs) { set_err("null jobs"); return HKBCN_ERR_BAD_ARG; }
+    const size_t nd = g_devs.size();
+    std::vector<size_t> order(n_jobs);
+    for (size_t i = 0; i < n_jobs; i++) order[i] = i;
+    auto out_bytes = [](const hkbcn_job& j) {
+        const int c = codec_of(j.fmt);
+        return c < 0 ? (size_t)0 : (size_t)(j.width / 4) * 4 * (j.height / 4) * 4 * dst_bpp(c, j.flags);
+    };
+    std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return out_bytes(jobs[a]) > out_bytes(jobs[b]); });
+    std::vector<std::vector<size_t>> bins(nd);
+    std::vector<size_t> load(nd, 0);
+    for (size_t idx : order) {
+        size_t best = 0;
+        for (size_t d = 1; d < nd; d++) if (load[d] < load[best]) best = d;
+        bins[best].push_back(idx);
+        load[best] += out_bytes(jobs[idx]);
+    }
+    std::vector<std::thread> th;
+    std::vector<int> first_err(nd, 0);
+    std::vector<std::string> err_msg(nd);
+    for (size_t dv = 0; dv < nd; dv++) {
+        th.emplace_back([&, dv]() {
+            Device* D = g_devs[dv];
+            std::lock_guard<std::mutex> lk(D->mu);
+            auto fail = [&](hkbcn_job& j, int e) {
+                j.status = e;
+                if (!first_err[dv]) { first_err[dv] = e; err_msg[dv] = t_err; }
+            };
+            if (cudaSetDevice(D->id) != cudaSuccess) { set_err("cudaSetDevice failed"); for (size_t idx : bins[dv]) fail(jobs[idx], HKBCN_ERR_CUDA); return; }
+            // device scratch for the whole bin: every job gets its own range, so nothing waits for a buffer
+            size_t sb = 0, db = 0;
+            for (size_t idx : bins[dv]) {
+                const hkbcn_job& j = jobs[idx];
+                const int c = codec_of(j.fmt);
+                if (c < 0) continue;
+                sb += ((size_t)(j.width / 4) * (j.height / 4) * blk_bytes(c) + 255) & ~(size_t)255;
+                db += (out_bytes(j) + 255) & ~(size_t)255;
+            }
+            int e;
+            if ((e = grow(&D->d_src, &D->src_cap, sb)) != HKBCN_OK || (e = grow(&D->d_dst, &D->dst_cap, db)) != HKBCN_OK) {
+                for (size_t idx : bins[dv]) fail(jobs[idx], e);
+                return;
+            }
+            size_t so = 0, dof = 0;
+            for (size_t idx : bins[dv]) {
+                hkbcn_job& j = jobs[idx];
+                j.status = HKBCN_OK;
+                const int c = codec_of(j.fmt);
+                if (c < 0) { set_err("bad format %d", j.fmt); fail(j, HKBCN_ERR_BAD_FORMAT); continue; }
+                const uint32_t nbx = j.width / 4, nby = j.height / 4;
+                if (!nbx || !nby) continue;
+                if (!j.src || !j.dst) { set_err("null pointer"); fail(j, HKBCN_ERR_BAD_ARG); continue; }
+                const size_t sbytes = (size_t)nbx * nby * blk_bytes(c), dbytes = out_bytes(j);
+                cudaError_t ce = cudaMemcpyAsync((uint8_t*)D->d_src + so, j.src, sbytes, cudaMemcpyHostToDevice, D->stream);
+                if (ce == cudaSuccess) {
+                    e = hkbcn_decompress_dev((int)dv, j.fmt, (uint8_t*)D->d_src + so, (uint8_t*)D->d_dst + dof, nbx * 4, nby * 4,
+                                             (size_t)nbx * 4 * dst_bpp(c, j.flags), j.flags, D->stream);
+                    if (e) { fail(j, e); continue; }
+                    ce = cudaMemcpyAsync(j.dst, (uint8_t*)D->d_dst + dof, dbytes, cudaMemcpyDeviceToHost, D->stream);
+                }
+                if (ce != cudaSuccess) { set_err("copy failed: %s", cudaGetErrorString(ce)); fail(j, HKBCN_ERR_CUDA); }
+                so += (sbytes + 255) & ~(size_t)255;
+                dof += (dbytes + 255) & ~(size_t)255;
+            }
+            if (cudaStreamSynchronize(D->stream) != cudaSuccess) { set_err("decode batch failed on device %d", D->id); for (size_t idx : bins[dv]) fail(jobs[idx], HKBCN_ERR_CUDA); }
         });
     }
     for (auto& t : th) t.join();

@@ -30,6 +30,8 @@ EXPORTS = [
     "hkbcn_compress_dev", "hkbcn_decompress_dev", "hkbcn_compress_chain_dev", "hkbcn_compress_chain",
     "hkbcn_slices_src_bytes", "hkbcn_compress_slices_dev", "hkbcn_compress_slices", "hkbcn_compress_chain_multi", "hkbcn_plan_bands",
     "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
+    "hkbcn_decoded_chain_bytes", "hkbcn_decompress_slices_dev", "hkbcn_decompress_slices", "hkbcn_decompress_chain_dev", "hkbcn_decompress_chain",
+    "hkbcn_decompress_batch",
     "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
     "hkbcn_texture_header", "hkbcn_write_texture", "hkbcn_read_texture", "hkbcn_import_batch",
     "hkbcn_envprobe_texels", "hkbcn_envprobe_prefilter", "hkbcn_irradiance", "hkbcn_envprobe_prefilter_dev", "hkbcn_irradiance_dev",
@@ -93,6 +95,13 @@ def lib():
         L.hkbcn_compress_chain_multi.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
         L.hkbcn_plan_bands.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         L.hkbcn_compress_batch.argtypes = [C.POINTER(Job), C.c_size_t]
+        L.hkbcn_decompress_batch.argtypes = [C.POINTER(Job), C.c_size_t]
+        L.hkbcn_decoded_chain_bytes.restype = C.c_size_t
+        L.hkbcn_decoded_chain_bytes.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_decompress_slices_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.hkbcn_decompress_slices.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.hkbcn_decompress_chain_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.hkbcn_decompress_chain.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
         L.hkbcn_plan_batch.argtypes = [C.POINTER(Job), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
         L.hkbcn_mip_taps.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
         L.hkbcn_chain_src_bytes.restype = C.c_size_t
@@ -209,6 +218,28 @@ def decode_blocks(fmt, blocks, n, row_stride, flags=0):
     dst = np.zeros(n * 4 * row_stride, np.uint8)
     check(lib().hkbcn_decode_blocks(fmt, _ptr(blocks), _ptr(dst), n, row_stride, flags))
     return dst
+
+
+def decompress_slices(fmt, blocks, width, height, slices, mips, flags=0):
+    """whole storage (all slices of all levels, ImageStorage order) -> decoded levels back to back"""
+    blocks = np.ascontiguousarray(blocks)
+    dst = np.zeros(lib().hkbcn_decoded_chain_bytes(fmt, width, height, slices, mips, flags), np.uint8)
+    check(lib().hkbcn_decompress_slices(fmt, _ptr(blocks), _ptr(dst), width, height, slices, mips, flags))
+    return dst
+
+
+def decompress_batch(jobs):
+    """jobs: list of (fmt, blocks ndarray, width, height, flags) -> list of decoded ndarrays (tightly packed)"""
+    arr = (Job * len(jobs))()
+    keep, outs = [], []
+    for i, (fmt, blocks, w, h, flags) in enumerate(jobs):
+        blocks = np.ascontiguousarray(blocks)
+        dst = np.zeros((w // 4) * 4 * (h // 4) * 4 * lib().hkbcn_dst_texel_bytes(fmt, flags), np.uint8)
+        keep.append(blocks)
+        outs.append(dst)
+        arr[i] = Job(fmt, w, h, flags, blocks.ctypes.data, dst.ctypes.data, 0)
+    check(lib().hkbcn_decompress_batch(arr, len(jobs)))
+    return outs
 
 
 def compress_batch(jobs):

@@ -113,6 +113,20 @@ HKBCN_API int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width
 HKBCN_API int hkbcn_decompress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height,
                                size_t dst_row_stride, uint32_t flags);
 
+/* Decode of whole storages: every slice (cube face, array layer) of every mip level of an ImageStorage (Image.cpp:498-574)
+ * with one launch per LEVEL -- the slices of a level are contiguous in the storage and decode as one tall surface -- instead
+ * of one call per block (the reference's Decode_BC* loop, ImageEncoders.cpp:77-136) or one launch per surface.  src: the
+ * compressed storage (hkbcn_chain_bytes()); dst: the decoded levels back to back, level i = slices x max(w>>i,4) x max(h>>i,4)
+ * texels tightly packed (hkbcn_decoded_chain_bytes()).  A batch of same-sized textures is the slices form with num_mips = 1. */
+HKBCN_API size_t hkbcn_decoded_chain_bytes(int fmt, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips, uint32_t flags);
+HKBCN_API int hkbcn_decompress_slices_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                          uint32_t slices, uint32_t num_mips, uint32_t flags, void* stream);
+HKBCN_API int hkbcn_decompress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices,
+                                      uint32_t num_mips, uint32_t flags);
+HKBCN_API int hkbcn_decompress_chain_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                         uint32_t num_mips, uint32_t flags, void* stream);
+HKBCN_API int hkbcn_decompress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags);
+
 /* ---- per-block entry points (ImageEncoders.h:48-64), host pointers ----------
  * n_blocks contiguous 4x4 blocks (src: n * 16 texels, dst: n * block_bytes). The
  * reference signatures are the n_blocks == 1 case. */
@@ -200,6 +214,8 @@ typedef struct hkbcn_job {
     int         status;/* out */
 } hkbcn_job;
 HKBCN_API int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs);
+/* the same for decode: job.src = blocks, job.dst = texels tightly packed ((width / 4) * 4 texels per row), job.flags = HKBCN_FLAG_DST_F32 */
+HKBCN_API int hkbcn_decompress_batch(hkbcn_job* jobs, size_t n_jobs);
 /* The planning step of hkbcn_compress_batch on its own (host only, no device needed): device_of_job[i] = index (0..n_gpus-1)
  * of the GPU job i would be sent to.  Greedy longest-processing-time by pixel count x per-format cost weight; deterministic. */
 HKBCN_API int hkbcn_plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job);
