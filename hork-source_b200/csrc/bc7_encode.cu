@@ -35,7 +35,7 @@ __device__ bc7::Tables g_bc7_tables;
 #define BC7_THREADS 512
 #endif
 constexpr int BC7_NT = BC7_THREADS;
-constexpr int BC7_OCC = 512 / BC7_NT; // 128 registers per thread
+constexpr int BC7_OCC = BC7_NT >= 512 ? 1 : 512 / BC7_NT; // 128 registers per thread at 512 threads
 constexpr int BC7_TB = BC7_TILE_BLOCKS;
 constexpr size_t BC7_SMEM = 4 * BC7_TB * 16 + 64 * BC7_NT + sizeof(bc7::Tables); // stage, transposed texels, tables
 

@@ -1,14 +1,19 @@
-"""Row f4 parity: normal-map packers / unpackers, NormalizeVectors and the roughness bake on the device against the C
-restatement of the reference loops (oracle/oracle_pack.c; ImageEncoders.cpp:693-878, Image.cpp:2251-2260, :2526-2580).
+"""Row f4 parity: normal-map packers / unpackers, NormalizeVectors and the roughness bake on the device against the
+REFERENCE'S OWN functions compiled from the reference tree (oracle/_ref/libhkref_pack.so: ImageEncoders.cpp:692-878,
+Image.cpp:2251-2260, :2541-2579 with the engine's Float3 / Math::, oracle/ref_pack_shim.cpp); the plain-C restatement
+(oracle/oracle_pack.c, pinned to that library by tests/test_normals_cpu.py) stands in where the library is absent.
 Packers, unpackers and normalisation: bit-exact.  Bake: the averaged normals come from the device cascade (within 1e-6 of
 stbir, tests/test_gpu_mips.py), so a roughness value may land on the other side of a rounding boundary: +-1 LSB."""
 import numpy as np
 import pytest
 
 import hkbcn
-import oracle_c
+import oracle_c as oracle_port
+import refpack
 import refshim
 import synth
+
+oracle_c = refpack if refpack.have() else oracle_port  # the checker: reference object code when built
 
 pytestmark = pytest.mark.gpu
 VARIANTS = [0, 1, 2, 3, 4, 5]
