@@ -39,6 +39,9 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
     uint32_t phase = 0;
     const int k = threadIdx.x / G;
     const int sub = threadIdx.x % G;
+    // HKBCN_FLAG_LEVEL: rgbcx level + 1 in bits 4..8 (0 = the Compress* preset, level 5); HKBCN_FLAG_FAST: non-hq BC3 alpha
+    const int level = ((P.flags >> 4) & 31u) ? (int)((P.flags >> 4) & 31u) - 1 : 5;
+    const bool fastAlpha = (P.flags & 2u) != 0;
 
     for (uint32_t tile = blockIdx.x; tile < P.totalTiles; tile += gridDim.x) {
         const Level& L = P.lv[find_level(P, tile)];
@@ -60,7 +63,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
         }
 
         if (CODEC == C_BC1) {
-            if (valid) *(uint2*)(L.dst + (size_t)(b0 + k) * 8) = bc1_encode_block(px);
+            if (valid) *(uint2*)(L.dst + (size_t)(b0 + k) * 8) = bc1_encode_block(px, level);
         } else if (CODEC == C_BC2) {
             if (valid) {
                 uint32_t a[2] = {0, 0};
@@ -71,7 +74,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
                     q = min(q, 15);
                     a[i >> 3] |= (uint32_t)q << (4 * (i & 7));
                 }
-                uint2 c = bc1_encode_block(px);
+                uint2 c = bc1_encode_block(px, level);
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(a[0], a[1], c.x, c.y);
             }
         } else { // BC3
@@ -85,11 +88,12 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
                 maxv = max(maxv, max(p0, p1));
             }
             uint32_t key = 0xFFFFFFFFu;
-            if (minv != maxv) key = bc4hq_search_mode(a2, minv, maxv, sub);
+            if (minv != maxv && !fastAlpha) key = bc4hq_search_mode(a2, minv, maxv, sub);
             key = min(key, __shfl_xor_sync(0xFFFFFFFFu, key, 1));
             if (valid && sub == 0) {
-                uint2 al = (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
-                uint2 c = bc1_encode_block(px);
+                // bMaxQuality = false: rgbcx::encode_bc3 = the non-hq encode_bc4 on alpha (rgbcx.cpp:2886-2903)
+                uint2 al = fastAlpha ? bc4_fast(a2, minv, maxv) : (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
+                uint2 c = bc1_encode_block(px, level);
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(al.x, al.y, c.x, c.y);
             }
         }

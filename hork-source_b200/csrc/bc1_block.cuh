@@ -1,9 +1,15 @@
 // bc1_block.cuh -- BC1 colour-block encoder for one 4x4 RGBA8 block (one thread).
 //
-// Behaviour contract: byte-identical to rgbcx::encode_bc1(level = 5, dst, px, false, false)
-// (ThirdParty/bc7enc_rdo/rgbcx.cpp:1692-1726 -> flags TwoLeastSquaresPasses|UseFasterMSEEval
-// -> :2263-2604, the `!needs_block_error` branch :2316-2371), the call behind
-// Encode_BC1/2/3 in Hork/Image/ImageEncoders.cpp:138-169.
+// Behaviour contract: byte-identical to rgbcx::encode_bc1(level, dst, px, false, false) for the levels whose flag sets
+// take the encoder's `!needs_block_error` branch (ThirdParty/bc7enc_rdo/rgbcx.cpp:1692-1726 -> :2263-2604, branch
+// :2316-2371) -- the call behind Encode_BC1/2/3 in Hork/Image/ImageEncoders.cpp:138-169:
+//   level 0  cEncodeBC1BoundingBoxInt: inset bounding box as initial endpoints (:2030-2085), one least-squares pass
+//   level 1  cEncodeBC1Use2DLS: 2-D least squares on the widest channel (:1837-1986), one pass
+//   level 2  principal axis (:2086-2174), one pass
+//   level 3  principal axis, two passes            level 5 (the Compress* preset): the same -- its extra flag,
+//            cEncodeBC1UseFasterMSEEval, is only read by the other branch
+// Levels 4 and 6..18 and the 3-colour flags take the error-tracking branch (total orderings, endpoint search rounds):
+// not built, the C ABI answers HKBCN_ERR_UNSUPPORTED for them.
 //
 // FP32 discipline: the reference is built without FMA contraction (baseline x86-64,
 // SURVEY.md 7), so every float op here is an explicitly rounded __fmul_rn/__fadd_rn/
@@ -105,8 +111,85 @@ __device__ __forceinline__ uint2 bc1_pack4(const Bc1Ep& e, uint32_t sels)
     return make_uint2(lc16 | (hc16 << 16), packed ^ inv);
 }
 
-// The whole level-5 colour path.  px[i] = R | G<<8 | B<<16 | A<<24 (alpha ignored).
-__device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16])
+// precise_round_565_noscale (rgbcx.cpp:1230-1243) for one endpoint
+__device__ __forceinline__ void round_565_noscale(float x0, float x1, float x2, int& r, int& g, int& b)
+{
+    round_565(__fmul_rn(x0, 1.0f / 255.0f), __fmul_rn(x1, 1.0f / 255.0f), __fmul_rn(x2, 1.0f / 255.0f), r, g, b);
+}
+
+// cEncodeBC1Use2DLS (rgbcx.cpp:1837-1986): regress the two narrower channels on the widest one (x), endpoints at x's range
+// inset by 1/16.  c[0] = x, c[1], c[2] = the other two in R, G, B order; the three branches of the reference differ only in
+// which channel plays x.
+__device__ __forceinline__ void bc1_initial_2dls(const uint32_t px[16], int min_v[3], int max_v[3], const int total[3], Bc1Ep& e)
+{
+    int big = 0, min_c = min_v[0], max_c = max_v[0];
+    if ((max_v[1] - min_v[1]) > (max_c - min_c)) { big = 1; min_c = min_v[1]; max_c = max_v[1]; }
+    if ((max_v[2] - min_v[2]) > (max_c - min_c)) { big = 2; min_c = min_v[2]; max_c = max_v[2]; }
+    const int o1 = big == 0 ? 1 : 0, o2 = big == 2 ? 1 : 2; // the other two channels, ascending
+    int sum_x2 = 0, sum_xy1 = 0, sum_xy2 = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int c0 = px[i] & 0xFF, c1 = (px[i] >> 8) & 0xFF, c2 = (px[i] >> 16) & 0xFF;
+        const int x = big == 0 ? c0 : big == 1 ? c1 : c2;
+        const int y1 = o1 == 0 ? c0 : c1, y2 = o2 == 1 ? c1 : c2;
+        sum_x2 += x * x; sum_xy1 += x * y1; sum_xy2 += x * y2;
+    }
+    const int sum_x = total[big], t1 = total[o1], t2 = total[o2];
+    float div = (float)(16 * sum_x2 - sum_x * sum_x);
+    float b1 = 0.0f, b2 = 0.0f;
+    if (fabsf(div) > 1e-8f) {
+        div = __fdiv_rn(1.0f, div);
+        b1 = __fmul_rn((float)(16 * sum_xy1 - sum_x * t1), div);
+        b2 = __fmul_rn((float)(16 * sum_xy2 - sum_x * t2), div);
+    }
+    const float a1 = __fdiv_rn(__fadd_rn((float)t1, -__fmul_rn(b1, (float)sum_x)), 16.0f);
+    const float a2 = __fdiv_rn(__fadd_rn((float)t2, -__fmul_rn(b2, (float)sum_x)), 16.0f);
+    float l1 = __fadd_rn(a1, __fmul_rn(b1, (float)min_c)), l2 = __fadd_rn(a2, __fmul_rn(b2, (float)min_c));
+    float h1 = __fadd_rn(a1, __fmul_rn(b1, (float)max_c)), h2 = __fadd_rn(a2, __fmul_rn(b2, (float)max_c));
+    const float d1 = __fadd_rn(h1, -l1), d2 = __fadd_rn(h2, -l2);
+    h1 = __fadd_rn(l1, __fmul_rn(d1, 15.0f / 16.0f));
+    h2 = __fadd_rn(l2, __fmul_rn(d2, 15.0f / 16.0f));
+    l1 = __fadd_rn(l1, __fmul_rn(d1, 1.0f / 16.0f));
+    l2 = __fadd_rn(l2, __fmul_rn(d2, 1.0f / 16.0f));
+    const float d = (float)(max_c - min_c);
+    const float l0 = __fadd_rn((float)min_c, __fmul_rn(d, 1.0f / 16.0f)), h0 = __fadd_rn((float)min_c, __fmul_rn(d, 15.0f / 16.0f));
+    float l[3], h[3];
+    l[big] = l0; h[big] = h0;
+    l[o1] = l1; h[o1] = h1;
+    l[o2] = l2; h[o2] = h2;
+    round_565_noscale(l[0], l[1], l[2], e.lr, e.lg, e.lb);
+    round_565_noscale(h[0], h[1], h[2], e.hr, e.hg, e.hb);
+}
+
+// cEncodeBC1BoundingBoxInt (rgbcx.cpp:2030-2085)
+__device__ __forceinline__ void bc1_initial_bbox_int(const uint32_t px[16], int min_r, int min_g, int min_b, int max_r, int max_g, int max_b, int avg_r,
+                                                     int avg_g, int avg_b, Bc1Ep& e)
+{
+    const int inset_r = (max_r - min_r - 8) >> 4, inset_g = (max_g - min_g - 8) >> 4, inset_b = (max_b - min_b - 8) >> 4;
+    min_r += inset_r; min_g += inset_g; min_b += inset_b;
+    if ((uint32_t)(min_r | min_g | min_b) > 255u) {
+        min_r = min(max(min_r, 0), 255); min_g = min(max(min_g, 0), 255); min_b = min(max(min_b, 0), 255);
+    }
+    max_r -= inset_r; max_g -= inset_g; max_b -= inset_b;
+    if ((uint32_t)(max_r | max_g | max_b) > 255u) {
+        max_r = min(max(max_r, 0), 255); max_g = min(max(max_g, 0), 255); max_b = min(max(max_b, 0), 255);
+    }
+    int icov_xz = 0, icov_yz = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int r = (int)(px[i] & 0xFF) - avg_r, g = (int)((px[i] >> 8) & 0xFF) - avg_g, b = (int)((px[i] >> 16) & 0xFF) - avg_b;
+        icov_xz += r * b;
+        icov_yz += g * b;
+    }
+    int x0 = min_r, y0 = min_g, x1 = max_r, y1 = max_g;
+    if (icov_xz < 0) { const int t = x0; x0 = x1; x1 = t; }
+    if (icov_yz < 0) { const int t = y0; y0 = y1; y1 = t; }
+    e.lr = to_5(x0); e.lg = to_6(y0); e.lb = to_5(min_b);
+    e.hr = to_5(x1); e.hg = to_6(y1); e.hb = to_5(max_b);
+}
+
+// The colour path of levels 0, 1, 2, 3 and 5 (see the header).  px[i] = R | G<<8 | B<<16 | A<<24 (alpha ignored).
+__device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16], const int level = 5)
 {
     const uint32_t rgb0 = px[0] & 0xFFFFFFu;
     const int fr = rgb0 & 0xFF, fg = (rgb0 >> 8) & 0xFF, fb = rgb0 >> 16;
@@ -138,6 +221,12 @@ __device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16])
             e.lr = e.lb = to_5(min_r); e.lg = to_6(min_r);
             e.hr = e.hb = to_5(max_r); e.hg = to_6(max_r);
         }
+    } else if (level == 1) {
+        int mn[3] = {min_r, min_g, min_b}, mx[3] = {max_r, max_g, max_b};
+        const int tot[3] = {total_r, total_g, total_b};
+        bc1_initial_2dls(px, mn, mx, tot, e);
+    } else if (level == 0) {
+        bc1_initial_bbox_int(px, min_r, min_g, min_b, max_r, max_g, max_b, avg_r, avg_g, avg_b, e);
     } else {
         int ic0 = 0, ic1 = 0, ic2 = 0, ic3 = 0, ic4 = 0, ic5 = 0;
 #pragma unroll
@@ -190,9 +279,10 @@ __device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16])
 
     uint32_t sels = bc1_find_sels4(px, e);
 
-    // ---- two least-squares passes (rgbcx.cpp:2333-2370; LS solve :727-773)
+    // ---- one (levels 0..2) or two least-squares passes (rgbcx.cpp:2333-2370; LS solve :727-773)
+    const int passes = level >= 3 ? 2 : 1;
 #pragma unroll 1
-    for (int pass = 0; pass < 2; pass++) {
+    for (int pass = 0; pass < passes; pass++) {
         uint32_t wacc = 0, uq_r = 0, uq_g = 0, uq_b = 0;
 #pragma unroll
         for (int i = 0; i < 16; i++) {

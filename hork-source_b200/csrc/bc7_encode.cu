@@ -26,13 +26,13 @@ __device__ bc7::Tables g_bc7_tables;
 #define BC7_DYNAMIC 1
 #endif
 #ifndef BC7_TILE_BLOCKS
-#define BC7_TILE_BLOCKS 512
+#define BC7_TILE_BLOCKS 640
 #endif
 #ifndef BC7_PHASE_SYNC
 #define BC7_PHASE_SYNC 1
 #endif
 #ifndef BC7_THREADS
-#define BC7_THREADS 512
+#define BC7_THREADS 640
 #endif
 constexpr int BC7_NT = BC7_THREADS;
 constexpr int BC7_OCC = BC7_NT >= 512 ? 1 : 512 / BC7_NT; // 128 registers per thread at 512 threads
@@ -62,6 +62,8 @@ __global__ void __launch_bounds__(BC7_NT, BC7_OCC) bc7_encode_kernel(const __gri
     }
     __syncthreads();
     uint32_t phase = 0;
+    // HKBCN_FLAG_LEVEL: uber level + 1 in bits 4..8 of the flags (0 = the CompressBC7 preset, level 4)
+    const int level = ((P.flags >> 4) & 31u) ? min(4, (int)((P.flags >> 4) & 31u) - 1) : 4;
     bc7::Block blk;
     blk.px = tpx + threadIdx.x;
     blk.stride = BC7_NT;
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(BC7_NT, BC7_OCC) bc7_encode_kernel(const __gri
                     tpx[(4 * r + 3) * BC7_NT + threadIdx.x] = v.w;
                 }
             }
-            const uint4 out = bc7::encode_phased(blk, T, c);
+            const uint4 out = bc7::encode_phased(blk, T, c, level);
             if (c < 2) *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }
 #else
@@ -129,7 +131,7 @@ __global__ void __launch_bounds__(BC7_NT, BC7_OCC) bc7_encode_kernel(const __gri
                 tpx[(4 * r + 2) * BC7_NT + threadIdx.x] = v.z;
                 tpx[(4 * r + 3) * BC7_NT + threadIdx.x] = v.w;
             }
-            const uint4 out = (item >= count[0]) ? bc7::encode_alpha(blk, T) : bc7::encode_opaque(blk, T);
+            const uint4 out = (item >= count[0]) ? bc7::encode_alpha(blk, T, level) : bc7::encode_opaque(blk, T, level);
             *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = out;
         }
 #endif

@@ -1,7 +1,7 @@
 // bc7_thread.cuh -- BC7 block encoder, device side (sm_100a): one thread per 4x4 block.
 //
-// Replaces bc7enc_compress_block at uber level 4 with perceptual weights, the configuration
-// Hk::TextureBlockCompression::CompressBC7 bakes in (Hork/Image/ImageEncoders.cpp:59-63, 207-212,
+// Replaces bc7enc_compress_block with perceptual weights at uber level 4, the configuration
+// Hk::TextureBlockCompression::CompressBC7 bakes in, and at levels 0..3 for Encode_BC7(.., Level) (Hork/Image/ImageEncoders.cpp:59-63, 207-212,
 // 524-557 -> ThirdParty/bc7enc_rdo/bc7enc.cpp:2402-2438).  Same mode set (opaque: 6 then 1; any
 // alpha < 255: 6, 5, 7), same candidate generators (principal axis, least-squares refits, selector
 // perturbation and rescale sweep, single-colour tables), same integer YCbCr error metric, and every
@@ -496,7 +496,8 @@ __device__ __forceinline__ void pca_endpoints(const Block& blk, uint32_t mask, c
 
 // Selector the trial t feeds to the least-squares refit for a texel whose best selector is `cur` and whose
 // snapshot selector (taken at t = 2) is `snap` (bc7enc.cpp:1281-1410).
-template <int N> __device__ __forceinline__ int trial_selector(int t, int cur, int snap, int min_sel, int max_sel)
+// level: the uber level (bc7enc.cpp:1384): Q = level - 2 at level 4, else 1; the sweep runs ly in -Q..1, hy in N-2..N-1+Q.
+template <int N> __device__ __forceinline__ int trial_selector(int t, int cur, int snap, int min_sel, int max_sel, int level)
 {
     if (t == 1) return cur;
     if (t < 5) {
@@ -504,8 +505,16 @@ template <int N> __device__ __forceinline__ int trial_selector(int t, int cur, i
         const bool dn = (t != 2) && snap == max_sel && snap > 0;
         return up ? snap + 1 : (dn ? snap - 1 : snap);
     }
-    const int q = (t - 5 < 9) ? t - 5 : t - 4; // skips (ly, hy) = (0, N - 1)
-    const int ly = -2 + (q >> 2), hy = N - 2 + (q & 3);
+    int ly, hy;
+    if (level >= 4) {
+        const int q = (t - 5 < 9) ? t - 5 : t - 4; // skips (ly, hy) = (0, N - 1)
+        ly = -2 + (q >> 2);
+        hy = N - 2 + (q & 3);
+    } else {
+        const int q = (t - 5 < 4) ? t - 5 : t - 4; // 3 x 3 grid minus the identity
+        ly = -1 + q / 3;
+        hy = N - 2 + q % 3;
+    }
     float f = floorf((float)(N - 1) * ((float)snap - (float)ly) / ((float)hy - (float)ly) + .5f);
     f = f < 0.0f ? 0.0f : (f > (float)(N - 1) ? (float)(N - 1) : f);
     return (int)f;
@@ -515,7 +524,7 @@ template <int N> __device__ __forceinline__ int trial_selector(int t, int cur, i
 // Output already multiplied by 1/255 as every call site does.
 template <int MODE, bool ALPHA>
 __device__ __forceinline__ void least_squares(const Block& blk, uint32_t mask, const Tables& T, int t, uint64_t sels, uint64_t st, const int min_sel[],
-                                              const int max_sel[], const int n[], const int sum[][4], float xl[][4], float xh[][4])
+                                              const int max_sel[], const int n[], const int sum[][4], float xl[][4], float xh[][4], int level)
 {
     using C = Cfg<MODE>;
     constexpr int NS = C::NS, N = C::N, NC = ALPHA ? 4 : 3;
@@ -530,7 +539,7 @@ __device__ __forceinline__ void least_squares(const Block& blk, uint32_t mask, c
         const uint32_t v = blk[i];
         const int sb = NS == 2 ? (int)((mask >> i) & 1) : 0;
         const int mn = (NS == 2 && sb) ? min_sel[NS - 1] : min_sel[0], mx = (NS == 2 && sb) ? max_sel[NS - 1] : max_sel[0];
-        const int sel = trial_selector<N>(t, (int)(sels >> (4 * i)) & 15, (int)(st >> (4 * i)) & 15, mn, mx);
+        const int sel = trial_selector<N>(t, (int)(sels >> (4 * i)) & 15, (int)(st >> (4 * i)) & 15, mn, mx, level);
         const float4 wr = *(const float4*)wx_row<N>(T, sel);
         const float c[4] = {(float)(v & 255), (float)((v >> 8) & 255), (float)((v >> 16) & 255), (float)(v >> 24)};
 #pragma unroll
@@ -652,7 +661,9 @@ __device__ __forceinline__ void evaluate_solution(const Block& blk, uint32_t mas
     }
 }
 
-// color_cell_compression (bc7enc.cpp:1101-1441) at uber level 4, for all NS subsets of the mode at once.
+// color_cell_compression (bc7enc.cpp:1101-1441) at uber level `level` (4 = the Compress* preset), for all NS subsets of the mode
+// at once.  The level only shortens the trial schedule: level 0 stops after t = 1 (:1300), level 1 after t = 4 (:1382), levels
+// 2 and 3 sweep a 3 x 3 grid (t = 5..12), level 4 the 4 x 4 one (t = 5..19) (:1384).
 // mask: bit i = subset of texel i (0 for one-subset modes).  res[s]: best per subset; sels: 4 bits per texel.
 //
 // Trial schedule (one loop, so that the quantise + evaluate body exists once in the instruction stream):
@@ -664,8 +675,10 @@ __device__ __forceinline__ void evaluate_solution(const Block& blk, uint32_t mas
 // then, modes 1 / 7, the single-colour encoding of the subset mean (:1413-1438).  A subset whose error reaches 0
 // stops (the reference returns), as does one whose texels are all equal (:1108-1141).
 template <int MODE, bool ALPHA>
-__device__ __forceinline__ void color_cell_compression(const Block& blk, uint32_t mask, const Tables& T, Sub res[Cfg<MODE>::NS], uint64_t& sels)
+__device__ __forceinline__ void color_cell_compression(const Block& blk, uint32_t mask, const Tables& T, Sub res[Cfg<MODE>::NS], uint64_t& sels,
+                                                       const int level = 4)
 {
+    const int tmax = level >= 4 ? 20 : level >= 2 ? 13 : level == 1 ? 5 : 2;
     using C = Cfg<MODE>;
     constexpr int NS = C::NS, N = C::N;
     constexpr bool ONECOL = (MODE == 1 || MODE == 7);
@@ -744,7 +757,7 @@ __device__ __forceinline__ void color_cell_compression(const Block& blk, uint32_
     }
 
 #pragma unroll 1
-    for (int t = 0; t < 20; t++) {
+    for (int t = 0; t < tmax; t++) {
         bool live = false;
 #pragma unroll
         for (int s = 0; s < NS; s++) live |= !fin[s];
@@ -783,7 +796,7 @@ __device__ __forceinline__ void color_cell_compression(const Block& blk, uint32_
                 for (int s = 0; s < NS; s++) left |= !fin[s];
                 if (!left) break;
             }
-            least_squares<MODE, ALPHA>(blk, mask, T, t, sels, st, min_sel, max_sel, n, sum, xl, xh);
+            least_squares<MODE, ALPHA>(blk, mask, T, t, sels, st, min_sel, max_sel, n, sum, xl, xh, level);
         }
         // find_optimal_solution: quantise, then evaluate unless these are the current best endpoints (bc7enc.cpp:1083-1084, 1094-1095)
         uint32_t lo[NS], hi[NS], pb[NS];
@@ -1052,18 +1065,18 @@ __device__ __forceinline__ uint4 pack_mode5(const Sub& r, uint64_t csels, int al
 __device__ __forceinline__ uint64_t weighted(uint64_t err) { return (uint64_t)(__ull2float_rn(err) * 1.0f + .5f); }
 
 // handle_opaque_block (bc7enc.cpp:2293-2400): mode 6, then mode 1 on the estimated partition.
-__device__ __forceinline__ uint4 encode_opaque(const Block& blk, const Tables& T)
+__device__ __forceinline__ uint4 encode_opaque(const Block& blk, const Tables& T, const int level = 4)
 {
     Sub r6[1];
     uint64_t s6;
-    color_cell_compression<6, false>(blk, 0, T, r6, s6);
+    color_cell_compression<6, false>(blk, 0, T, r6, s6, level);
     uint4 out = pack_mode6(r6[0], s6);
     const uint64_t best = weighted(r6[0].err);
     if (best > 0) {
         const uint32_t part = estimate_partition<false>(blk);
         Sub r1[2];
         uint64_t s1;
-        color_cell_compression<1, false>(blk, kShape2[part], T, r1, s1);
+        color_cell_compression<1, false>(blk, kShape2[part], T, r1, s1, level);
         // a first subset already above the mode-6 error ends the trial (bc7enc.cpp:2380-2382); the sum can only be larger
         if (weighted((uint64_t)r1[0].err + r1[1].err) < best) out = pack_mode17<1>(part, r1, s1);
     }
@@ -1072,8 +1085,9 @@ __device__ __forceinline__ uint4 encode_opaque(const Block& blk, const Tables& T
 
 // Alpha half of mode 5 (handle_alpha_block_mode5, bc7enc.cpp:2078-2136): up to 3 passes of nearest-of-4
 // selection and least-squares endpoint refit on the alpha channel alone.
-__device__ __forceinline__ uint32_t mode5_alpha(const Block& blk, const Tables& T, int& out_lo, int& out_hi, uint64_t& out_sels)
+__device__ __forceinline__ uint32_t mode5_alpha(const Block& blk, const Tables& T, int& out_lo, int& out_hi, uint64_t& out_sels, const int level = 4)
 {
+    const int total_passes = level >= 1 ? 3 : 2; // bc7enc.cpp:2078
     int lo_a = 255, hi_a = 0, ta = 0;
 #pragma unroll 1
     for (int i = 0; i < 16; i++) {
@@ -1088,7 +1102,7 @@ __device__ __forceinline__ uint32_t mode5_alpha(const Block& blk, const Tables& 
     if (lo_a == hi_a) return 0;
     uint32_t best = 0xFFFFFFFFu;
 #pragma unroll 1
-    for (int pass = 0; pass < 3; pass++) {
+    for (int pass = 0; pass < total_passes; pass++) {
         int vals[4];
         vals[0] = lo_a;
         vals[3] = hi_a;
@@ -1120,7 +1134,7 @@ __device__ __forceinline__ uint32_t mode5_alpha(const Block& blk, const Tables& 
             out_hi = hi_a;
             out_sels = tsel;
         }
-        if (pass != 2) {
+        if (pass != total_passes - 1) {
             // compute_least_squares_endpoints_a (bc7enc.cpp:410-459); its min == max fallback cannot trigger here (lo_a != hi_a at entry)
             const float q10 = (float)ta - q00;
             const float z01 = z10;
@@ -1139,19 +1153,19 @@ __device__ __forceinline__ uint32_t mode5_alpha(const Block& blk, const Tables& 
 }
 
 // handle_alpha_block (bc7enc.cpp:2139-2291): mode 6 (RGBA), mode 5, mode 7 on the estimated partition.
-__device__ __forceinline__ uint4 encode_alpha(const Block& blk, const Tables& T)
+__device__ __forceinline__ uint4 encode_alpha(const Block& blk, const Tables& T, const int level = 4)
 {
     Sub r6[1];
     uint64_t s6;
-    color_cell_compression<6, true>(blk, 0, T, r6, s6);
+    color_cell_compression<6, true>(blk, 0, T, r6, s6, level);
     uint4 out = pack_mode6(r6[0], s6);
     uint64_t best = weighted(r6[0].err);
     if (best > 0) {
         Sub r5[1];
         uint64_t s5, as5;
-        color_cell_compression<5, false>(blk, 0, T, r5, s5);
+        color_cell_compression<5, false>(blk, 0, T, r5, s5, level);
         int alo, ahi;
-        const uint32_t aerr = mode5_alpha(blk, T, alo, ahi, as5);
+        const uint32_t aerr = mode5_alpha(blk, T, alo, ahi, as5, level);
         const uint64_t e5 = weighted((uint64_t)r5[0].err + aerr);
         if (e5 < best) {
             best = e5;
@@ -1162,7 +1176,7 @@ __device__ __forceinline__ uint4 encode_alpha(const Block& blk, const Tables& T)
         const uint32_t part = estimate_partition<true>(blk);
         Sub r7[2];
         uint64_t s7;
-        color_cell_compression<7, true>(blk, kShape2[part], T, r7, s7);
+        color_cell_compression<7, true>(blk, kShape2[part], T, r7, s7, level);
         if (weighted((uint64_t)r7[0].err + r7[1].err) < best) out = pack_mode17<7>(part, r7, s7);
     }
     return out;
@@ -1173,7 +1187,7 @@ __device__ __forceinline__ uint4 encode_alpha(const Block& blk, const Tables& T)
 // warps inside the same stage share the fetches.  cls: 0 opaque, 1 alpha, 2 no block (takes part in the barriers only).
 // Every thread of the CTA must call this the same number of times.
 #ifdef __CUDACC__
-__device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T, int cls)
+__device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T, int cls, const int level = 4)
 {
     uint4 out = make_uint4(0, 0, 0, 0);
     uint64_t best = 0;
@@ -1181,9 +1195,9 @@ __device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T
         Sub r6[1];
         uint64_t s6;
         if (cls == 0)
-            color_cell_compression<6, false>(blk, 0, T, r6, s6);
+            color_cell_compression<6, false>(blk, 0, T, r6, s6, level);
         else
-            color_cell_compression<6, true>(blk, 0, T, r6, s6);
+            color_cell_compression<6, true>(blk, 0, T, r6, s6, level);
         out = pack_mode6(r6[0], s6);
         best = weighted(r6[0].err);
     }
@@ -1193,9 +1207,9 @@ __device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T
         if (cls == 1) {
             Sub r5[1];
             uint64_t s5, as5;
-            color_cell_compression<5, false>(blk, 0, T, r5, s5);
+            color_cell_compression<5, false>(blk, 0, T, r5, s5, level);
             int alo, ahi;
-            const uint32_t aerr = mode5_alpha(blk, T, alo, ahi, as5);
+            const uint32_t aerr = mode5_alpha(blk, T, alo, ahi, as5, level);
             const uint64_t e5 = weighted((uint64_t)r5[0].err + aerr);
             if (e5 < best) {
                 best = e5;
@@ -1211,10 +1225,10 @@ __device__ __forceinline__ uint4 encode_phased(const Block& blk, const Tables& T
         Sub r[2];
         uint64_t s;
         if (cls == 1) {
-            color_cell_compression<7, true>(blk, kShape2[part], T, r, s);
+            color_cell_compression<7, true>(blk, kShape2[part], T, r, s, level);
             if (weighted((uint64_t)r[0].err + r[1].err) < best) out = pack_mode17<7>(part, r, s);
         } else {
-            color_cell_compression<1, false>(blk, kShape2[part], T, r, s);
+            color_cell_compression<1, false>(blk, kShape2[part], T, r, s, level);
             if (weighted((uint64_t)r[0].err + r[1].err) < best) out = pack_mode17<1>(part, r, s);
         }
     }

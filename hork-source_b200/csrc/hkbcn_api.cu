@@ -8,6 +8,7 @@
 #include "../../include/hkbcn.h"
 #include "hkbcn_kernels.h"
 
+#include <nvtx3/nvToolsExt.h> // header-only; ranges cost nothing unless a tool (nsys / ncu --nvtx) is attached
 #include <atomic>
 #include <condition_variable>
 #include <deque>
@@ -36,6 +37,12 @@ void set_err(const char* fmt, ...)
     vsnprintf(t_err, sizeof(t_err), fmt, ap);
     va_end(ap);
 }
+
+// NVTX range over one C-ABI call (tracing): the entry points show up by name on a timeline
+struct Range {
+    explicit Range(const char* name) { nvtxRangePushA(name); }
+    ~Range() { nvtxRangePop(); }
+};
 
 struct Device {
     int          id = -1;
@@ -221,6 +228,14 @@ int check_dev_ptrs(int codec, const void* d_src, const void* d_dst)
 int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStream_t st)
 {
     if (P0.totalTiles == 0) return HKBCN_OK;
+    if (P0.flags & HKBCN_FLAG_LEVEL_MASK) {
+        const int level = (int)((P0.flags & HKBCN_FLAG_LEVEL_MASK) >> 4) - 1;
+        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? (level <= 3 || level == 5) : codec == C_BC7 ? level <= 4 : false;
+        if (!ok) {
+            set_err("quality level %d of format %d is not built (BC1/2/3: 0, 1, 2, 3, 5; BC7: 0..4; see hkbcn.h)", level, fmt);
+            return HKBCN_ERR_UNSUPPORTED;
+        }
+    }
     EncodeParams P = P0;
     if (!(P.sched = sched_slot(D, st))) return HKBCN_ERR_CUDA;
     cudaError_t e = cudaSuccess;
@@ -601,6 +616,7 @@ static int compress_bands_on(Device* D, int d, int nd, int fmt, int codec, const
 int hkbcn_compress_chain_multi(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags,
                                int n_gpus)
 {
+    Range nvtx_("hkbcn_compress_chain_multi");
     int rc = ensure_init();
     if (rc) return rc;
     const int codec = codec_of(fmt);
@@ -632,6 +648,7 @@ static bool worth_banding(uint32_t w, uint32_t h) { return g_devs.size() > 1 && 
 
 int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t flags)
 {
+    Range nvtx_("hkbcn_compress");
     int rc = ensure_init();
     if (rc) return rc;
     if (width / 4 == 0 || height / 4 == 0) return HKBCN_OK; // reference: zero blocks, nothing written
@@ -641,6 +658,7 @@ int hkbcn_compress(int fmt, const void* src, void* dst, uint32_t width, uint32_t
 
 int hkbcn_compress_chain(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t num_mips, uint32_t flags)
 {
+    Range nvtx_("hkbcn_compress_chain");
     int rc = ensure_init();
     if (rc) return rc;
     if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
@@ -760,6 +778,7 @@ size_t hkbcn_chain_src_bytes(int fmt, uint32_t width, uint32_t height, uint32_t 
 int hkbcn_generate_mips_dev(int device, int fmt, void* d_chain, uint32_t width, uint32_t height, uint32_t num_mips,
                             const hkbcn_mip_config* cfg, uint32_t flags, void* stream)
 {
+    Range nvtx_("hkbcn_generate_mips_dev");
     int rc = ensure_init();
     if (rc) return rc;
     Device* D = dev_at(device);
@@ -772,6 +791,7 @@ int hkbcn_generate_mips_dev(int device, int fmt, void* d_chain, uint32_t width, 
 int hkbcn_generate_mips(int fmt, const void* src_level0, void* dst_chain, uint32_t width, uint32_t height, uint32_t num_mips,
                         const hkbcn_mip_config* cfg, uint32_t flags)
 {
+    Range nvtx_("hkbcn_generate_mips");
     int rc = ensure_init();
     if (rc) return rc;
     const int codec = codec_of(fmt);
@@ -828,6 +848,7 @@ static int import_host_on(Device* D, int fmt, const void* src_level0, void* dst,
 int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
                        const hkbcn_mip_config* cfg, uint32_t flags)
 {
+    Range nvtx_("hkbcn_import_chain");
     int rc = ensure_init();
     if (rc) return rc;
     return import_host_on(g_devs[0], fmt, src_level0, dst, width, height, num_mips, cfg, flags);
@@ -864,6 +885,7 @@ int hkbcn_compress_dev(int device, int fmt, const void* d_src, void* d_dst, uint
 int hkbcn_compress_chain_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, uint32_t num_mips,
                              uint32_t flags, void* stream)
 {
+    Range nvtx_("hkbcn_compress_chain_dev");
     int rc = ensure_init();
     if (rc) return rc;
     Device* D = dev_at(device);
@@ -902,6 +924,7 @@ int hkbcn_compress_slices_dev(int device, int fmt, const void* d_src, void* d_ds
 int hkbcn_compress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips,
                           uint32_t flags)
 {
+    Range nvtx_("hkbcn_compress_slices");
     int rc = ensure_init();
     if (rc) return rc;
     if ((rc = check_chain_dims(width, height, num_mips)) != HKBCN_OK) return rc;
@@ -918,6 +941,7 @@ size_t hkbcn_slices_src_bytes(int fmt, uint32_t width, uint32_t height, uint32_t
 int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, uint32_t width, uint32_t height, size_t dst_row_stride,
                          uint32_t flags, void* stream)
 {
+    Range nvtx_("hkbcn_decompress_dev");
     int rc = ensure_init();
     if (rc) return rc;
     Device* D = dev_at(device);
@@ -947,6 +971,7 @@ int hkbcn_decompress_dev(int device, int fmt, const void* d_src, void* d_dst, ui
 
 int hkbcn_decompress(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, size_t dst_row_stride, uint32_t flags)
 {
+    Range nvtx_("hkbcn_decompress");
     int rc = ensure_init();
     if (rc) return rc;
     const int codec = codec_of(fmt);
@@ -1006,6 +1031,7 @@ int hkbcn_decompress_slices_dev(int device, int fmt, const void* d_src, void* d_
 
 int hkbcn_decompress_slices(int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t slices, uint32_t num_mips, uint32_t flags)
 {
+    Range nvtx_("hkbcn_decompress_slices");
     int rc = ensure_init();
     if (rc) return rc;
     const int codec = codec_of(fmt);
@@ -1077,6 +1103,7 @@ int hkbcn_plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus, int* devi
 
 int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
 {
+    Range nvtx_("hkbcn_compress_batch");
     int rc = ensure_init();
     if (rc) return rc;
     if (n_jobs == 0) return HKBCN_OK;
@@ -1109,6 +1136,7 @@ int hkbcn_compress_batch(hkbcn_job* jobs, size_t n_jobs)
 // each job's dst; per GPU the uploads, launches and downloads of consecutive jobs are queued without a host sync in between
 int hkbcn_decompress_batch(hkbcn_job* jobs, size_t n_jobs)
 {
+    Range nvtx_("hkbcn_decompress_batch");
     int rc = ensure_init();
     if (rc) return rc;
     if (n_jobs == 0) return HKBCN_OK;
@@ -1525,6 +1553,7 @@ static bool complete_texture_exists(const hkbcn_import_job& j)
 
 int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
 {
+    Range nvtx_("hkbcn_import_batch");
     int rc = ensure_init();
     if (rc) return rc;
     if (n_jobs == 0) return HKBCN_OK;

@@ -41,20 +41,17 @@ void Decode_BC6h_f32(void const* s, void* d, size_t RowStride, bool bSigned)
 }
 void Decode_BC7(void const* s, void* d, size_t RowStride) { Check(hkbcn_decode_blocks(HKBCN_BC7_UNORM, s, d, 1, RowStride, 0), "Decode_BC7"); }
 
+// Levels: rgbcx levels 0, 1, 2, 3, 5 are built (the ones without error tracking); the library answers
+// HKBCN_ERR_UNSUPPORTED for the others and for the 3-colour flags (levels >= 5 only read them), which Check() turns into an abort.
 void Encode_BC1(void const* s, void* d, uint32_t Level, bool b3ColorMode, bool bTransparentPixelsForBlack)
 {
-    if (Level != 5 || b3ColorMode || bTransparentPixelsForBlack) Unsupported("Encode_BC1 (Level != 5 or 3-colour modes)");
-    Check(hkbcn_encode_blocks(HKBCN_BC1_UNORM, s, d, 1, 0), "Encode_BC1");
+    if (Level >= 5 && (b3ColorMode || bTransparentPixelsForBlack)) Unsupported("Encode_BC1 (3-colour modes)");
+    Check(hkbcn_encode_blocks(HKBCN_BC1_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level)), "Encode_BC1");
 }
-void Encode_BC2(void const* s, void* d, uint32_t Level)
-{
-    if (Level != 5) Unsupported("Encode_BC2 (Level != 5)");
-    Check(hkbcn_encode_blocks(HKBCN_BC2_UNORM, s, d, 1, 0), "Encode_BC2");
-}
+void Encode_BC2(void const* s, void* d, uint32_t Level) { Check(hkbcn_encode_blocks(HKBCN_BC2_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level)), "Encode_BC2"); }
 void Encode_BC3(void const* s, void* d, uint32_t Level, bool bMaxQuality)
 {
-    if (Level != 5 || !bMaxQuality) Unsupported("Encode_BC3 (Level != 5 or bMaxQuality = false)");
-    Check(hkbcn_encode_blocks(HKBCN_BC3_UNORM, s, d, 1, 0), "Encode_BC3");
+    Check(hkbcn_encode_blocks(HKBCN_BC3_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level) | (bMaxQuality ? 0u : (uint32_t)HKBCN_FLAG_FAST)), "Encode_BC3");
 }
 void Encode_BC4(void const* s, void* d, bool bMaxQuality) { Check(hkbcn_encode_blocks(HKBCN_BC4_UNORM, s, d, 1, bMaxQuality ? 0 : HKBCN_FLAG_FAST), "Encode_BC4"); }
 void Encode_BC5(void const* s, void* d, bool bMaxQuality) { Check(hkbcn_encode_blocks(HKBCN_BC5_UNORM, s, d, 1, bMaxQuality ? 0 : HKBCN_FLAG_FAST), "Encode_BC5"); }
@@ -63,11 +60,7 @@ void Encode_BC6h_f16(void const* s, void* d, bool bSigned)
     Check(hkbcn_encode_blocks(bSigned ? HKBCN_BC6H_SFLOAT : HKBCN_BC6H_UFLOAT, s, d, 1, HKBCN_FLAG_SRC_F16), "Encode_BC6h_f16");
 }
 void Encode_BC6h_f32(void const* s, void* d, bool bSigned) { Check(hkbcn_encode_blocks(bSigned ? HKBCN_BC6H_SFLOAT : HKBCN_BC6H_UFLOAT, s, d, 1, 0), "Encode_BC6h_f32"); }
-void Encode_BC7(void const* s, void* d, uint32_t Level)
-{
-    if (Level != BC7_ENCODE_MAX_LEVEL) Unsupported("Encode_BC7 (Level != 4)");
-    Check(hkbcn_encode_blocks(HKBCN_BC7_UNORM, s, d, 1, 0), "Encode_BC7");
-}
+void Encode_BC7(void const* s, void* d, uint32_t Level) { Check(hkbcn_encode_blocks(HKBCN_BC7_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level)), "Encode_BC7"); }
 
 void CompressBC1(void const* s, void* d, uint32_t w, uint32_t h) { Check(hkbcn_compress(HKBCN_BC1_UNORM, s, d, w, h, 0), "CompressBC1"); }
 void CompressBC2(void const* s, void* d, uint32_t w, uint32_t h) { Check(hkbcn_compress(HKBCN_BC2_UNORM, s, d, w, h, 0), "CompressBC2"); }

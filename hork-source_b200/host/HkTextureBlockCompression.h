@@ -36,9 +36,10 @@ void Decode_BC6h_f16(void const* pSrc, void* pDest, size_t RowStride, bool bSign
 void Decode_BC6h_f32(void const* pSrc, void* pDest, size_t RowStride, bool bSigned);
 void Decode_BC7(void const* pSrc, void* pDest, size_t RowStride);
 
-// per 4x4 block (ImageEncoders.cpp:138-212).  The device encoders implement the presets the whole-surface
-// functions bake in (BC1/2/3 level 5 without 3-colour modes, BC7 level 4) plus the non-hq BC4/BC5 variants;
-// any other Level / flag combination aborts with a message rather than silently encoding something else.
+// per 4x4 block (ImageEncoders.cpp:138-212).  Built on the device: BC1/2/3 levels 0, 1, 2, 3, 5 (the rgbcx levels without
+// error tracking; 5 is what the whole-surface functions bake in), BC3 with and without bMaxQuality, BC4/BC5 hq and non-hq,
+// BC7 levels 0..4, BC6H signed / unsigned from f16 / f32.  BC1/2/3 levels 4 and 6..18 and the 3-colour flags of Encode_BC1
+// abort with a message rather than silently encoding something else.
 void Encode_BC1(void const* pSrc, void* pDest, uint32_t Level, bool b3ColorMode, bool bTransparentPixelsForBlack);
 void Encode_BC2(void const* pSrc, void* pDest, uint32_t Level);
 void Encode_BC3(void const* pSrc, void* pDest, uint32_t Level, bool bMaxQuality);

@@ -68,11 +68,17 @@ typedef enum hkbcn_status {
 enum {
     HKBCN_FLAG_NONE        = 0,
     HKBCN_FLAG_SRC_F16     = 1u << 0, /* BC6H: source texels are RGBA16F (Encode_BC6h_f16, ImageEncoders.cpp:187) */
-    HKBCN_FLAG_FAST        = 1u << 1, /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:171-185) */
+    HKBCN_FLAG_FAST        = 1u << 1, /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:161-185) */
+    /* bits 4..8: quality level of Encode_BC1/2/3(Level) and Encode_BC7(Level) (ImageEncoders.cpp:138-169, 207-212), stored
+     * as level + 1; 0 = the preset the Compress* functions bake in (BC1/2/3 level 5, BC7 level 4).  Use HKBCN_FLAG_LEVEL(n).
+     * Built: BC1/2/3 levels 0, 1, 2, 3, 5 (the rgbcx levels without error tracking: rgbcx.cpp:1692-1726) and BC7 levels
+     * 0..4.  BC1/2/3 levels 4 and 6..18, and the 3-colour flags of Encode_BC1, return HKBCN_ERR_UNSUPPORTED. */
+    HKBCN_FLAG_LEVEL_MASK  = 31u << 4,
     HKBCN_FLAG_SKIP_EXISTING = 1u << 16 /* hkbcn_import_batch: leave a job alone (status HKBCN_SKIPPED) when its out_path already holds a
                                            complete .texture of the job's format, size and mip count -- re-running an interrupted
                                            batch only does what is missing (files are written to a temporary name and renamed) */
 };
+#define HKBCN_FLAG_LEVEL(n) ((((uint32_t)(n)) + 1u) << 4)
 /* flags for hkbcn_decompress* */
 enum {
     HKBCN_FLAG_DST_F32     = 1u << 8  /* BC6H: decode to RGB32F (Decode_BC6h_f32) instead of RGB16F (Decode_BC6h_f16) */

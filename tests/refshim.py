@@ -136,3 +136,25 @@ def psnr(a, b, peak=255.0):
     b = b.astype(np.float64)
     mse = np.mean((a - b) ** 2)
     return 99.0 if mse == 0 else 10.0 * np.log10(peak * peak / mse)
+
+
+def encode_bc1_level_blocks(src_rgba, n, level, allow3=False, transparent_black=False):
+    """rgbcx::encode_bc1(level, ..) over n packed blocks (Encode_BC1(.., Level, b3ColorMode, bTransparentPixelsForBlack))"""
+    src = np.ascontiguousarray(src_rgba, np.uint8).ravel()
+    dst = np.zeros(n * 8, np.uint8)
+    L = ref()
+    L.ref_encode_bc1_level.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int]
+    for i in range(n):
+        L.ref_encode_bc1_level(src.ctypes.data + i * 64, dst.ctypes.data + i * 8, level, int(allow3), int(transparent_black))
+    return dst
+
+
+def encode_bc7_level_blocks(src_rgba, n, level):
+    """bc7enc_compress_block with bc7_params[level] over n packed blocks (Encode_BC7(.., Level))"""
+    src = np.ascontiguousarray(src_rgba, np.uint8).ravel()
+    dst = np.zeros(n * 16, np.uint8)
+    L = ref()
+    L.ref_encode_bc7_level.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    for i in range(n):
+        L.ref_encode_bc7_level(src.ctypes.data + i * 64, dst.ctypes.data + i * 16, level)
+    return dst

@@ -21,6 +21,8 @@ typedef void (*ref_decode_block_t)(int, const void*, void*, size_t, int);
 typedef void (*ref_encode_bc45_t)(const void*, void*, int);
 typedef void (*ref_encode_bc6h_f16_t)(const void*, void*, int);
 typedef uint16_t (*ref_half_from_float_t)(uint32_t);
+typedef void (*ref_encode_bc1_level_t)(const void*, void*, uint32_t, int, int);
+typedef void (*ref_encode_bc7_level_t)(const void*, void*, uint32_t);
 
 static uint32_t g_rng = 12345;
 static uint32_t rnd() { g_rng = g_rng * 1664525u + 1013904223u; return g_rng >> 8; }
@@ -55,6 +57,9 @@ int main(int argc, char** argv)
     ref_encode_bc45_t ref_encode_bc5 = (ref_encode_bc45_t)dlsym(R, "ref_encode_bc5");
     ref_encode_bc6h_f16_t ref0_encode_bc6h_f16 = (ref_encode_bc6h_f16_t)dlsym(R0, "ref_encode_bc6h_f16");
     ref_half_from_float_t ref_half_from_float = (ref_half_from_float_t)dlsym(R, "ref_half_from_float");
+    ref_encode_bc1_level_t ref_encode_bc1_level = (ref_encode_bc1_level_t)dlsym(R, "ref_encode_bc1_level");
+    ref_encode_bc7_level_t ref_encode_bc7_level = (ref_encode_bc7_level_t)dlsym(R, "ref_encode_bc7_level");
+    if (!ref_encode_bc1_level || !ref_encode_bc7_level) { fprintf(stderr, "missing level symbols in the reference shim\n"); return 2; }
     if (!ref_compress || !ref0_compress || !ref_encode_block || !ref0_encode_block || !ref_decode_block || !ref_encode_bc4 || !ref_encode_bc5 ||
         !ref0_encode_bc6h_f16 || !ref_half_from_float) { fprintf(stderr, "missing symbol in the reference shim\n"); return 2; }
 
@@ -114,6 +119,19 @@ int main(int argc, char** argv)
             TBC::Encode_BC2(blk, g16, 5);               ref_encode_block(1, blk, w16); expect_equal("Encode_BC2", g16, w16, 16);
             TBC::Encode_BC3(blk, g16, 5, true);         ref_encode_block(2, blk, w16); expect_equal("Encode_BC3", g16, w16, 16);
             TBC::Encode_BC7(blk, g16, 4);               ref_encode_block(7, blk, w16); expect_equal("Encode_BC7", g16, w16, 16);
+            // quality levels (row a15): rgbcx levels 0..3 of Encode_BC1 (the 3-colour flags are only read from level 5 up),
+            // Encode_BC3 without bMaxQuality, bc7enc uber levels 0..3
+            const uint32_t lvl = (uint32_t)(t & 3);
+            TBC::Encode_BC1(blk, g16, lvl, true, true); ref_encode_bc1_level(blk, w16, lvl, 1, 1); expect_equal("Encode_BC1 level 0..3", g16, w16, 8);
+            TBC::Encode_BC7(blk, g16, lvl);             ref_encode_bc7_level(blk, w16, lvl);       expect_equal("Encode_BC7 level 0..3", g16, w16, 16);
+            {
+                uint8_t al[16];
+                for (int i = 0; i < 16; i++) al[i] = blk[4 * i + 3];
+                TBC::Encode_BC3(blk, g16, lvl, false);
+                ref_encode_bc4(al, w16, 0);
+                ref_encode_bc1_level(blk, w16 + 8, lvl, 0, 0);
+                expect_equal("Encode_BC3 bMaxQuality = false", g16, w16, 16);
+            }
             for (int hq = 0; hq < 2; hq++) {
                 TBC::Encode_BC4(blk, g16, hq != 0); ref_encode_bc4(blk, w16, hq); expect_equal(hq ? "Encode_BC4 hq" : "Encode_BC4", g16, w16, 8);
                 TBC::Encode_BC5(blk, g16, hq != 0); ref_encode_bc5(blk, w16, hq); expect_equal(hq ? "Encode_BC5 hq" : "Encode_BC5", g16, w16, 16);

@@ -68,9 +68,15 @@ int main(int argc, char** argv)
         bc7::Block blk{px, 1};
         bool alpha = false;
         for (int k = 0; k < 16; k++) alpha |= (px[k] >> 24) != 255;
-        uint4 o = alpha ? bc7::encode_alpha(blk, T) : bc7::encode_opaque(blk, T);
+        // HKBCN_BC7_LEVEL (environment): uber level 0..4 of Encode_BC7 (default 4, the CompressBC7 preset)
+        static const int level = getenv("HKBCN_BC7_LEVEL") ? atoi(getenv("HKBCN_BC7_LEVEL")) : 4;
+        uint4 o = alpha ? bc7::encode_alpha(blk, T, level) : bc7::encode_opaque(blk, T, level);
         uint8_t r[16];
-        ref_encode_block(7, px, r);
+        if (level == 4) ref_encode_block(7, px, r);
+        else {
+            static auto ref_level = (void (*)(const void*, void*, uint32_t))dlsym(h, "ref_encode_bc7_level");
+            ref_level(px, r, (uint32_t)level);
+        }
         if (memcmp(&o, r, 16)) {
             diff++;
             if (argc > 3) {
