@@ -231,8 +231,12 @@ class Ranks:
             import torch.distributed as dist
             if use_cuda:
                 dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+                # host-side waits (rank 0 driving all GPUs through the library while the others stand by) must not put a
+                # spinning NCCL kernel on the other ranks' GPUs: a gloo group carries those
+                self.host_group = dist.new_group(backend="gloo")
             else:
                 dist.init_process_group("gloo")
+                self.host_group = None
             self.dist = dist
 
     def barrier(self):
@@ -241,6 +245,11 @@ class Ranks:
         if self.use_cuda:
             import torch
             torch.cuda.synchronize()
+
+    def host_barrier(self):
+        """a barrier that leaves the GPUs alone"""
+        if self.dist:
+            self.dist.barrier(group=self.host_group) if self.host_group is not None else self.dist.barrier()
 
     def max(self, x):
         import torch
@@ -460,10 +469,138 @@ def run_gpu(args):
             while cur.shape[0] > 4:
                 cur = refshim.stbir_resize(cur, cur.shape[1] // 2, cur.shape[0] // 2, alpha_channel=3, flags=0, edge=3, filt=5, space=0)
             out["import_chain"]["cpu_stbir_cascade_ms"] = (time.perf_counter() - t0) * 1e3
-        print(json.dumps(out))
     L.hkbcn_free_pinned(h_src)
     L.hkbcn_free_pinned(h_dst)
+    # ---- the library's own sharding (BASELINE.json configs[4]): rank 0 alone re-initialises the library over
+    # all N GPUs of the job and drives them through hkbcn_import_batch / hkbcn_compress_chain_multi; the other ranks stand by
+    del d_src, d_dst, flush
+    torch.cuda.empty_cache()
+    ranks.host_barrier()
+    if rank == 0:
+        try:
+            out["batch_sharded"], out["banded"] = library_sharding(torch, hkbcn, L, world, levels)
+        except Exception as ex:  # the headline line must survive a failure of this extra
+            out["batch_sharded"] = {"error": repr(ex)}
+        print(json.dumps(out))
+    ranks.host_barrier()
     ranks.close()
+
+
+def device_texture(torch, dev, kind, n, seed):
+    """a distinct synthetic n x n source generated ON the GPU (no PCIe): smooth value noise from a random lattice upsampled
+    bilinearly over 4 octaves, hard-edged cells, fine grain -- the ingredients of python/synth.py, from torch's device RNG.
+    kind: 'albedo' RGBA8 (alpha 255), 'normal' RG8 (tangent-space normals of a noise height field)"""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    F = torch.nn.functional
+
+    def noise(ch, octaves=4, base=32):
+        acc, amp, tot = 0, 1.0, 0.0
+        for o in range(octaves):
+            cells = max(n // (base >> o), 2)
+            lat = torch.rand((1, ch, cells, cells), device=dev, generator=g)
+            acc = acc + amp * F.interpolate(lat, size=(n, n), mode="bilinear", align_corners=False)
+            tot += amp
+            amp *= 0.5
+        return (acc / tot)[0]
+    if kind == "albedo":
+        luma = noise(1)
+        img = (0.65 * luma + 0.35 * noise(3) + 0.04 * (torch.rand((3, n, n), device=dev, generator=g) - 0.5)).clamp(0, 1)
+        cell = torch.rand((1, 4, n // 16, n // 16), device=dev, generator=g)
+        cell = F.interpolate(cell, size=(n, n), mode="nearest")[0]
+        flat = cell[3:4] < 0.05
+        img = torch.where(flat, cell[:3], img)
+        rgba = torch.cat([img, torch.ones((1, n, n), device=dev)], 0)
+        return (rgba * 255.0 + 0.5).to(torch.uint8).permute(1, 2, 0).contiguous()
+    h = noise(1, 5, 64)[0] * 24.0
+    dx = (torch.roll(h, -1, 1) - torch.roll(h, 1, 1)) * 0.5
+    dy = (torch.roll(h, -1, 0) - torch.roll(h, 1, 0)) * 0.5
+    inv = torch.rsqrt(dx * dx + dy * dy + 1.0)
+    rg = torch.stack([(-dx * inv) * 0.5 + 0.5, (-dy * inv) * 0.5 + 0.5], -1).clamp(0, 1)
+    return (rg * 255.0 + 0.5).to(torch.uint8).contiguous()
+
+
+def library_sharding(torch, hkbcn, L, world, levels, per_gpu=256, n=2048):
+    """rank 0, library initialised over `world` GPUs:
+    batch_sharded -- per_gpu x world textures (50 % BC1_UNORM_SRGB, 25 % BC5_UNORM, 25 % BC7_UNORM, 2048^2 with full chains),
+                     every source distinct and generated on the GPU the library's plan assigns it to (HKBCN_FLAG_SRC_DEVICE),
+                     compressed chains into pinned host memory; whole textures per GPU, no collective
+    banded        -- ONE 4096^2 BC7 chain over the GPUs in bands of block rows (hkbcn_compress_chain_multi)"""
+    L.hkbcn_shutdown()
+    hkbcn.init((1 << world) - 1)
+    assert L.hkbcn_device_count() == world
+    mips = L.hkbcn_calc_num_mips(n, n)
+    total = per_gpu * world
+    fmts = [(55, "albedo", 5), (62, "normal", 2), (55, "albedo", 5), (66, "albedo", 5)]  # i % 4 -> 50 / 25 / 25
+    arr = (hkbcn.ImportJob * total)()
+    for i in range(total):
+        fmt, kind, filt = fmts[i % 4]
+        arr[i] = hkbcn.ImportJob(fmt, n, n, 1, hkbcn.MipConfig(3, filt, 0, 0), hkbcn.FLAG_SRC_DEVICE, None, None, None, 0)
+    plan = (C.c_int * total)()
+    hkbcn.check(L.hkbcn_plan_import_batch(arr, C.c_size_t(total), world, plan))
+    srcs, pinned, px = [], [], 0
+    t0 = time.perf_counter()
+    for i in range(total):
+        fmt, kind, filt = fmts[i % 4]
+        t = device_texture(torch, torch.device("cuda", plan[i]), kind, n, 0xB2100000 + i)
+        srcs.append(t)
+        nb = L.hkbcn_chain_bytes(fmt, n, n, 1, mips)
+        h_dst = L.hkbcn_alloc_pinned(nb)
+        if not h_dst:
+            raise RuntimeError("pinned allocation failed")
+        pinned.append(h_dst)
+        arr[i].src_level0 = t.data_ptr()
+        arr[i].dst = h_dst
+        px += sum(max(n >> l, 4) ** 2 for l in range(mips))
+    for d in range(world):
+        torch.cuda.synchronize(d)
+    gen_s = time.perf_counter() - t0
+    best, stats = None, None
+    for it in range(2):  # the first pass warms buffers and tap tables
+        t0 = time.perf_counter()
+        hkbcn.check(L.hkbcn_import_batch(arr, C.c_size_t(total)))
+        dt = time.perf_counter() - t0
+        if it:
+            best = dt
+            busy = (C.c_double * world)()
+            L.hkbcn_batch_stats(busy, world)
+            stats = [round(b, 1) for b in busy]
+    for i in range(total):
+        if arr[i].status:
+            raise RuntimeError(f"import job {i} failed: {arr[i].status}")
+    for p in pinned:
+        L.hkbcn_free_pinned(p)
+    del srcs
+    per_dev = [sum(1 for i in range(total) if plan[i] == d) for d in range(world)]
+    sharded = {"value": px / best / 1e6, "unit": "Mpix/s", "textures": total, "per_gpu": per_dev, "s": best, "busy_ms_per_gpu": stats,
+               "lpt_imbalance": round(max(stats) / (sum(stats) / len(stats)), 3), "source": "generated on the assigned GPU (torch device RNG), distinct per texture",
+               "generate_s": round(gen_s, 2), "mix": "50 % BC1_UNORM_SRGB / 25 % BC5_UNORM / 25 % BC7_UNORM, 2048^2 + full chains",
+               "d2h_bytes": int(sum(L.hkbcn_chain_bytes(fmts[i % 4][0], n, n, 1, mips) for i in range(total))), "h2d_bytes": 0,
+               "api": "hkbcn_plan_import_batch + hkbcn_import_batch (HKBCN_FLAG_SRC_DEVICE), one process driving all GPUs"}
+    # one 4096^2 BC7 chain in bands over the GPUs (pinned host buffers), byte-compared with the single-GPU result
+    src_np = np.concatenate([l.ravel() for l in levels])
+    nbytes = L.hkbcn_chain_bytes(BC7, SIZE, SIZE, 1, len(levels))
+    h_src, h_dst = L.hkbcn_alloc_pinned(src_np.nbytes), L.hkbcn_alloc_pinned(nbytes)
+    C.memmove(h_src, src_np.ctypes.data, src_np.nbytes)
+    times = {}
+    ref_out = None
+    for g in sorted({1, world}):
+        ts = []
+        for it in range(4):
+            t0 = time.perf_counter()
+            hkbcn.check(L.hkbcn_compress_chain_multi(BC7, h_src, h_dst, SIZE, SIZE, len(levels), 0, g))
+            ts.append(time.perf_counter() - t0)
+        times[g] = min(ts[1:])
+        got = np.ctypeslib.as_array(C.cast(h_dst, C.POINTER(C.c_uint8)), shape=(nbytes,)).copy()
+        if ref_out is None:
+            ref_out = got
+        elif not np.array_equal(got, ref_out):
+            raise RuntimeError("banded chain differs from the single-GPU chain")
+    L.hkbcn_free_pinned(h_src)
+    L.hkbcn_free_pinned(h_dst)
+    pxc = chain_pixels(levels)
+    banded = {"value": pxc / times[world] / 1e6, "unit": "Mpix/s", "gpus": world, "ms": round(times[world] * 1e3, 2), "ms_one_gpu": round(times[1] * 1e3, 2),
+              "identical_to_one_gpu": True, "api": "hkbcn_compress_chain_multi (host pointers, pinned): bands of block rows per GPU, no exchange"}
+    return sharded, banded
 
 
 def batch_import(hkbcn, L, rank, per_format=8, n=2048):
@@ -520,35 +657,68 @@ def _timed(torch, stream, flush, fn, iters, skip=2):
 
 
 def decode_sweep(torch, hkbcn, L, bc7_blocks, stream, flush, hbm):
-    """HBM-bound half of the path (BASELINE.json configs[4] 'decode bandwidth sweep'): whole-surface decode per format at
-    4096^2, 8192^2 and 16384^2, algorithmic bytes/px of SURVEY.md 8d (block bytes read + texel bytes written).  BC7 and BC6H
-    inputs are blocks this library's encoders produced (the mode mix of real content), tiled up to size; the others are
-    uniform random bits (every selector and both palette modes)."""
+    """HBM-bound half of the path (BASELINE.json configs[4] 'decode bandwidth sweep', SURVEY.md 8d: sizes 256^2 .. 8192^2, all
+    seven formats): whole-surface decode per format and size (16384^2 kept as the asymptote), algorithmic bytes/px of SURVEY.md
+    8d (block bytes read + texel bytes written).  `batched`: 2048^2 surfaces as ONE storage of slices (hkbcn_decompress_slices_dev,
+    one launch) sized to >= 64 MB of output -- what a texture set looks like to the path; a lone small surface is a 10 us
+    kernel whose launch, ramp and tail no memory system can hide.  BC7 and BC6H inputs are blocks this library's encoders
+    produced (the mode mix of real content), tiled up to size; the others are uniform random bits (every selector and both
+    palette modes).  `cpu`: the reference's decoders (bcdec / bc7decomp) over all host threads at 4096^2."""
+    import refshim
     import synth
     out = {}
     gen = torch.Generator(device="cuda").manual_seed(7)
     base7 = bc7_blocks[: (SIZE // 4) ** 2 * 16].view(SIZE // 4, SIZE // 4, 16)
-    hdr = torch.from_numpy(np.ascontiguousarray(synth.sky_rgba32f(512, 512, 0xB2000006, 0)).view(np.uint8).ravel()).cuda()
-    base6 = torch.empty(128 * 128 * 16, dtype=torch.uint8, device="cuda")
-    hkbcn.check(L.hkbcn_compress_dev(0, 64, hdr.data_ptr(), base6.data_ptr(), 512, 512, 0, C.c_void_p(stream.cuda_stream)))
-    torch.cuda.synchronize()
-    base6 = base6.view(128, 128, 16)
-    for name, fmt, blk, tex, flags in (("BC1", 54, 8, 4, 0), ("BC3", 58, 16, 4, 0), ("BC4", 60, 8, 1, 0), ("BC5", 62, 16, 2, 0),
-                                       ("BC7", 66, 16, 4, 0), ("BC6H_f16", 64, 16, 6, 0), ("BC6H_f32", 64, 16, 12, 1 << 8)):
+    base6 = {}
+    for fmt in (64, 65):
+        img = synth.sky_rgba32f(256, 256, 0xB2000006, 0)
+        if fmt == 65:
+            img[..., :3] -= 1.0
+        hdr = torch.from_numpy(np.ascontiguousarray(img).view(np.uint8).ravel()).cuda()
+        b6 = torch.empty(64 * 64 * 16, dtype=torch.uint8, device="cuda")
+        hkbcn.check(L.hkbcn_compress_dev(0, fmt, hdr.data_ptr(), b6.data_ptr(), 256, 256, 0, C.c_void_p(stream.cuda_stream)))
+        torch.cuda.synchronize()
+        base6[fmt] = b6.view(64, 64, 16)
+
+    def blocks_for(fmt, blk, nbx, nby):
+        if fmt == 66:
+            return base7.repeat((nby + base7.shape[0] - 1) // base7.shape[0], (nbx + base7.shape[1] - 1) // base7.shape[1], 1)[:nby, :nbx].contiguous().view(-1)
+        if fmt in (64, 65):
+            return base6[fmt].repeat((nby + 63) // 64, (nbx + 63) // 64, 1)[:nby, :nbx].contiguous().view(-1)
+        return torch.randint(0, 256, (nbx * nby * blk,), dtype=torch.uint8, device="cuda", generator=gen)
+
+    cs = C.c_void_p(stream.cuda_stream)
+    for name, fmt, blk, tex, flags in (("BC1", 54, 8, 4, 0), ("BC2", 56, 16, 4, 0), ("BC3", 58, 16, 4, 0), ("BC4", 60, 8, 1, 0), ("BC5", 62, 16, 2, 0),
+                                       ("BC7", 66, 16, 4, 0), ("BC6H_f16", 64, 16, 6, 0), ("BC6H_S_f16", 65, 16, 6, 0), ("BC6H_f32", 64, 16, 12, 1 << 8)):
         out[name] = {}
-        for n in (4096, 8192, 16384):
+        for n in (256, 512, 1024, 2048, 4096, 8192, 16384):
             nb = n // 4
-            if fmt == 66:
-                src = base7.repeat(nb // base7.shape[0], nb // base7.shape[1], 1).contiguous().view(-1)
-            elif fmt == 64:
-                src = base6.repeat(nb // 128, nb // 128, 1).contiguous().view(-1)
-            else:
-                src = torch.randint(0, 256, (nb * nb * blk,), dtype=torch.uint8, device="cuda", generator=gen)
+            src = blocks_for(fmt, blk, nb, nb)
             dst = torch.empty(n * n * tex, dtype=torch.uint8, device="cuda")
             ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_decompress_dev(
-                0, fmt, src.data_ptr(), dst.data_ptr(), n, n, n * tex, flags, C.c_void_p(stream.cuda_stream))), 5, 3)
+                0, fmt, src.data_ptr(), dst.data_ptr(), n, n, n * tex, flags, cs)), 5, 3)
             gbs = (nb * nb * blk + n * n * tex) / (ms * 1e-3) / 1e9
             out[name][str(n)] = {"GB/s": round(gbs, 1), "frac": round(gbs / hbm, 4), "Gpix/s": round(n * n / (ms * 1e-3) / 1e9, 2), "us": round(ms * 1e3, 1)}
+            if n == 4096 and refshim.have_ref():
+                hb = src.cpu().numpy()
+                t0 = time.perf_counter()
+                refshim.decompress(fmt, hb, n, n, f32out=bool(flags))
+                dt = time.perf_counter() - t0
+                out[name]["cpu_4096"] = {"GB/s": round((nb * nb * blk + n * n * tex) / dt / 1e9, 2), "Gpix/s": round(n * n / dt / 1e9, 3), "cores": refshim.hw_threads(),
+                                         "kind": "reference"}
+            del src, dst
+        # a set of 2048^2 textures as one storage of slices, decoded by ONE launch: 64 MB and 256 MB of decoded texels.  What a
+        # launch moves decides the fraction, not the shape: 64 MB is ~11 us of HBM time next to ~7 us of launch, ramp and tail
+        n = 2048
+        for mb in (64, 256):
+            slices = max(1, -(-(mb << 20) // (n * n * tex)))
+            src = blocks_for(fmt, blk, n // 4, (n // 4) * slices)
+            dst = torch.empty(n * n * tex * slices, dtype=torch.uint8, device="cuda")
+            ms = _timed(torch, stream, flush, lambda: hkbcn.check(L.hkbcn_decompress_slices_dev(
+                0, fmt, src.data_ptr(), dst.data_ptr(), n, n, slices, 1, flags, cs)), 5, 3)
+            gbs = slices * ((n // 4) ** 2 * blk + n * n * tex) / (ms * 1e-3) / 1e9
+            out[name][f"batched_2048_{mb}MB"] = {"slices": slices, "GB/s": round(gbs, 1), "frac": round(gbs / hbm, 4), "us": round(ms * 1e3, 1),
+                                                 "api": "hkbcn_decompress_slices_dev, one launch"}
             del src, dst
     return out
 

@@ -10,6 +10,7 @@
 
 #include <nvtx3/nvToolsExt.h> // header-only; ranges cost nothing unless a tool (nsys / ncu --nvtx) is attached
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <deque>
 #include <mutex>
@@ -87,6 +88,8 @@ std::mutex            g_mu;
 std::atomic<bool>     g_init{false}; // published (release) only after g_devs is complete; readers load with acquire
 std::vector<Device*>  g_devs;      // selected devices
 std::atomic<uint64_t> g_launches{0};
+std::vector<double>   g_batch_ms;  // per-device worker time of the last batch call (hkbcn_batch_stats)
+std::mutex            g_batch_mu;
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -1534,6 +1537,26 @@ int hkbcn_read_texture(const char* path, hkbcn_texture_desc* d, void* payload, s
     return rc;
 }
 
+int hkbcn_plan_import_batch(const hkbcn_import_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job)
+{
+    if (n_gpus == 0) n_gpus = (int)g_devs.size();
+    if (n_gpus <= 0 || (n_jobs && (!jobs || !device_of_job))) { set_err("bad arguments (n_gpus = 0 needs hkbcn_init first)"); return HKBCN_ERR_BAD_ARG; }
+    std::vector<hkbcn_job> plain(n_jobs);
+    for (size_t i = 0; i < n_jobs; i++) {
+        if (codec_of(jobs[i].fmt) < 0) { set_err("job %zu: bad format %d", i, jobs[i].fmt); return HKBCN_ERR_BAD_FORMAT; }
+        plain[i] = hkbcn_job{jobs[i].fmt, jobs[i].width, jobs[i].height, jobs[i].flags, nullptr, nullptr, 0};
+    }
+    plan_batch(plain.data(), n_jobs, n_gpus, device_of_job);
+    return HKBCN_OK;
+}
+
+int hkbcn_batch_stats(double* busy_ms, int capacity)
+{
+    std::lock_guard<std::mutex> lk(g_batch_mu);
+    for (int i = 0; i < capacity && i < (int)g_batch_ms.size(); i++) busy_ms[i] = g_batch_ms[(size_t)i];
+    return (int)g_batch_ms.size();
+}
+
 // re-run of an interrupted batch: the output is there, is a texture resource of the job's shape and holds its whole payload
 static bool complete_texture_exists(const hkbcn_import_job& j)
 {
@@ -1600,8 +1623,11 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
         }
     });
     std::vector<std::thread> th;
+    std::vector<double> busy(nd, 0.0);
     for (size_t dv = 0; dv < nd; dv++) {
         th.emplace_back([&, dv]() {
+            const auto t_begin = std::chrono::steady_clock::now();
+            struct Stamp { double& out; std::chrono::steady_clock::time_point t0; ~Stamp() { out = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); } } stamp{busy[dv], t_begin};
             Device* D = g_devs[dv];
             std::lock_guard<std::mutex> blk(D->batch_mu);
             auto fail = [&](hkbcn_import_job& j, int rc) {
@@ -1650,14 +1676,16 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                     f.out = f.d.own.data();
                 }
                 const void* hsrc = j.src_level0;
-                if (!is_pinned(hsrc)) { // pageable memory: stage through pinned so that the copy engine, not this thread, feeds the GPU
+                const bool src_dev = (j.flags & HKBCN_FLAG_SRC_DEVICE) != 0;
+                if (!src_dev && !is_pinned(hsrc)) { // pageable memory: stage through pinned so that the copy engine, not this thread, feeds the GPU
                     if ((rc = grow_pinned(&S.h_src, &S.hsc, l0)) != HKBCN_OK) return rc;
                     memcpy(S.h_src, hsrc, l0);
                     hsrc = S.h_src;
                 }
                 f.staged = !is_pinned(f.out);
                 if (f.staged && (rc = grow_pinned(&S.h_dst, &S.hdc, dbytes)) != HKBCN_OK) return rc;
-                CK(cudaMemcpyAsync(S.d_src, hsrc, l0, cudaMemcpyHostToDevice, S.st)); // level 0 only crosses PCIe
+                // level 0 only crosses PCIe -- or nothing does, when the source was produced on this GPU (HKBCN_FLAG_SRC_DEVICE)
+                CK(cudaMemcpyAsync(S.d_src, hsrc, l0, src_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, S.st));
                 if (mips > 1 && (rc = generate_mips_on(D, j.fmt, S.d_src, j.width, j.height, mips, &j.mip, j.flags, S.st)) != HKBCN_OK) return rc;
                 EncodeParams P;
                 if ((rc = build_chain(P, codec, j.flags, S.d_src, S.d_dst, j.width, j.height, mips)) != HKBCN_OK) return rc;
@@ -1688,6 +1716,10 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
     }
     for (auto& t : th) t.join();
     writer.join();
+    {
+        std::lock_guard<std::mutex> lk(g_batch_mu);
+        g_batch_ms = busy;
+    }
     for (size_t d = 0; d <= nd; d++)
         if (first_err[d]) { set_err("%s", err_msg[d].c_str()); return first_err[d]; }
     return HKBCN_OK;

@@ -22,6 +22,8 @@ BC4_UNORM, BC4_SNORM, BC5_UNORM, BC5_SNORM, BC6H_UFLOAT, BC6H_SFLOAT, BC7_UNORM,
 FLAG_SRC_F16 = 1 << 0
 FLAG_FAST = 1 << 1
 FLAG_DST_F32 = 1 << 8
+FLAG_SKIP_EXISTING = 1 << 16
+FLAG_SRC_DEVICE = 1 << 17
 
 EXPORTS = [
     "hkbcn_init", "hkbcn_shutdown", "hkbcn_device_count", "hkbcn_last_error", "hkbcn_version",
@@ -31,7 +33,7 @@ EXPORTS = [
     "hkbcn_slices_src_bytes", "hkbcn_compress_slices_dev", "hkbcn_compress_slices", "hkbcn_compress_chain_multi", "hkbcn_plan_bands",
     "hkbcn_compress_batch", "hkbcn_plan_batch", "hkbcn_launch_count",
     "hkbcn_decoded_chain_bytes", "hkbcn_decompress_slices_dev", "hkbcn_decompress_slices", "hkbcn_decompress_chain_dev", "hkbcn_decompress_chain",
-    "hkbcn_decompress_batch",
+    "hkbcn_decompress_batch", "hkbcn_plan_import_batch", "hkbcn_batch_stats",
     "hkbcn_mip_taps", "hkbcn_chain_src_bytes", "hkbcn_generate_mips_dev", "hkbcn_generate_mips", "hkbcn_import_chain_dev", "hkbcn_import_chain", "hkbcn_alloc_pinned", "hkbcn_free_pinned",
     "hkbcn_texture_header", "hkbcn_write_texture", "hkbcn_read_texture", "hkbcn_import_batch",
     "hkbcn_envprobe_texels", "hkbcn_envprobe_prefilter", "hkbcn_irradiance", "hkbcn_envprobe_prefilter_dev", "hkbcn_irradiance_dev",
@@ -116,6 +118,8 @@ def lib():
         L.hkbcn_write_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_read_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.hkbcn_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t]
+        L.hkbcn_plan_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
+        L.hkbcn_batch_stats.argtypes = [C.POINTER(C.c_double), C.c_int]
         L.hkbcn_envprobe_texels.restype = C.c_size_t
         L.hkbcn_envprobe_texels.argtypes = [C.c_int]
         L.hkbcn_envprobe_prefilter.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]

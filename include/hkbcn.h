@@ -74,6 +74,8 @@ enum {
      * Built: BC1/2/3 levels 0, 1, 2, 3, 5 (the rgbcx levels without error tracking: rgbcx.cpp:1692-1726) and BC7 levels
      * 0..4.  BC1/2/3 levels 4 and 6..18, and the 3-colour flags of Encode_BC1, return HKBCN_ERR_UNSUPPORTED. */
     HKBCN_FLAG_LEVEL_MASK  = 31u << 4,
+    HKBCN_FLAG_SRC_DEVICE  = 1u << 17, /* hkbcn_import_batch: src_level0 is DEVICE memory on the GPU hkbcn_plan_import_batch assigns the
+                                          job to (sources produced on the device never cross PCIe); the default is host memory */
     HKBCN_FLAG_SKIP_EXISTING = 1u << 16 /* hkbcn_import_batch: leave a job alone (status HKBCN_SKIPPED) when its out_path already holds a
                                            complete .texture of the job's format, size and mip count -- re-running an interrupted
                                            batch only does what is missing (files are written to a temporary name and renamed) */
@@ -267,6 +269,12 @@ typedef struct hkbcn_import_job {
 /* Jobs are sharded over the selected GPUs as in hkbcn_compress_batch (whole textures, no collective); each GPU's worker runs
  * upload -> mip cascade -> encode -> download, and the files are written by a separate thread behind it. */
 HKBCN_API int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs);
+/* The planning step of hkbcn_import_batch on its own (host only; deterministic, the plan hkbcn_import_batch itself uses):
+ * device_of_job[i] = index (0 .. n_gpus-1, in hkbcn_init's device order) of the GPU job i runs on.  n_gpus = 0: the selected GPUs. */
+HKBCN_API int hkbcn_plan_import_batch(const hkbcn_import_job* jobs, size_t n_jobs, int n_gpus, int* device_of_job);
+/* Per-GPU wall time (ms) of the workers of the last hkbcn_import_batch / hkbcn_compress_batch call of this process, in
+ * hkbcn_init's device order; returns the number of devices (at most `capacity` values are written). */
+HKBCN_API int hkbcn_batch_stats(double* busy_ms, int capacity);
 
 /* ---- normal maps and roughness anti-aliasing ----------
  * The element-wise work of the PBRImporter path between load and the BC5 / BC4 / BC1 / BC3 encoders:

@@ -253,3 +253,37 @@ def test_import_batch_skip_existing_and_atomic_write(tmp_path):
     assert [open(p, "rb").read() for p in paths] == first
     assert os.stat(paths[0]).st_mtime_ns == mt[0] and os.stat(paths[2]).st_mtime_ns == mt[2]
     assert run(0) == [0, 0, 0]
+
+
+def test_import_batch_device_sources_and_plan():
+    """HKBCN_FLAG_SRC_DEVICE: level 0 already on the GPU the plan assigns the job to -- same chains as from host memory; the
+    plan is the one hkbcn_plan_batch gives for the same shapes; per-GPU worker times are reported"""
+    import ctypes as C
+    import torch
+    L = hkbcn.lib()
+    hkbcn.init()
+    nd = L.hkbcn_device_count()
+    jobs = [(BC1S, synth.albedo_rgba8(128, 128, 60 + i)) for i in range(3)] + [(BC5, synth.normals_rg8(64, 64, 70))]
+    arr = (hkbcn.ImportJob * len(jobs))()
+    outs, keep = [], []
+    for i, (fmt, img) in enumerate(jobs):
+        h, w = img.shape[:2]
+        arr[i] = hkbcn.ImportJob(fmt, w, h, 1, hkbcn.MipConfig(), hkbcn.FLAG_SRC_DEVICE, None, None, None, 0)
+    plan = (C.c_int * len(jobs))()
+    hkbcn.check(L.hkbcn_plan_import_batch(arr, C.c_size_t(len(jobs)), 0, plan))
+    assert list(plan) == hkbcn.plan_batch([(f, im.shape[1], im.shape[0]) for f, im in jobs], nd)
+    for i, (fmt, img) in enumerate(jobs):
+        h, w = img.shape[:2]
+        t = torch.from_numpy(np.ascontiguousarray(img).view(np.uint8).ravel().copy()).to(torch.device("cuda", plan[i]))
+        dst = np.zeros(L.hkbcn_chain_bytes(fmt, w, h, 1, L.hkbcn_calc_num_mips(w, h)), np.uint8)
+        keep.append(t)
+        outs.append(dst)
+        arr[i].src_level0 = t.data_ptr()
+        arr[i].dst = dst.ctypes.data
+    torch.cuda.synchronize()
+    hkbcn.check(L.hkbcn_import_batch(arr, C.c_size_t(len(jobs))))
+    for (fmt, img), got in zip(jobs, outs):
+        h, w = img.shape[:2]
+        assert np.array_equal(got, hkbcn.import_chain(fmt, img, w, h, L.hkbcn_calc_num_mips(w, h)))
+    busy = (C.c_double * 8)()
+    assert L.hkbcn_batch_stats(busy, 8) == nd and busy[0] > 0
