@@ -1735,3 +1735,101 @@ void* hkbcn_alloc_pinned(size_t bytes)
 void hkbcn_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 } // extern "C"
+
+// ---- hkbcn_compress_static: the host-pointer compress with no allocation of any kind ----------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code
+// under graph capture, tight serving loops, harnesses that forbid it).  hkbcn_compress stages the surface and the blocks in
+// device buffers it grows with cudaMalloc and takes the persistent kernels' tile counters from sched_slot(); here all three
+// live in one file-scope device array that every GPU which loads the library holds until exit:
+//
+//   [0, 256)                    the {next tile, finished CTAs} pair of the encode kernel -- cleared at the start of every call
+//   [256, 256 + src)            the source texels as uploaded
+//   [.. rounded up to 256, +dst) the encoded blocks before they are copied back
+//
+// In host code `g_static_scratch` is a host-side stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, asked once per device with that device current (static_scratch_of).  Every call on a device shares the
+// array and finds the previous call's bytes in it; calls that overlap on one GPU would race, so they are serialised on a mutex
+// per device and each call ends with a stream synchronise.
+static __device__ __align__(256) unsigned char g_static_scratch[HKBCN_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu[kStaticMaxDevices];
+void*      g_static_ptr[kStaticMaxDevices]; // device address of g_static_scratch on g_devs[i], set on first use
+
+int static_scratch_of(int device, Device* D, unsigned char** out)
+{
+    // caller holds g_static_mu[device] and has made D current
+    if (!g_static_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            set_err("cudaGetSymbolAddress(g_static_scratch) failed on device %d: %s", D->id, cudaGetErrorString(e));
+            return HKBCN_ERR_CUDA;
+        }
+        g_static_ptr[device] = p;
+    }
+    *out = (unsigned char*)g_static_ptr[device];
+    return HKBCN_OK;
+}
+} // namespace
+
+extern "C" {
+
+size_t hkbcn_static_scratch_bytes(void) { return HKBCN_STATIC_SCRATCH_BYTES; }
+
+int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t flags)
+{
+    Range nvtx_("hkbcn_compress_static");
+    // hkbcn_init allocates (streams, decode tables): it must have run already -- this call does not do it on the caller's behalf
+    if (!g_init.load(std::memory_order_acquire)) { set_err("hkbcn_compress_static allocates nothing: call hkbcn_init first"); return HKBCN_ERR_NOT_INIT; }
+    Device* D = dev_at(device);
+    if (!D || device >= kStaticMaxDevices) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    const int codec = codec_of(fmt);
+    if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
+    if (!src || !dst) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    if (flags & HKBCN_FLAG_SRC_DEVICE) { set_err("hkbcn_compress_static takes host pointers"); return HKBCN_ERR_BAD_ARG; }
+    const size_t sbytes = (size_t)width * height * src_bpp(codec, flags);
+    const size_t dbytes = (size_t)(width / 4) * (height / 4) * blk_bytes(codec);
+    if (dbytes == 0) return HKBCN_OK;
+    const size_t soff = 256, doff = (soff + sbytes + 255) & ~(size_t)255;
+    if (doff + dbytes > HKBCN_STATIC_SCRATCH_BYTES) {
+        set_err("%u x %u texels of format %d need %zu bytes of staging; the static scratch holds %zu (HKBCN_STATIC_SCRATCH_BYTES) -- use hkbcn_compress",
+                width, height, fmt, doff + dbytes, (size_t)HKBCN_STATIC_SCRATCH_BYTES);
+        return HKBCN_ERR_BAD_ARG;
+    }
+    std::lock_guard<std::mutex> lk(g_static_mu[device]);
+    CK(cudaSetDevice(D->id));
+    unsigned char* base = nullptr;
+    int rc = static_scratch_of(device, D, &base);
+    if (rc) return rc;
+    cudaStream_t st = D->stream;
+    CK(cudaMemsetAsync(base, 0, 256, st)); // the tile counters must start at zero whatever the last call left
+    CK(cudaMemcpyAsync(base + soff, src, sbytes, cudaMemcpyHostToDevice, st));
+    EncodeParams P;
+    memset(&P, 0, sizeof(P));
+    P.flags = flags;
+    // Width % 4 != 0: rows keep their full length, the last Width % 4 texels of each are never read (as hkbcn_compress)
+    add_level(P, codec, flags, base + soff, base + doff, width & ~3u, height, width);
+    if (P.flags & HKBCN_FLAG_LEVEL_MASK) {
+        const int level = (int)((P.flags & HKBCN_FLAG_LEVEL_MASK) >> 4) - 1;
+        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? (level <= 3 || level == 5) : codec == C_BC7 ? level <= 4 : false;
+        if (!ok) { set_err("quality level %d of format %d is not built", level, fmt); return HKBCN_ERR_UNSUPPORTED; }
+    }
+    P.sched = (uint32_t*)base;
+    cudaError_t e = cudaSuccess;
+    switch (codec) {
+    case C_BC4: e = launch_bc45_encode(1, P, D->sm_count, st); break;
+    case C_BC5: e = launch_bc45_encode(2, P, D->sm_count, st); break;
+    case C_BC1: case C_BC2: case C_BC3: e = launch_bc123_encode(codec, P, D->sm_count, st); break;
+    case C_BC7: e = launch_bc7_encode(P, D->sm_count, st); break;
+    case C_BC6H: e = launch_bc6h_encode(fmt == HKBCN_BC6H_SFLOAT, (P.flags & HKBCN_FLAG_SRC_F16) != 0, P, D->sm_count, st); break;
+    }
+    if (e != cudaSuccess) { set_err("kernel launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CK(cudaMemcpyAsync(dst, base + doff, dbytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return HKBCN_OK;
+}
+
+} // extern "C"

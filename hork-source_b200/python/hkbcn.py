@@ -39,6 +39,7 @@ EXPORTS = [
     "hkbcn_envprobe_texels", "hkbcn_envprobe_prefilter", "hkbcn_irradiance", "hkbcn_envprobe_prefilter_dev", "hkbcn_irradiance_dev",
     "hkbcn_pack_texel_bytes", "hkbcn_pack_normals", "hkbcn_unpack_normals", "hkbcn_normalize_vectors", "hkbcn_bake_roughness",
     "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
+    "hkbcn_static_scratch_bytes", "hkbcn_compress_static",
 ]
 
 
@@ -138,6 +139,8 @@ def lib():
         L.hkbcn_bake_roughness_dev.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
         L.hkbcn_free_pinned.argtypes = [C.c_void_p]
+        L.hkbcn_static_scratch_bytes.restype = C.c_size_t
+        L.hkbcn_compress_static.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
         _lib = L
     return _lib
 

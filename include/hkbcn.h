@@ -335,6 +335,23 @@ HKBCN_API uint64_t hkbcn_launch_count(void);
 HKBCN_API void* hkbcn_alloc_pinned(size_t bytes);
 HKBCN_API void hkbcn_free_pinned(void* p);
 
+/* ---- compress without any allocation ----------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, kernels and bytes out as hkbcn_compress (host pointers, one surface, synchronous, Width % 4 != 0 allowed),
+ * on library device `device`.  The device staging of the texels and of the blocks and the encode kernel's tile counters live
+ * in ONE file-scope __device__ array of HKBCN_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit;
+ * the call runs no cudaMalloc / cudaFree / cudaHostAlloc and creates no stream or event.  Consequences:
+ *   - hkbcn_init must have been called (it allocates streams and tables): otherwise HKBCN_ERR_NOT_INIT;
+ *   - 256 + source bytes (rounded up to 256) + block bytes must fit: 1024 x 1024 RGBA8 -> BC7 or 512 x 512 RGBA32F -> BC6H
+ *     do; anything larger is refused with HKBCN_ERR_BAD_ARG and a message that names both sizes -- use hkbcn_compress;
+ *   - all calls on one device share the array, which keeps the previous call's contents: the counters are cleared at the
+ *     start of each call, and calls from several threads are serialised on a per-device mutex.  Work that reaches the array
+ *     any other way while a call is running would race with it. */
+#define HKBCN_STATIC_SCRATCH_BYTES (6u << 20)
+HKBCN_API size_t hkbcn_static_scratch_bytes(void);
+HKBCN_API int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint32_t width, uint32_t height, uint32_t flags);
+
 #ifdef __cplusplus
 }
 #endif
