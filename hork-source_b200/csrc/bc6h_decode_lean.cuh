@@ -116,48 +116,75 @@ HKD void endpoints(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, int e[12]
 //             so the float's bit pattern is bits(1.5*2^31) + v; (bits * 124 - bits(C) * 124) = v * 124 has
 //             bcdec's (v * 31) >> 6 in bytes 1..2, where the PRMT that packs two halfs picks it up.
 //   signed:   x = D*w + A with A = 64a + 32, D = b - a; v = x >> 6 = round((x - 31.5) / 64), ulp 64 at 1.5*2^29.
+//             r = RZ(|z| * 31/2048 + k) with z = 64 v (exact), k = 1.5*2^23 (+ 32768 when v <= -2, i.e. when bcdec sets the
+//             sign bit: the magnitude (|v| * 31) >> 5 is zero for |v| <= 1): the float's low 16 bits are the half.
+//             The "v <= -2" flag is sat(-z/64 - 1), one FFMA.SAT -- no compare, no select, nothing on the ALU pipe.
+// Two channels of a texel share one packed instruction (fma / add .f32x2, SASS FFMA2 / FADD2: one issue slot, two results,
+// each rounded as the scalar instruction rounds it -- and everything here is exact anyway); weights and region masks are
+// stored as duplicated pairs so that one 8-byte shared-memory load yields the packed operand.
 #ifdef HKBCN_HOST_EMU
 static inline float hk_fma(float a, float b, float c) { return fmaf(a, b, c); }
 static inline float hk_add(float a, float b) { return a + b; }
 static inline uint32_t hk_fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
 static inline float hk_bitsf(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline float hk_fma_sat(float a, float b, float c) { const float r = fmaf(a, b, c); return r < 0.0f ? 0.0f : r > 1.0f ? 1.0f : r; }
+static inline float hk_fma_rz_abs(float a, float b, float c)
+{   // |a| * b + c rounded toward zero; the exact sum fits a double
+    const double t = fabs((double)a) * (double)b + (double)c;
+    float f = (float)t;
+    if (fabs((double)f) > fabs(t)) f = nextafterf(f, 0.0f);
+    return f;
+}
+struct fp2 { float x, y; };
+static inline fp2 hk_pack2(float a, float b) { return fp2{a, b}; }
+static inline fp2 hk_fma2(fp2 a, fp2 b, fp2 c) { return fp2{fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)}; }
+static inline fp2 hk_add2(fp2 a, fp2 b) { return fp2{a.x + b.x, a.y + b.y}; }
+static inline float hk_lo(fp2 a) { return a.x; }
+static inline float hk_hi(fp2 a) { return a.y; }
+static inline fp2 hk_ld2(const void* p) { fp2 r; memcpy(&r, p, 8); return r; }
 #else
 HKD float hk_fma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 HKD float hk_add(float a, float b) { return __fadd_rn(a, b); }
 HKD uint32_t hk_fbits(float f) { return __float_as_uint(f); }
 HKD float hk_bitsf(uint32_t u) { return __uint_as_float(u); }
+HKD float hk_fma_sat(float a, float b, float c) { float r; asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+HKD float hk_fma_rz_abs(float a, float b, float c) { return __fmaf_rz(fabsf(a), b, c); }
+typedef unsigned long long fp2;
+HKD fp2 hk_pack2(float a, float b) { fp2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+HKD fp2 hk_fma2(fp2 a, fp2 b, fp2 c) { fp2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+HKD fp2 hk_add2(fp2 a, fp2 b) { fp2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+HKD float hk_lo(fp2 a) { float x, y; asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(a)); return x; }
+HKD float hk_hi(fp2 a) { float x, y; asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(a)); return y; }
+HKD fp2 hk_ld2(const void* p) { return *(const fp2*)p; }
 #endif
 
-// aWeight3 / aWeight4 as floats and the region of every texel of the 32 two-region shapes as 0.0f / 1.0f.
-// m is texel-major so that a warp's lookups (one texel, 32 shapes) fall into 32 different banks.
+// aWeight3 / aWeight4 as floats and the region of every texel of the 32 two-region shapes as 0.0f / 1.0f, every value twice
+// (one 8-byte load = the packed operand of two channels).  m is texel-major so that a warp's lookups (one texel, 32 shapes)
+// fall into different banks.
 struct FTab {
-    float w3[8], w4[16];
-    float m[16][32];
+    float w3[8][2], w4[16][2];
+    float m[16][32][2];
 };
 inline void fill_ftab(FTab* F, const uint16_t* shape2)
 {
     static const int w3[8] = {0, 9, 18, 27, 37, 46, 55, 64}, w4[16] = {0, 4, 9, 13, 17, 21, 26, 30, 34, 38, 43, 47, 51, 55, 60, 64};
-    for (int i = 0; i < 8; i++) F->w3[i] = (float)w3[i];
-    for (int i = 0; i < 16; i++) F->w4[i] = (float)w4[i];
+    for (int i = 0; i < 8; i++) F->w3[i][0] = F->w3[i][1] = (float)w3[i];
+    for (int i = 0; i < 16; i++) F->w4[i][0] = F->w4[i][1] = (float)w4[i];
     for (int s = 0; s < 32; s++)
-        for (int i = 0; i < 16; i++) F->m[i][s] = ((shape2[s] >> i) & 1) ? 1.0f : 0.0f;
+        for (int i = 0; i < 16; i++) F->m[i][s][0] = F->m[i][s][1] = ((shape2[s] >> i) & 1) ? 1.0f : 0.0f;
 }
 
-// One interpolated + finished channel value, returned with the half in bytes 1..2 (bits 8..23).
+// x = D * w + A (see above) -> the finished half: unsigned in bytes 1..2 of the result, signed in bytes 0..1
 template <bool SIGNED>
-HKD uint32_t channel(float A, float D, float w)
+HKD uint32_t finish_y(float y)
 {
-    const float x = hk_fma(D, w, A);
-    if (!SIGNED) {
-        const uint32_t yb = hk_fbits(hk_add(x, 3221225472.0f)); // 1.5 * 2^31 = 0x4F400000
-        return yb * 124u - 0x4F400000u * 124u;
-    } else {
-        const int v = (int)(hk_fbits(hk_add(x, 805306368.0f)) - 0x4E400000u); // 1.5 * 2^29
-        const int a = v < 0 ? -v : v;
-        const uint32_t mag = (uint32_t)(a * 31) >> 5;
-        return (mag | ((v < 0 && mag != 0) ? 0x8000u : 0u)) << 8;
-    }
+    if (!SIGNED) return hk_fbits(y) * 124u - 0x4F400000u * 124u;
+    const float z = hk_add(y, -805306368.0f);                   // 64 v
+    const float n = hk_fma_sat(z, -0.015625f, -1.0f);           // v <= -2 ? 1 : 0
+    const float k = hk_fma(n, 32768.0f, 12582912.0f);           // 1.5 * 2^23 (+ the sign bit of the half)
+    return hk_fbits(hk_fma_rz_abs(z, 0.01513671875f, k));       // |v| * 31 / 32, floored
 }
+template <bool SIGNED> HKD constexpr float finish_magic() { return SIGNED ? 805306368.0f : 3221225472.0f; } // 1.5 * 2^29 / 1.5 * 2^31
 
 // Texel rows of one block.  sink.row(r, w) receives the six output words of texel row r (RGB16F x 4, bcdec's layout).
 template <bool SIGNED, bool TWO, class Sink>
@@ -173,7 +200,7 @@ HKD void texels(const int e[12], uint32_t part, uint32_t w2, uint32_t w3, const 
             D[s][c] = SIGNED ? (float)(b - a) : (float)(4 * (b - a));
         }
     uint32_t lo, hi;
-    const float* mrow = &F.m[0][0];
+    const float* mrow = &F.m[0][0][0];
     if (TWO) {
         // 46 index bits from bit 82; implicit zeros after texel 0's two bits and the anchor's (as BC7 mode 1)
         unsigned long long S = ((unsigned long long)(w3 >> 18) << 32) | hk_funnel_r(w2, w3, 18);
@@ -181,7 +208,7 @@ HKD void texels(const int e[12], uint32_t part, uint32_t w2, uint32_t w3, const 
         S += S & (((unsigned long long)T.ins3[part][1] << 32) | T.ins3[part][0]);
         lo = (uint32_t)S;
         hi = (uint32_t)(S >> 32);
-        mrow = &F.m[0][part];
+        mrow = &F.m[0][part][0];
 #pragma unroll
         for (int c = 0; c < 3; c++) { // region 1 as an offset from region 0
             A[1][c] = hk_add(A[1][c], -A[0][c]);
@@ -191,37 +218,43 @@ HKD void texels(const int e[12], uint32_t part, uint32_t w2, uint32_t w3, const 
         lo = w2 & ~1u; // texel 0: 3 bits at 65..67 -> a 4-bit field with its top bit clear, after >> 1 below
         hi = w3;
     }
+    // channels R, G as one packed pair, B scalar
+    const fp2 A0 = hk_pack2(A[0][0], A[0][1]), D0 = hk_pack2(D[0][0], D[0][1]);
+    const fp2 A1 = TWO ? hk_pack2(A[1][0], A[1][1]) : A0, D1 = TWO ? hk_pack2(D[1][0], D[1][1]) : D0;
+    const fp2 K = hk_pack2(finish_magic<SIGNED>(), finish_magic<SIGNED>());
 #pragma unroll
     for (int r = 0; r < 4; r++) {
         uint32_t y[12];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int i = 4 * r + k;
-            float w, a0, a1, a2, d0, d1, d2;
+            fp2 wd, a01, d01;
+            float a2, d2;
             if (TWO) {
-                // byte offset of the weight: 4 * ((S >> 3i) & 7)
+                // byte offset of the weight pair: 8 * ((S >> 3i) & 7)
                 const int p = 3 * i;
-                const uint32_t off = p == 0 ? (lo << 2) : p + 3 <= 32 ? (lo >> (p - 2)) : p >= 34 ? (hi >> (p - 34)) : p >= 32 ? (hi << (34 - p)) : hk_funnel_r(lo, hi, p - 2);
-                w = *(const float*)((const char*)F.w3 + (off & 0x1Cu));
-                const float m = mrow[32 * i];
-                a0 = hk_fma(m, A[1][0], A[0][0]); d0 = hk_fma(m, D[1][0], D[0][0]);
-                a1 = hk_fma(m, A[1][1], A[0][1]); d1 = hk_fma(m, D[1][1], D[0][1]);
-                a2 = hk_fma(m, A[1][2], A[0][2]); d2 = hk_fma(m, D[1][2], D[0][2]);
+                const uint32_t off = p == 0 ? (lo << 3) : p <= 29 ? (lo >> (p - 3)) : p >= 35 ? (hi >> (p - 35)) : hk_funnel_r(lo, hi, p - 3);
+                wd = hk_ld2((const char*)F.w3 + (off & 0x38u));
+                const fp2 md = hk_ld2(mrow + 64 * i);
+                a01 = hk_fma2(md, A1, A0); d01 = hk_fma2(md, D1, D0);
+                a2 = hk_fma(hk_lo(md), A[1][2], A[0][2]); d2 = hk_fma(hk_lo(md), D[1][2], D[0][2]);
             } else {
                 const uint32_t word = i < 8 ? lo : hi;
                 const int q = 4 * (i & 7);
-                const uint32_t off = i == 0 ? ((word << 1) & 0x1Cu) : q == 0 ? ((word << 2) & 0x3Cu) : ((word >> (q - 2)) & 0x3Cu);
-                w = *(const float*)((const char*)F.w4 + off);
-                a0 = A[0][0]; a1 = A[0][1]; a2 = A[0][2];
-                d0 = D[0][0]; d1 = D[0][1]; d2 = D[0][2];
+                const uint32_t off = i == 0 ? ((word << 2) & 0x38u) : q == 0 ? ((word << 3) & 0x78u) : ((word >> (q - 3)) & 0x78u);
+                wd = hk_ld2((const char*)F.w4 + off);
+                a01 = A0; d01 = D0;
+                a2 = A[0][2]; d2 = D[0][2];
             }
-            y[3 * k + 0] = channel<SIGNED>(a0, d0, w);
-            y[3 * k + 1] = channel<SIGNED>(a1, d1, w);
-            y[3 * k + 2] = channel<SIGNED>(a2, d2, w);
+            const fp2 y01 = hk_add2(hk_fma2(d01, wd, a01), K);
+            const float y2 = hk_add(hk_fma(d2, hk_lo(wd), a2), finish_magic<SIGNED>());
+            y[3 * k + 0] = finish_y<SIGNED>(hk_lo(y01));
+            y[3 * k + 1] = finish_y<SIGNED>(hk_hi(y01));
+            y[3 * k + 2] = finish_y<SIGNED>(y2);
         }
         uint32_t o[6];
 #pragma unroll
-        for (int j = 0; j < 6; j++) o[j] = hk_prmt(y[2 * j], y[2 * j + 1], 0x6521); // halfs sit in bytes 1..2
+        for (int j = 0; j < 6; j++) o[j] = hk_prmt(y[2 * j], y[2 * j + 1], SIGNED ? 0x5410 : 0x6521); // halfs in bytes 0..1 / 1..2
         sink.row(r, o);
     }
 }

@@ -19,7 +19,7 @@ sys.path.insert(0, os.path.join(ROOT, "hork-source_b200", "python"))
 
 # name: (format id, block bytes, decoded texel bytes, flags)
 FORMATS = {"BC1": (54, 8, 4, 0), "BC2": (56, 16, 4, 0), "BC3": (58, 16, 4, 0), "BC4": (60, 8, 1, 0), "BC5": (62, 16, 2, 0),
-           "BC7": (66, 16, 4, 0), "BC6H_f16": (64, 16, 6, 0), "BC6H_f32": (64, 16, 12, 1 << 8)}
+           "BC7": (66, 16, 4, 0), "BC6H_f16": (64, 16, 6, 0), "BC6H_S_f16": (65, 16, 6, 0), "BC6H_f32": (64, 16, 12, 1 << 8)}
 
 
 def peak():
@@ -44,9 +44,11 @@ def real_blocks(torch, hkbcn, L, name, n, stream):
     else:
         # BC6H encode is slow: encode 512^2 once and tile the BLOCKS up to n x n
         img = synth.sky_rgba32f(t, t, 0xB2000006, 0)
+        if name == "BC6H_S":
+            img[..., :3] -= 1.0  # mixed signs
         d_src = torch.from_numpy(np.ascontiguousarray(img).view(np.uint8).ravel()).cuda()
         d_dst = torch.empty((t // 4) * (t // 4) * 16, dtype=torch.uint8, device="cuda")
-        hkbcn.check(L.hkbcn_compress_dev(0, 64, d_src.data_ptr(), d_dst.data_ptr(), t, t, 0, C.c_void_p(stream.cuda_stream)))
+        hkbcn.check(L.hkbcn_compress_dev(0, 65 if name == "BC6H_S" else 64, d_src.data_ptr(), d_dst.data_ptr(), t, t, 0, C.c_void_p(stream.cuda_stream)))
         torch.cuda.synchronize()
         return d_dst.view(t // 4, t // 4, 16).repeat(n // t, n // t, 1).contiguous().view(-1)
     d_src = torch.from_numpy(np.ascontiguousarray(img).view(np.uint8).ravel()).cuda()
@@ -80,8 +82,8 @@ def main():
         fmt, blk, tex, flags = FORMATS[name]
         for n in [int(s) for s in args.sizes.split(",")]:
             nblk = (n // 4) * (n // 4)
-            if args.real and name in ("BC7", "BC6H_f16", "BC6H_f32") and n >= 512:
-                src = real_blocks(torch, hkbcn, L, "BC7" if name == "BC7" else "BC6H", n, stream)
+            if args.real and name in ("BC7", "BC6H_f16", "BC6H_S_f16", "BC6H_f32") and n >= 512:
+                src = real_blocks(torch, hkbcn, L, "BC7" if name == "BC7" else "BC6H_S" if name == "BC6H_S_f16" else "BC6H", n, stream)
                 kind = "encoded"
             else:
                 src = torch.randint(0, 256, (nblk * blk,), dtype=torch.uint8, device="cuda", generator=gen)
