@@ -74,6 +74,11 @@ struct Device {
     std::map<cudaStream_t, uint32_t*> sched_of_stream;
     uint32_t     sched_used = 0;
     std::mutex   sched_mu;
+    // BC7 work lists (bc7_encode.cu): one buffer per stream, grown on demand; a buffer that was outgrown may still be read by a
+    // kernel in flight, so it is parked until shutdown instead of freed
+    struct Aux { uint32_t* p = nullptr; size_t cap = 0; };
+    std::map<cudaStream_t, Aux> aux_of_stream;
+    std::vector<uint32_t*> aux_retired;
     // hkbcn_import_batch: two pipeline slots, each with its own stream, device buffers and pinned staging, so the upload of
     // texture i + 1 and the download of texture i - 1 overlap the kernels of texture i
     struct Slot {
@@ -171,6 +176,25 @@ uint32_t* sched_slot(Device* D, cudaStream_t st)
     return p;
 }
 
+// the stream's BC7 work-list scratch, at least `bytes` large, first 16 bytes zero; nullptr + error text on failure
+uint32_t* bc7_aux(Device* D, cudaStream_t st, size_t bytes)
+{
+    std::lock_guard<std::mutex> lk(D->sched_mu);
+    Device::Aux& a = D->aux_of_stream[st];
+    if (a.cap >= bytes) return a.p;
+    const size_t want = std::max(bytes + bytes / 2, (size_t)1 << 20);
+    uint32_t* p = nullptr;
+    if (cudaMalloc((void**)&p, want) != cudaSuccess || cudaMemset(p, 0, 16) != cudaSuccess) {
+        set_err("cannot allocate %zu bytes of BC7 work-list scratch: %s", want, cudaGetErrorString(cudaGetLastError()));
+        if (p) cudaFree(p);
+        return nullptr;
+    }
+    if (a.p) D->aux_retired.push_back(a.p);
+    a.p = p;
+    a.cap = want;
+    return p;
+}
+
 Device* dev_at(int i) { return (i >= 0 && i < (int)g_devs.size()) ? g_devs[i] : nullptr; }
 
 int grow(void** p, size_t* cap, size_t need)
@@ -241,6 +265,11 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
     }
     EncodeParams P = P0;
     if (!(P.sched = sched_slot(D, st))) return HKBCN_ERR_CUDA;
+    if (codec == C_BC7) {
+        uint32_t nb = 0;
+        for (uint32_t i = 0; i < P.nLevels; i++) nb += P.lv[i].nblocks;
+        if (!(P.aux = bc7_aux(D, st, bc7_aux_bytes(nb)))) return HKBCN_ERR_CUDA;
+    }
     cudaError_t e = cudaSuccess;
     switch (codec) {
     case C_BC4: e = launch_bc45_encode(1, P, D->sm_count, st); break;
@@ -252,7 +281,7 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
     }
     if (e == cudaErrorNotSupported) { set_err("encoder for format %d not built yet", fmt); return HKBCN_ERR_UNSUPPORTED; }
     if (e != cudaSuccess) { set_err("kernel launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    g_launches.fetch_add(codec == C_BC7 ? 2 : 1, std::memory_order_relaxed); // BC7: classify + encode
     return HKBCN_OK;
 }
 
@@ -432,6 +461,8 @@ static void destroy_device(Device* D)
     for (cudaEvent_t e : D->ev_piece) if (e) cudaEventDestroy(e);
     if (D->copy_stream) cudaStreamDestroy(D->copy_stream);
     for (uint32_t* c : D->sched_chunks) cudaFree(c);
+    for (auto& kv : D->aux_of_stream) cudaFree(kv.second.p);
+    for (uint32_t* c : D->aux_retired) cudaFree(c);
     for (auto& sl : D->slots) {
         if (sl.d_src) cudaFree(sl.d_src);
         if (sl.d_dst) cudaFree(sl.d_dst);
@@ -855,6 +886,161 @@ int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t widt
     int rc = ensure_init();
     if (rc) return rc;
     return import_host_on(g_devs[0], fmt, src_level0, dst, width, height, num_mips, cfg, flags);
+}
+
+// ---- CreateImage(RawImage ...) with compression (Image.cpp:866-1289) and CreateRoughnessMap (:2399-2456) -------------------------
+static uint32_t closest_pow2(uint32_t v)
+{   // Math::ToClosestPowerOfTwo (Hork/Core/BaseMath.h:417-423): the nearer of the two enclosing powers, ties go to the smaller
+    if (v == 0) return 1;
+    uint32_t hi = 1;
+    while (hi < v) hi <<= 1;
+    const uint32_t lo = hi >> 1;
+    return (hi - v) < (v - lo) ? hi : lo;
+}
+
+int hkbcn_plan_image(int raw_format, uint32_t width, uint32_t height, int mipmapped, uint32_t storage_flags, uint32_t import_flags,
+                     hkbcn_image_plan* plan)
+{
+    if (!plan) { set_err("null plan"); return HKBCN_ERR_BAD_ARG; }
+    memset(plan, 0, sizeof(*plan));
+    const bool srgb = (import_flags & HKBCN_IMPORT_ASSUME_8BIT_RGB_IMAGES_ARE_SRGB) != 0;
+    const bool hdr_ok = (import_flags & HKBCN_IMPORT_USE_COMPRESSION) && (import_flags & HKBCN_IMPORT_ALLOW_HDRI_COMPRESSION);
+    int fmt = 0, ch = 0;
+    switch (raw_format) {
+    case HKBCN_RAW_R8: ch = 1; fmt = HKBCN_BC4_UNORM; break;
+    case HKBCN_RAW_R8_ALPHA: ch = 2; fmt = HKBCN_BC5_UNORM; break;
+    case HKBCN_RAW_RGB8: case HKBCN_RAW_BGR8:
+        ch = 3; plan->add_alpha = 1; storage_flags |= HKBCN_STORAGE_NO_ALPHA; // BC1: no alpha channel is used
+        fmt = srgb ? HKBCN_BC1_UNORM_SRGB : HKBCN_BC1_UNORM;
+        plan->swap_rb = raw_format == HKBCN_RAW_BGR8;
+        break;
+    case HKBCN_RAW_RGBA8: case HKBCN_RAW_BGRA8:
+        ch = 4;
+        if (storage_flags & HKBCN_STORAGE_NO_ALPHA) fmt = srgb ? HKBCN_BC1_UNORM_SRGB : HKBCN_BC1_UNORM;
+        else fmt = srgb ? HKBCN_BC3_UNORM_SRGB : HKBCN_BC3_UNORM;
+        plan->swap_rb = raw_format == HKBCN_RAW_BGRA8;
+        break;
+    case HKBCN_RAW_R32F: ch = 1; break;        // no compressed analogue
+    case HKBCN_RAW_R32_ALPHA_F: ch = 2; break; // no compressed analogue
+    case HKBCN_RAW_RGB32F: case HKBCN_RAW_BGR32F:
+        ch = 3;
+        plan->swap_rb = raw_format == HKBCN_RAW_BGR32F;
+        if (hdr_ok) { fmt = HKBCN_BC6H_UFLOAT; plan->add_alpha = 1; storage_flags |= HKBCN_STORAGE_NO_ALPHA; }
+        break;
+    case HKBCN_RAW_RGBA32F: case HKBCN_RAW_BGRA32F:
+        ch = 4;
+        plan->swap_rb = raw_format == HKBCN_RAW_BGRA32F;
+        if (hdr_ok) fmt = HKBCN_BC6H_UFLOAT; // the alpha channel is lost
+        break;
+    default: set_err("bad raw image format %d", raw_format); return HKBCN_ERR_BAD_FORMAT;
+    }
+    if (!(import_flags & HKBCN_IMPORT_USE_COMPRESSION)) fmt = 0;
+    plan->format = fmt;
+    plan->storage_flags = storage_flags;
+    plan->src_channels = ch;
+    // Image.cpp:1064-1068 (block size 4 for every BCn format)
+    plan->required_width = mipmapped ? std::max<uint32_t>(closest_pow2(width), 4) : (width + 3) & ~3u;
+    plan->required_height = mipmapped ? std::max<uint32_t>(closest_pow2(height), 4) : (height + 3) & ~3u;
+    return HKBCN_OK;
+}
+
+// raw texels (host) -> level 0 in the encoder's source layout -> device cascade -> encode -> host; device 0
+static int create_image_on(Device* D, const hkbcn_image_plan& plan, const void* src, uint32_t w, uint32_t h, uint32_t mips, const hkbcn_mip_config* cfg,
+                           void* dst)
+{
+    const int fmt = plan.format, codec = codec_of(fmt);
+    const bool f32 = codec == C_BC6H;
+    const size_t texel = f32 ? 4 : 1;
+    const bool pass = plan.add_alpha || plan.swap_rb; // the channel pass is needed
+    const size_t raw_bytes = (size_t)w * h * plan.src_channels * texel;
+    const size_t sbytes = chain_src_bytes(codec, 0, w, h, mips), dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
+    const size_t raw_off = (sbytes + 255) & ~(size_t)255;
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    int rc;
+    if ((rc = grow(&D->d_src, &D->src_cap, raw_off + (pass ? raw_bytes : 0))) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    if (pass) {
+        uint8_t* d_raw = (uint8_t*)D->d_src + raw_off;
+        CK(cudaMemcpyAsync(d_raw, src, raw_bytes, cudaMemcpyHostToDevice, D->stream));
+        CK(launch_expand_channels(d_raw, D->d_src, (size_t)w * h, plan.src_channels, plan.swap_rb != 0, f32, D->stream));
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+    } else {
+        CK(cudaMemcpyAsync(D->d_src, src, raw_bytes, cudaMemcpyHostToDevice, D->stream));
+    }
+    if (mips > 1 && (rc = generate_mips_on(D, fmt, D->d_src, w, h, mips, cfg, 0, D->stream)) != HKBCN_OK) return rc;
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, 0, D->d_src, D->d_dst, w, h, mips)) != HKBCN_OK) return rc;
+    if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
+int hkbcn_create_image(int raw_format, const void* src, uint32_t width, uint32_t height, const hkbcn_mip_config* cfg, uint32_t storage_flags,
+                       uint32_t import_flags, hkbcn_texture_desc* desc, void* dst, size_t capacity)
+{
+    Range nvtx_("hkbcn_create_image");
+    hkbcn_image_plan plan;
+    int rc = hkbcn_plan_image(raw_format, width, height, cfg != nullptr, storage_flags, import_flags, &plan);
+    if (rc) return rc;
+    if (!src || !dst || !width || !height) { set_err("null pointer or empty image"); return HKBCN_ERR_BAD_ARG; }
+    if (!plan.format) { set_err("the reference stores raw format %d uncompressed under these import flags: nothing to block-compress", raw_format); return HKBCN_ERR_UNSUPPORTED; }
+    if (plan.required_width != width || plan.required_height != height) {
+        set_err("the reference first resamples %u x %u to %u x %u (Image.cpp:1064-1096); the general resampler is not part of this path", width, height,
+                plan.required_width, plan.required_height);
+        return HKBCN_ERR_UNSUPPORTED;
+    }
+    const uint32_t mips = cfg ? hkbcn_calc_num_mips(width, height) : 1;
+    const size_t need = hkbcn_chain_bytes(plan.format, width, height, 1, mips);
+    if (capacity < need) { set_err("dst holds %zu bytes, the storage needs %zu", capacity, need); return HKBCN_ERR_BAD_ARG; }
+    if ((rc = ensure_init()) != HKBCN_OK) return rc;
+    // ImageStorage::GenerateMipmaps (Image.cpp:767-774): alpha weighting unless NO_ALPHA, premultiplied flag passed on
+    hkbcn_mip_config mc = cfg ? *cfg : hkbcn_mip_config{0, 0, 0, 0};
+    mc.no_alpha = (plan.storage_flags & HKBCN_STORAGE_NO_ALPHA) ? 1 : 0;
+    mc.alpha_premultiplied = (plan.storage_flags & HKBCN_STORAGE_ALPHA_PREMULTIPLIED) ? 1 : 0;
+    if ((rc = create_image_on(g_devs[0], plan, src, width, height, mips, &mc, dst)) != HKBCN_OK) return rc;
+    if (desc) {
+        desc->type = HKBCN_TEXTURE_2D;
+        desc->width = width; desc->height = height; desc->depth = 1;
+        desc->num_mips = mips;
+        desc->fmt = plan.format;
+        desc->storage_flags = plan.storage_flags;
+    }
+    return HKBCN_OK;
+}
+
+int hkbcn_create_roughness_map(const uint8_t* roughness, uint32_t width, uint32_t height, int mipmapped, int edge_mode, int filter,
+                               hkbcn_texture_desc* desc, void* dst, size_t capacity)
+{
+    Range nvtx_("hkbcn_create_roughness_map");
+    if (!roughness || !dst || !width || !height) { set_err("null pointer or empty image"); return HKBCN_ERR_BAD_ARG; }
+    const uint32_t rw = mipmapped ? std::max<uint32_t>(closest_pow2(width), 4) : (width + 3) & ~3u;
+    const uint32_t rh = mipmapped ? std::max<uint32_t>(closest_pow2(height), 4) : (height + 3) & ~3u;
+    if (rw != width || rh != height) {
+        set_err("CreateRoughnessMap: The width and height of the roughness map must be a power of two and a multiple of blockSize if compression is enabled.");
+        return HKBCN_ERR_BAD_ARG;
+    }
+    const uint32_t mips = mipmapped ? hkbcn_calc_num_mips(width, height) : 1;
+    const size_t need = hkbcn_chain_bytes(HKBCN_BC4_UNORM, width, height, 1, mips);
+    if (capacity < need) { set_err("dst holds %zu bytes, the storage needs %zu", capacity, need); return HKBCN_ERR_BAD_ARG; }
+    int rc = ensure_init();
+    if (rc) return rc;
+    hkbcn_image_plan plan;
+    memset(&plan, 0, sizeof(plan));
+    plan.format = HKBCN_BC4_UNORM;
+    plan.storage_flags = HKBCN_STORAGE_NO_ALPHA;
+    plan.src_channels = 1;
+    hkbcn_mip_config mc{edge_mode, filter, 1, 0};
+    if ((rc = create_image_on(g_devs[0], plan, roughness, width, height, mips, &mc, dst)) != HKBCN_OK) return rc;
+    if (desc) {
+        desc->type = HKBCN_TEXTURE_2D;
+        desc->width = width; desc->height = height; desc->depth = 1;
+        desc->num_mips = mips;
+        desc->fmt = HKBCN_BC4_UNORM;
+        desc->storage_flags = HKBCN_STORAGE_NO_ALPHA;
+    }
+    return HKBCN_OK;
 }
 
 int hkbcn_encode_blocks(int fmt, const void* src, void* dst, size_t n_blocks, uint32_t flags)
@@ -1793,9 +1979,11 @@ int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint3
     const size_t dbytes = (size_t)(width / 4) * (height / 4) * blk_bytes(codec);
     if (dbytes == 0) return HKBCN_OK;
     const size_t soff = 256, doff = (soff + sbytes + 255) & ~(size_t)255;
-    if (doff + dbytes > HKBCN_STATIC_SCRATCH_BYTES) {
+    // BC7 keeps a work list (two counters + 4 bytes per block) behind the blocks
+    const size_t loff = (doff + dbytes + 255) & ~(size_t)255, lbytes = codec == C_BC7 ? bc7_aux_bytes((uint32_t)(dbytes / 16)) : 0;
+    if (loff + lbytes > HKBCN_STATIC_SCRATCH_BYTES) {
         set_err("%u x %u texels of format %d need %zu bytes of staging; the static scratch holds %zu (HKBCN_STATIC_SCRATCH_BYTES) -- use hkbcn_compress",
-                width, height, fmt, doff + dbytes, (size_t)HKBCN_STATIC_SCRATCH_BYTES);
+                width, height, fmt, loff + lbytes, (size_t)HKBCN_STATIC_SCRATCH_BYTES);
         return HKBCN_ERR_BAD_ARG;
     }
     std::lock_guard<std::mutex> lk(g_static_mu[device]);
@@ -1817,6 +2005,10 @@ int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint3
         if (!ok) { set_err("quality level %d of format %d is not built", level, fmt); return HKBCN_ERR_UNSUPPORTED; }
     }
     P.sched = (uint32_t*)base;
+    if (codec == C_BC7) {
+        P.aux = (uint32_t*)(base + loff);
+        CK(cudaMemsetAsync(P.aux, 0, 16, st)); // the list's counters: whatever an earlier call staged here must go
+    }
     cudaError_t e = cudaSuccess;
     switch (codec) {
     case C_BC4: e = launch_bc45_encode(1, P, D->sm_count, st); break;
@@ -1826,7 +2018,7 @@ int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint3
     case C_BC6H: e = launch_bc6h_encode(fmt == HKBCN_BC6H_SFLOAT, (P.flags & HKBCN_FLAG_SRC_F16) != 0, P, D->sm_count, st); break;
     }
     if (e != cudaSuccess) { set_err("kernel launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    g_launches.fetch_add(codec == C_BC7 ? 2 : 1, std::memory_order_relaxed);
     CK(cudaMemcpyAsync(dst, base + doff, dbytes, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     return HKBCN_OK;

@@ -34,6 +34,7 @@ struct EncodeParams {
     uint32_t flags;
     uint32_t pad;
     uint32_t* sched; // {next tile, finished CTAs} of this launch (persistent encoders); both zero between launches
+    uint32_t* aux;   // BC7: {blocks with alpha, opaque blocks, 2 unused} + one work-list entry per block of the launch (bc7_encode.cu)
 };
 
 // ---- mbarrier / bulk-copy (TMA 1-D) wrappers --------------------------------

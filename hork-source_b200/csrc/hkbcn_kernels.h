@@ -16,6 +16,8 @@ cudaError_t launch_bc123_encode(int codec, const EncodeParams& P, int sm_count, 
 cudaError_t bc1_upload_tables(); // a12: single-colour match + 565 midpoint tables
 
 uint32_t bc7_tile_blocks();
+// P.aux: bc7_aux_bytes(blocks of the launch) bytes of device scratch whose first 16 bytes are zero (the kernels leave them zero)
+size_t bc7_aux_bytes(uint32_t total_blocks);
 cudaError_t launch_bc7_encode(const EncodeParams& P, int sm_count, cudaStream_t stream);
 cudaError_t bc7_upload_tables();
 
@@ -74,6 +76,8 @@ cudaError_t launch_pack_normals(int variant, const float* d_normals, uint8_t* d_
 cudaError_t launch_unpack_normals(int variant, const uint8_t* d_src, float* d_normals, size_t count, cudaStream_t st);
 cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st);
 cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t* d_rough, size_t count, cudaStream_t st);
+// RGB -> RGBA (alpha 255 / 1.0) and / or R <-> B: CreateImage's channel pass (Image.cpp:1152-1228)
+cudaError_t launch_expand_channels(const void* d_src, void* d_dst, size_t count, int src_channels, bool swap_rb, bool f32, cudaStream_t st);
 
 } // namespace hkbcn
 

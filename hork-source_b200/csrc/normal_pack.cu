@@ -231,6 +231,30 @@ cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st)
     return cudaGetLastError();
 }
 
+// ---- CreateImage's channel pass (Image.cpp:1152-1228): three-channel raw images gain an alpha of 255 / 1.0, BGR(A) images
+// get R and B exchanged before compression.  T = uint8_t or float; one texel per thread.
+template <typename T>
+__global__ void __launch_bounds__(256) expand_channels_kernel(const T* __restrict__ src, T* __restrict__ dst, size_t count, int src_ch, int swap, T one)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    const T* s = src + i * (size_t)src_ch;
+    T* d = dst + i * 4;
+    const T r = s[swap ? 2 : 0], g = s[1], b = s[swap ? 0 : 2];
+    const T a = src_ch == 4 ? s[3] : one;
+    d[0] = r; d[1] = g; d[2] = b; d[3] = a;
+}
+
+cudaError_t launch_expand_channels(const void* d_src, void* d_dst, size_t count, int src_channels, bool swap_rb, bool f32, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    if (src_channels != 3 && src_channels != 4) return cudaErrorInvalidValue;
+    const unsigned g = (unsigned)((count + 255) / 256);
+    if (f32) expand_channels_kernel<float><<<g, 256, 0, st>>>((const float*)d_src, (float*)d_dst, count, src_channels, swap_rb ? 1 : 0, 1.0f);
+    else expand_channels_kernel<uint8_t><<<g, 256, 0, st>>>((const uint8_t*)d_src, (uint8_t*)d_dst, count, src_channels, swap_rb ? 1 : 0, (uint8_t)255);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t* d_rough, size_t count, cudaStream_t st)
 {
     if (count == 0) return cudaSuccess;

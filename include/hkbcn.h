@@ -209,6 +209,45 @@ HKBCN_API int hkbcn_import_chain_dev(int device, int fmt, void* d_chain, void* d
 HKBCN_API int hkbcn_import_chain(int fmt, const void* src_level0, void* dst, uint32_t width, uint32_t height, uint32_t num_mips,
                                  const hkbcn_mip_config* cfg, uint32_t flags);
 
+/* ---- CreateImage from a raw image: format selection + channel pass + cascade + compress -------------------------------
+ * Replaces the compressed branch of Hk::CreateImage(RawImage const&, ImageMipmapConfig const*, IMAGE_STORAGE_FLAGS,
+ * IMAGE_IMPORT_FLAGS) (Image.cpp:866-1289).  raw_format: Hk::RAW_IMAGE_FORMAT values (RawImage.h:38-55); storage_flags:
+ * IMAGE_STORAGE_FLAGS (Image.h:221-226); import_flags: IMAGE_IMPORT_FLAGS (Image.h:546-553). */
+enum hkbcn_raw_format {
+    HKBCN_RAW_R8 = 1, HKBCN_RAW_R8_ALPHA = 2, HKBCN_RAW_RGB8 = 3, HKBCN_RAW_BGR8 = 4, HKBCN_RAW_RGBA8 = 5, HKBCN_RAW_BGRA8 = 6,
+    HKBCN_RAW_R32F = 7, HKBCN_RAW_R32_ALPHA_F = 8, HKBCN_RAW_RGB32F = 9, HKBCN_RAW_BGR32F = 10, HKBCN_RAW_RGBA32F = 11, HKBCN_RAW_BGRA32F = 12
+};
+/* storage_flags: HKBCN_STORAGE_NO_ALPHA / HKBCN_STORAGE_ALPHA_PREMULTIPLIED (below, with hkbcn_texture_desc) */
+enum { HKBCN_IMPORT_STORE_HDRI_AS_HALF_FLOAT = 1, HKBCN_IMPORT_USE_COMPRESSION = 2, HKBCN_IMPORT_ALLOW_HDRI_COMPRESSION = 4,
+       HKBCN_IMPORT_ASSUME_8BIT_RGB_IMAGES_ARE_SRGB = 8 };
+typedef struct hkbcn_image_plan {
+    int      format;          /* the block-compressed TEXTURE_FORMAT the reference picks (Image.cpp:878-1056); 0 = it stores the image uncompressed */
+    uint32_t storage_flags;   /* storage_flags as the reference leaves them (RGB sources add NO_ALPHA) */
+    int      src_channels;    /* channels of the raw image */
+    int      add_alpha;       /* a fourth channel of 255 / 1.0 is appended before compression */
+    int      swap_rb;         /* R and B are exchanged before compression (BGR / BGRA sources) */
+    uint32_t required_width;  /* the size the reference resamples to first (Image.cpp:1064-1068): closest power of two, at least 4, */
+    uint32_t required_height; /*   when mipmapped; the next multiple of 4 otherwise */
+} hkbcn_image_plan;
+/* host only.  mipmapped: whether a mip config will be passed.  Unknown raw formats: HKBCN_ERR_BAD_FORMAT. */
+HKBCN_API int hkbcn_plan_image(int raw_format, uint32_t width, uint32_t height, int mipmapped, uint32_t storage_flags,
+                               uint32_t import_flags, hkbcn_image_plan* plan);
+/* The whole call on device 0: raw image in (host, tightly packed), compressed ImageStorage payload out (host).  cfg != NULL:
+ * full mip chain (CalcNumMips levels) built on the device with cfg's edge mode and filter; alpha weighting follows the
+ * storage flags as in ImageStorage::GenerateMipmaps (Image.cpp:767-774).  desc receives type / size / mips / format / flags
+ * for hkbcn_write_texture.  capacity: bytes available at dst (hkbcn_chain_bytes(plan.format, w, h, 1, mips) are needed).
+ * Returns HKBCN_ERR_UNSUPPORTED when the reference would not compress (plan.format == 0) or would first resample the image
+ * to plan.required_width x required_height (the general resampler, stbir upsampling included, stays on the CPU: §8f). */
+struct hkbcn_texture_desc;
+HKBCN_API int hkbcn_create_image(int raw_format, const void* src, uint32_t width, uint32_t height, const hkbcn_mip_config* cfg,
+                                 uint32_t storage_flags, uint32_t import_flags, struct hkbcn_texture_desc* desc, void* dst,
+                                 size_t capacity);
+/* Replaces Hk::CreateRoughnessMap(pRoughnessMap, Width, Height, bUseCompression = true, bMipmapped, edge mode, filter)
+ * (Image.cpp:2399-2456): R8 in, BC4 chain out.  Sizes the reference refuses (not a power of two / multiple of 4) return
+ * HKBCN_ERR_BAD_ARG with its message. */
+HKBCN_API int hkbcn_create_roughness_map(const uint8_t* roughness, uint32_t width, uint32_t height, int mipmapped, int edge_mode,
+                                         int filter, struct hkbcn_texture_desc* desc, void* dst, size_t capacity);
+
 /* ---- batch API: independent surfaces sharded over the selected GPUs ---------
  * No collective: each job is sent whole to one GPU (greedy by pixel-cost), results land
  * directly in the caller's dst ("host gather").  Replaces one-process-per-texture use of
@@ -343,7 +382,8 @@ HKBCN_API void hkbcn_free_pinned(void* p);
  * in ONE file-scope __device__ array of HKBCN_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit;
  * the call runs no cudaMalloc / cudaFree / cudaHostAlloc and creates no stream or event.  Consequences:
  *   - hkbcn_init must have been called (it allocates streams and tables): otherwise HKBCN_ERR_NOT_INIT;
- *   - 256 + source bytes (rounded up to 256) + block bytes must fit: 1024 x 1024 RGBA8 -> BC7 or 512 x 512 RGBA32F -> BC6H
+ *   - 256 + source bytes (rounded up to 256) + block bytes (+ for BC7 a work list of 4 bytes per block) must fit:
+ *     1024 x 1024 RGBA8 -> BC7 or 512 x 512 RGBA32F -> BC6H
  *     do; anything larger is refused with HKBCN_ERR_BAD_ARG and a message that names both sizes -- use hkbcn_compress;
  *   - all calls on one device share the array, which keeps the previous call's contents: the counters are cleared at the
  *     start of each call, and calls from several threads are serialised on a per-device mutex.  Work that reaches the array
