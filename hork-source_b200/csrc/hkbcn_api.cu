@@ -1844,11 +1844,12 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                 int rc;
                 const int codec = codec_of(j.fmt);
                 if (codec < 0) { set_err("bad format %d", j.fmt); return HKBCN_ERR_BAD_FORMAT; }
-                const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
+                const bool prebuilt = (j.flags & HKBCN_FLAG_SRC_CHAIN) != 0; // the caller's own chain: upload all of it, generate nothing
+                const uint32_t mips = (j.generate_mips || prebuilt) ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
                 if ((rc = check_chain_dims(j.width, j.height, mips)) != HKBCN_OK) return rc;
                 if (!j.src_level0) { set_err("null source"); return HKBCN_ERR_BAD_ARG; }
                 const size_t sbytes = chain_src_bytes(codec, j.flags, j.width, j.height, mips);
-                const size_t l0 = (size_t)j.width * j.height * src_bpp(codec, j.flags);
+                const size_t l0 = prebuilt ? sbytes : (size_t)j.width * j.height * src_bpp(codec, j.flags);
                 const size_t dbytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips);
                 CK(cudaSetDevice(D->id));
                 if (!S.st) CK(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking));
@@ -1872,7 +1873,7 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                 if (f.staged && (rc = grow_pinned(&S.h_dst, &S.hdc, dbytes)) != HKBCN_OK) return rc;
                 // level 0 only crosses PCIe -- or nothing does, when the source was produced on this GPU (HKBCN_FLAG_SRC_DEVICE)
                 CK(cudaMemcpyAsync(S.d_src, hsrc, l0, src_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, S.st));
-                if (mips > 1 && (rc = generate_mips_on(D, j.fmt, S.d_src, j.width, j.height, mips, &j.mip, j.flags, S.st)) != HKBCN_OK) return rc;
+                if (mips > 1 && !prebuilt && (rc = generate_mips_on(D, j.fmt, S.d_src, j.width, j.height, mips, &j.mip, j.flags, S.st)) != HKBCN_OK) return rc;
                 EncodeParams P;
                 if ((rc = build_chain(P, codec, j.flags, S.d_src, S.d_dst, j.width, j.height, mips)) != HKBCN_OK) return rc;
                 if ((rc = launch_encode(D, j.fmt, codec, P, S.st)) != HKBCN_OK) return rc;

@@ -76,6 +76,8 @@ enum {
     HKBCN_FLAG_LEVEL_MASK  = 31u << 4,
     HKBCN_FLAG_SRC_DEVICE  = 1u << 17, /* hkbcn_import_batch: src_level0 is DEVICE memory on the GPU hkbcn_plan_import_batch assigns the
                                           job to (sources produced on the device never cross PCIe); the default is host memory */
+    HKBCN_FLAG_SRC_CHAIN   = 1u << 18, /* hkbcn_import_batch: src_level0 holds the whole uncompressed chain (hkbcn_chain_src_bytes() bytes, e.g. built
+                                          by the caller's own cascade): every level is uploaded and encoded, no mips are generated */
     HKBCN_FLAG_SKIP_EXISTING = 1u << 16 /* hkbcn_import_batch: leave a job alone (status HKBCN_SKIPPED) when its out_path already holds a
                                            complete .texture of the job's format, size and mip count -- re-running an interrupted
                                            batch only does what is missing (files are written to a temporary name and renamed) */
