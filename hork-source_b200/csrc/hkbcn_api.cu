@@ -745,8 +745,9 @@ static void set_tile_taps(ResizeParams& P, const Device::Taps& tx, const Device:
     for (int k = 0; k < 8; k++) { P.ux[k] = tx.u[k]; P.uy[k] = ty.u[k]; }
 }
 
+// slices > 1: d_chain is in ImageStorage order (all slices of level 0, then of level 1, ...) and every slice runs its own cascade
 static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint32_t h, uint32_t mips, const hkbcn_mip_config* cfg,
-                            uint32_t flags, cudaStream_t st)
+                            uint32_t flags, cudaStream_t st, uint32_t slices = 1)
 {
     const int codec = codec_of(fmt);
     if (codec < 0) { set_err("bad format %d", fmt); return HKBCN_ERR_BAD_FORMAT; }
@@ -763,7 +764,7 @@ static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint3
     uint8_t* cur = (uint8_t*)d_chain;
     for (uint32_t i = 1; i < mips; i++) {
         const uint32_t iw = mip_dim(w, i - 1), ih = mip_dim(h, i - 1), ow = mip_dim(w, i), oh = mip_dim(h, i);
-        uint8_t* next = cur + (size_t)iw * ih * bpp;
+        uint8_t* next = cur + (size_t)iw * ih * bpp * slices;
         Device::Taps tx, ty;
         int rc;
         if ((rc = get_taps(D, (int)iw, (int)ow, filter, edge, tx)) != HKBCN_OK) return rc;
@@ -777,9 +778,13 @@ static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint3
         P.weight = (has_alpha && !(cfg && cfg->alpha_premultiplied)) ? 1 : 0;
         P.srgb = srgb ? 1 : 0;
         set_tile_taps(P, tx, ty);
-        cudaError_t e = launch_mip_resize(P, channels, f32, st);
-        if (e != cudaSuccess) { set_err("mip resize launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
-        g_launches.fetch_add(1, std::memory_order_relaxed);
+        for (uint32_t sl = 0; sl < slices; sl++) {
+            P.src = cur + (size_t)sl * iw * ih * bpp;
+            P.dst = next + (size_t)sl * ow * oh * bpp;
+            cudaError_t e = launch_mip_resize(P, channels, f32, st);
+            if (e != cudaSuccess) { set_err("mip resize launch failed: %s", cudaGetErrorString(e)); return HKBCN_ERR_CUDA; }
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+        }
         cur = next;
     }
     return HKBCN_OK;
@@ -1730,7 +1735,7 @@ int hkbcn_plan_import_batch(const hkbcn_import_job* jobs, size_t n_jobs, int n_g
     std::vector<hkbcn_job> plain(n_jobs);
     for (size_t i = 0; i < n_jobs; i++) {
         if (codec_of(jobs[i].fmt) < 0) { set_err("job %zu: bad format %d", i, jobs[i].fmt); return HKBCN_ERR_BAD_FORMAT; }
-        plain[i] = hkbcn_job{jobs[i].fmt, jobs[i].width, jobs[i].height, jobs[i].flags, nullptr, nullptr, 0};
+        plain[i] = hkbcn_job{jobs[i].fmt, jobs[i].width, jobs[i].height * std::max(1u, jobs[i].slices), jobs[i].flags, nullptr, nullptr, 0};
     }
     plan_batch(plain.data(), n_jobs, n_gpus, device_of_job);
     return HKBCN_OK;
@@ -1749,9 +1754,10 @@ static bool complete_texture_exists(const hkbcn_import_job& j)
     hkbcn_texture_desc d;
     size_t n = 0;
     if (hkbcn_read_texture(j.out_path, &d, nullptr, 0, &n) != HKBCN_OK) return false;
-    const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
-    if (d.width != j.width || d.height != j.height || d.fmt != j.fmt || d.num_mips != mips) return false;
-    if (n != hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips)) return false;
+    const uint32_t mips = (j.generate_mips || (j.flags & HKBCN_FLAG_SRC_CHAIN)) ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
+    const uint32_t slices = std::max(1u, j.slices);
+    if (d.width != j.width || d.height != j.height || d.fmt != j.fmt || d.num_mips != mips || d.depth != slices) return false;
+    if (n != hkbcn_chain_bytes(j.fmt, j.width, j.height, slices, mips)) return false;
     FILE* f = fopen(j.out_path, "rb");
     if (!f) return false;
     fseek(f, 0, SEEK_END);
@@ -1771,7 +1777,7 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
     // plan as hkbcn_compress_batch does (pixel count x per-format weight; a mip chain adds a third everywhere alike)
     std::vector<hkbcn_job> plain(n_jobs);
     for (size_t i = 0; i < n_jobs; i++) {
-        plain[i] = hkbcn_job{jobs[i].fmt, jobs[i].width, jobs[i].height, jobs[i].flags, nullptr, nullptr, 0};
+        plain[i] = hkbcn_job{jobs[i].fmt, jobs[i].width, jobs[i].height * std::max(1u, jobs[i].slices), jobs[i].flags, nullptr, nullptr, 0};
         jobs[i].status = HKBCN_OK;
     }
     std::vector<int> assign(n_jobs);
@@ -1799,7 +1805,8 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                 queue.pop_front();
             }
             hkbcn_import_job& j = jobs[d.idx];
-            hkbcn_texture_desc desc{HKBCN_TEXTURE_2D, j.width, j.height, 1, d.mips, j.fmt,
+            const uint32_t nsl = std::max(1u, j.slices);
+            hkbcn_texture_desc desc{nsl == 1 ? HKBCN_TEXTURE_2D : nsl == 6 ? HKBCN_TEXTURE_CUBE : HKBCN_TEXTURE_2D_ARRAY, j.width, j.height, nsl, d.mips, j.fmt,
                                     (j.mip.no_alpha ? (uint32_t)HKBCN_STORAGE_NO_ALPHA : 0u) | (j.mip.alpha_premultiplied ? (uint32_t)HKBCN_STORAGE_ALPHA_PREMULTIPLIED : 0u)};
             const int wrc = hkbcn_write_texture(j.out_path, &desc, d.data, d.bytes);
             if (wrc) {
@@ -1848,9 +1855,11 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                 const uint32_t mips = (j.generate_mips || prebuilt) ? hkbcn_calc_num_mips(j.width, j.height) : 1u;
                 if ((rc = check_chain_dims(j.width, j.height, mips)) != HKBCN_OK) return rc;
                 if (!j.src_level0) { set_err("null source"); return HKBCN_ERR_BAD_ARG; }
-                const size_t sbytes = chain_src_bytes(codec, j.flags, j.width, j.height, mips);
-                const size_t l0 = prebuilt ? sbytes : (size_t)j.width * j.height * src_bpp(codec, j.flags);
-                const size_t dbytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, 1, mips);
+                const uint32_t slices = std::max(1u, j.slices);
+                if (slices > 1 && j.width != j.height && slices == 6) { set_err("cube faces must be square"); return HKBCN_ERR_BAD_ARG; }
+                const size_t sbytes = chain_src_bytes(codec, j.flags, j.width, j.height, mips, slices);
+                const size_t l0 = prebuilt ? sbytes : (size_t)j.width * j.height * src_bpp(codec, j.flags) * slices;
+                const size_t dbytes = hkbcn_chain_bytes(j.fmt, j.width, j.height, slices, mips);
                 CK(cudaSetDevice(D->id));
                 if (!S.st) CK(cudaStreamCreateWithFlags(&S.st, cudaStreamNonBlocking));
                 if ((rc = grow(&S.d_src, &S.dsc, sbytes)) != HKBCN_OK) return rc;
@@ -1873,9 +1882,9 @@ int hkbcn_import_batch(hkbcn_import_job* jobs, size_t n_jobs)
                 if (f.staged && (rc = grow_pinned(&S.h_dst, &S.hdc, dbytes)) != HKBCN_OK) return rc;
                 // level 0 only crosses PCIe -- or nothing does, when the source was produced on this GPU (HKBCN_FLAG_SRC_DEVICE)
                 CK(cudaMemcpyAsync(S.d_src, hsrc, l0, src_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, S.st));
-                if (mips > 1 && !prebuilt && (rc = generate_mips_on(D, j.fmt, S.d_src, j.width, j.height, mips, &j.mip, j.flags, S.st)) != HKBCN_OK) return rc;
+                if (mips > 1 && !prebuilt && (rc = generate_mips_on(D, j.fmt, S.d_src, j.width, j.height, mips, &j.mip, j.flags, S.st, slices)) != HKBCN_OK) return rc;
                 EncodeParams P;
-                if ((rc = build_chain(P, codec, j.flags, S.d_src, S.d_dst, j.width, j.height, mips)) != HKBCN_OK) return rc;
+                if ((rc = build_chain(P, codec, j.flags, S.d_src, S.d_dst, j.width, j.height, mips, slices)) != HKBCN_OK) return rc;
                 if ((rc = launch_encode(D, j.fmt, codec, P, S.st)) != HKBCN_OK) return rc;
                 CK(cudaMemcpyAsync(f.staged ? S.h_dst : f.out, S.d_dst, dbytes, cudaMemcpyDeviceToHost, S.st));
                 f.idx = (long)idx;

@@ -270,20 +270,19 @@ int run_cubemap(const std::vector<std::string>& t, uint32_t mask)
         memcpy(packed + (size_t)f * face_bytes, one, face_bytes);
         hkbcn_free_pinned(one);
     }
-    const size_t nbytes = hkbcn_chain_bytes(fmt, w, w, 6, 1);
-    std::vector<uint8_t> blocks(nbytes);
+    // one cube job through the batch entry point: six slices, one mip, IMAGE_STORAGE_NO_ALPHA; the library compresses the six
+    // faces in one launch and writes the TEXTURE_CUBE storage
     printf("Importing texture %s...\n", out.c_str());
     const auto t0 = std::chrono::steady_clock::now();
-    if (hkbcn_compress_slices(fmt, packed, blocks.data(), w, w, 6, 1, 0) != HKBCN_OK) { fprintf(stderr, "import failed: %s\n", hkbcn_last_error()); return -1; }
-    hkbcn_texture_desc d;
-    memset(&d, 0, sizeof(d));
-    d.type = HKBCN_TEXTURE_CUBE;
-    d.width = d.height = w;
-    d.depth = 6;
-    d.num_mips = 1;
-    d.fmt = fmt;
-    d.storage_flags = HKBCN_STORAGE_NO_ALPHA;
-    if (hkbcn_write_texture(out.c_str(), &d, blocks.data(), nbytes) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+    hkbcn_import_job job;
+    memset(&job, 0, sizeof(job));
+    job.fmt = fmt;
+    job.width = job.height = w;
+    job.slices = 6;
+    job.mip.no_alpha = 1;
+    job.src_level0 = packed;
+    job.out_path = out.c_str();
+    if (hkbcn_import_batch(&job, 1) != HKBCN_OK) { fprintf(stderr, "import failed: %s\n", hkbcn_last_error()); return -1; }
     const double s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     printf("cubemap 6 x %u^2, %.1f Mpix in %.3f s: %.2f Mpix/s including upload, download and the file write\n", w, 6.0 * w * w / 1e6, s,
            6.0 * w * w / 1e6 / s);

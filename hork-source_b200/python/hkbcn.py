@@ -69,7 +69,7 @@ class TextureDesc(C.Structure):
 
 class ImportJob(C.Structure):
     _fields_ = [("fmt", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("generate_mips", C.c_int), ("mip", MipConfig),
-                ("flags", C.c_uint32), ("src_level0", C.c_void_p), ("out_path", C.c_char_p), ("dst", C.c_void_p), ("status", C.c_int)]
+                ("flags", C.c_uint32), ("src_level0", C.c_void_p), ("out_path", C.c_char_p), ("dst", C.c_void_p), ("status", C.c_int), ("slices", C.c_uint32)]
 
 
 _lib = None

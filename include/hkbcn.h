@@ -277,6 +277,7 @@ HKBCN_API int hkbcn_plan_batch(const hkbcn_job* jobs, size_t n_jobs, int n_gpus,
  * (Core/BinaryStream.h:408-412).  30 header bytes.  These three entry points are host-only (no device needed). */
 #define HKBCN_TEXTURE_HEADER_BYTES 30
 #define HKBCN_TEXTURE_2D 2            /* TEXTURE_TYPE (Image.h:40-51) */
+#define HKBCN_TEXTURE_2D_ARRAY 3
 #define HKBCN_TEXTURE_CUBE 5
 #define HKBCN_STORAGE_NO_ALPHA 1      /* IMAGE_STORAGE_FLAGS (Image.h:221-226) */
 #define HKBCN_STORAGE_ALPHA_PREMULTIPLIED 2
@@ -306,6 +307,11 @@ typedef struct hkbcn_import_job {
     const char*      out_path;        /* .texture file to write; NULL = keep the chain in `dst` only */
     void*            dst;             /* optional host buffer for the compressed chain (hkbcn_chain_bytes), may be NULL */
     int              status;          /* out */
+    uint32_t         slices;          /* 0 or 1: a 2D texture.  6: a cube map (TEXTURE_CUBE: CubemapImporter, Tools/CubemapImporter/Main.cpp:58-145 ->
+                                         LoadSkyboxImages, Image.cpp:1918-2040), any other count: a 2D array.  src_level0 then holds the slices'
+                                         level 0 back to back, each slice gets its own cascade when generate_mips is set (ImageStorage::
+                                         GenerateMipmaps slice by slice, Image.cpp:806-819), and the payload is in ImageStorage order: all slices
+                                         of level 0, then of level 1, ... */
 } hkbcn_import_job;
 /* Jobs are sharded over the selected GPUs as in hkbcn_compress_batch (whole textures, no collective); each GPU's worker runs
  * upload -> mip cascade -> encode -> download, and the files are written by a separate thread behind it. */

@@ -3,6 +3,8 @@ CreateImage, Hork/Image/Image.cpp:1700-1803 -> AssetUtils::CreateTexture), as on
 bytes the reference's writer would produce around the chain (oracle restatement in test_texture_file_cpu.py), the
 chain must be hkbcn_import_chain's, and where the whole pipeline is deterministic integer work (BC4 / BC5: linear uint8
 cascade, bit-exact encoders) the file must equal the one built from the reference's own stbir + rgbcx chain."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -287,3 +289,43 @@ def test_import_batch_device_sources_and_plan():
         assert np.array_equal(got, hkbcn.import_chain(fmt, img, w, h, L.hkbcn_calc_num_mips(w, h)))
     busy = (C.c_double * 8)()
     assert L.hkbcn_batch_stats(busy, 8) == nd and busy[0] > 0
+
+
+def test_import_batch_sliced_jobs(tmp_path):
+    """hkbcn_import_job.slices: a cube map (six faces, one mip: CubemapImporter) and a 2D array with per-slice cascades next to
+    a plain 2D job in one batch; payloads in ImageStorage order (all slices of level 0, then of level 1, ...), files typed
+    TEXTURE_CUBE / TEXTURE_2D_ARRAY with depth = slice count"""
+    L = hkbcn.lib()
+    BC1, BC6U, BC7 = 54, 64, 66
+    w = 64
+    faces = np.stack([synth.sky_rgba32f(w, w, 0x600 + f, f).reshape(w, w, 4) for f in range(6)])
+    layers = np.stack([synth.albedo_rgba8(w, w, 0x610 + s, "mask").reshape(w, w, 4) for s in range(3)])
+    flat = synth.albedo_rgba8(w, w, 0x620).reshape(w, w, 4)
+    mips = L.hkbcn_calc_num_mips(w, w)
+    paths = [str(tmp_path / n).encode() for n in ("cube.texture", "array.texture", "flat.texture")]
+    jobs = (hkbcn.ImportJob * 3)()
+    for j, (fmt, src, gen, slices, noa) in enumerate(((BC6U, faces, 0, 6, 1), (BC7, layers, 1, 3, 0), (BC1, flat, 1, 0, 0))):
+        jobs[j].fmt, jobs[j].width, jobs[j].height, jobs[j].generate_mips, jobs[j].slices = fmt, w, w, gen, slices
+        jobs[j].mip.no_alpha = noa
+        jobs[j].src_level0 = np.ascontiguousarray(src).ctypes.data_as(C.c_void_p)
+        jobs[j].out_path = paths[j]
+    keep = [faces, layers, flat]  # the arrays must outlive the call
+    hkbcn.check(L.hkbcn_import_batch(jobs, 3))
+    assert [jobs[j].status for j in range(3)] == [0, 0, 0] and keep
+    # cube: six faces through the reference's CompressBC6h, one after another
+    d, payload = hkbcn.read_texture(paths[0].decode())
+    assert (d.type, d.depth, d.num_mips, d.fmt, d.storage_flags) == (5, 6, 1, BC6U, 1)
+    want = np.concatenate([refshim.compress(BC6U, faces[f], w, w, lib=refshim.ref0()) for f in range(6)])
+    assert np.array_equal(payload, want)
+    # array: every slice's own chain (device cascade = stbir for this linear format), interleaved level by level
+    d, payload = hkbcn.read_texture(paths[1].decode())
+    assert (d.type, d.depth, d.num_mips, d.fmt) == (3, 3, mips, BC7)
+    chains = [hkbcn.import_chain(BC7, layers[s], w, w, mips) for s in range(3)]
+    off, parts = 0, []
+    for i in range(mips):
+        n = max(w >> i, 4) ** 2
+        parts += [c[off: off + n] for c in chains]
+        off += n
+    assert np.array_equal(payload, np.concatenate(parts))
+    d, payload = hkbcn.read_texture(paths[2].decode())
+    assert (d.type, d.depth) == (2, 1) and np.array_equal(payload, hkbcn.import_chain(BC1, flat, w, w, mips))
