@@ -27,8 +27,11 @@
 namespace hkbcn {
 namespace bc6h {
 
-constexpr int COOP_TB = 8;          // blocks per warp tile
-constexpr int COOP_MAX_TASKS = 192; // candidates per round: TB blocks x 3 precision groups x 8 ranks
+#ifndef BC6_COOP_TB
+#define BC6_COOP_TB 8
+#endif
+constexpr int COOP_TB = BC6_COOP_TB;           // blocks per warp tile
+constexpr int COOP_MAX_TASKS = COOP_TB * 24;  // candidates per round: TB blocks x 3 precision groups x 8 ranks
 
 // precision groups of the two-region modes (modes of one group share RGBAPrec[0][0] and the transform flag)
 #ifdef HKBCN_HOST_EMU
@@ -181,9 +184,12 @@ template <int N, bool SIGNED> struct OptChan {
     int          phase, do_b;
     float        err0;
     int          val_a;
-    int          cur, cand, beststep;
+    int          cur, cand;      // the perturbed endpoint as it stands at this step size, the candidate on trial
+    int          cur_u, cand_u;  // ... unquantised: carried along so that no step of the search unquantises a value twice
+    int          best_c, best_u; // the best candidate of this step size so far (cur itself while neither sign has improved)
+    int          val_a_u;
     int          t;       // index of the current trial within the perturbation: step = 2^(prec-1-t/2), sign = t odd ? + : -
-    bool         improved, trial_valid;
+    bool         trial_valid;
     float        min_err;
     f2           pal1[N / 2], pal2[N / 2]; // palettes of the channels at rest (committed endpoints), entries (2q, 2q + 1) as float
                                            // pairs: integers < 2^16, exact
@@ -211,10 +217,11 @@ template <int N, bool SIGNED> struct OptChan {
     {
         do_b = db;
         cur = db ? b : a;
+        cur_u = db ? ub : ua;
+        best_c = cur;
+        best_u = cur_u;
         min_err = opt_err;
         t = -1;
-        improved = false;
-        beststep = 0;
         trial_valid = false;
     }
     // e: the region's committed endpoints (all three channels), err: their error
@@ -246,15 +253,12 @@ template <int N, bool SIGNED> struct OptChan {
         phase = 0;
         start_perturb(0);
     }
-    __device__ __forceinline__ void commit(int db, int v, float err)
+    __device__ __forceinline__ void commit(int db, int v, int vu, float err)
     {
-        if (db) {
-            b = v;
-            ub = unq(v);
-        } else {
-            a = v;
-            ua = unq(v);
-        }
+        a = db ? a : v;
+        ua = db ? ua : vu;
+        b = db ? v : b;
+        ub = db ? vu : ub;
         opt_err = err;
     }
     __device__ __forceinline__ void perturb_end()
@@ -263,51 +267,56 @@ template <int N, bool SIGNED> struct OptChan {
         if (phase == 0) {
             err0 = err;
             val_a = cur;
+            val_a_u = cur_u;
             phase = 1;
             start_perturb(1);
         } else if (phase == 1) {
             if (err0 < err) {
                 if (err0 >= opt_err) { busy = false; return; }
-                commit(0, val_a, err0);
+                commit(0, val_a, val_a_u, err0);
                 phase = 2;
                 start_perturb(1);
             } else {
                 if (err >= opt_err) { busy = false; return; }
-                commit(1, cur, err);
+                commit(1, cur, cur_u, err);
                 phase = 2;
                 start_perturb(0);
             }
         } else {
             if (err >= opt_err) { busy = false; return; }
-            commit(do_b, cur, err);
+            commit(do_b, cur, cur_u, err);
             start_perturb(1 - do_b);
         }
     }
     // The previous trial (if any) is over: account for it and move to the next candidate -- ONE transition per call, written
-    // as straight-line selects: a candidate outside [0, 2^prec) leaves the lane without a trial until the next call, and only
-    // the end of a perturbation (every 2 * prec calls) branches.  The warp's iteration is this plus one texel evaluation.
+    // as straight-line selects (the warp runs this body every iteration for the few lanes that are between trials, so every
+    // instruction here is paid by all 32): only the end of a perturbation (every 2 * prec calls) branches.  A "-" candidate
+    // below zero is skipped on the spot (its "+" twin shares the step and the state); a "+" candidate above the range leaves the
+    // lane without a trial until the next call.
     __device__ __forceinline__ void advance()
     {
         const bool better = trial_valid && tot < min_err;
-        improved = improved || better;
         min_err = better ? tot : min_err;
-        beststep = better ? cand - cur : beststep;
+        best_c = better ? cand : best_c;
+        best_u = better ? cand_u : best_u;
         trial_valid = false;
         t++;
-        if (!(t & 1)) { // both signs of a step have been tried (nothing to do before the first step: improved is false)
-            cur += improved ? beststep : 0;
-            improved = false;
+        if (!(t & 1)) { // both signs of a step have been tried: the endpoint moves to the better one (or stays)
+            cur = best_c;
+            cur_u = best_u;
         }
         if (t == 2 * prec) {
             perturb_end();
             return;
         }
         const int step = 1 << (prec - 1 - (t >> 1));
+        const bool skip = !(t & 1) && cur < step; // cur - step < 0: straight to cur + step
+        t += skip ? 1 : 0;
         cand = cur + ((t & 1) ? step : -step);
         // an out-of-range candidate is skipped; an empty trial (error to beat already 0) would total 0, not below min_err
         const bool ok = (unsigned)cand < (1u << prec) && min_err > 0.0f;
-        const int uc = unq(cand);
-        const int u0 = do_b ? ua : uc, u1 = do_b ? uc : ub;
+        cand_u = unq(cand);
+        const int u0 = do_b ? ua : cand_u, u1 = do_b ? cand_u : ub;
         base = u0 * 64 + 32;
         delta = u1 - u0;
         tot = 0.0f;

@@ -27,8 +27,11 @@ __device__ bc6h::Layout g_bc6h_enc_layout;
 #define BC6E_CTAS_PER_SM 12 // resident one-warp CTAs per SM
 #endif
 #ifndef BC6E_MIN_CTAS
-#define BC6E_MIN_CTAS 12    // launch bound: 12 one-warp CTAs per SM = 168 registers per thread.  Measured on a 1024^2 face:
-                            // 128 registers / 16 warps 57 ms, 168 / 12 warps 48 ms, 255 / 8 warps 55 ms
+#define BC6E_MIN_CTAS 12    // launch bound: 12 one-warp CTAs per SM = 168 registers per thread, which is also what 17.8 KB of shared
+                            // memory per CTA allows.  Measured on a 1024^2 face: 128 registers 57 ms (spills, still 12 resident),
+                            // 168 registers 43 ms, 255 registers / 8 warps 55 ms.  Tiles of 4 blocks (9.3 KB, -DBC6_COOP_TB=4) make
+                            // room for more: 12 / 14 / 16 warps 46.7 / 45.7 / 43.6 ms -- the smaller tile's worse balance of the
+                            // optimise items costs what the four extra warps bring
 #endif
 constexpr int BC6_NT = 32;
 constexpr int BC6_TB = bc6h::COOP_TB;
@@ -157,10 +160,8 @@ __device__ __noinline__ void optimise_pass(Bc6Smem& S, int nSurv, const int CH, 
                 continue;
             }
         }
-        // a lane whose trial has ended moves to its next candidate; a second attempt when that one was out of range (about
-        // one candidate in three is: endpoints near 0 or 2^prec - 1 under the wide steps), so it does not sit out the evaluation
-#pragma unroll 1
-        for (int k = 0; k < 2 && M.busy && !M.in_trial; k++) M.advance();
+        // a lane whose trial has ended moves to its next candidate
+        if (M.busy && !M.in_trial) M.advance();
         if (M.in_trial) M.eval_texel();
     }
     __syncwarp(); // the next pass reads what this one wrote
