@@ -792,8 +792,8 @@ static int generate_mips_on(Device* D, int fmt, void* d_chain, uint32_t w, uint3
 
 int hkbcn_mip_taps(int in_size, int out_size, int filter, int edge_mode, int* idx, float* weight, int capacity, int* taps_per_output)
 {
-    if (in_size <= 0 || out_size <= 0 || out_size > in_size || filter < 1 || filter > 5 || edge_mode < 1 || edge_mode > 4 || !taps_per_output) {
-        set_err("bad arguments (downsampling only: out_size <= in_size)");
+    if (in_size <= 0 || out_size <= 0 || filter < 1 || filter > 5 || edge_mode < 1 || edge_mode > 4 || !taps_per_output) {
+        set_err("bad arguments");
         return HKBCN_ERR_BAD_ARG;
     }
     AxisTaps a;
@@ -949,29 +949,118 @@ int hkbcn_plan_image(int raw_format, uint32_t width, uint32_t height, int mipmap
     return HKBCN_OK;
 }
 
+static int raw_format_info(int raw_format, int* channels, bool* f32)
+{
+    switch (raw_format) {
+    case HKBCN_RAW_R8: *channels = 1; *f32 = false; return HKBCN_OK;
+    case HKBCN_RAW_R8_ALPHA: *channels = 2; *f32 = false; return HKBCN_OK;
+    case HKBCN_RAW_RGB8: case HKBCN_RAW_BGR8: *channels = 3; *f32 = false; return HKBCN_OK;
+    case HKBCN_RAW_RGBA8: case HKBCN_RAW_BGRA8: *channels = 4; *f32 = false; return HKBCN_OK;
+    case HKBCN_RAW_R32F: *channels = 1; *f32 = true; return HKBCN_OK;
+    case HKBCN_RAW_R32_ALPHA_F: *channels = 2; *f32 = true; return HKBCN_OK;
+    case HKBCN_RAW_RGB32F: case HKBCN_RAW_BGR32F: *channels = 3; *f32 = true; return HKBCN_OK;
+    case HKBCN_RAW_RGBA32F: case HKBCN_RAW_BGRA32F: *channels = 4; *f32 = true; return HKBCN_OK;
+    }
+    set_err("bad raw image format %d", raw_format);
+    return HKBCN_ERR_BAD_FORMAT;
+}
+
+// ResampleRawImage (Image.cpp:2188-2243) on device pointers of the current device
+static int resample_on(Device* D, int raw_format, const void* d_src, uint32_t w, uint32_t h, const hkbcn_resample_params& rp, void* d_dst, cudaStream_t st)
+{
+    int ch = 0;
+    bool f32 = false;
+    int rc = raw_format_info(raw_format, &ch, &f32);
+    if (rc) return rc;
+    if (!w || !h || !rp.scaled_width || !rp.scaled_height) { set_err("ResampleRawImage: invalid size"); return HKBCN_ERR_BAD_ARG; }
+    const int eh = rp.edge_h ? rp.edge_h : 3, ev = rp.edge_v ? rp.edge_v : 3, fh = rp.filter_h ? rp.filter_h : 5, fv = rp.filter_v ? rp.filter_v : 5;
+    if (eh < 1 || eh > 4 || ev < 1 || ev > 4 || fh < 1 || fh > 5 || fv < 1 || fv > 5) { set_err("bad edge mode / filter"); return HKBCN_ERR_BAD_ARG; }
+    const bool srgb = (rp.flags & HKBCN_RESAMPLE_COLORSPACE_SRGB) != 0, has_alpha = (rp.flags & HKBCN_RESAMPLE_HAS_ALPHA) != 0;
+    if (f32 && srgb) { set_err("float images in the sRGB colour space are not supported"); return HKBCN_ERR_UNSUPPORTED; }
+    Device::Taps tx, ty;
+    if ((rc = get_taps(D, (int)w, (int)rp.scaled_width, fh, eh, tx)) != HKBCN_OK) return rc;
+    if ((rc = get_taps(D, (int)h, (int)rp.scaled_height, fv, ev, ty)) != HKBCN_OK) return rc;
+    ResizeParams P;
+    memset(&P, 0, sizeof(P));
+    P.src = (const uint8_t*)d_src; P.dst = (uint8_t*)d_dst;
+    P.ix = tx.idx; P.wx = tx.w; P.iy = ty.idx; P.wy = ty.w;
+    P.lut = srgb ? D->lut_srgb : D->lut_lin;
+    P.in_w = (int)w; P.in_h = (int)h; P.out_w = (int)rp.scaled_width; P.out_h = (int)rp.scaled_height; P.Tx = tx.T; P.Ty = ty.T;
+    P.alpha = has_alpha ? ch - 1 : -1;
+    P.weight = (has_alpha && !(rp.flags & HKBCN_RESAMPLE_ALPHA_PREMULTIPLIED)) ? 1 : 0;
+    P.srgb = srgb ? 1 : 0;
+    CK(launch_resample_general(P, ch, f32, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return HKBCN_OK;
+}
+
+int hkbcn_resample_raw_image_dev(int device, int raw_format, const void* d_src, uint32_t width, uint32_t height, const hkbcn_resample_params* params,
+                                 void* d_dst, void* stream)
+{
+    Range nvtx_("hkbcn_resample_raw_image_dev");
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = dev_at(device);
+    if (!D) { set_err("bad device index %d", device); return HKBCN_ERR_BAD_ARG; }
+    if (!d_src || !d_dst || !params) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    CK(cudaSetDevice(D->id));
+    return resample_on(D, raw_format, d_src, width, height, *params, d_dst, (cudaStream_t)stream);
+}
+
+int hkbcn_resample_raw_image(int raw_format, const void* src, uint32_t width, uint32_t height, const hkbcn_resample_params* params, void* dst)
+{
+    Range nvtx_("hkbcn_resample_raw_image");
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (!src || !dst || !params) { set_err("null pointer"); return HKBCN_ERR_BAD_ARG; }
+    int ch = 0;
+    bool f32 = false;
+    if ((rc = raw_format_info(raw_format, &ch, &f32)) != HKBCN_OK) return rc;
+    const size_t texel = (size_t)ch * (f32 ? 4 : 1);
+    const size_t sbytes = (size_t)width * height * texel, dbytes = (size_t)params->scaled_width * params->scaled_height * texel;
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(D->d_src, src, sbytes, cudaMemcpyHostToDevice, D->stream));
+    if ((rc = resample_on(D, raw_format, D->d_src, width, height, *params, D->d_dst, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(dst, D->d_dst, dbytes, cudaMemcpyDeviceToHost, D->stream));
+    CK(cudaStreamSynchronize(D->stream));
+    return HKBCN_OK;
+}
+
 // raw texels (host) -> level 0 in the encoder's source layout -> device cascade -> encode -> host; device 0
+// (w, h): the size of the storage; (sw, sh): the size of the raw image -- resampled first when they differ (rs, raw_format)
 static int create_image_on(Device* D, const hkbcn_image_plan& plan, const void* src, uint32_t w, uint32_t h, uint32_t mips, const hkbcn_mip_config* cfg,
-                           void* dst)
+                           void* dst, uint32_t sw = 0, uint32_t sh = 0, int raw_format = 0, const hkbcn_resample_params* rs = nullptr)
 {
     const int fmt = plan.format, codec = codec_of(fmt);
     const bool f32 = codec == C_BC6H;
     const size_t texel = f32 ? 4 : 1;
     const bool pass = plan.add_alpha || plan.swap_rb; // the channel pass is needed
-    const size_t raw_bytes = (size_t)w * h * plan.src_channels * texel;
+    const bool scale = rs != nullptr;
+    if (!scale) { sw = w; sh = h; }
+    const size_t raw_bytes = (size_t)w * h * plan.src_channels * texel, in_bytes = (size_t)sw * sh * plan.src_channels * texel;
     const size_t sbytes = chain_src_bytes(codec, 0, w, h, mips), dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
-    const size_t raw_off = (sbytes + 255) & ~(size_t)255;
+    // d_src: [ the chain | the raw image at the storage's size (channel pass) | the raw image as handed over (resample) ]
+    const size_t raw_off = (sbytes + 255) & ~(size_t)255, in_off = (raw_off + (pass ? raw_bytes : 0) + 255) & ~(size_t)255;
     std::lock_guard<std::mutex> lk(D->mu);
     CK(cudaSetDevice(D->id));
     int rc;
-    if ((rc = grow(&D->d_src, &D->src_cap, raw_off + (pass ? raw_bytes : 0))) != HKBCN_OK) return rc;
+    if ((rc = grow(&D->d_src, &D->src_cap, in_off + (scale ? in_bytes : 0))) != HKBCN_OK) return rc;
     if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
-    if (pass) {
-        uint8_t* d_raw = (uint8_t*)D->d_src + raw_off;
+    uint8_t* const d_raw = pass ? (uint8_t*)D->d_src + raw_off : (uint8_t*)D->d_src; // where the raw image at storage size goes
+    if (scale) {
+        uint8_t* d_in = (uint8_t*)D->d_src + in_off;
+        CK(cudaMemcpyAsync(d_in, src, in_bytes, cudaMemcpyHostToDevice, D->stream));
+        if ((rc = resample_on(D, raw_format, d_in, sw, sh, *rs, d_raw, D->stream)) != HKBCN_OK) return rc;
+    } else {
         CK(cudaMemcpyAsync(d_raw, src, raw_bytes, cudaMemcpyHostToDevice, D->stream));
+    }
+    if (pass) {
         CK(launch_expand_channels(d_raw, D->d_src, (size_t)w * h, plan.src_channels, plan.swap_rb != 0, f32, D->stream));
         g_launches.fetch_add(1, std::memory_order_relaxed);
-    } else {
-        CK(cudaMemcpyAsync(D->d_src, src, raw_bytes, cudaMemcpyHostToDevice, D->stream));
     }
     if (mips > 1 && (rc = generate_mips_on(D, fmt, D->d_src, w, h, mips, cfg, 0, D->stream)) != HKBCN_OK) return rc;
     EncodeParams P;
@@ -991,11 +1080,25 @@ int hkbcn_create_image(int raw_format, const void* src, uint32_t width, uint32_t
     if (rc) return rc;
     if (!src || !dst || !width || !height) { set_err("null pointer or empty image"); return HKBCN_ERR_BAD_ARG; }
     if (!plan.format) { set_err("the reference stores raw format %d uncompressed under these import flags: nothing to block-compress", raw_format); return HKBCN_ERR_UNSUPPORTED; }
-    if (plan.required_width != width || plan.required_height != height) {
-        set_err("the reference first resamples %u x %u to %u x %u (Image.cpp:1064-1096); the general resampler is not part of this path", width, height,
-                plan.required_width, plan.required_height);
-        return HKBCN_ERR_UNSUPPORTED;
+    // Image.cpp:1070-1093: the image goes to the required size first, with the mip config's edge mode and filter on both axes
+    const bool scale = plan.required_width != width || plan.required_height != height;
+    hkbcn_resample_params rs;
+    memset(&rs, 0, sizeof(rs));
+    if (scale) {
+        rs.edge_h = rs.edge_v = cfg && cfg->edge_mode ? cfg->edge_mode : 3;
+        rs.filter_h = rs.filter_v = cfg && cfg->filter ? cfg->filter : 5;
+        const bool srgb_fmt = plan.format == HKBCN_BC1_UNORM_SRGB || plan.format == HKBCN_BC3_UNORM_SRGB;
+        if (srgb_fmt) rs.flags |= HKBCN_RESAMPLE_COLORSPACE_SRGB;
+        if (plan.src_channels == 4 && !(plan.storage_flags & HKBCN_STORAGE_NO_ALPHA)) {
+            rs.flags |= HKBCN_RESAMPLE_HAS_ALPHA;
+            if (plan.storage_flags & HKBCN_STORAGE_ALPHA_PREMULTIPLIED) rs.flags |= HKBCN_RESAMPLE_ALPHA_PREMULTIPLIED;
+        }
+        rs.scaled_width = plan.required_width;
+        rs.scaled_height = plan.required_height;
     }
+    const uint32_t src_w = width, src_h = height;
+    width = plan.required_width;
+    height = plan.required_height;
     const uint32_t mips = cfg ? hkbcn_calc_num_mips(width, height) : 1;
     const size_t need = hkbcn_chain_bytes(plan.format, width, height, 1, mips);
     if (capacity < need) { set_err("dst holds %zu bytes, the storage needs %zu", capacity, need); return HKBCN_ERR_BAD_ARG; }
@@ -1004,7 +1107,7 @@ int hkbcn_create_image(int raw_format, const void* src, uint32_t width, uint32_t
     hkbcn_mip_config mc = cfg ? *cfg : hkbcn_mip_config{0, 0, 0, 0};
     mc.no_alpha = (plan.storage_flags & HKBCN_STORAGE_NO_ALPHA) ? 1 : 0;
     mc.alpha_premultiplied = (plan.storage_flags & HKBCN_STORAGE_ALPHA_PREMULTIPLIED) ? 1 : 0;
-    if ((rc = create_image_on(g_devs[0], plan, src, width, height, mips, &mc, dst)) != HKBCN_OK) return rc;
+    if ((rc = create_image_on(g_devs[0], plan, src, width, height, mips, &mc, dst, src_w, src_h, raw_format, scale ? &rs : nullptr)) != HKBCN_OK) return rc;
     if (desc) {
         desc->type = HKBCN_TEXTURE_2D;
         desc->width = width; desc->height = height; desc->depth = 1;

@@ -64,6 +64,8 @@ struct ResizeParams {
     float          ux[8], uy[8];
 };
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
+// any size to any size, 1..4 channels, alpha weighting for float images too (ResampleRawImage): one thread per output texel
+cudaError_t launch_resample_general(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
 
 // ---- environment probes (envprobe.cu) ----------------------------------------
 uint32_t envprobe_texels(int max_lod); // 6 * sum of (2^max_lod >> lod)^2

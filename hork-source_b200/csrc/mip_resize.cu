@@ -17,6 +17,7 @@
 // 25 ms of BC7 encode for the same chain.  Algorithmic HBM bytes per output texel: 4 source texels read + 1 written.
 #include <math.h>
 #include <stdint.h>
+#include <algorithm>
 #include <vector>
 #include "hkbcn_kernels.h"
 
@@ -67,8 +68,76 @@ int edge_index(int edge, int n, int max)
 
 // Taps of one axis: output i reads idx[i*T + k] with weight w[i*T + k], k < T (padded with weight 0), ascending input order.
 // The contributors of an output are consecutive inputs first[i] .. first[i] + cnt[i] - 1 (before edge mapping; map[] maps them).
+// Upsampling (out_size > in_size: the -resample pre-pass, CreateImage's resample to a power of two): stbir looks at every
+// OUTPUT pixel instead (stbir__calculate_sample_range_upsample :1009, stbir__calculate_coefficients_upsample :1038): the
+// inputs inside the filter's support around the output's centre, kernel(centre - input centre, 1 / scale), leading and
+// trailing zero weights dropped, the rest normalised to sum 1.
+static void build_axis_taps_up(int in_size, int out_size, int filter, int edge, AxisTaps& t)
+{
+    const float scale = (float)out_size / (float)in_size, shift = 0.0f;
+    const float out_radius = filter_support(filter, 1 / scale) * scale;
+    std::vector<std::vector<std::pair<int, float>>> per_out((size_t)out_size);
+    int lo_n = 0, hi_n = in_size - 1;
+    for (int n = 0; n < out_size; n++) {
+        const float out_center = (float)n + 0.5f;
+        const float in_lo = (out_center - out_radius + shift) / scale, in_hi = (out_center + out_radius + shift) / scale;
+        const float in_center_of_out = (out_center + shift) / scale;
+        int first = (int)floor(in_lo + 0.5);
+        const int last = (int)floor(in_hi - 0.5);
+        std::vector<float> c;
+        float total = 0;
+        for (int i = 0; i <= last - first; i++) {
+            const float in_center = (float)(i + first) + 0.5f;
+            const float k = filter_kernel(filter, in_center_of_out - in_center, 1 / scale);
+            if (c.empty() && !k) { // a leading zero weight moves the first contributor up
+                first++;
+                i--;
+                continue;
+            }
+            c.push_back(k);
+            total += k;
+        }
+        const float fs = 1 / total;
+        for (float& k : c) k *= fs;
+        while (!c.empty() && !c.back()) c.pop_back();
+        for (size_t i = 0; i < c.size(); i++) per_out[(size_t)n].push_back({first + (int)i, c[i]});
+        if (!c.empty()) {
+            lo_n = std::min(lo_n, first);
+            hi_n = std::max(hi_n, first + (int)c.size() - 1);
+        }
+    }
+    int T = 0;
+    for (auto& v : per_out) T = std::max(T, (int)v.size());
+    const int margin = std::max(-lo_n, hi_n - (in_size - 1));
+    t.T = T;
+    t.margin = margin;
+    t.uniform = false;
+    t.idx.assign((size_t)out_size * T, 0);
+    t.w.assign((size_t)out_size * T, 0.0f);
+    t.first.assign((size_t)out_size, 0);
+    t.cnt.assign((size_t)out_size, 0);
+    t.map.assign((size_t)(in_size + 2 * margin), 0);
+    for (int n = -margin; n < in_size + margin; n++) {
+        const int e = edge_index(edge, n, in_size);
+        t.map[(size_t)(n + margin)] = e < 0 ? 0 : e;
+    }
+    for (int i = 0; i < out_size; i++) {
+        t.first[(size_t)i] = per_out[(size_t)i].empty() ? 0 : per_out[(size_t)i][0].first;
+        t.cnt[(size_t)i] = (int)per_out[(size_t)i].size();
+        for (size_t k = 0; k < per_out[(size_t)i].size(); k++) {
+            const int e = edge_index(edge, per_out[(size_t)i][k].first, in_size);
+            t.idx[(size_t)i * T + k] = e < 0 ? 0 : e;
+            t.w[(size_t)i * T + k] = e < 0 ? 0.0f : per_out[(size_t)i][k].second;
+        }
+    }
+}
+
 void build_axis_taps(int in_size, int out_size, int filter, int edge, AxisTaps& t)
 {
+    if (out_size > in_size) { // stbir__use_upsampling: scale > 1
+        build_axis_taps_up(in_size, out_size, filter, edge, t);
+        return;
+    }
     std::vector<int>& idx = t.idx;
     std::vector<float>& w = t.w;
     int& T = t.T;
@@ -249,6 +318,84 @@ __global__ void __launch_bounds__(256) mip_resize_f32x3_kernel(const ResizeParam
     }
     float* d = (float*)P.dst + ((size_t)oy * P.out_w + ox) * 3;
     d[0] = ax; d[1] = ay; d[2] = az;
+}
+
+// ---- the general resampler (ResampleRawImage, Image.cpp:2188-2243: any size to any size, 1..4 channels, uint8 or float, the
+// alpha channel weighted or not): one thread per output texel, the same sums in the same order as above.  Used for the
+// -resample / resample-to-a-power-of-two pre-pass, which runs once per image; the cascade keeps its own kernels.
+template <int CH, bool F32>
+__global__ void __launch_bounds__(256) resample_gather_kernel(const ResizeParams P)
+{
+    __shared__ float lut[F32 ? 1 : 256], alut[F32 ? 1 : 256];
+    if (!F32) {
+        lut[threadIdx.x] = P.lut[threadIdx.x];
+        alut[threadIdx.x] = (float)threadIdx.x / 255.0f;
+        __syncthreads();
+    }
+    const int ox = blockIdx.x * 32 + (threadIdx.x & 31), oy = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (ox >= P.out_w || oy >= P.out_h) return;
+    float acc[CH];
+#pragma unroll
+    for (int c = 0; c < CH; c++) acc[c] = 0;
+    for (int ky = 0; ky < P.Ty; ky++) {
+        const float wy = P.wy[oy * P.Ty + ky];
+        const size_t row = (size_t)P.iy[oy * P.Ty + ky] * P.in_w;
+        float h[CH];
+#pragma unroll
+        for (int c = 0; c < CH; c++) h[c] = 0;
+        for (int kx = 0; kx < P.Tx; kx++) {
+            const float wx = P.wx[ox * P.Tx + kx];
+            const size_t t = (row + (size_t)P.ix[ox * P.Tx + kx]) * CH;
+            float v[CH];
+#pragma unroll
+            for (int c = 0; c < CH; c++) {
+                if (F32) v[c] = ((const float*)P.src)[t + c];
+                else v[c] = ((c == P.alpha) ? alut : lut)[P.src[t + c]];
+            }
+            if (P.weight) { // alpha weighting (:1375-1400)
+                float a = 0;
+#pragma unroll
+                for (int c = 0; c < CH; c++) if (c == P.alpha) a = v[c];
+                a += 1.0f / (1 << 20) / (1 << 20) / (1 << 20) / (1 << 20);
+#pragma unroll
+                for (int c = 0; c < CH; c++) v[c] = (c == P.alpha) ? a : v[c] * a;
+            }
+#pragma unroll
+            for (int c = 0; c < CH; c++) h[c] += v[c] * wx;
+        }
+#pragma unroll
+        for (int c = 0; c < CH; c++) acc[c] += h[c] * wy;
+    }
+    if (P.weight) {
+        float a = 0;
+#pragma unroll
+        for (int c = 0; c < CH; c++) if (c == P.alpha) a = acc[c];
+        const float r = a != 0 ? 1.0f / a : 0.0f;
+#pragma unroll
+        for (int c = 0; c < CH; c++) if (c != P.alpha) acc[c] *= r;
+    }
+    const size_t o = ((size_t)oy * P.out_w + ox) * CH;
+#pragma unroll
+    for (int c = 0; c < CH; c++) {
+        if (F32) ((float*)P.dst)[o + c] = acc[c];
+        else P.dst[o + c] = (P.srgb && c != P.alpha) ? encode_srgb8(acc[c]) : encode_linear8(acc[c]);
+    }
+}
+
+cudaError_t launch_resample_general(const ResizeParams& P, int channels, bool f32, cudaStream_t stream)
+{
+    const dim3 grid((unsigned)(P.out_w + 31) / 32, (unsigned)(P.out_h + 7) / 8);
+#define HK_RS(CH)                                                                           \
+    case CH:                                                                                \
+        if (f32) resample_gather_kernel<CH, true><<<grid, 256, 0, stream>>>(P);             \
+        else resample_gather_kernel<CH, false><<<grid, 256, 0, stream>>>(P);                \
+        break;
+    switch (channels) {
+        HK_RS(1) HK_RS(2) HK_RS(3) HK_RS(4)
+    default: return cudaErrorInvalidValue;
+    }
+#undef HK_RS
+    return cudaGetLastError();
 }
 
 // ---- the separable form: stbir's own structure (horizontal pass per input row, then the vertical pass), per output tile ----

@@ -8,8 +8,10 @@
 // Giving either -mip_* flag turns mip generation on, as in the reference (Main.cpp:124-143); -format takes the
 // TexFormat[] names of Hork/Image/Image.cpp:105-118.
 //
-// Out of scope (stay on the CPU in the reference): file decoding through stb_image / tinyexr / webp and
-// the -resample pre-pass.  Sources are raw containers that need no decoder: binary PGM / PPM (P5 / P6, 8 bit), PFM
+// -resample <w> <h> [-resample_edge_mode h v] [-resample_filter h v] scale the source first (Main.cpp:145-192 -> ResampleRawImage)
+// through hkbcn_resample_raw_image, on the device.
+// Out of scope (stays on the CPU in the reference): file decoding through stb_image / tinyexr / webp.
+// Sources are raw containers that need no decoder: binary PGM / PPM (P5 / P6, 8 bit), PFM
 // (Pf / PF), or `gen:<kind>:<width>:<height>:<seed>` procedural images (kind: albedo, mask, rough, normal, sky).
 // Channel mapping follows CreateImage (Image.cpp:1700-1716): BC1/2/3/7 take RGBA8 (alpha 255 when the file has none), BC4
 // the first channel, BC5 the first two, BC6H RGBA32F.
@@ -19,6 +21,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <chrono>
 #include <fstream>
 #include <sstream>
@@ -33,6 +36,10 @@ struct Args {
     std::string src, out, format;
     bool no_alpha = false, alpha_premult = false, mips = false;
     int edge = 0, filter = 0;
+    // -resample <w> <h> [-resample_edge_mode h v] [-resample_filter h v] (Tools/TextureImporter/Main.cpp:145-192)
+    bool resample = false;
+    uint32_t rs_w = 0, rs_h = 0;
+    int rs_edge_h = 0, rs_edge_v = 0, rs_filter_h = 0, rs_filter_v = 0;
 };
 
 struct Pixels {
@@ -70,6 +77,15 @@ bool parse_flags(const std::vector<std::string>& t, Args& a, std::string& err)
         else if (t[i] == "-alpha_premult") a.alpha_premult = true;
         else if (t[i] == "-mip_edge_mode" && need(1)) { a.edge = edge_mode(t[++i]); a.mips = true; }
         else if (t[i] == "-mip_filter" && need(1)) { a.filter = filter_of(t[++i]); a.mips = true; }
+        else if (t[i] == "-resample" && need(2)) {
+            a.resample = true;
+            a.rs_w = (uint32_t)strtoul(t[i + 1].c_str(), nullptr, 10);
+            a.rs_h = (uint32_t)strtoul(t[i + 2].c_str(), nullptr, 10);
+            i += 2;
+            if (a.rs_w == 0 || a.rs_h == 0) { err = "Invalid resample size " + std::to_string(a.rs_w) + " x " + std::to_string(a.rs_h); return false; }
+            if (a.rs_w > 4096 || a.rs_h > 4096) { err = "Resulting texture size is too large " + std::to_string(a.rs_w) + " x " + std::to_string(a.rs_h); return false; }
+        } else if (t[i] == "-resample_edge_mode" && need(2)) { a.rs_edge_h = edge_mode(t[i + 1]); a.rs_edge_v = edge_mode(t[i + 2]); i += 2; }
+        else if (t[i] == "-resample_filter" && need(2)) { a.rs_filter_h = filter_of(t[i + 1]); a.rs_filter_v = filter_of(t[i + 2]); i += 2; }
         else { err = "unknown or incomplete flag '" + t[i] + "'"; return false; }
     }
     if (a.out.empty()) { err = "Output file is not specified. Use -o <filename>"; return false; }
@@ -453,6 +469,9 @@ const char* kHelp = R"(hk_texture_import -- BCn texture import on the GPU (libhk
     -format <name>          -- Output texture format: BC1_UNORM[_SRGB] BC2_.. BC3_.. BC4_UNORM BC5_UNORM BC6H_UFLOAT BC6H_SFLOAT BC7_UNORM[_SRGB]
     -mip_edge_mode <mode>   -- clamp | reflect | wrap | zero          (giving either -mip_* flag generates the mip chain)
     -mip_filter <filter>    -- box | triangle | cubicspline | catmullrom | mitchell
+    -resample <width> <height>                  -- Scale input textures (on the device; rounded to a power of two with mips, else to 4)
+    -resample_edge_mode <mode_h> <mode_v>       -- Use edge mode for resampling (clamp/reflect/wrap/zero)
+    -resample_filter <filter_h> <filter_v>      -- Use filter for resampling (box/triangle/cubicspline/catmullrom/mitchell)
     -batch <manifest>       -- one flag set per line; all lines are imported as one batch sharded over the GPUs
     -gpus <mask>            -- bit mask of the CUDA devices to use (default: all)
     -skip_existing          -- leave textures alone whose output file is already complete (re-run of an interrupted batch)
@@ -531,6 +550,28 @@ int main(int argc, char** argv)
         const bool ok = a.src.rfind("gen:", 0) == 0 ? generate(a.src, p, err) : read_pnm(a.src, p, err);
         const int fmt = find_format(a.format);
         if (!ok || !to_source(p, fmt, sources[i], err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        if (a.resample) {
+            // Main.cpp:163-178: the requested size goes to the closest power of two (at least one block) when mips are generated,
+            // up to the next multiple of the block size otherwise; alpha weighting and colour space follow the format
+            auto pow2 = [](uint32_t v) { uint32_t hi = 1; while (hi < v) hi <<= 1; const uint32_t lo = hi >> 1; return (hi - v) < (v - lo) ? hi : lo; };
+            hkbcn_resample_params rp;
+            memset(&rp, 0, sizeof(rp));
+            rp.scaled_width = a.mips ? std::max<uint32_t>(pow2(a.rs_w), 4) : (a.rs_w + 3) & ~3u;
+            rp.scaled_height = a.mips ? std::max<uint32_t>(pow2(a.rs_h), 4) : (a.rs_h + 3) & ~3u;
+            rp.edge_h = a.rs_edge_h; rp.edge_v = a.rs_edge_v; rp.filter_h = a.rs_filter_h; rp.filter_v = a.rs_filter_v;
+            const int bpp = hkbcn_src_texel_bytes(fmt, 0);
+            const bool has_alpha = bpp == 4; // TexFormat[].bHasAlpha: BC1 / 2 / 3 / 7
+            const bool srgb = fmt == HKBCN_BC1_UNORM_SRGB || fmt == HKBCN_BC2_UNORM_SRGB || fmt == HKBCN_BC3_UNORM_SRGB || fmt == HKBCN_BC7_UNORM_SRGB;
+            if (has_alpha && !a.no_alpha) rp.flags |= HKBCN_RESAMPLE_HAS_ALPHA | (a.alpha_premult ? HKBCN_RESAMPLE_ALPHA_PREMULTIPLIED : 0);
+            if (srgb) rp.flags |= HKBCN_RESAMPLE_COLORSPACE_SRGB;
+            const int raw = bpp == 1 ? HKBCN_RAW_R8 : bpp == 2 ? HKBCN_RAW_R8_ALPHA : bpp == 4 ? HKBCN_RAW_RGBA8 : HKBCN_RAW_RGBA32F;
+            uint8_t* scaled = (uint8_t*)hkbcn_alloc_pinned((size_t)rp.scaled_width * rp.scaled_height * (size_t)bpp);
+            if (!scaled || hkbcn_resample_raw_image(raw, sources[i], p.w, p.h, &rp, scaled) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+            hkbcn_free_pinned(sources[i]);
+            sources[i] = scaled;
+            p.w = rp.scaled_width;
+            p.h = rp.scaled_height;
+        }
         // CalcNumMips / ImageStorage (Image.cpp:203-204, :415-416)
         if ((p.w & 3) || (p.h & 3)) { fprintf(stderr, "%s: width and height must be multiples of the block size 4\n", a.src.c_str()); return -1; }
         if (a.mips && ((p.w & (p.w - 1)) || (p.h & (p.h - 1)))) {

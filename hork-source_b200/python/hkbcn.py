@@ -40,12 +40,17 @@ EXPORTS = [
     "hkbcn_pack_texel_bytes", "hkbcn_pack_normals", "hkbcn_unpack_normals", "hkbcn_normalize_vectors", "hkbcn_bake_roughness",
     "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
     "hkbcn_static_scratch_bytes", "hkbcn_compress_static",
-    "hkbcn_plan_image", "hkbcn_create_image", "hkbcn_create_roughness_map",
+    "hkbcn_plan_image", "hkbcn_create_image", "hkbcn_create_roughness_map", "hkbcn_resample_raw_image", "hkbcn_resample_raw_image_dev",
 ]
 
 
 class HkbcnError(RuntimeError):
     pass
+
+
+class ResampleParams(C.Structure):
+    _fields_ = [("flags", C.c_uint32), ("edge_h", C.c_int), ("edge_v", C.c_int), ("filter_h", C.c_int), ("filter_v", C.c_int),
+                ("scaled_width", C.c_uint32), ("scaled_height", C.c_uint32)]
 
 
 class ImagePlan(C.Structure):
@@ -145,6 +150,8 @@ def lib():
         L.hkbcn_bake_roughness_dev.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.hkbcn_alloc_pinned.argtypes = [C.c_size_t]
         L.hkbcn_free_pinned.argtypes = [C.c_void_p]
+        L.hkbcn_resample_raw_image.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(ResampleParams), C.c_void_p]
+        L.hkbcn_resample_raw_image_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(ResampleParams), C.c_void_p, C.c_void_p]
         L.hkbcn_plan_image.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(ImagePlan)]
         L.hkbcn_create_image.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32, C.c_uint32, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_create_roughness_map.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]

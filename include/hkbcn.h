@@ -231,6 +231,25 @@ typedef struct hkbcn_image_plan {
     uint32_t required_width;  /* the size the reference resamples to first (Image.cpp:1064-1068): closest power of two, at least 4, */
     uint32_t required_height; /*   when mipmapped; the next multiple of 4 otherwise */
 } hkbcn_image_plan;
+/* ---- ResampleRawImage (Image.cpp:2188-2243; the -resample pre-pass of the importers, Tools/TextureImporter/Main.cpp:145-200, and
+ * CreateImage's resample to a power of two, Image.cpp:1064-1096): stbir_resize of a raw image to scaled_width x scaled_height,
+ * up or down, each axis with its own edge mode and filter, on the device.  Bit-identical to stbir for linear data (uint8 and
+ * float, with and without alpha weighting); sRGB uint8 within +-1 LSB (as the mip cascade).  Float images in the sRGB colour
+ * space are refused (no caller in the reference asks for them). */
+enum { HKBCN_RESAMPLE_HAS_ALPHA = 1, HKBCN_RESAMPLE_ALPHA_PREMULTIPLIED = 2, HKBCN_RESAMPLE_COLORSPACE_SRGB = 4 }; /* RAW_IMAGE_RESAMPLE_FLAG, Image.h:518-524 */
+typedef struct hkbcn_resample_params {
+    uint32_t flags;
+    int      edge_h, edge_v;       /* IMAGE_RESAMPLE_EDGE_MODE, 0 = wrap (RawImageResampleParams' default) */
+    int      filter_h, filter_v;   /* IMAGE_RESAMPLE_FILTER, 0 = mitchell */
+    uint32_t scaled_width, scaled_height;
+} hkbcn_resample_params;
+/* host pointers, device 0, synchronous; dst: scaled_width * scaled_height texels of the source's raw format */
+HKBCN_API int hkbcn_resample_raw_image(int raw_format, const void* src, uint32_t width, uint32_t height,
+                                       const hkbcn_resample_params* params, void* dst);
+/* device pointers on `device`, asynchronous on `stream` (tap tables are built and uploaded on first use of a size pair) */
+HKBCN_API int hkbcn_resample_raw_image_dev(int device, int raw_format, const void* d_src, uint32_t width, uint32_t height,
+                                           const hkbcn_resample_params* params, void* d_dst, void* stream);
+
 /* host only.  mipmapped: whether a mip config will be passed.  Unknown raw formats: HKBCN_ERR_BAD_FORMAT. */
 HKBCN_API int hkbcn_plan_image(int raw_format, uint32_t width, uint32_t height, int mipmapped, uint32_t storage_flags,
                                uint32_t import_flags, hkbcn_image_plan* plan);
@@ -238,8 +257,10 @@ HKBCN_API int hkbcn_plan_image(int raw_format, uint32_t width, uint32_t height, 
  * full mip chain (CalcNumMips levels) built on the device with cfg's edge mode and filter; alpha weighting follows the
  * storage flags as in ImageStorage::GenerateMipmaps (Image.cpp:767-774).  desc receives type / size / mips / format / flags
  * for hkbcn_write_texture.  capacity: bytes available at dst (hkbcn_chain_bytes(plan.format, w, h, 1, mips) are needed).
- * Returns HKBCN_ERR_UNSUPPORTED when the reference would not compress (plan.format == 0) or would first resample the image
- * to plan.required_width x required_height (the general resampler, stbir upsampling included, stays on the CPU: §8f). */
+ * An image whose size is not plan.required_width x required_height is first resampled to it on the device, with the mip
+ * config's edge mode and filter (wrap / mitchell without one) and the alpha / sRGB handling of Image.cpp:1074-1093, as the
+ * reference does; desc then carries the resampled size and capacity must cover it.
+ * Returns HKBCN_ERR_UNSUPPORTED when the reference would not compress (plan.format == 0). */
 struct hkbcn_texture_desc;
 HKBCN_API int hkbcn_create_image(int raw_format, const void* src, uint32_t width, uint32_t height, const hkbcn_mip_config* cfg,
                                  uint32_t storage_flags, uint32_t import_flags, struct hkbcn_texture_desc* desc, void* dst,

@@ -121,9 +121,11 @@ def test_create_image_hdr_and_srgb_and_refusals():
     # what the reference does not compress, or resamples first, is refused with a reason
     rc, _, _, _ = create_image(RGBA8, rgba, w, h, cfg, 0, SRGB | HALF)
     assert rc == -6 and b"uncompressed" in L.hkbcn_last_error()
+    # a size the reference resamples first is resampled here too (tests/test_gpu_resample.py)
     odd = np.zeros((60, 100, 4), np.uint8)
-    rc, _, _, p = create_image(RGBA8, odd, 100, 60, cfg, 0, COMPRESS)
-    assert rc == -6 and (p.required_width, p.required_height) == (128, 64) and b"resamples" in L.hkbcn_last_error()
+    rc, desc, _, p = create_image(RGBA8, odd, 100, 60, cfg, 0, COMPRESS)
+    assert rc == -2 and b"dst holds" in L.hkbcn_last_error()  # the helper sized dst for 100 x 60; the storage is 128 x 64
+    assert (p.required_width, p.required_height) == (128, 64)
 
 
 @pytest.mark.gpu

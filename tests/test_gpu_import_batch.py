@@ -329,3 +329,30 @@ def test_import_batch_sliced_jobs(tmp_path):
     assert np.array_equal(payload, np.concatenate(parts))
     d, payload = hkbcn.read_texture(paths[2].decode())
     assert (d.type, d.depth) == (2, 1) and np.array_equal(payload, hkbcn.import_chain(BC1, flat, w, w, mips))
+
+
+def test_tool_resample_flags(tmp_path):
+    """-resample / -resample_edge_mode / -resample_filter of the TextureImporter tool (Main.cpp:145-192): the source is scaled
+    on the device by hkbcn_resample_raw_image before the import; 96 x 80 -> 128 x 64 with mips (closest powers of two)"""
+    import subprocess
+    import os
+    tool = os.path.join(os.path.dirname(hkbcn.LIB_PATH), "hk_texture_import")
+    w, h = 96, 80
+    img = synth.albedo_rgba8(w, h, 0x700, "opaque").reshape(h, w, 4)
+    ppm = tmp_path / "src.ppm"
+    with open(ppm, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (w, h))
+        f.write(np.ascontiguousarray(img[..., :3]).tobytes())
+    out = tmp_path / "out.texture"
+    r = subprocess.run([tool, "-s", str(ppm), "-o", str(out), "-format", "BC1_UNORM", "-mip_filter", "triangle", "-resample", "100", "70",
+                        "-resample_edge_mode", "clamp", "clamp", "-resample_filter", "catmullrom", "catmullrom"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    d, payload = hkbcn.read_texture(str(out))
+    assert (d.width, d.height, d.fmt) == (128, 64, 54)
+    rgba = np.concatenate([img[..., :3], np.full((h, w, 1), 255, np.uint8)], -1)
+    big = refshim.stbir_resize(rgba, 128, 64, alpha_channel=3, flags=0, edge=1, filt=4, space=0)
+    levels = ref_cascade(np.ascontiguousarray(big), d.num_mips, 3, False, edge=3, filt=2)
+    want = refshim.compress_chain(54, np.concatenate([l.ravel() for l in levels]), 128, 64, d.num_mips)
+    assert np.array_equal(payload, want)
+    r = subprocess.run([tool, "-s", str(ppm), "-o", str(out), "-format", "BC1_UNORM", "-resample", "5000", "70"], capture_output=True, text=True)
+    assert r.returncode != 0 and "too large" in (r.stdout + r.stderr)

@@ -32,5 +32,5 @@ def test_taps_shape_and_normalisation():
     assert np.allclose(wx.sum(axis=1), 1.0, atol=1e-6)
     assert np.array_equal(wx[0], wx[1000])
     assert list(ix[0]) == [4093, 4094, 4095, 0, 1, 2, 3, 4]
-    with pytest.raises(hkbcn.HkbcnError):
-        hkbcn.mip_taps(4, 8)  # upsampling is not part of the cascade
+    ix, wx = hkbcn.mip_taps(4, 8)  # upsampling: stbir's other branch (tests/test_gpu_resample.py)
+    assert ix.shape[0] == 8 and np.allclose(wx.sum(axis=1), 1.0, atol=1e-6)
