@@ -1693,6 +1693,160 @@ int hkbcn_bake_roughness(const float* n, uint8_t* rough, uint32_t w, uint32_t h,
     return HKBCN_OK;
 }
 
+// ---- CreateNormalMap (Image.cpp:2262-2352) and CreateNormalAndRoughness (Image.cpp:2459-2638) as single calls -----------------
+namespace {
+struct DevBuf { // device scratch of one composed import call
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t n) { if (cudaMalloc(&p, n ? n : 1) != cudaSuccess) { set_err("cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(cudaGetLastError())); return HKBCN_ERR_CUDA; } return HKBCN_OK; }
+};
+int pack_format(int pack) { return pack == HKBCN_NORMALS_RGBA_BC1 ? HKBCN_BC1_UNORM : pack == HKBCN_NORMALS_RGBA_BC3 ? HKBCN_BC3_UNORM : HKBCN_BC5_UNORM; }
+uint32_t required_pow2(uint32_t v) { return std::max<uint32_t>(closest_pow2(v), 4); }
+
+// normalised Float3 normals on the device -> packed level 0 -> cascade of the packed texels (NO_ALPHA) -> encode -> d_out
+int normal_map_on(Device* D, const float* d_normals, uint32_t w, uint32_t h, int pack, uint32_t mips, int edge, int filter, void* d_out, cudaStream_t st)
+{
+    const int fmt = pack_format(pack), codec = codec_of(fmt);
+    DevBuf chain;
+    int rc = chain.alloc(chain_src_bytes(codec, 0, w, h, mips));
+    if (rc) return rc;
+    CK(launch_pack_normals(pack, d_normals, (uint8_t*)chain.p, (size_t)w * h, st)); // FIXME of the reference kept: packed once, not per level
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    hkbcn_mip_config mc{edge, filter, 1, 0};
+    if (mips > 1 && (rc = generate_mips_on(D, fmt, chain.p, w, h, mips, &mc, 0, st)) != HKBCN_OK) return rc;
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, 0, chain.p, d_out, w, h, mips)) != HKBCN_OK) return rc;
+    if ((rc = launch_encode(D, fmt, codec, P, st)) != HKBCN_OK) return rc;
+    CK(cudaStreamSynchronize(st)); // chain is freed on return
+    return HKBCN_OK;
+}
+void fill_desc(hkbcn_texture_desc* d, uint32_t w, uint32_t h, uint32_t mips, int fmt)
+{
+    if (!d) return;
+    d->type = HKBCN_TEXTURE_2D;
+    d->width = w; d->height = h; d->depth = 1;
+    d->num_mips = mips;
+    d->fmt = fmt;
+    d->storage_flags = HKBCN_STORAGE_NO_ALPHA;
+}
+} // namespace
+
+int hkbcn_create_normal_map(const float* normals_xyz, uint32_t width, uint32_t height, int pack, int mipmapped, int edge_mode, int filter,
+                            hkbcn_texture_desc* desc, void* dst, size_t capacity)
+{
+    Range nvtx_("hkbcn_create_normal_map");
+    if (hkbcn_pack_texel_bytes(pack) < 0) { set_err("bad normal-map packing %d", pack); return HKBCN_ERR_BAD_ARG; }
+    if (!normals_xyz || !width || !height) { set_err("null pointer or empty image"); return HKBCN_ERR_BAD_ARG; }
+    const uint32_t rw = mipmapped ? required_pow2(width) : (width + 3) & ~3u, rh = mipmapped ? required_pow2(height) : (height + 3) & ~3u;
+    if (rw != width || rh != height) {
+        set_err("CreateNormalMap: The width and height of the normal map must be a power of two and a multiple of blockSize if compression is enabled.");
+        return HKBCN_ERR_BAD_ARG;
+    }
+    const int fmt = pack_format(pack);
+    const uint32_t mips = mipmapped ? hkbcn_calc_num_mips(width, height) : 1;
+    const size_t need = hkbcn_chain_bytes(fmt, width, height, 1, mips);
+    fill_desc(desc, width, height, mips, fmt);
+    if (!dst) return HKBCN_OK; // size query
+    if (capacity < need) { set_err("dst holds %zu bytes, the storage needs %zu", capacity, need); return HKBCN_ERR_BAD_ARG; }
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    DevBuf n, out;
+    if ((rc = n.alloc((size_t)width * height * 12)) != HKBCN_OK || (rc = out.alloc(need)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(n.p, normals_xyz, (size_t)width * height * 12, cudaMemcpyHostToDevice, D->stream));
+    if ((rc = normal_map_on(D, (const float*)n.p, width, height, pack, mips, edge_mode ? edge_mode : 3, filter ? filter : 5, out.p, D->stream)) != HKBCN_OK) return rc;
+    CK(cudaMemcpy(dst, out.p, need, cudaMemcpyDeviceToHost));
+    return HKBCN_OK;
+}
+
+int hkbcn_create_normal_and_roughness(const hkbcn_normal_roughness_settings* s, hkbcn_texture_desc* normal_desc, void* normal_dst, size_t normal_capacity,
+                                      hkbcn_texture_desc* rough_desc, void* rough_dst, size_t rough_capacity)
+{
+    Range nvtx_("hkbcn_create_normal_and_roughness");
+    if (!s || !s->normals_rgb32f || !s->roughness_r8 || !s->normal_width || !s->normal_height || !s->roughness_width || !s->roughness_height) {
+        set_err("null pointer or empty image");
+        return HKBCN_ERR_BAD_ARG;
+    }
+    if (hkbcn_pack_texel_bytes(s->pack) < 0) { set_err("bad normal-map packing %d", s->pack); return HKBCN_ERR_BAD_ARG; }
+    if (s->roughness_bake != HKBCN_ROUGHNESS_BAKE_VMF && s->roughness_bake != HKBCN_ROUGHNESS_BAKE_TOKSVIG) { set_err("bad roughness bake %d", s->roughness_bake); return HKBCN_ERR_BAD_ARG; }
+    const int edge = s->edge_mode ? s->edge_mode : 3, tri = 2; // NormalMapResampleFilter = RoughnessMapResampleFilter = triangle (:2463-2464)
+    if (edge < 1 || edge > 4) { set_err("bad edge mode %d", edge); return HKBCN_ERR_BAD_ARG; }
+    // sizes (:2475-2490, :2601-2602): the roughness map goes to powers of two, the normal map first to the roughness map's size
+    // (for the bake), then to the powers of two of its OWN size for its storage
+    const uint32_t rw = required_pow2(s->roughness_width), rh = required_pow2(s->roughness_height);
+    const uint32_t nw = required_pow2(s->normal_width), nh = required_pow2(s->normal_height);
+    // :2604-2626: the normalised image made for the bake (roughness-sized) is the one stored when it already has the normal map's
+    // required size -- and also when the SOURCE has it (neither branch of the reference's if / else-if replaces it then)
+    const bool use_bake = (nw == rw && nh == rh) || (s->normal_width == nw && s->normal_height == nh);
+    const uint32_t ow = use_bake ? rw : nw, oh = use_bake ? rh : nh;
+    const uint32_t rmips = hkbcn_calc_num_mips(rw, rh), omips = hkbcn_calc_num_mips(ow, oh);
+    const int nfmt = pack_format(s->pack);
+    const size_t rneed = hkbcn_chain_bytes(HKBCN_BC4_UNORM, rw, rh, 1, rmips), oneed = hkbcn_chain_bytes(nfmt, ow, oh, 1, omips);
+    fill_desc(rough_desc, rw, rh, rmips, HKBCN_BC4_UNORM);
+    fill_desc(normal_desc, ow, oh, omips, nfmt);
+    if (!normal_dst && !rough_dst) return HKBCN_OK; // size query
+    if (!normal_dst || !rough_dst) { set_err("both destinations or neither"); return HKBCN_ERR_BAD_ARG; }
+    if (normal_capacity < oneed || rough_capacity < rneed) { set_err("destinations hold %zu / %zu bytes, the storages need %zu / %zu", normal_capacity, rough_capacity, oneed, rneed); return HKBCN_ERR_BAD_ARG; }
+    int rc = ensure_init();
+    if (rc) return rc;
+    Device* D = g_devs[0];
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    cudaStream_t st = D->stream;
+    const size_t src_n = (size_t)s->normal_width * s->normal_height, src_r = (size_t)s->roughness_width * s->roughness_height;
+    DevBuf n_src, r_src, r_chain, n_bake, scratch, r_out, n_out, n_own;
+    // ---- roughness level 0 at its power-of-two size
+    if ((rc = r_src.alloc(src_r)) != HKBCN_OK || (rc = r_chain.alloc(chain_src_bytes(C_BC4, 0, rw, rh, rmips))) != HKBCN_OK) return rc;
+    if (rw != s->roughness_width || rh != s->roughness_height) {
+        CK(cudaMemcpyAsync(r_src.p, s->roughness_r8, src_r, cudaMemcpyHostToDevice, st));
+        hkbcn_resample_params rp{0, edge, edge, tri, tri, rw, rh};
+        if ((rc = resample_on(D, HKBCN_RAW_R8, r_src.p, s->roughness_width, s->roughness_height, rp, r_chain.p, st)) != HKBCN_OK) return rc;
+    } else {
+        CK(cudaMemcpyAsync(r_chain.p, s->roughness_r8, src_r, cudaMemcpyHostToDevice, st));
+    }
+    // ---- the normal map as loaded (green inverted for DirectX maps), then at the roughness map's size, normalised
+    if ((rc = n_src.alloc(src_n * 12)) != HKBCN_OK || (rc = n_bake.alloc((size_t)rw * rh * 12)) != HKBCN_OK) return rc;
+    CK(cudaMemcpyAsync(n_src.p, s->normals_rgb32f, src_n * 12, cudaMemcpyHostToDevice, st));
+    if (s->convert_from_directx) { CK(launch_invert_green((float*)n_src.p, src_n, st)); g_launches.fetch_add(1, std::memory_order_relaxed); }
+    if (s->normal_width != rw || s->normal_height != rh) {
+        hkbcn_resample_params rp{0, edge, edge, tri, tri, rw, rh};
+        if ((rc = resample_on(D, HKBCN_RAW_RGB32F, n_src.p, s->normal_width, s->normal_height, rp, n_bake.p, st)) != HKBCN_OK) return rc;
+    } else {
+        CK(cudaMemcpyAsync(n_bake.p, n_src.p, src_n * 12, cudaMemcpyDeviceToDevice, st));
+    }
+    CK(launch_normalize_vectors((float*)n_bake.p, (size_t)rw * rh, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    // ---- roughness chain (CreateRoughnessMap, uncompressed, mipmapped: :2517), the update of levels >= 1, BC4
+    hkbcn_mip_config rmc{edge, tri, 1, 0};
+    if (rmips > 1 && (rc = generate_mips_on(D, HKBCN_BC4_UNORM, r_chain.p, rw, rh, rmips, &rmc, 0, st)) != HKBCN_OK) return rc;
+    if ((rc = scratch.alloc(hkbcn_bake_scratch_bytes(rw, rh))) != HKBCN_OK) return rc;
+    if ((rc = bake_roughness_on(D, (const float*)n_bake.p, (uint8_t*)r_chain.p, scratch.p, rw, rh, rmips, s->roughness_bake, tri, edge, st)) != HKBCN_OK) return rc;
+    if ((rc = r_out.alloc(rneed)) != HKBCN_OK) return rc;
+    {
+        EncodeParams P;
+        if ((rc = build_chain(P, C_BC4, 0, r_chain.p, r_out.p, rw, rh, rmips)) != HKBCN_OK) return rc;
+        if ((rc = launch_encode(D, HKBCN_BC4_UNORM, C_BC4, P, st)) != HKBCN_OK) return rc;
+    }
+    // ---- the normal map's own storage (:2601-2628)
+    const float* d_normals = (const float*)n_bake.p;
+    if (!use_bake) {
+        if ((rc = n_own.alloc((size_t)nw * nh * 12)) != HKBCN_OK) return rc;
+        hkbcn_resample_params rp{0, edge, edge, tri, tri, nw, nh};
+        if ((rc = resample_on(D, HKBCN_RAW_RGB32F, n_src.p, s->normal_width, s->normal_height, rp, n_own.p, st)) != HKBCN_OK) return rc;
+        CK(launch_normalize_vectors((float*)n_own.p, (size_t)nw * nh, st));
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        d_normals = (const float*)n_own.p;
+    }
+    if ((rc = n_out.alloc(oneed)) != HKBCN_OK) return rc;
+    if ((rc = normal_map_on(D, d_normals, ow, oh, s->pack, omips, edge, tri, n_out.p, st)) != HKBCN_OK) return rc;
+    CK(cudaStreamSynchronize(st));
+    CK(cudaMemcpy(rough_dst, r_out.p, rneed, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(normal_dst, n_out.p, oneed, cudaMemcpyDeviceToHost));
+    return HKBCN_OK;
+}
+
 // ---- environment probes (row f3) --------------------------------------------------------------------------------------
 size_t hkbcn_envprobe_texels(int max_lod) { return (max_lod < 1 || max_lod > 12) ? 0 : envprobe_texels(max_lod); }
 

@@ -78,6 +78,7 @@ cudaError_t launch_pack_normals(int variant, const float* d_normals, uint8_t* d_
 cudaError_t launch_unpack_normals(int variant, const uint8_t* d_src, float* d_normals, size_t count, cudaStream_t st);
 cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st);
 cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t* d_rough, size_t count, cudaStream_t st);
+cudaError_t launch_invert_green(float* d_xyz, size_t count, cudaStream_t st); // RawImage::InvertGreen on Float3 texels
 // RGB -> RGBA (alpha 255 / 1.0) and / or R <-> B: CreateImage's channel pass (Image.cpp:1152-1228)
 cudaError_t launch_expand_channels(const void* d_src, void* d_dst, size_t count, int src_channels, bool swap_rb, bool f32, cudaStream_t st);
 

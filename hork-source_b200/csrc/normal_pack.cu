@@ -231,6 +231,19 @@ cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st)
     return cudaGetLastError();
 }
 
+// RawImage::InvertGreen on Float3 texels (RawImage.cpp:745-760: g = 1 - g): DirectX -> OpenGL normal maps
+__global__ void __launch_bounds__(256) invert_green_kernel(float* __restrict__ xyz, size_t count)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i < count) xyz[3 * i + 1] = 1.0f - xyz[3 * i + 1];
+}
+cudaError_t launch_invert_green(float* d_xyz, size_t count, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    invert_green_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(d_xyz, count);
+    return cudaGetLastError();
+}
+
 // ---- CreateImage's channel pass (Image.cpp:1152-1228): three-channel raw images gain an alpha of 255 / 1.0, BGR(A) images
 // get R and B exchanged before compression.  T = uint8_t or float; one texel per thread.
 template <typename T>

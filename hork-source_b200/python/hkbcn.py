@@ -41,6 +41,7 @@ EXPORTS = [
     "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
     "hkbcn_static_scratch_bytes", "hkbcn_compress_static",
     "hkbcn_plan_image", "hkbcn_create_image", "hkbcn_create_roughness_map", "hkbcn_resample_raw_image", "hkbcn_resample_raw_image_dev",
+    "hkbcn_create_normal_map", "hkbcn_create_normal_and_roughness",
 ]
 
 
@@ -51,6 +52,12 @@ class HkbcnError(RuntimeError):
 class ResampleParams(C.Structure):
     _fields_ = [("flags", C.c_uint32), ("edge_h", C.c_int), ("edge_v", C.c_int), ("filter_h", C.c_int), ("filter_v", C.c_int),
                 ("scaled_width", C.c_uint32), ("scaled_height", C.c_uint32)]
+
+
+class NormalRoughnessSettings(C.Structure):
+    _fields_ = [("normals_rgb32f", C.c_void_p), ("normal_width", C.c_uint32), ("normal_height", C.c_uint32),
+                ("roughness_r8", C.c_void_p), ("roughness_width", C.c_uint32), ("roughness_height", C.c_uint32),
+                ("pack", C.c_int), ("convert_from_directx", C.c_int), ("edge_mode", C.c_int), ("roughness_bake", C.c_int)]
 
 
 class ImagePlan(C.Structure):
@@ -152,6 +159,9 @@ def lib():
         L.hkbcn_free_pinned.argtypes = [C.c_void_p]
         L.hkbcn_resample_raw_image.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(ResampleParams), C.c_void_p]
         L.hkbcn_resample_raw_image_dev.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(ResampleParams), C.c_void_p, C.c_void_p]
+        L.hkbcn_create_normal_map.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
+        L.hkbcn_create_normal_and_roughness.argtypes = [C.POINTER(NormalRoughnessSettings), C.POINTER(TextureDesc), C.c_void_p, C.c_size_t,
+                                                        C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_plan_image.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(ImagePlan)]
         L.hkbcn_create_image.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(MipConfig), C.c_uint32, C.c_uint32, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_create_roughness_map.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]

@@ -381,6 +381,31 @@ HKBCN_API int hkbcn_bake_roughness_dev(int device, const float* d_normals_xyz, u
                                        uint32_t width, uint32_t height, uint32_t num_mips, int bake, int filter, int edge_mode,
                                        void* stream);
 
+/* The two composed importer calls around them, on device 0 (host pointers, synchronous).  dst == NULL: only the descriptor(s)
+ * are filled in (size query: hkbcn_chain_bytes(desc.fmt, desc.width, desc.height, 1, desc.num_mips) bytes are needed).
+ * hkbcn_create_normal_map = Hk::CreateNormalMap(Float3 const*, Width, Height, Pack, bUseCompression = true, bMipmapped,
+ * ResampleEdgeMode, ResampleFilter) (Image.cpp:2262-2352): normalised normals -> pack -> cascade of the packed texels ->
+ * BC1 / BC5 / BC3 by packing.  Sizes the reference refuses return HKBCN_ERR_BAD_ARG with its message. */
+HKBCN_API int hkbcn_create_normal_map(const float* normals_xyz, uint32_t width, uint32_t height, int pack, int mipmapped, int edge_mode,
+                                      int filter, struct hkbcn_texture_desc* desc, void* dst, size_t capacity);
+/* hkbcn_create_normal_and_roughness = Hk::CreateNormalAndRoughness(NormalRoughnessImportSettings) (Image.cpp:2459-2638) with
+ * bCompressNormals and bCompressRoughness_BC4 set, from the two images already decoded (the reference loads them from files
+ * as RGB32F and R8): the roughness map is resampled to powers of two, the normal map (green inverted for DirectX maps) to the
+ * roughness map's size, normalised; the roughness chain's levels >= 1 are updated from the averaged normals (vMF / Toksvig)
+ * and compressed to BC4; the normal map is packed, mipped and compressed at the powers of two of its own size.  All
+ * resampling uses `edge_mode` and the triangle filter, as the reference does. */
+typedef struct hkbcn_normal_roughness_settings {
+    const float*   normals_rgb32f; uint32_t normal_width, normal_height;       /* Float3 per texel, as loaded (not yet normalised) */
+    const uint8_t* roughness_r8;   uint32_t roughness_width, roughness_height;
+    int pack;                  /* hkbcn_normal_pack */
+    int convert_from_directx;  /* bConvertFromDirectXNormalMap: g = 1 - g first */
+    int edge_mode;             /* 0 = wrap */
+    int roughness_bake;        /* HKBCN_ROUGHNESS_BAKE_VMF / _TOKSVIG */
+} hkbcn_normal_roughness_settings;
+HKBCN_API int hkbcn_create_normal_and_roughness(const hkbcn_normal_roughness_settings* settings, struct hkbcn_texture_desc* normal_desc,
+                                                void* normal_dst, size_t normal_capacity, struct hkbcn_texture_desc* roughness_desc,
+                                                void* roughness_dst, size_t roughness_capacity);
+
 /* ---- environment probes: GGX-prefiltered reflection chain and irradiance cube ----
  * The reference computes these by rendering into layered cubemaps through OpenGL (EnvProbeGenerator::Generate,
  * Hork/RenderUtils/EnvProbeGenerator.cpp:182-240 with envprobegen.frag; IrradianceGenerator::Generate,
