@@ -8,8 +8,11 @@
 //   level 2  principal axis (:2086-2174), one pass
 //   level 3  principal axis, two passes            level 5 (the Compress* preset): the same -- its extra flag,
 //            cEncodeBC1UseFasterMSEEval, is only read by the other branch
-// Levels 4 and 6..18 and the 3-colour flags take the error-tracking branch (total orderings, endpoint search rounds):
-// not built, the C ABI answers HKBCN_ERR_UNSUPPORTED for them.
+//   level 4  cEncodeBC1UseFullMSEEval | cEncodeBC1Use6PowerIters: the error-tracking branch (:2371-2470) in its simplest form --
+//            six power iterations, selectors by exhaustive search with the block error (bc1_find_sels4_fullerr, :1047-1081), a
+//            least-squares pass is kept only if it lowers the error
+// Levels 6..18 and the 3-colour flags add the total-orderings search and the endpoint search rounds of that branch: not built,
+// the C ABI answers HKBCN_ERR_UNSUPPORTED for them.
 //
 // FP32 discipline: the reference is built without FMA contraction (baseline x86-64,
 // SURVEY.md 7), so every float op here is an explicitly rounded __fmul_rn/__fadd_rn/
@@ -56,6 +59,42 @@ __device__ __forceinline__ uint32_t bc1_find_sels4(const uint32_t px[16], const 
         sels |= (uint32_t)(3 - c) << (2 * i);
     }
     return sels;
+}
+
+// rgbcx.cpp:1047-1081 (bc1_find_sels4_fullerr): the nearest of the four colours per texel (ties: the later one only for
+// j = 3), the block's squared error; stops at the texel where the total reaches cur_err (the caller then drops the result).
+__device__ __forceinline__ uint32_t bc1_find_sels4_fullerr(const uint32_t px[16], const Bc1Ep& e, uint32_t& sels_out, uint32_t cur_err)
+{
+    int pr[4], pg[4], pb[4];
+    pr[0] = (e.lr << 3) | (e.lr >> 2); pg[0] = (e.lg << 2) | (e.lg >> 4); pb[0] = (e.lb << 3) | (e.lb >> 2);
+    pr[3] = (e.hr << 3) | (e.hr >> 2); pg[3] = (e.hg << 2) | (e.hg >> 4); pb[3] = (e.hb << 3) | (e.hb >> 2);
+    pr[1] = (pr[0] * 2 + pr[3]) / 3; pg[1] = (pg[0] * 2 + pg[3]) / 3; pb[1] = (pb[0] * 2 + pb[3]) / 3;
+    pr[2] = (pr[3] * 2 + pr[0]) / 3; pg[2] = (pg[3] * 2 + pg[0]) / 3; pb[2] = (pb[3] * 2 + pb[0]) / 3;
+    uint32_t total = 0, sels = 0;
+    bool open = true; // the reference breaks out of the texel loop; here the remaining texels are predicated off
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        const int r = px[i] & 0xFF, g = (px[i] >> 8) & 0xFF, b = (px[i] >> 16) & 0xFF;
+        uint32_t best = (uint32_t)((pr[0] - r) * (pr[0] - r) + (pg[0] - g) * (pg[0] - g) + (pb[0] - b) * (pb[0] - b));
+        uint32_t bs = 0;
+#pragma unroll
+        for (int j = 1; j < 4; j++) {
+            const uint32_t err = (uint32_t)((pr[j] - r) * (pr[j] - r) + (pg[j] - g) * (pg[j] - g) + (pb[j] - b) * (pb[j] - b));
+            // `(j < 4) && best_err` in the loop header: an exact match ends the scan (later entries cannot be strictly better,
+            // and the j == 3 tie rule does not apply once the loop has ended)
+            if (best != 0 && (err < best || (err == best && j == 3))) {
+                best = err;
+                bs = (uint32_t)j;
+            }
+        }
+        if (open) {
+            total += best;
+            if (total >= cur_err) open = false;
+            else sels |= bs << (2 * i);
+        }
+    }
+    sels_out = sels;
+    return total;
 }
 
 // rgbcx.cpp:1194-1228 (precise_round_565) for one endpoint.
@@ -241,12 +280,15 @@ __device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16], const i
         const float inv255 = 1.0f / 255.0f;
         const float c0 = __fmul_rn((float)ic0, inv255), c1 = __fmul_rn((float)ic1, inv255), c2 = __fmul_rn((float)ic2, inv255);
         const float c3 = __fmul_rn((float)ic3, inv255), c4 = __fmul_rn((float)ic4, inv255), c5 = __fmul_rn((float)ic5, inv255);
+        const int power_iters = level == 4 ? 6 : 4; // cEncodeBC1Use6PowerIters (rgbcx.cpp:2121)
 #pragma unroll
-        for (int it = 0; it < 4; it++) {
-            float r = __fadd_rn(__fadd_rn(__fmul_rn(xr, c0), __fmul_rn(xg, c1)), __fmul_rn(xb, c2));
-            float g = __fadd_rn(__fadd_rn(__fmul_rn(xr, c1), __fmul_rn(xg, c3)), __fmul_rn(xb, c4));
-            float b = __fadd_rn(__fadd_rn(__fmul_rn(xr, c2), __fmul_rn(xg, c4)), __fmul_rn(xb, c5));
-            xr = r; xg = g; xb = b;
+        for (int it = 0; it < 6; it++) {
+            if (it < power_iters) {
+                float r = __fadd_rn(__fadd_rn(__fmul_rn(xr, c0), __fmul_rn(xg, c1)), __fmul_rn(xb, c2));
+                float g = __fadd_rn(__fadd_rn(__fmul_rn(xr, c1), __fmul_rn(xg, c3)), __fmul_rn(xb, c4));
+                float b = __fadd_rn(__fadd_rn(__fmul_rn(xr, c2), __fmul_rn(xg, c4)), __fmul_rn(xb, c5));
+                xr = r; xg = g; xb = b;
+            }
         }
         float k = fmaxf(fmaxf(fabsf(xr), fabsf(xg)), fabsf(xb));
         if (k >= 2.0f) {
@@ -277,7 +319,11 @@ __device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16], const i
         e.hr = to_5(hc & 0xFF); e.hg = to_6((hc >> 8) & 0xFF); e.hb = to_5((hc >> 16) & 0xFF);
     }
 
-    uint32_t sels = bc1_find_sels4(px, e);
+    // level 4: the error-tracking form of the same loop (rgbcx.cpp:2388-2440)
+    const bool track = level == 4;
+    uint32_t sels, cur_err = 0xFFFFFFFFu;
+    if (track) cur_err = bc1_find_sels4_fullerr(px, e, sels, 0xFFFFFFFFu);
+    else sels = bc1_find_sels4(px, e);
 
     // ---- one (levels 0..2) or two least-squares passes (rgbcx.cpp:2333-2370; LS solve :727-773)
     const int passes = level >= 3 ? 2 : 1;
@@ -318,6 +364,15 @@ __device__ __forceinline__ uint2 bc1_encode_block(const uint32_t px[16], const i
             round_565(xh0, xh1, xh2, t.lr, t.lg, t.lb);
         }
         if (e.lr == t.lr && e.lg == t.lg && e.lb == t.lb && e.hr == t.hr && e.hg == t.hg && e.hb == t.hb) break;
+        if (track) {
+            uint32_t tsels;
+            const uint32_t terr = bc1_find_sels4_fullerr(px, t, tsels, cur_err);
+            if (!(terr < cur_err)) break; // the pass did not help: keep what there is
+            cur_err = terr;
+            sels = tsels;
+            e = t;
+            continue;
+        }
         sels = bc1_find_sels4(px, t);
         e = t;
     }

@@ -257,9 +257,9 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
     if (P0.totalTiles == 0) return HKBCN_OK;
     if (P0.flags & HKBCN_FLAG_LEVEL_MASK) {
         const int level = (int)((P0.flags & HKBCN_FLAG_LEVEL_MASK) >> 4) - 1;
-        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? (level <= 3 || level == 5) : codec == C_BC7 ? level <= 4 : false;
+        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? level <= 5 : codec == C_BC7 ? level <= 4 : false;
         if (!ok) {
-            set_err("quality level %d of format %d is not built (BC1/2/3: 0, 1, 2, 3, 5; BC7: 0..4; see hkbcn.h)", level, fmt);
+            set_err("quality level %d of format %d is not built (BC1/2/3: 0..5; BC7: 0..4; see hkbcn.h)", level, fmt);
             return HKBCN_ERR_UNSUPPORTED;
         }
     }
@@ -2268,7 +2268,7 @@ int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint3
     add_level(P, codec, flags, base + soff, base + doff, width & ~3u, height, width);
     if (P.flags & HKBCN_FLAG_LEVEL_MASK) {
         const int level = (int)((P.flags & HKBCN_FLAG_LEVEL_MASK) >> 4) - 1;
-        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? (level <= 3 || level == 5) : codec == C_BC7 ? level <= 4 : false;
+        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? level <= 5 : codec == C_BC7 ? level <= 4 : false;
         if (!ok) { set_err("quality level %d of format %d is not built", level, fmt); return HKBCN_ERR_UNSUPPORTED; }
     }
     P.sched = (uint32_t*)base;

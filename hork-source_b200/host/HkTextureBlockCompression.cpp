@@ -41,7 +41,7 @@ void Decode_BC6h_f32(void const* s, void* d, size_t RowStride, bool bSigned)
 }
 void Decode_BC7(void const* s, void* d, size_t RowStride) { Check(hkbcn_decode_blocks(HKBCN_BC7_UNORM, s, d, 1, RowStride, 0), "Decode_BC7"); }
 
-// Levels: rgbcx levels 0, 1, 2, 3, 5 are built (the ones without error tracking); the library answers
+// Levels: rgbcx levels 0..5 are built (everything below the total-orderings search); the library answers
 // HKBCN_ERR_UNSUPPORTED for the others and for the 3-colour flags (levels >= 5 only read them), which Check() turns into an abort.
 void Encode_BC1(void const* s, void* d, uint32_t Level, bool b3ColorMode, bool bTransparentPixelsForBlack)
 {

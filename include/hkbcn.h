@@ -71,8 +71,8 @@ enum {
     HKBCN_FLAG_FAST        = 1u << 1, /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:161-185) */
     /* bits 4..8: quality level of Encode_BC1/2/3(Level) and Encode_BC7(Level) (ImageEncoders.cpp:138-169, 207-212), stored
      * as level + 1; 0 = the preset the Compress* functions bake in (BC1/2/3 level 5, BC7 level 4).  Use HKBCN_FLAG_LEVEL(n).
-     * Built: BC1/2/3 levels 0, 1, 2, 3, 5 (the rgbcx levels without error tracking: rgbcx.cpp:1692-1726) and BC7 levels
-     * 0..4.  BC1/2/3 levels 4 and 6..18, and the 3-colour flags of Encode_BC1, return HKBCN_ERR_UNSUPPORTED. */
+     * Built: BC1/2/3 levels 0..5 (the rgbcx levels below the total-orderings search: rgbcx.cpp:1692-1726) and BC7 levels
+     * 0..4.  BC1/2/3 levels 6..18, and the 3-colour flags of Encode_BC1, return HKBCN_ERR_UNSUPPORTED. */
     HKBCN_FLAG_LEVEL_MASK  = 31u << 4,
     HKBCN_FLAG_SRC_DEVICE  = 1u << 17, /* hkbcn_import_batch: src_level0 is DEVICE memory on the GPU hkbcn_plan_import_batch assigns the
                                           job to (sources produced on the device never cross PCIe); the default is host memory */

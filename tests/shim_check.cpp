@@ -124,6 +124,7 @@ int main(int argc, char** argv)
             const uint32_t lvl = (uint32_t)(t & 3);
             TBC::Encode_BC1(blk, g16, lvl, true, true); ref_encode_bc1_level(blk, w16, lvl, 1, 1); expect_equal("Encode_BC1 level 0..3", g16, w16, 8);
             TBC::Encode_BC7(blk, g16, lvl);             ref_encode_bc7_level(blk, w16, lvl);       expect_equal("Encode_BC7 level 0..3", g16, w16, 16);
+            TBC::Encode_BC1(blk, g16, 4, true, true);   ref_encode_bc1_level(blk, w16, 4, 1, 1);   expect_equal("Encode_BC1 level 4", g16, w16, 8);
             {
                 uint8_t al[16];
                 for (int i = 0; i < 16; i++) al[i] = blk[4 * i + 3];
