@@ -345,6 +345,22 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
     const uint32_t nby = h / 4;
     const size_t l0 = (size_t)w * h * bpp;
     int nb = (int)std::min<size_t>(6, std::max<size_t>(1, l0 / (12u << 20)));
+    if (nb > 1) {
+        // Every band is a launch of its own, and a persistent encoder works in rounds of one tile per SM: a band of 2.2 rounds
+        // costs three (measured, BC7 4096^2 chain from pageable memory: 5 bands 25.5 ms, 4 bands 22.3, 6 bands 21.9).  Among
+        // the band counts that keep a piece at 8 MB or more, take the one whose last round is fullest; ties go to more bands.
+        const uint32_t tb = tile_blocks(codec), sms = (uint32_t)std::max(1, D->sm_count);
+        double best = -1.0;
+        int best_nb = nb;
+        for (int c = 2; c <= 7; c++) {
+            if (l0 / (size_t)c < ((size_t)8 << 20) || (uint32_t)c > nby) break;
+            const uint64_t tiles = ((uint64_t)((nby + c - 1) / c) * (w / 4) + tb - 1) / tb;
+            const double eff = (double)tiles / (double)(((tiles + sms - 1) / sms) * sms);
+            if (eff >= best - 1e-9) { best = eff; best_nb = c; }
+        }
+        nb = best_nb;
+    }
+    if (const char* e = getenv("HKBCN_PIPE_BANDS")) nb = std::max(1, std::min(7, atoi(e))); // A/B timing
     if ((uint32_t)nb > nby) nb = (int)nby;
     for (int b = 0; b < nb; b++) {
         const uint32_t r0 = (uint32_t)((uint64_t)nby * b / nb), r1 = (uint32_t)((uint64_t)nby * (b + 1) / nb);
