@@ -2224,11 +2224,12 @@ static __device__ __align__(256) unsigned char g_static_scratch[HKBCN_STATIC_SCR
 namespace {
 constexpr int kStaticMaxDevices = 64;
 std::mutex g_static_mu[kStaticMaxDevices];
-void*      g_static_ptr[kStaticMaxDevices]; // device address of g_static_scratch on g_devs[i], set on first use
+void*      g_static_ptr[kStaticMaxDevices]; // device address of g_static_scratch on CUDA device i (the array belongs to the GPU,
+                                            // not to a slot of hkbcn_init's selection, which a later init may fill differently)
 
 int static_scratch_of(int device, Device* D, unsigned char** out)
 {
-    // caller holds g_static_mu[device] and has made D current
+    // caller holds g_static_mu[device] (device = D->id) and has made D current
     if (!g_static_ptr[device]) {
         void* p = nullptr;
         cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
@@ -2269,10 +2270,11 @@ int hkbcn_compress_static(int device, int fmt, const void* src, void* dst, uint3
                 width, height, fmt, loff + lbytes, (size_t)HKBCN_STATIC_SCRATCH_BYTES);
         return HKBCN_ERR_BAD_ARG;
     }
-    std::lock_guard<std::mutex> lk(g_static_mu[device]);
+    if (D->id < 0 || D->id >= kStaticMaxDevices) { set_err("CUDA device %d is beyond the %d the static scratch is tracked for", D->id, kStaticMaxDevices); return HKBCN_ERR_BAD_ARG; }
+    std::lock_guard<std::mutex> lk(g_static_mu[D->id]);
     CK(cudaSetDevice(D->id));
     unsigned char* base = nullptr;
-    int rc = static_scratch_of(device, D, &base);
+    int rc = static_scratch_of(D->id, D, &base);
     if (rc) return rc;
     cudaStream_t st = D->stream;
     CK(cudaMemsetAsync(base, 0, 256, st)); // the tile counters must start at zero whatever the last call left

@@ -77,3 +77,17 @@ def test_largest_surface_that_fits_and_the_first_that_does_not():
     small = source(BC4, 64, 64, 80)
     assert np.array_equal(compress_static(BC4, small, 64, 64), hkbcn.compress(BC4, small, 64, 64))
     assert L.hkbcn_compress_static(99, BC7, big.ctypes.data_as(C.c_void_p), dst.ctypes.data_as(C.c_void_p), 64, 64, 0) == -2
+
+
+def test_after_shutdown_and_reinit():
+    """the scratch belongs to the GPU, not to a slot of hkbcn_init's selection: shut the library down, bring it up again, call again"""
+    L = hkbcn.lib()
+    hkbcn.init()
+    src = source(BC7, 64, 64, 81)
+    want = hkbcn.compress(BC7, src, 64, 64)
+    assert np.array_equal(compress_static(BC7, src, 64, 64), want)
+    L.hkbcn_shutdown()
+    assert L.hkbcn_compress_static(0, BC7, src.ctypes.data_as(C.c_void_p), np.zeros(4096, np.uint8).ctypes.data_as(C.c_void_p), 64, 64, 0) == -5  # not initialised
+    hkbcn.init()
+    assert np.array_equal(compress_static(BC7, src, 64, 64), want)
+    assert np.array_equal(hkbcn.compress(BC7, src, 64, 64), want)
