@@ -267,7 +267,11 @@ __global__ void __launch_bounds__(BC6_NT, BC6E_MIN_CTAS) bc6h_encode_kernel(cons
 
         // ---- the three rounds: setup -> optimise -> finish
 #pragma unroll 1
-        for (int round = 0; round < 3; round++) {
+#ifndef BC6_ROUND_LO
+#define BC6_ROUND_LO 0
+#define BC6_ROUND_HI 3
+#endif
+        for (int round = BC6_ROUND_LO; round < BC6_ROUND_HI; round++) { // (timing experiments cut rounds out)
             const int ntask = round < 2 ? nb * 24 : nb * 4;
             int nSurv = 0;
 #pragma unroll 1
