@@ -356,3 +356,28 @@ def test_tool_resample_flags(tmp_path):
     assert np.array_equal(payload, want)
     r = subprocess.run([tool, "-s", str(ppm), "-o", str(out), "-format", "BC1_UNORM", "-resample", "5000", "70"], capture_output=True, text=True)
     assert r.returncode != 0 and "too large" in (r.stdout + r.stderr)
+
+
+def test_import_batch_takes_a_prebuilt_chain():
+    """HKBCN_FLAG_SRC_CHAIN: the job hands over its own uncompressed chain (here: the reference's stbir cascade); every level is
+    uploaded and encoded, nothing is generated -- the in-memory result equals hkbcn_compress_chain and the reference"""
+    L = hkbcn.lib()
+    BC7 = 66
+    w = h = 128
+    mips = L.hkbcn_calc_num_mips(w, h)
+    outs, chains, jobs = [], [], (hkbcn.ImportJob * 3)()
+    for i in range(3):
+        img = synth.albedo_rgba8(w, h, 0x730 + i, "mask").reshape(h, w, 4)
+        chain = np.concatenate([l.ravel() for l in ref_cascade(img, mips, 3, False)])
+        chains.append(np.ascontiguousarray(chain))
+        outs.append(np.zeros(L.hkbcn_chain_bytes(BC7, w, h, 1, mips), np.uint8))
+        jobs[i].fmt, jobs[i].width, jobs[i].height, jobs[i].generate_mips = BC7, w, h, 0
+        jobs[i].flags = 1 << 18
+        jobs[i].src_level0 = chains[i].ctypes.data_as(C.c_void_p)
+        jobs[i].out_path = None
+        jobs[i].dst = outs[i].ctypes.data_as(C.c_void_p)
+    hkbcn.check(L.hkbcn_import_batch(jobs, 3))
+    for i in range(3):
+        assert jobs[i].status == 0
+        assert np.array_equal(outs[i], hkbcn.compress_chain(BC7, chains[i], w, h, mips))
+        assert np.array_equal(outs[i], refshim.compress_chain(BC7, chains[i], w, h, mips))
