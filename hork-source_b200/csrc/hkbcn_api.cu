@@ -267,7 +267,11 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
     if (!(P.sched = sched_slot(D, st))) return HKBCN_ERR_CUDA;
     if (codec == C_BC7) {
         uint32_t nb = 0;
-        for (uint32_t i = 0; i < P.nLevels; i++) nb += P.lv[i].nblocks;
+        for (uint32_t i = 0; i < P.nLevels; i++) {
+            // a work-list entry is level << 28 | block: 2^28 blocks = a 65536 x 65536 level
+            if (P.lv[i].nblocks >= (1u << 28)) { set_err("BC7: a level of %u blocks is beyond the 2^28 the work list addresses", P.lv[i].nblocks); return HKBCN_ERR_BAD_ARG; }
+            nb += P.lv[i].nblocks;
+        }
         if (!(P.aux = bc7_aux(D, st, bc7_aux_bytes(nb)))) return HKBCN_ERR_CUDA;
     }
     cudaError_t e = cudaSuccess;
