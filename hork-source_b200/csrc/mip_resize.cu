@@ -545,9 +545,12 @@ __global__ void __launch_bounds__(256) mip_resize_tile_kernel(const ResizeParams
 // under wrap / clamp / reflect).  The weights come as kernel parameters, the staged columns are dealt over eight shared-memory
 // lanes (column c at [c & 7][c >> 3]) so that a thread computing four adjacent outputs of a row reads its 6 + Tx inputs without
 // bank conflicts -- 14 loads for 4 outputs instead of 8 each -- and stores during the decode are conflict-free as well.
-template <int CH, bool F32>
+// TT: taps per output on both axes as a compile-time constant (8: Mitchell / Catmull-Rom / B-spline at 2 : 1, the importers'
+// default), so that the tap loops carry no run-time bounds; 0 = taken from the parameters.
+template <int CH, bool F32, int TT>
 __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizeParams P)
 {
+    const int TX = TT ? TT : P.Tx, TY = TT ? TT : P.Ty;
     constexpr int OCT = MT_SX / 8; // 9 slots per lane of columns
     __shared__ __align__(16) float dec[MT_SY * MT_SX * CH];
     __shared__ __align__(16) float hbuf[MT_SY * MT_W * CH];
@@ -556,8 +559,8 @@ __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizePa
     const int tid = threadIdx.x;
     const int ox0 = blockIdx.x * MT_W, oy0 = blockIdx.y * MT_H;
     const int tw = min(MT_W, P.out_w - ox0), th = min(MT_H, P.out_h - oy0);
-    const int nx_lo = 2 * ox0 + P.x0, sx = 2 * (tw - 1) + P.Tx;
-    const int ny_lo = 2 * oy0 + P.y0, sy = 2 * (th - 1) + P.Ty;
+    const int nx_lo = 2 * ox0 + P.x0, sx = 2 * (tw - 1) + TX;
+    const int ny_lo = 2 * oy0 + P.y0, sy = 2 * (th - 1) + TY;
     if (!F32) {
         lut[tid] = P.lut[tid];
         alut[tid] = (float)tid / 255.0f; // alpha decode: the reference's IEEE division, once per CTA
@@ -618,7 +621,7 @@ __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizePa
         // input t of the group (column 8 g + t of the staged row) feeds output o as its tap t - 2 o
 #pragma unroll
         for (int t = 0; t < 14; t++) {
-            if (t < 6 + P.Tx) {
+            if (t < 6 + TX) {
                 float v[CH];
                 const float* s = row + ((size_t)(t & 7) * OCT + g + (t >> 3)) * CH;
                 if (CH == 4) {
@@ -631,7 +634,7 @@ __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizePa
 #pragma unroll
                 for (int o = 0; o < 4; o++) {
                     const int kx = t - 2 * o;
-                    if (kx >= 0 && kx < 8 && kx < P.Tx) {
+                    if (kx >= 0 && kx < 8 && kx < TX) {
 #pragma unroll
                         for (int k = 0; k < CH; k++) h[o][k] += v[k] * P.ux[kx];
                     }
@@ -656,7 +659,7 @@ __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizePa
         const float* col = hbuf + ((size_t)(2 * y) * MT_W + x) * CH;
 #pragma unroll
         for (int ky = 0; ky < 8; ky++) {
-            if (ky < P.Ty) {
+            if (ky < TY) {
 #pragma unroll
                 for (int k = 0; k < CH; k++) acc[k] += col[(size_t)ky * MT_W * CH + k] * P.uy[ky];
             }
@@ -695,11 +698,18 @@ cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cud
 {
     if (P.uniform && P.tileOk) {
         const dim3 grid2((unsigned)(P.out_w + 31) / 32, (unsigned)(P.out_h + 7) / 8);
-        if (f32 && channels == 3) mip_resize_tile2_kernel<3, true><<<grid2, 256, 0, stream>>>(P);
-        else if (f32 && channels == 4) mip_resize_tile2_kernel<4, true><<<grid2, 256, 0, stream>>>(P);
-        else if (!f32 && channels == 1) mip_resize_tile2_kernel<1, false><<<grid2, 256, 0, stream>>>(P);
-        else if (!f32 && channels == 2) mip_resize_tile2_kernel<2, false><<<grid2, 256, 0, stream>>>(P);
-        else if (!f32 && channels == 4) mip_resize_tile2_kernel<4, false><<<grid2, 256, 0, stream>>>(P);
+        const bool t8 = P.Tx == 8 && P.Ty == 8;
+#define HK_T2(CH, F)                                                                            \
+    do {                                                                                        \
+        if (t8) mip_resize_tile2_kernel<CH, F, 8><<<grid2, 256, 0, stream>>>(P);                \
+        else mip_resize_tile2_kernel<CH, F, 0><<<grid2, 256, 0, stream>>>(P);                   \
+    } while (0)
+        if (f32 && channels == 3) HK_T2(3, true);
+        else if (f32 && channels == 4) HK_T2(4, true);
+        else if (!f32 && channels == 1) HK_T2(1, false);
+        else if (!f32 && channels == 2) HK_T2(2, false);
+        else if (!f32 && channels == 4) HK_T2(4, false);
+#undef HK_T2
         else return cudaErrorInvalidValue;
         return cudaGetLastError();
     }
