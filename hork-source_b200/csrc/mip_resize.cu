@@ -17,6 +17,7 @@
 // 25 ms of BC7 encode for the same chain.  Algorithmic HBM bytes per output texel: 4 source texels read + 1 written.
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <vector>
 #include "hkbcn_kernels.h"
@@ -694,8 +695,133 @@ __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizePa
     }
 }
 
+// ---- RGBA8, exact 2 : 1, eight taps per axis (the importers' default: Mitchell; also Catmull-Rom and the B-spline): the
+// level-1 kernel of every colour chain.  Same arithmetic in the same order as above; what changes is who computes what:
+//   stage       the 70 x 32 input texels of a 32 x 13 output tile as RAW words (4 bytes each, not 16)
+//   horizontal  warp = group of 4 adjacent output columns, lane = staged row: a thread reads its row's 14 inputs with four
+//               16-byte loads (row pitch 76 words: the eight rows of a quarter-warp fall into disjoint banks), decodes and
+//               alpha-weights them in registers and produces 4 horizontal results -- 4 loads of raw words where the general
+//               tile kernel spends 14 loads of decoded texels, and no 16-byte decoded copy of every texel in shared memory
+//   vertical    thread = (column, pair of output rows): the pair shares 6 of its 10 inputs
+// The horizontal buffer is column-major ([x][row], pitch 33 float4) so that both the row-parallel writes and the
+// column-parallel reads are conflict-free.
+constexpr int M3_W = 32, M3_H = 13, M3_SX = 2 * M3_W + 6, M3_SY = 2 * M3_H + 6, M3_P = 76, M3_HP = 33;
+static_assert(M3_SY == 32, "one staged row per lane");
+
+#ifndef M3_MINB
+#define M3_MINB 6  // resident CTAs per SM asked of ptxas (40 registers)
+#endif
+// HAS_A: the fourth channel is alpha (decoded linearly; colour weighted by it when P.weight); else it is a colour channel
+template <bool HAS_A>
+__global__ void __launch_bounds__(256, M3_MINB) mip_resize_rgba8_t8_kernel(const ResizeParams P)
+{
+    __shared__ __align__(16) uint32_t raw[M3_SY * M3_P];
+    __shared__ __align__(16) float4 hb[M3_W * M3_HP + 2]; // + 2: the last pair of rows loads two entries it does not use
+    __shared__ float lut[256], alut[256];
+    __shared__ int s_mx[M3_SX + 2], s_my[M3_SY];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ox0 = blockIdx.x * M3_W, oy0 = blockIdx.y * M3_H;
+    const int tw = min(M3_W, P.out_w - ox0), th = min(M3_H, P.out_h - oy0);
+    const int nx_lo = 2 * ox0 + P.x0, sx = 2 * (tw - 1) + 8;
+    const int ny_lo = 2 * oy0 + P.y0, sy = 2 * (th - 1) + 8;
+    lut[tid] = P.lut[tid];
+    alut[tid] = (float)tid / 255.0f;
+    if (tid < sx) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
+    if (tid >= 128 && tid < 128 + sy) s_my[tid - 128] = P.mapy[ny_lo + tid - 128 + P.marginy];
+    __syncthreads();
+    // ---- stage
+    {
+        const float inv_sx = 1.0f / (float)sx;
+        for (int i = tid; i < sy * sx; i += 256) {
+            const int r = (int)(((float)i + 0.5f) * inv_sx), c = i - r * sx; // i < 2240: the float quotient is exact enough to floor
+            raw[r * M3_P + c] = __ldg((const uint32_t*)(P.src + ((size_t)s_my[r] * P.in_w + s_mx[c]) * 4));
+        }
+    }
+    __syncthreads();
+    // ---- horizontal pass: warp = four adjacent output columns (4 w .. 4 w + 3), lane = staged row
+    if (lane < sy && 4 * warp < tw) {
+        const uint32_t* row = raw + lane * M3_P + 8 * warp;
+        uint32_t q[16];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint4 v = *(const uint4*)(row + 4 * j);
+            q[4 * j + 0] = v.x; q[4 * j + 1] = v.y; q[4 * j + 2] = v.z; q[4 * j + 3] = v.w;
+        }
+        float h[4][4];
+#pragma unroll
+        for (int o = 0; o < 4; o++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) h[o][k] = 0;
+        // input t of the group feeds output o as its tap t - 2 o; inputs ascending per output
+#pragma unroll
+        for (int t = 0; t < 14; t++) {
+            float v[4];
+            const uint32_t w = q[t];
+            const int b[4] = {(int)(w & 255u), (int)((w >> 8) & 255u), (int)((w >> 16) & 255u), (int)(w >> 24)};
+#pragma unroll
+            for (int k = 0; k < 3; k++) v[k] = lut[b[k]];
+            v[3] = (HAS_A ? alut : lut)[b[3]];
+            if (HAS_A && P.weight) {
+                // alpha weighting (:1375-1400): the epsilon keeps the colour of fully transparent texels
+                const float a = v[3] + 1.0f / (1 << 20) / (1 << 20) / (1 << 20) / (1 << 20);
+                v[0] *= a; v[1] *= a; v[2] *= a;
+                v[3] = a;
+            }
+#pragma unroll
+            for (int o = 0; o < 4; o++) {
+                const int kx = t - 2 * o;
+                if (kx >= 0 && kx < 8) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) h[o][k] += v[k] * P.ux[kx];
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < 4; o++) hb[(4 * warp + o) * M3_HP + lane] = make_float4(h[o][0], h[o][1], h[o][2], h[o][3]);
+    }
+    __syncthreads();
+    // ---- vertical pass (rows ascending), un-weighting, encode: thread = (column, output rows 2 p and 2 p + 1)
+    const int x = lane, p = warp;
+    if (x >= tw || 2 * p >= th) return;
+    const float4* col = hb + x * M3_HP + 4 * p;
+    float4 in[10];
+#pragma unroll
+    for (int j = 0; j < 10; j++) in[j] = col[j];
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const int y = 2 * p + half;
+        if (y >= th) break;
+        float acc[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int ky = 0; ky < 8; ky++) {
+            const float4 v = in[2 * half + ky];
+            acc[0] += v.x * P.uy[ky];
+            acc[1] += v.y * P.uy[ky];
+            acc[2] += v.z * P.uy[ky];
+            acc[3] += v.w * P.uy[ky];
+        }
+        if (HAS_A && P.weight) {
+            const float a = acc[3];
+            const float r = a != 0 ? 1.0f / a : 0.0f;
+            acc[0] *= r; acc[1] *= r; acc[2] *= r;
+        }
+        uint8_t o[4];
+#pragma unroll
+        for (int k = 0; k < 3; k++) o[k] = P.srgb ? encode_srgb8(acc[k]) : encode_linear8(acc[k]);
+        o[3] = (P.srgb && !HAS_A) ? encode_srgb8(acc[3]) : encode_linear8(acc[3]);
+        *(uchar4*)(P.dst + ((size_t)(oy0 + y) * P.out_w + ox0 + x) * 4) = make_uchar4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream)
 {
+    if (P.uniform && P.tileOk && !f32 && channels == 4 && P.Tx == 8 && P.Ty == 8 && !getenv("HKBCN_MIP_TILE2")) {
+        const dim3 grid3((unsigned)(P.out_w + M3_W - 1) / M3_W, (unsigned)(P.out_h + M3_H - 1) / M3_H);
+        if (P.alpha == 3) mip_resize_rgba8_t8_kernel<true><<<grid3, 256, 0, stream>>>(P);
+        else if (P.alpha < 0) mip_resize_rgba8_t8_kernel<false><<<grid3, 256, 0, stream>>>(P);
+        else return cudaErrorInvalidValue;
+        return cudaGetLastError();
+    }
     if (P.uniform && P.tileOk) {
         const dim3 grid2((unsigned)(P.out_w + 31) / 32, (unsigned)(P.out_h + 7) / 8);
         const bool t8 = P.Tx == 8 && P.Ty == 8;
