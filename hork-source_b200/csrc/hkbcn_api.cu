@@ -763,6 +763,8 @@ static void set_tile_taps(ResizeParams& P, const Device::Taps& tx, const Device:
     P.x0 = tx.first0;
     P.y0 = ty.first0;
     for (int k = 0; k < 8; k++) { P.ux[k] = tx.u[k]; P.uy[k] = ty.u[k]; }
+    for (int k = 0; k < 16; k++) { P.ux2[k] = tx.u[k / 2]; P.uy2[k] = ty.u[k / 2]; }
+    P.zero2[0] = P.zero2[1] = 0.0f;
 }
 
 // slices > 1: d_chain is in ImageStorage order (all slices of level 0, then of level 1, ...) and every slice runs its own cascade

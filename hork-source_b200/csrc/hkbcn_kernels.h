@@ -62,6 +62,8 @@ struct ResizeParams {
     // Tx inputs 2 * i + x0 .. with the same weights ux[]): the register-blocked tile kernel applies
     int            uniform, x0, y0;
     float          ux[8], uy[8];
+    // every weight twice (the 64-bit operand of a packed f32x2 instruction) and a +0.0 pair that ptxas cannot fold
+    float          ux2[16], uy2[16], zero2[2];
 };
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
 // any size to any size, 1..4 channels, alpha weighting for float images too (ResampleRawImage): one thread per output texel

@@ -708,6 +708,16 @@ __global__ void __launch_bounds__(256, 3) mip_resize_tile2_kernel(const ResizePa
 constexpr int M3_W = 32, M3_H = 13, M3_SX = 2 * M3_W + 6, M3_SY = 2 * M3_H + 6, M3_P = 76, M3_HP = 33;
 static_assert(M3_SY == 32, "one staged row per lane");
 
+// packed f32x2 arithmetic (two channels of a texel per instruction, each half rounded as the scalar instruction rounds).
+// ptxas contracts mul.f32x2 + add.f32x2 into one FFMA2 whatever -fmad says, so a product that is then added is taken as
+// fma(a, b, +0) with the zero pair coming from a kernel parameter: round(a * b), as the multiply gives it (a -0 product
+// would become +0, and added to an accumulator that started at +0 either gives the same sum).
+typedef unsigned long long fp2;
+__device__ __forceinline__ fp2 m_pack2(float a, float b) { fp2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void m_unpack2(fp2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ fp2 m_fma2(fp2 a, fp2 b, fp2 c) { fp2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ fp2 m_add2(fp2 a, fp2 b) { fp2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ fp2 m_mul2(fp2 a, fp2 b) { fp2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 #ifndef M3_MINB
 #define M3_MINB 6  // resident CTAs per SM asked of ptxas (40 registers)
 #endif
@@ -729,12 +739,27 @@ __global__ void __launch_bounds__(256, M3_MINB) mip_resize_rgba8_t8_kernel(const
     if (tid < sx) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
     if (tid >= 128 && tid < 128 + sy) s_my[tid - 128] = P.mapy[ny_lo + tid - 128 + P.marginy];
     __syncthreads();
-    // ---- stage
-    {
-        const float inv_sx = 1.0f / (float)sx;
+    // ---- stage: word c of staged row r goes to raw[r * M3_P + c + 1] (the + 1 makes the 16-byte groups of an interior tile,
+    // whose first texel 2 ox0 - 3 sits one word past a 16-byte boundary of the image row, land on 16-byte boundaries here)
+    const int ax = nx_lo - 1;
+    if (tw == M3_W && (ax & 3) == 0 && ax >= 0 && ax + 72 <= P.in_w && (P.in_w & 3) == 0 && ((uintptr_t)P.src & 15) == 0) {
+        // interior in x: 18 aligned 16-byte loads per row, all of a thread's loads in flight before the first store
+        uint4 v[3];
+        int at[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const int i = tid + 256 * k, r = (i * 3641) >> 16, g = i - 18 * r; // i / 18 for i < 768
+            at[k] = r < sy ? r * M3_P + 4 * g : -1;
+            if (r < sy) v[k] = __ldg((const uint4*)(P.src + ((size_t)s_my[r] * P.in_w + ax + 4 * g) * 4));
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+            if (at[k] >= 0) *(uint4*)(raw + at[k]) = v[k];
+    } else {
+        const uint32_t magic = ((1u << 20) + (uint32_t)sx - 1) / (uint32_t)sx; // i / sx = i * magic >> 20 for i < 32 sx, 8 <= sx <= 70
         for (int i = tid; i < sy * sx; i += 256) {
-            const int r = (int)(((float)i + 0.5f) * inv_sx), c = i - r * sx; // i < 2240: the float quotient is exact enough to floor
-            raw[r * M3_P + c] = __ldg((const uint32_t*)(P.src + ((size_t)s_my[r] * P.in_w + s_mx[c]) * 4));
+            const int r = (int)(((uint32_t)i * magic) >> 20), c = i - r * sx;
+            raw[r * M3_P + c + 1] = __ldg((const uint32_t*)(P.src + ((size_t)s_my[r] * P.in_w + s_mx[c]) * 4));
         }
     }
     __syncthreads();
@@ -747,59 +772,59 @@ __global__ void __launch_bounds__(256, M3_MINB) mip_resize_rgba8_t8_kernel(const
             const uint4 v = *(const uint4*)(row + 4 * j);
             q[4 * j + 0] = v.x; q[4 * j + 1] = v.y; q[4 * j + 2] = v.z; q[4 * j + 3] = v.w;
         }
-        float h[4][4];
+        const fp2 Z = *(const fp2*)P.zero2;
+        fp2 h01[4], h23[4];
 #pragma unroll
-        for (int o = 0; o < 4; o++)
-#pragma unroll
-            for (int k = 0; k < 4; k++) h[o][k] = 0;
+        for (int o = 0; o < 4; o++) h01[o] = h23[o] = Z;
         // input t of the group feeds output o as its tap t - 2 o; inputs ascending per output
 #pragma unroll
         for (int t = 0; t < 14; t++) {
-            float v[4];
-            const uint32_t w = q[t];
-            const int b[4] = {(int)(w & 255u), (int)((w >> 8) & 255u), (int)((w >> 16) & 255u), (int)(w >> 24)};
-#pragma unroll
-            for (int k = 0; k < 3; k++) v[k] = lut[b[k]];
-            v[3] = (HAS_A ? alut : lut)[b[3]];
+            const uint32_t w = q[t + 1];
+            const float v0 = lut[w & 255u], v1 = lut[(w >> 8) & 255u], v2 = lut[(w >> 16) & 255u];
+            float v3 = (HAS_A ? alut : lut)[w >> 24];
+            fp2 v01 = m_pack2(v0, v1), v23;
             if (HAS_A && P.weight) {
                 // alpha weighting (:1375-1400): the epsilon keeps the colour of fully transparent texels
-                const float a = v[3] + 1.0f / (1 << 20) / (1 << 20) / (1 << 20) / (1 << 20);
-                v[0] *= a; v[1] *= a; v[2] *= a;
-                v[3] = a;
-            }
+                v3 += 1.0f / (1 << 20) / (1 << 20) / (1 << 20) / (1 << 20);
+                v01 = m_mul2(v01, m_pack2(v3, v3));
+                v23 = m_pack2(v2 * v3, v3);
+            } else v23 = m_pack2(v2, v3);
 #pragma unroll
             for (int o = 0; o < 4; o++) {
                 const int kx = t - 2 * o;
                 if (kx >= 0 && kx < 8) {
-#pragma unroll
-                    for (int k = 0; k < 4; k++) h[o][k] += v[k] * P.ux[kx];
+                    const fp2 W = *(const fp2*)(P.ux2 + 2 * kx);
+                    h01[o] = m_add2(h01[o], m_fma2(v01, W, Z));
+                    h23[o] = m_add2(h23[o], m_fma2(v23, W, Z));
                 }
             }
         }
 #pragma unroll
-        for (int o = 0; o < 4; o++) hb[(4 * warp + o) * M3_HP + lane] = make_float4(h[o][0], h[o][1], h[o][2], h[o][3]);
+        for (int o = 0; o < 4; o++) *(ulonglong2*)(hb + (4 * warp + o) * M3_HP + lane) = make_ulonglong2(h01[o], h23[o]);
     }
     __syncthreads();
     // ---- vertical pass (rows ascending), un-weighting, encode: thread = (column, output rows 2 p and 2 p + 1)
     const int x = lane, p = warp;
     if (x >= tw || 2 * p >= th) return;
-    const float4* col = hb + x * M3_HP + 4 * p;
-    float4 in[10];
+    const ulonglong2* col = (const ulonglong2*)(hb + x * M3_HP + 4 * p);
+    ulonglong2 in[10];
 #pragma unroll
     for (int j = 0; j < 10; j++) in[j] = col[j];
+    const fp2 Z = *(const fp2*)P.zero2;
 #pragma unroll
     for (int half = 0; half < 2; half++) {
         const int y = 2 * p + half;
         if (y >= th) break;
-        float acc[4] = {0, 0, 0, 0};
+        fp2 a01 = Z, a23 = Z;
 #pragma unroll
         for (int ky = 0; ky < 8; ky++) {
-            const float4 v = in[2 * half + ky];
-            acc[0] += v.x * P.uy[ky];
-            acc[1] += v.y * P.uy[ky];
-            acc[2] += v.z * P.uy[ky];
-            acc[3] += v.w * P.uy[ky];
+            const fp2 W = *(const fp2*)(P.uy2 + 2 * ky);
+            a01 = m_add2(a01, m_fma2(in[2 * half + ky].x, W, Z));
+            a23 = m_add2(a23, m_fma2(in[2 * half + ky].y, W, Z));
         }
+        float acc[4];
+        m_unpack2(a01, acc[0], acc[1]);
+        m_unpack2(a23, acc[2], acc[3]);
         if (HAS_A && P.weight) {
             const float a = acc[3];
             const float r = a != 0 ? 1.0f / a : 0.0f;
