@@ -734,15 +734,22 @@ __global__ void __launch_bounds__(256, M3_MINB) mip_resize_rgba8_t8_kernel(const
     const int tw = min(M3_W, P.out_w - ox0), th = min(M3_H, P.out_h - oy0);
     const int nx_lo = 2 * ox0 + P.x0, sx = 2 * (tw - 1) + 8;
     const int ny_lo = 2 * oy0 + P.y0, sy = 2 * (th - 1) + 8;
-    lut[tid] = P.lut[tid];
-    alut[tid] = (float)tid / 255.0f;
-    if (tid < sx) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
-    if (tid >= 128 && tid < 128 + sy) s_my[tid - 128] = P.mapy[ny_lo + tid - 128 + P.marginy];
-    __syncthreads();
+    {
+        const float v = P.lut[tid];
+        lut[tid] = v;
+        alut[tid] = P.srgb ? (float)tid / 255.0f : v; // the linear table is v / 255 itself
+    }
+    const int ax = nx_lo - 1;
+    const bool interior = tw == M3_W && (ax & 3) == 0 && ax >= 0 && ax + 72 <= P.in_w && (P.in_w & 3) == 0 && ((uintptr_t)P.src & 15) == 0;
+    const int* __restrict__ my = P.mapy + ny_lo + P.marginy;
+    if (!interior) {
+        if (tid < sx) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
+        if (tid >= 128 && tid < 128 + sy) s_my[tid - 128] = my[tid - 128];
+        __syncthreads();
+    }
     // ---- stage: word c of staged row r goes to raw[r * M3_P + c + 1] (the + 1 makes the 16-byte groups of an interior tile,
     // whose first texel 2 ox0 - 3 sits one word past a 16-byte boundary of the image row, land on 16-byte boundaries here)
-    const int ax = nx_lo - 1;
-    if (tw == M3_W && (ax & 3) == 0 && ax >= 0 && ax + 72 <= P.in_w && (P.in_w & 3) == 0 && ((uintptr_t)P.src & 15) == 0) {
+    if (interior) {
         // interior in x: 18 aligned 16-byte loads per row, all of a thread's loads in flight before the first store
         uint4 v[3];
         int at[3];
@@ -750,7 +757,7 @@ __global__ void __launch_bounds__(256, M3_MINB) mip_resize_rgba8_t8_kernel(const
         for (int k = 0; k < 3; k++) {
             const int i = tid + 256 * k, r = (i * 3641) >> 16, g = i - 18 * r; // i / 18 for i < 768
             at[k] = r < sy ? r * M3_P + 4 * g : -1;
-            if (r < sy) v[k] = __ldg((const uint4*)(P.src + ((size_t)s_my[r] * P.in_w + ax + 4 * g) * 4));
+            if (r < sy) v[k] = __ldg((const uint4*)(P.src + ((size_t)__ldg(my + r) * P.in_w + ax + 4 * g) * 4));
         }
 #pragma unroll
         for (int k = 0; k < 3; k++)
