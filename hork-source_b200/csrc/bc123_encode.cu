@@ -15,13 +15,17 @@
 #include "hkbcn_kernels.h"
 #include "bc4_search.cuh"
 #include "bc1_block.cuh"
+#include "bc1_hq.cuh"
+#include "build/bc1_orderings.inc"
 #include <stdio.h>
 #include <stdlib.h>
 #include <math.h>
+#include <string.h>
 
 namespace hkbcn {
 
-template <int CODEC>
+// HQ: the colour block goes through the error-tracking branch of bc1_hq.cuh (levels 6..18, level 5 with a 3-colour flag)
+template <int CODEC, bool HQ>
 __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant__ EncodeParams P)
 {
     constexpr int NT = 128;
@@ -42,6 +46,10 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
     // HKBCN_FLAG_LEVEL: rgbcx level + 1 in bits 4..8 (0 = the Compress* preset, level 5); HKBCN_FLAG_FAST: non-hq BC3 alpha
     const int level = ((P.flags >> 4) & 31u) ? (int)((P.flags >> 4) & 31u) - 1 : 5;
     const bool fastAlpha = (P.flags & 2u) != 0;
+    // Encode_BC2 / Encode_BC3 pass (false, false) for the 3-colour options (ImageEncoders.cpp:158, rgbcx.cpp:2897-2911)
+    uint32_t to4 = 1, to3 = 1;
+    const uint32_t rflags = HQ ? bc1_level_flags(level, CODEC == C_BC1 && (P.flags & (1u << 9)), CODEC == C_BC1 && (P.flags & (1u << 10)), to4, to3) : 0u;
+    auto colour_block = [&](const uint32_t* px16) { return HQ ? bc1_hq_encode_block(px16, rflags, to4, to3) : bc1_encode_block(px16, level); };
 
     for (uint32_t tile = blockIdx.x; tile < P.totalTiles; tile += gridDim.x) {
         const Level& L = P.lv[find_level(P, tile)];
@@ -63,7 +71,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
         }
 
         if (CODEC == C_BC1) {
-            if (valid) *(uint2*)(L.dst + (size_t)(b0 + k) * 8) = bc1_encode_block(px, level);
+            if (valid) *(uint2*)(L.dst + (size_t)(b0 + k) * 8) = colour_block(px);
         } else if (CODEC == C_BC2) {
             if (valid) {
                 uint32_t a[2] = {0, 0};
@@ -74,7 +82,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
                     q = min(q, 15);
                     a[i >> 3] |= (uint32_t)q << (4 * (i & 7));
                 }
-                uint2 c = bc1_encode_block(px, level);
+                uint2 c = colour_block(px);
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(a[0], a[1], c.x, c.y);
             }
         } else { // BC3
@@ -93,7 +101,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
             if (valid && sub == 0) {
                 // bMaxQuality = false: rgbcx::encode_bc3 = the non-hq encode_bc4 on alpha (rgbcx.cpp:2886-2903)
                 uint2 al = fastAlpha ? bc4_fast(a2, minv, maxv) : (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
-                uint2 c = bc1_encode_block(px, level);
+                uint2 c = colour_block(px);
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(al.x, al.y, c.x, c.y);
             }
         }
@@ -138,6 +146,43 @@ static void gen_mid(float* out, int size)
     out[size - 1] = 1e+37f;
 }
 
+// the same search keeping the error, for the 2/3-1/3 interpolant (prepare_bc1_single_color_table, :485-522) or the midpoint
+// (prepare_bc1_single_color_table_half, :447-483): hi | lo << 8 | e << 16
+static void gen_match_e(uint32_t* out, int size, bool half)
+{
+    uint8_t expand[64];
+    for (int i = 0; i < size; i++) expand[i] = (uint8_t)(size == 32 ? ((i << 3) | (i >> 2)) : ((i << 2) | (i >> 4)));
+    for (int i = 0; i < 256; i++) {
+        int lowest = 256, bh = 0, bl = 0;
+        for (int lo = 0; lo < size; lo++) {
+            for (int hi = 0; hi < size; hi++) {
+                const int lo_e = expand[lo], hi_e = expand[hi];
+                const int v = half ? (hi_e + lo_e) / 2 : (hi_e * 2 + lo_e) / 3;
+                const int e = abs(v - i) + (abs(hi_e - lo_e) * 3) / 100;
+                if (e < lowest || (e == lowest && lo == hi)) { bh = hi; bl = lo; lowest = e; }
+            }
+        }
+        out[i] = (uint32_t)(bh | (bl << 8) | (lowest << 16));
+    }
+}
+// compute_selector_factors4 / 3 (rgbcx.cpp:529-571): the inverse of the 2 x 2 normal matrix of a selector histogram
+static void selector_factors(const uint8_t* hist, int n, float* out)
+{
+    static const uint32_t w4[4] = {0x000009, 0x010204, 0x040201, 0x090000}, w3[3] = {0x000004, 0x040000, 0x010101};
+    uint32_t acc = 0;
+    for (int s = 0; s < n; s++) acc += (n == 4 ? w4[s] : w3[s]) * hist[s];
+    const float z00 = (float)((acc >> 16) & 0xFF), z10 = (float)((acc >> 8) & 0xFF), z11 = (float)(acc & 0xFF), z01 = z10;
+    volatile float a = z00 * z11, b = z01 * z10; // two rounded products, as the reference's baseline x86-64 build computes them
+    float det = a - b;
+    if (fabsf(det) < 1e-8f) det = 0.0f;
+    else det = ((n == 4 ? 3.0f : 2.0f) / 255.0f) / det;
+    out[0] = z11 * det;
+    out[1] = -z10 * det;
+    out[2] = z00 * det;
+}
+
+bool bc1_hq_available() { return HK_HAVE_BC1_ORDERINGS != 0; }
+
 cudaError_t bc1_upload_tables()
 {
     uint16_t m5[256], m6[256];
@@ -150,7 +195,50 @@ cudaError_t bc1_upload_tables()
     if ((e = cudaMemcpyToSymbol(g_bc1_match5, m5, sizeof(m5))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(g_bc1_match6, m6, sizeof(m6))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(g_bc1_mid5, mid5, sizeof(mid5))) != cudaSuccess) return e;
-    return cudaMemcpyToSymbol(g_bc1_mid6, mid6, sizeof(mid6));
+    if ((e = cudaMemcpyToSymbol(g_bc1_mid6, mid6, sizeof(mid6))) != cudaSuccess) return e;
+    uint32_t t[256];
+    gen_match_e(t, 32, false);
+    if ((e = cudaMemcpyToSymbol(g_hq_eq5, t, sizeof(t))) != cudaSuccess) return e;
+    gen_match_e(t, 64, false);
+    if ((e = cudaMemcpyToSymbol(g_hq_eq6, t, sizeof(t))) != cudaSuccess) return e;
+    gen_match_e(t, 32, true);
+    if ((e = cudaMemcpyToSymbol(g_hq_half5, t, sizeof(t))) != cudaSuccess) return e;
+    gen_match_e(t, 64, true);
+    if ((e = cudaMemcpyToSymbol(g_hq_half6, t, sizeof(t))) != cudaSuccess) return e;
+#if HK_HAVE_BC1_ORDERINGS
+    // rgbcx::init (:591-625): histogram -> index, and the least-squares factors of every histogram
+    static uint16_t hash4[4096], hash3[256];
+    static float fac4[HQ_N4 * 3], fac3[HQ_N3 * 3];
+    memset(hash4, 0, sizeof(hash4));
+    memset(hash3, 0, sizeof(hash3));
+    for (int i = 0; i < HQ_N4; i++) {
+        const uint8_t* h = HK_ORDERS4[i];
+        if (h[0] != 16 && h[1] != 16 && h[2] != 16 && h[3] != 16) hash4[h[0] | (h[1] << 4) | (h[2] << 8)] = (uint16_t)i;
+        selector_factors(h, 4, fac4 + 3 * i);
+    }
+    for (int i = 0; i < HQ_N3; i++) {
+        const uint8_t* h = HK_ORDERS3[i];
+        if (h[0] != 16 && h[1] != 16 && h[2] != 16) hash3[h[0] | (h[1] << 4)] = (uint16_t)i;
+        selector_factors(h, 3, fac3 + 3 * i);
+    }
+    if ((e = cudaMemcpyToSymbol(g_hq_orders4, HK_ORDERS4, sizeof(HK_ORDERS4))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_best4, HK_BEST4, sizeof(HK_BEST4))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_hash4, hash4, sizeof(hash4))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_fac4, fac4, sizeof(fac4))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_orders3, HK_ORDERS3, sizeof(HK_ORDERS3))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_best3, HK_BEST3, sizeof(HK_BEST3))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_hash3, hash3, sizeof(hash3))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_fac3, fac3, sizeof(fac3))) != cudaSuccess) return e;
+#endif
+    return cudaSuccess;
+}
+
+// the branch of rgbcx::encode_bc1 a launch takes: levels 6..18 always track the block error, level 5 when a 3-colour option
+// is on (BC1 only -- Encode_BC2 / Encode_BC3 never pass one); below 5 the options are not read (rgbcx.cpp:1700-1726)
+bool bc123_needs_hq(int codec, uint32_t flags)
+{
+    const int level = ((flags >> 4) & 31u) ? (int)((flags >> 4) & 31u) - 1 : 5;
+    return level >= 6 || (level == 5 && codec == C_BC1 && (flags & ((1u << 9) | (1u << 10))) != 0);
 }
 
 cudaError_t launch_bc123_encode(int codec, const EncodeParams& P, int sm_count, cudaStream_t stream)
@@ -158,9 +246,16 @@ cudaError_t launch_bc123_encode(int codec, const EncodeParams& P, int sm_count, 
     if (P.totalTiles == 0) return cudaSuccess;
     uint32_t g = (uint32_t)sm_count * 8;
     int grid = (int)(P.totalTiles < g ? P.totalTiles : g);
-    if (codec == C_BC1) bc123_encode_kernel<C_BC1><<<grid, 128, 0, stream>>>(P);
-    else if (codec == C_BC2) bc123_encode_kernel<C_BC2><<<grid, 128, 0, stream>>>(P);
-    else bc123_encode_kernel<C_BC3><<<grid, 128, 0, stream>>>(P);
+    if (bc123_needs_hq(codec, P.flags)) {
+        if (!bc1_hq_available()) return cudaErrorNotSupported;
+        if (codec == C_BC1) bc123_encode_kernel<C_BC1, true><<<grid, 128, 0, stream>>>(P);
+        else if (codec == C_BC2) bc123_encode_kernel<C_BC2, true><<<grid, 128, 0, stream>>>(P);
+        else bc123_encode_kernel<C_BC3, true><<<grid, 128, 0, stream>>>(P);
+        return cudaGetLastError();
+    }
+    if (codec == C_BC1) bc123_encode_kernel<C_BC1, false><<<grid, 128, 0, stream>>>(P);
+    else if (codec == C_BC2) bc123_encode_kernel<C_BC2, false><<<grid, 128, 0, stream>>>(P);
+    else bc123_encode_kernel<C_BC3, false><<<grid, 128, 0, stream>>>(P);
     return cudaGetLastError();
 }
 

@@ -257,11 +257,15 @@ int launch_encode(Device* D, int fmt, int codec, const EncodeParams& P0, cudaStr
     if (P0.totalTiles == 0) return HKBCN_OK;
     if (P0.flags & HKBCN_FLAG_LEVEL_MASK) {
         const int level = (int)((P0.flags & HKBCN_FLAG_LEVEL_MASK) >> 4) - 1;
-        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? level <= 5 : codec == C_BC7 ? level <= 4 : false;
+        const bool ok = (codec == C_BC1 || codec == C_BC2 || codec == C_BC3) ? level <= 18 : codec == C_BC7 ? level <= 4 : false;
         if (!ok) {
-            set_err("quality level %d of format %d is not built (BC1/2/3: 0..5; BC7: 0..4; see hkbcn.h)", level, fmt);
+            set_err("quality level %d of format %d does not exist (BC1/2/3: 0..18; BC7: 0..4; see hkbcn.h)", level, fmt);
             return HKBCN_ERR_UNSUPPORTED;
         }
+    }
+    if ((codec == C_BC1 || codec == C_BC2 || codec == C_BC3) && bc123_needs_hq(codec, P0.flags) && !bc1_hq_available()) {
+        set_err("BC1/2/3 levels 6..18 and the 3-colour options need rgbcx's total-ordering tables; this libhkbcn.so was built without them (csrc/Makefile: RGBCX_DIR)");
+        return HKBCN_ERR_UNSUPPORTED;
     }
     EncodeParams P = P0;
     if (!(P.sched = sched_slot(D, st))) return HKBCN_ERR_CUDA;

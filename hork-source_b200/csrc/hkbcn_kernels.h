@@ -13,7 +13,9 @@ cudaError_t launch_bc45_encode(int channels, const EncodeParams& P, int sm_count
 
 uint32_t bc123_tile_blocks(int codec);
 cudaError_t launch_bc123_encode(int codec, const EncodeParams& P, int sm_count, cudaStream_t stream);
-cudaError_t bc1_upload_tables(); // a12: single-colour match + 565 midpoint tables
+cudaError_t bc1_upload_tables(); // a12: single-colour match + 565 midpoint tables; the orderings tables of levels 6..18
+bool bc1_hq_available();           // the library was built with rgbcx's total-ordering tables (build/bc1_orderings.inc)
+bool bc123_needs_hq(int codec, uint32_t flags); // this level / option set takes the error-tracking branch (bc1_hq.cuh)
 
 uint32_t bc7_tile_blocks();
 // P.aux: bc7_aux_bytes(blocks of the launch) bytes of device scratch whose first 16 bytes are zero (the kernels leave them zero)

@@ -19,11 +19,6 @@ void Check(int rc, const char* what)
     fprintf(stderr, "Hk::TextureBlockCompression::%s failed (%d): %s\n", what, rc, hkbcn_last_error());
     abort(); // the reference API has no error channel and this path has no CPU fallback
 }
-[[noreturn]] void Unsupported(const char* what)
-{
-    fprintf(stderr, "Hk::TextureBlockCompression::%s: only the presets baked into Compress* are implemented on the device\n", what);
-    abort();
-}
 } // namespace
 
 void Decode_BC1(void const* s, void* d, size_t RowStride) { Check(hkbcn_decode_blocks(HKBCN_BC1_UNORM, s, d, 1, RowStride, 0), "Decode_BC1"); }
@@ -41,12 +36,12 @@ void Decode_BC6h_f32(void const* s, void* d, size_t RowStride, bool bSigned)
 }
 void Decode_BC7(void const* s, void* d, size_t RowStride) { Check(hkbcn_decode_blocks(HKBCN_BC7_UNORM, s, d, 1, RowStride, 0), "Decode_BC7"); }
 
-// Levels: rgbcx levels 0..5 are built (everything below the total-orderings search); the library answers
-// HKBCN_ERR_UNSUPPORTED for the others and for the 3-colour flags (levels >= 5 only read them), which Check() turns into an abort.
+// Levels 0..18 of rgbcx and both 3-colour options (read at levels >= 5, as in rgbcx::encode_bc1).  A library built without
+// rgbcx's total-ordering tables answers HKBCN_ERR_UNSUPPORTED above level 5, which Check() turns into an abort.
 void Encode_BC1(void const* s, void* d, uint32_t Level, bool b3ColorMode, bool bTransparentPixelsForBlack)
 {
-    if (Level >= 5 && (b3ColorMode || bTransparentPixelsForBlack)) Unsupported("Encode_BC1 (3-colour modes)");
-    Check(hkbcn_encode_blocks(HKBCN_BC1_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level)), "Encode_BC1");
+    const uint32_t opts = (b3ColorMode ? (uint32_t)HKBCN_FLAG_BC1_3COLOR : 0u) | (bTransparentPixelsForBlack ? (uint32_t)HKBCN_FLAG_BC1_TRANSPARENT_BLACK : 0u);
+    Check(hkbcn_encode_blocks(HKBCN_BC1_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level) | opts), "Encode_BC1");
 }
 void Encode_BC2(void const* s, void* d, uint32_t Level) { Check(hkbcn_encode_blocks(HKBCN_BC2_UNORM, s, d, 1, HKBCN_FLAG_LEVEL(Level)), "Encode_BC2"); }
 void Encode_BC3(void const* s, void* d, uint32_t Level, bool bMaxQuality)

@@ -22,6 +22,8 @@ BC4_UNORM, BC4_SNORM, BC5_UNORM, BC5_SNORM, BC6H_UFLOAT, BC6H_SFLOAT, BC7_UNORM,
 FLAG_SRC_F16 = 1 << 0
 FLAG_FAST = 1 << 1
 FLAG_DST_F32 = 1 << 8
+FLAG_BC1_3COLOR = 1 << 9
+FLAG_BC1_TRANSPARENT_BLACK = 1 << 10
 FLAG_SKIP_EXISTING = 1 << 16
 FLAG_SRC_DEVICE = 1 << 17
 

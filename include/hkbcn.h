@@ -71,9 +71,16 @@ enum {
     HKBCN_FLAG_FAST        = 1u << 1, /* BC4/BC5/BC3-alpha: non-hq encoder (bMaxQuality=false, ImageEncoders.cpp:161-185) */
     /* bits 4..8: quality level of Encode_BC1/2/3(Level) and Encode_BC7(Level) (ImageEncoders.cpp:138-169, 207-212), stored
      * as level + 1; 0 = the preset the Compress* functions bake in (BC1/2/3 level 5, BC7 level 4).  Use HKBCN_FLAG_LEVEL(n).
-     * Built: BC1/2/3 levels 0..5 (the rgbcx levels below the total-orderings search: rgbcx.cpp:1692-1726) and BC7 levels
-     * 0..4.  BC1/2/3 levels 6..18, and the 3-colour flags of Encode_BC1, return HKBCN_ERR_UNSUPPORTED. */
+     * Built: BC1/2/3 levels 0..18 (every level Hork's BC1/2/3_ENCODE_MAX_LEVEL admits, rgbcx.cpp:1692-1811) and BC7 levels
+     * 0..4.  BC1/2/3 levels 6..18 and the two 3-colour options need rgbcx's total-ordering tables, which are data of the
+     * engine's ThirdParty/bc7enc_rdo and are taken from the engine tree when the library is built (csrc/Makefile: RGBCX_DIR);
+     * a library built without them answers HKBCN_ERR_UNSUPPORTED for those. */
     HKBCN_FLAG_LEVEL_MASK  = 31u << 4,
+    /* Encode_BC1(.., b3ColorMode, bTransparentPixelsForBlack) (ImageEncoders.cpp:138-143): BC1 only, read at levels >= 5 as in
+     * rgbcx::encode_bc1 (levels 0..4 ignore them; Encode_BC2 / Encode_BC3 never pass them).  Blocks may then come out in
+     * 3-colour mode (colour0 <= colour1), with selector 3 = transparent black when the second option is on. */
+    HKBCN_FLAG_BC1_3COLOR  = 1u << 9,
+    HKBCN_FLAG_BC1_TRANSPARENT_BLACK = 1u << 10,
     HKBCN_FLAG_SRC_DEVICE  = 1u << 17, /* hkbcn_import_batch: src_level0 is DEVICE memory on the GPU hkbcn_plan_import_batch assigns the
                                           job to (sources produced on the device never cross PCIe); the default is host memory */
     HKBCN_FLAG_SRC_CHAIN   = 1u << 18, /* hkbcn_import_batch: src_level0 holds the whole uncompressed chain (hkbcn_chain_src_bytes() bytes, e.g. built

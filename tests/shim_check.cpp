@@ -125,6 +125,11 @@ int main(int argc, char** argv)
             TBC::Encode_BC1(blk, g16, lvl, true, true); ref_encode_bc1_level(blk, w16, lvl, 1, 1); expect_equal("Encode_BC1 level 0..3", g16, w16, 8);
             TBC::Encode_BC7(blk, g16, lvl);             ref_encode_bc7_level(blk, w16, lvl);       expect_equal("Encode_BC7 level 0..3", g16, w16, 16);
             TBC::Encode_BC1(blk, g16, 4, true, true);   ref_encode_bc1_level(blk, w16, 4, 1, 1);   expect_equal("Encode_BC1 level 4", g16, w16, 8);
+            // the levels with the total-orderings search and the 3-colour options (read from level 5 up)
+            const uint32_t hi = 5 + (uint32_t)(t * 7 % 14);
+            if (t & 2) for (int i = 0; i < 16; i += 3) blk[4 * i] = blk[4 * i + 1] = blk[4 * i + 2] = (uint8_t)(i & 3); // near-black texels
+            TBC::Encode_BC1(blk, g16, hi, (t & 1) != 0, (t & 2) != 0); ref_encode_bc1_level(blk, w16, hi, t & 1, (t & 2) >> 1); expect_equal("Encode_BC1 level 5..18 with options", g16, w16, 8);
+            TBC::Encode_BC2(blk, g16, hi); ref_encode_bc1_level(blk, w16 + 8, hi, 0, 0); expect_equal("Encode_BC2 level 5..18 (colour)", g16 + 8, w16 + 8, 8);
             {
                 uint8_t al[16];
                 for (int i = 0; i < 16; i++) al[i] = blk[4 * i + 3];
