@@ -55,6 +55,7 @@ struct Device {
     // pageable callers (Image.cpp hands over HeapBlob memory): upload ring of two pinned pieces, a pinned copy of the output,
     // a copy stream and events -- see compress_host_pipelined
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t stream2 = nullptr; // second encode stream of the piece pipeline (compress_host_pipelined)
     void*        h_in[2] = {nullptr, nullptr}; size_t h_in_cap[2] = {0, 0};
     void*        h_out = nullptr; size_t h_out_cap = 0;
     cudaEvent_t  ev_in[2] = {nullptr, nullptr};
@@ -339,13 +340,22 @@ size_t chain_src_bytes(int codec, uint32_t flags, uint32_t w, uint32_t h, uint32
     return n;
 }
 
-// Host-pointer compress of a large PAGEABLE surface or chain.  The copy engine cannot read pageable memory: a plain
-// cudaMemcpyAsync from it is staged by the driver and serialises with everything else (27.6 ms for the 4096^2 BC7 chain
-// against 21.0 ms from pinned memory).  Here the chain is cut into pieces -- bands of block rows of level 0, then levels 1..
-// together -- and each piece is copied by this thread into one of two pinned buffers, uploaded on a copy stream and encoded
-// by its own launch as soon as it has arrived, so the staging copy of piece i + 1 runs under the kernel of piece i; outputs
-// come back through a pinned buffer the same way.  Same kernels, same bytes out.
-int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, uint8_t* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags)
+// the device cascade (generate_mips_on, defined with the mip entry points below), handed in by the import form
+typedef int (*MipCascadeFn)(Device* D, int fmt, void* d_chain, uint32_t w, uint32_t h, uint32_t mips, const hkbcn_mip_config* cfg, uint32_t flags,
+                            cudaStream_t st, uint32_t slices);
+
+// Host-pointer compress of a large surface or chain, cut into pieces -- bands of block rows of level 0, then levels 1..
+// together -- each uploaded on a copy stream and encoded by its own launch as soon as it has arrived, so the upload of piece
+// i + 1 runs under the kernel of piece i and the blocks of piece i go back under the kernel of piece i + 1.
+//   pinned source / destination: the copy engine reads and writes the caller's buffers directly;
+//   PAGEABLE ones: the copy engine cannot touch them -- a plain cudaMemcpyAsync is staged by the driver and serialises with
+//     everything else (27.6 ms for the 4096^2 BC7 chain against 21.0 ms from pinned memory) -- so this thread copies each
+//     piece through one of two pinned buffers (outputs through a third), still under the kernels;
+//   gen (the import form: src holds level 0 only): after the last band the device cascade builds levels 1.. in place and the
+//     last piece encodes them -- nothing but level 0 crosses PCIe.
+// Same kernels, same bytes out.
+int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, uint8_t* dst, uint32_t w, uint32_t h, uint32_t mips, uint32_t flags,
+                            MipCascadeFn gen = nullptr, const hkbcn_mip_config* gen_cfg = nullptr)
 {
     const uint32_t bpp = src_bpp(codec, flags), bb = blk_bytes(codec);
     struct Piece { size_t soff, sbytes, doff, dbytes; uint32_t lvl0, lvl1, row0, rows; };
@@ -381,28 +391,50 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
     if (pieces.size() > 8) { set_err("internal: too many pieces"); return HKBCN_ERR_BAD_ARG; }
     const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips), dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
     size_t maxp = 0;
-    for (auto& p : pieces) maxp = std::max(maxp, p.sbytes);
+    for (auto& p : pieces)
+        if (!(gen && p.lvl0 > 0)) maxp = std::max(maxp, p.sbytes);
     std::lock_guard<std::mutex> lk(D->mu);
     CK(cudaSetDevice(D->id));
+    const bool src_pinned = is_pinned(src), dst_pinned = is_pinned(dst);
     int rc;
     if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
     if ((rc = grow(&D->d_dst, &D->dst_cap, dbytes)) != HKBCN_OK) return rc;
     for (int i = 0; i < 2; i++) {
-        if ((rc = grow_pinned(&D->h_in[i], &D->h_in_cap[i], maxp)) != HKBCN_OK) return rc;
+        if (!src_pinned && (rc = grow_pinned(&D->h_in[i], &D->h_in_cap[i], maxp)) != HKBCN_OK) return rc;
         if (!D->ev_in[i]) CK(cudaEventCreateWithFlags(&D->ev_in[i], cudaEventDisableTiming));
     }
-    if ((rc = grow_pinned(&D->h_out, &D->h_out_cap, dbytes)) != HKBCN_OK) return rc;
+    if (!dst_pinned && (rc = grow_pinned(&D->h_out, &D->h_out_cap, dbytes)) != HKBCN_OK) return rc;
     if (!D->copy_stream) CK(cudaStreamCreateWithFlags(&D->copy_stream, cudaStreamNonBlocking));
+    if (!D->stream2) CK(cudaStreamCreateWithFlags(&D->stream2, cudaStreamNonBlocking));
+    // Consecutive pieces are launched on two alternating streams: a persistent encoder ends with a round in which SMs run
+    // out of tiles one by one, and on one stream the next piece's kernel could not start until the last of them had finished
+    // (six bands of the BC7 4096^2 level: ~1.5 ms of idle SMs in total); on the other stream its CTAs take over each SM as
+    // it frees up.  Tile counters and the BC7 work list are per stream (sched_slot, bc7_aux).
+    cudaStream_t es[2] = {D->stream, D->stream2};
+    if (getenv("HKBCN_PIPE_ONE_STREAM")) es[1] = D->stream; // A/B timing
     for (size_t i = 0; i < pieces.size(); i++)
         if (!D->ev_piece[i]) CK(cudaEventCreateWithFlags(&D->ev_piece[i], cudaEventDisableTiming));
+    uint8_t* const out = dst_pinned ? dst : (uint8_t*)D->h_out;
     for (size_t i = 0; i < pieces.size(); i++) {
         const Piece& p = pieces[i];
         const int slot = (int)(i & 1);
-        if (i >= 2) CK(cudaEventSynchronize(D->ev_in[slot])); // the slot's previous upload has left it
-        memcpy(D->h_in[slot], src + p.soff, p.sbytes);
-        CK(cudaMemcpyAsync((uint8_t*)D->d_src + p.soff, D->h_in[slot], p.sbytes, cudaMemcpyHostToDevice, D->copy_stream));
-        CK(cudaEventRecord(D->ev_in[slot], D->copy_stream));
-        CK(cudaStreamWaitEvent(D->stream, D->ev_in[slot], 0));
+        cudaStream_t st = es[i & 1];
+        if (gen && p.lvl0 > 0) {
+            // every band is on the device once the copy stream has passed its last upload: build levels 1.. from level 0 there
+            CK(cudaStreamWaitEvent(st, D->ev_in[0], 0));
+            CK(cudaStreamWaitEvent(st, D->ev_in[1], 0));
+            if ((rc = gen(D, fmt, D->d_src, w, h, mips, gen_cfg, flags, st, 1)) != HKBCN_OK) return rc;
+        } else {
+            const uint8_t* from = src + p.soff;
+            if (!src_pinned) {
+                if (i >= 2) CK(cudaEventSynchronize(D->ev_in[slot])); // the slot's previous upload has left it
+                memcpy(D->h_in[slot], src + p.soff, p.sbytes);
+                from = (const uint8_t*)D->h_in[slot];
+            }
+            CK(cudaMemcpyAsync((uint8_t*)D->d_src + p.soff, from, p.sbytes, cudaMemcpyHostToDevice, D->copy_stream));
+            CK(cudaEventRecord(D->ev_in[slot], D->copy_stream));
+            CK(cudaStreamWaitEvent(st, D->ev_in[slot], 0));
+        }
         EncodeParams P;
         memset(&P, 0, sizeof(P));
         P.flags = flags;
@@ -417,13 +449,13 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
                 dof += (size_t)(lw / 4) * (lh / 4) * bb;
             }
         }
-        if ((rc = launch_encode(D, fmt, codec, P, D->stream)) != HKBCN_OK) return rc;
-        CK(cudaMemcpyAsync((uint8_t*)D->h_out + p.doff, (uint8_t*)D->d_dst + p.doff, p.dbytes, cudaMemcpyDeviceToHost, D->stream));
-        CK(cudaEventRecord(D->ev_piece[i], D->stream));
+        if ((rc = launch_encode(D, fmt, codec, P, st)) != HKBCN_OK) return rc;
+        CK(cudaMemcpyAsync(out + p.doff, (uint8_t*)D->d_dst + p.doff, p.dbytes, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(D->ev_piece[i], st));
     }
     for (size_t i = 0; i < pieces.size(); i++) {
         CK(cudaEventSynchronize(D->ev_piece[i]));
-        memcpy(dst + pieces[i].doff, (uint8_t*)D->h_out + pieces[i].doff, pieces[i].dbytes);
+        if (!dst_pinned) memcpy(dst + pieces[i].doff, (uint8_t*)D->h_out + pieces[i].doff, pieces[i].dbytes);
     }
     return HKBCN_OK;
 }
@@ -442,7 +474,9 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
     if (dbytes == 0) return HKBCN_OK;
     if (!ragged && slices == 1 && sbytes >= (16u << 20) && !getenv("HKBCN_NO_PIPELINE")) {
         CK(cudaSetDevice(D->id));
-        if (!is_pinned(src)) return compress_host_pipelined(D, fmt, codec, (const uint8_t*)src, (uint8_t*)dst, w, h, mips, flags);
+        // pageable callers always; pinned ones too unless HKBCN_PIPE_PINNED=0 (A/B timing of the blocking form)
+        const char* pp = getenv("HKBCN_PIPE_PINNED");
+        if (!is_pinned(src) || !(pp && pp[0] == '0')) return compress_host_pipelined(D, fmt, codec, (const uint8_t*)src, (uint8_t*)dst, w, h, mips, flags);
     }
     std::lock_guard<std::mutex> lk(D->mu);
     CK(cudaSetDevice(D->id));
@@ -484,6 +518,7 @@ static void destroy_device(Device* D)
     if (D->h_out) cudaFreeHost(D->h_out);
     for (cudaEvent_t e : D->ev_piece) if (e) cudaEventDestroy(e);
     if (D->copy_stream) cudaStreamDestroy(D->copy_stream);
+    if (D->stream2) cudaStreamDestroy(D->stream2);
     for (uint32_t* c : D->sched_chunks) cudaFree(c);
     for (auto& kv : D->aux_of_stream) cudaFree(kv.second.p);
     for (uint32_t* c : D->aux_retired) cudaFree(c);
@@ -895,6 +930,15 @@ static int import_host_on(Device* D, int fmt, const void* src_level0, void* dst,
     const size_t sbytes = chain_src_bytes(codec, flags, width, height, num_mips);
     const size_t l0 = (size_t)width * height * src_bpp(codec, flags);
     const size_t dbytes = hkbcn_chain_bytes(fmt, width, height, 1, num_mips);
+    if (l0 >= (16u << 20) && !getenv("HKBCN_NO_PIPELINE")) {
+        // bands of level 0 uploaded under the kernels of the bands before them, then the cascade and levels 1..
+        if (num_mips > 1) { // argument errors of the cascade before anything is launched
+            const int edge = cfg && cfg->edge_mode ? cfg->edge_mode : 3, filter = cfg && cfg->filter ? cfg->filter : 5;
+            if (edge < 1 || edge > 4 || filter < 1 || filter > 5) { set_err("bad edge mode %d / filter %d", edge, filter); return HKBCN_ERR_BAD_ARG; }
+            if (codec == C_BC6H && (flags & HKBCN_FLAG_SRC_F16)) { set_err("mip cascade of RGBA16F sources is not supported (the importers resample RGBA32F)"); return HKBCN_ERR_UNSUPPORTED; }
+        }
+        return compress_host_pipelined(D, fmt, codec, (const uint8_t*)src_level0, (uint8_t*)dst, width, height, num_mips, flags, &generate_mips_on, cfg);
+    }
     std::lock_guard<std::mutex> lk(D->mu);
     CK(cudaSetDevice(D->id));
     if ((rc = grow(&D->d_src, &D->src_cap, sbytes)) != HKBCN_OK) return rc;
