@@ -59,7 +59,7 @@ struct Device {
     void*        h_in[2] = {nullptr, nullptr}; size_t h_in_cap[2] = {0, 0};
     void*        h_out = nullptr; size_t h_out_cap = 0;
     cudaEvent_t  ev_in[2] = {nullptr, nullptr};
-    cudaEvent_t  ev_piece[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t  ev_piece[12] = {};
     // mip cascade: decode tables and tap tables (one pair per in/out size, filter and edge mode), built on first use
     float*       lut_srgb = nullptr;
     float*       lut_lin = nullptr;
@@ -380,15 +380,26 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
     }
     if (const char* e = getenv("HKBCN_PIPE_BANDS")) nb = std::max(1, std::min(7, atoi(e))); // A/B timing
     if ((uint32_t)nb > nby) nb = (int)nby;
+    // What nothing can overlap is the way in of the first piece and the way out of the last: with two streams the band size no
+    // longer matters to the encoder, so the first band is cut once more (its first quarter goes up alone) and level 1 is a
+    // piece of its own ahead of levels 2.., whose blocks are a sixteenth of the chain's.
+    const bool fine = nb > 1 && !getenv("HKBCN_PIPE_COARSE");
     for (int b = 0; b < nb; b++) {
         const uint32_t r0 = (uint32_t)((uint64_t)nby * b / nb), r1 = (uint32_t)((uint64_t)nby * (b + 1) / nb);
-        pieces.push_back({(size_t)r0 * 4 * w * bpp, (size_t)(r1 - r0) * 4 * w * bpp, (size_t)r0 * (w / 4) * bb, (size_t)(r1 - r0) * (w / 4) * bb, 0, 1, r0, r1 - r0});
+        const uint32_t cut = (b == 0 && fine && r1 - r0 >= 8) ? r0 + (r1 - r0) / 4 : r0;
+        if (cut > r0) pieces.push_back({(size_t)r0 * 4 * w * bpp, (size_t)(cut - r0) * 4 * w * bpp, (size_t)r0 * (w / 4) * bb, (size_t)(cut - r0) * (w / 4) * bb, 0, 1, r0, cut - r0});
+        pieces.push_back({(size_t)cut * 4 * w * bpp, (size_t)(r1 - cut) * 4 * w * bpp, (size_t)cut * (w / 4) * bb, (size_t)(r1 - cut) * (w / 4) * bb, 0, 1, cut, r1 - cut});
     }
     if (mips > 1) {
-        const size_t s1 = chain_src_bytes(codec, flags, w, h, mips) - l0, d0 = (size_t)(w / 4) * nby * bb;
-        pieces.push_back({l0, s1, d0, hkbcn_chain_bytes(fmt, w, h, 1, mips) - d0, 1, mips, 0, 0});
+        const size_t send = chain_src_bytes(codec, flags, w, h, mips), dend = hkbcn_chain_bytes(fmt, w, h, 1, mips), d0 = (size_t)(w / 4) * nby * bb;
+        if (fine && mips > 2 && !gen) {
+            const uint32_t w1 = mip_dim(w, 1), h1 = mip_dim(h, 1);
+            const size_t s1 = (size_t)w1 * h1 * bpp, d1 = (size_t)(w1 / 4) * (h1 / 4) * bb;
+            pieces.push_back({l0, s1, d0, d1, 1, 2, 0, 0});
+            pieces.push_back({l0 + s1, send - l0 - s1, d0 + d1, dend - d0 - d1, 2, mips, 0, 0});
+        } else pieces.push_back({l0, send - l0, d0, dend - d0, 1, mips, 0, 0});
     }
-    if (pieces.size() > 8) { set_err("internal: too many pieces"); return HKBCN_ERR_BAD_ARG; }
+    if (pieces.size() > 12) { set_err("internal: too many pieces"); return HKBCN_ERR_BAD_ARG; }
     const size_t sbytes = chain_src_bytes(codec, flags, w, h, mips), dbytes = hkbcn_chain_bytes(fmt, w, h, 1, mips);
     size_t maxp = 0;
     for (auto& p : pieces)
@@ -441,7 +452,7 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
         if (p.lvl0 == 0) {
             add_level(P, codec, flags, (uint8_t*)D->d_src + p.soff, (uint8_t*)D->d_dst + p.doff, w, p.rows * 4);
         } else {
-            size_t so = l0, dof = p.doff;
+            size_t so = p.soff, dof = p.doff;
             for (uint32_t l = p.lvl0; l < p.lvl1; l++) {
                 const uint32_t lw = mip_dim(w, l), lh = mip_dim(h, l);
                 add_level(P, codec, flags, (uint8_t*)D->d_src + so, (uint8_t*)D->d_dst + dof, lw, lh);

@@ -34,7 +34,7 @@ want = None
 
 def run(label, fn, out, env):
     global want
-    for k in ("HKBCN_PIPE_BANDS", "HKBCN_PIPE_ONE_STREAM", "HKBCN_PIPE_PINNED", "HKBCN_NO_PIPELINE"):
+    for k in ("HKBCN_PIPE_BANDS", "HKBCN_PIPE_ONE_STREAM", "HKBCN_PIPE_PINNED", "HKBCN_NO_PIPELINE", "HKBCN_PIPE_COARSE"):
         os.environ.pop(k, None)
     os.environ.update(env)
     ts = []
@@ -69,7 +69,10 @@ run("compress_chain pinned, pieces, two streams", pinned_chain, pd, {})
 for b in ("2", "3", "4", "7"):
     run(f"compress_chain pinned, two streams, {b} bands", pinned_chain, pd, {"HKBCN_PIPE_BANDS": b})
 run("compress_chain pageable, one stream", pageable_chain, pg_dst, {"HKBCN_PIPE_ONE_STREAM": "1"})
+run("compress_chain pageable, two streams, coarse pieces", pageable_chain, pg_dst, {"HKBCN_PIPE_COARSE": "1"})
 run("compress_chain pageable, two streams", pageable_chain, pg_dst, {})
+run("compress_chain pinned, two streams, coarse pieces", pinned_chain, pd, {"HKBCN_PIPE_COARSE": "1"})
 run("import_chain pinned, blocking", pinned_import, pd, {"HKBCN_NO_PIPELINE": "1"})
 run("import_chain pinned, pieces, one stream", pinned_import, pd, {"HKBCN_PIPE_ONE_STREAM": "1"})
+run("import_chain pinned, pieces, two streams, coarse", pinned_import, pd, {"HKBCN_PIPE_COARSE": "1"})
 run("import_chain pinned, pieces, two streams", pinned_import, pd, {})
