@@ -1928,6 +1928,111 @@ int hkbcn_create_normal_and_roughness(const hkbcn_normal_roughness_settings* s, 
     return HKBCN_OK;
 }
 
+// ---- PBRImporter's ORMX texture (Tools/PBRImporter/Main.cpp:284-735) as a batch job ------------------------------------------
+// maps up -> CreateORMX gather -> cascade of the RGBA8 storage (NO_ALPHA) -> roughness channel of levels >= 1 from the
+// triangle-filtered normals -> encode -> compressed chain down.  One job at a time per device, under the device's mutex.
+static int import_pbr_on(Device* D, hkbcn_pbr_job& j, std::vector<uint8_t>& out, uint32_t& mips_out)
+{
+    const int codec = codec_of(j.fmt);
+    const uint32_t w = j.width, h = j.height;
+    const uint32_t mips = j.generate_mips ? hkbcn_calc_num_mips(w, h) : 1u;
+    mips_out = mips;
+    const size_t n = (size_t)w * h, cbytes = chain_src_bytes(codec, 0, w, h, mips), dbytes = hkbcn_chain_bytes(j.fmt, w, h, 1, mips);
+    const bool bake = j.roughness_bake != 0 && j.normals && mips > 1; // no normals or no mips: nothing to anti-alias (Main.cpp:616)
+    std::lock_guard<std::mutex> lk(D->mu);
+    CK(cudaSetDevice(D->id));
+    cudaStream_t st = D->stream;
+    int rc;
+    DevBuf maps[4], chain, blocks, normals, plane, scratch;
+    if ((rc = chain.alloc(cbytes)) != HKBCN_OK || (rc = blocks.alloc(dbytes)) != HKBCN_OK) return rc;
+    const void* d_maps[4] = {nullptr, nullptr, nullptr, nullptr};
+    int ch[4];
+    for (int k = 0; k < 4; k++) {
+        ch[k] = j.channel[k];
+        if (!j.maps[k]) continue;
+        if ((rc = maps[k].alloc(n * 4)) != HKBCN_OK) return rc;
+        CK(cudaMemcpyAsync(maps[k].p, j.maps[k], n * 4, cudaMemcpyHostToDevice, st));
+        d_maps[k] = maps[k].p;
+    }
+    CK(launch_ormx_gather(d_maps, ch, chain.p, n, st));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    hkbcn_mip_config cfg = j.mip;
+    cfg.no_alpha = 1; // ImageStorageDesc.Flags = IMAGE_STORAGE_NO_ALPHA (:601): the fourth channel is data, not coverage
+    cfg.alpha_premultiplied = 0;
+    // the cascade is that of an RGBA8 storage whatever the preset compresses to (:596-613)
+    if (mips > 1 && (rc = generate_mips_on(D, HKBCN_BC7_UNORM, chain.p, w, h, mips, &cfg, 0, st)) != HKBCN_OK) return rc;
+    if (bake) {
+        size_t texels = 0;
+        for (uint32_t i = 0; i < mips; i++) texels += (size_t)mip_dim(w, i) * mip_dim(h, i);
+        if ((rc = normals.alloc(n * 12)) != HKBCN_OK || (rc = plane.alloc(texels)) != HKBCN_OK || (rc = scratch.alloc(hkbcn_bake_scratch_bytes(w, h))) != HKBCN_OK) return rc;
+        CK(cudaMemcpyAsync(normals.p, j.normals, n * 12, cudaMemcpyHostToDevice, st));
+        CK(launch_channel_move(chain.p, plane.p, texels, 1, false, st));
+        if ((rc = bake_roughness_on(D, (const float*)normals.p, (uint8_t*)plane.p, scratch.p, w, h, mips, j.roughness_bake, 2 /* triangle, :640 */,
+                                    cfg.edge_mode, st)) != HKBCN_OK) return rc;
+        CK(launch_channel_move(chain.p, plane.p, texels, 1, true, st));
+        g_launches.fetch_add(2, std::memory_order_relaxed);
+    }
+    EncodeParams P;
+    if ((rc = build_chain(P, codec, 0, chain.p, blocks.p, w, h, mips)) != HKBCN_OK) return rc;
+    if ((rc = launch_encode(D, j.fmt, codec, P, st)) != HKBCN_OK) return rc;
+    out.resize(dbytes);
+    void* to = j.dst ? j.dst : (void*)out.data();
+    CK(cudaMemcpyAsync(to, blocks.p, dbytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (j.dst && j.out_path) memcpy(out.data(), j.dst, dbytes);
+    return HKBCN_OK;
+}
+
+int hkbcn_import_pbr_batch(hkbcn_pbr_job* jobs, size_t n_jobs)
+{
+    Range nvtx_("hkbcn_import_pbr_batch");
+    int rc = ensure_init();
+    if (rc) return rc;
+    if (n_jobs == 0) return HKBCN_OK;
+    if (!jobs) { set_err("null jobs"); return HKBCN_ERR_BAD_ARG; }
+    for (size_t i = 0; i < n_jobs; i++) {
+        hkbcn_pbr_job& j = jobs[i];
+        j.status = HKBCN_OK;
+        if (j.fmt != HKBCN_BC1_UNORM && j.fmt != HKBCN_BC3_UNORM && j.fmt != HKBCN_BC7_UNORM) {
+            set_err("job %zu: the ORMX presets compress to BC1, BC3 or BC7, not format %d", i, j.fmt);
+            return HKBCN_ERR_BAD_FORMAT;
+        }
+        if (!j.maps[0] && !j.maps[1] && !j.maps[2] && !j.maps[3]) { set_err("job %zu: at least one source map is needed", i); return HKBCN_ERR_BAD_ARG; }
+        if (!j.out_path && !j.dst) { set_err("job %zu: neither out_path nor dst", i); return HKBCN_ERR_BAD_ARG; }
+        for (int k = 0; k < 4; k++)
+            if (j.channel[k] > 3) { set_err("job %zu: invalid channel index %d", i, (int)j.channel[k]); return HKBCN_ERR_BAD_ARG; }
+        if (j.roughness_bake != 0 && j.roughness_bake != HKBCN_ROUGHNESS_BAKE_VMF && j.roughness_bake != HKBCN_ROUGHNESS_BAKE_TOKSVIG) {
+            set_err("job %zu: bad roughness bake %d", i, j.roughness_bake);
+            return HKBCN_ERR_BAD_ARG;
+        }
+        if ((rc = check_chain_dims(j.width, j.height, j.generate_mips ? hkbcn_calc_num_mips(j.width, j.height) : 1u)) != HKBCN_OK) return rc;
+    }
+    const size_t nd = g_devs.size();
+    std::vector<int> first_err(nd, 0);
+    std::vector<std::string> err_msg(nd);
+    std::vector<std::thread> th;
+    for (size_t dv = 0; dv < nd && dv < n_jobs; dv++) {
+        th.emplace_back([&, dv]() {
+            std::vector<uint8_t> out;
+            for (size_t i = dv; i < n_jobs; i += nd) {
+                hkbcn_pbr_job& j = jobs[i];
+                uint32_t mips = 1;
+                int r = import_pbr_on(g_devs[dv], j, out, mips);
+                if (r == HKBCN_OK && j.out_path) {
+                    hkbcn_texture_desc desc{HKBCN_TEXTURE_2D, j.width, j.height, 1, mips, j.fmt, (uint32_t)HKBCN_STORAGE_NO_ALPHA};
+                    r = hkbcn_write_texture(j.out_path, &desc, out.data(), out.size());
+                }
+                j.status = r;
+                if (r != HKBCN_OK && !first_err[dv]) { first_err[dv] = r; err_msg[dv] = t_err; }
+            }
+        });
+    }
+    for (auto& t : th) t.join();
+    for (size_t dv = 0; dv < nd; dv++)
+        if (first_err[dv]) { set_err("%s", err_msg[dv].c_str()); return first_err[dv]; }
+    return HKBCN_OK;
+}
+
 // ---- environment probes (row f3) --------------------------------------------------------------------------------------
 size_t hkbcn_envprobe_texels(int max_lod) { return (max_lod < 1 || max_lod > 12) ? 0 : envprobe_texels(max_lod); }
 

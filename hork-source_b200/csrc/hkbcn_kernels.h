@@ -84,6 +84,9 @@ cudaError_t launch_normalize_vectors(float* d_v, size_t count, cudaStream_t st);
 cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t* d_rough, size_t count, cudaStream_t st);
 cudaError_t launch_invert_green(float* d_xyz, size_t count, cudaStream_t st); // RawImage::InvertGreen on Float3 texels
 // RGB -> RGBA (alpha 255 / 1.0) and / or R <-> B: CreateImage's channel pass (Image.cpp:1152-1228)
+// PBRImporter's CreateORMX gather (Tools/PBRImporter/Main.cpp:86-190) and one channel of an RGBA8 image <-> a planar R8 image
+cudaError_t launch_ormx_gather(const void* const d_maps[4], const int channel[4], void* d_dst, size_t count, cudaStream_t st);
+cudaError_t launch_channel_move(void* d_rgba, void* d_plane, size_t count, int channel, bool insert, cudaStream_t st);
 cudaError_t launch_expand_channels(const void* d_src, void* d_dst, size_t count, int src_channels, bool swap_rb, bool f32, cudaStream_t st);
 
 } // namespace hkbcn

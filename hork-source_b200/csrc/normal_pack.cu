@@ -278,4 +278,46 @@ cudaError_t launch_roughness_bake(int bake, const float* d_avg_normals, uint8_t*
     return cudaGetLastError();
 }
 
+// ---- PBRImporter's ORMX image (Tools/PBRImporter/Main.cpp:86-190, CreateORMX): channel k of the result is channel ch[k] of
+// map k (an RGBA8 image of the same size), or the default {255, 255, 0, 255} where no map was given
+struct OrmxMaps { const uint8_t* map[4]; int ch[4]; };
+__global__ void __launch_bounds__(256) ormx_gather_kernel(const OrmxMaps M, uchar4* __restrict__ dst, size_t count)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    uint8_t v[4] = {255, 255, 0, 255};
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (M.map[k]) v[k] = (uint8_t)(__ldg((const uint32_t*)M.map[k] + i) >> (8 * M.ch[k]));
+    dst[i] = make_uchar4(v[0], v[1], v[2], v[3]);
+}
+cudaError_t launch_ormx_gather(const void* const d_maps[4], const int channel[4], void* d_dst, size_t count, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    OrmxMaps M;
+    for (int k = 0; k < 4; k++) {
+        if (channel[k] < 0 || channel[k] > 3) return cudaErrorInvalidValue;
+        M.map[k] = (const uint8_t*)d_maps[k];
+        M.ch[k] = channel[k];
+    }
+    ormx_gather_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(M, (uchar4*)d_dst, count);
+    return cudaGetLastError();
+}
+
+// one channel of an RGBA8 image out to / back from a planar R8 image (the roughness channel of an ORMX chain: the bake works on R8)
+__global__ void __launch_bounds__(256) channel_move_kernel(uint8_t* __restrict__ rgba, uint8_t* __restrict__ plane, size_t count, int ch, int insert)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    if (insert) rgba[i * 4 + ch] = plane[i];
+    else plane[i] = rgba[i * 4 + ch];
+}
+cudaError_t launch_channel_move(void* d_rgba, void* d_plane, size_t count, int channel, bool insert, cudaStream_t st)
+{
+    if (count == 0) return cudaSuccess;
+    if (channel < 0 || channel > 3) return cudaErrorInvalidValue;
+    channel_move_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>((uint8_t*)d_rgba, (uint8_t*)d_plane, count, channel, insert ? 1 : 0);
+    return cudaGetLastError();
+}
+
 } // namespace hkbcn

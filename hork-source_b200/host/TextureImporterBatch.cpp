@@ -398,46 +398,38 @@ int run_pbr(const std::vector<std::string>& t, uint32_t mask)
     double mpix = 0;
     // ---- ORMX
     if (fmt >= 0) {
-        std::vector<uint8_t> ormx;
+        // one hkbcn_pbr_job: gather, cascade, roughness update, encode and the file all happen behind hkbcn_import_pbr_batch
+        std::vector<uint8_t> rgba[4];
         uint32_t w = 0, h = 0;
         bool any = false;
+        hkbcn_pbr_job job;
+        memset(&job, 0, sizeof(job));
         for (int k = 0; k < 4; k++) {
+            job.channel[k] = (uint8_t)maps[k].ch;
             if (maps[k].file.empty()) continue;
             Pixels p;
-            std::vector<uint8_t> rgba;
             printf("Loading %s...\n", maps[k].file.c_str());
-            if (!load_rgba8(maps[k].file, p, rgba, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
-            if (!any) {
-                w = p.w; h = p.h; any = true;
-                ormx.resize((size_t)w * h * 4);
-                for (size_t i = 0; i < (size_t)w * h; i++) { ormx[i * 4] = 255; ormx[i * 4 + 1] = 255; ormx[i * 4 + 2] = 0; ormx[i * 4 + 3] = 255; } // Clear({1, 1, 0, 1})
-            } else if (p.w != w || p.h != h) {
+            if (!load_rgba8(maps[k].file, p, rgba[k], err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+            if (!any) { w = p.w; h = p.h; any = true; }
+            else if (p.w != w || p.h != h) {
                 fputs("The source images have different sizes. Use the -resample option to configure resampling parameters.\n", stderr);
                 return -1;
             }
-            for (size_t i = 0; i < (size_t)w * h; i++) ormx[i * 4 + (size_t)k] = rgba[i * 4 + (size_t)maps[k].ch];
+            job.maps[k] = rgba[k].data();
         }
         if (!any) { fputs("-pbr_preset needs at least one source map\n", stderr); return -1; }
         if (!check_dims(w, h, "ORMX")) return -1;
         if (bake && !normals.empty() && (w != nw || h != nh)) { fputs("Can't apply antialiasing. ORMX and NormalMap must be the same size.\n", stderr); return -1; }
-        const uint32_t nm = mips ? hkbcn_calc_num_mips(w, h) : 1;
-        hkbcn_mip_config cfg = {edge, filter, 1, 0};
-        std::vector<uint8_t> chain(hkbcn_chain_src_bytes(HKBCN_BC7_UNORM, w, h, nm, 0));
-        if (nm > 1) {
-            if (hkbcn_generate_mips(HKBCN_BC7_UNORM, ormx.data(), chain.data(), w, h, nm, &cfg, 0) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
-        } else memcpy(chain.data(), ormx.data(), ormx.size());
-        if (bake && !normals.empty() && nm > 1) {
-            std::vector<uint8_t> rough(chain.size() / 4); // roughness = second channel of every level
-            for (size_t i = 0; i < rough.size(); i++) rough[i] = chain[i * 4 + 1];
-            if (hkbcn_bake_roughness(normals.data(), rough.data(), w, h, nm, bake, 2 /* triangle */, edge) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
-            for (size_t i = 0; i < rough.size(); i++) chain[i * 4 + 1] = rough[i];
-        }
-        std::vector<uint8_t> blocks(hkbcn_chain_bytes(fmt, w, h, 1, nm));
+        job.fmt = fmt;
+        job.width = w; job.height = h;
+        job.normals = (bake && !normals.empty()) ? normals.data() : nullptr;
+        job.roughness_bake = job.normals ? bake : 0;
+        job.generate_mips = mips ? 1 : 0;
+        job.mip.edge_mode = edge; job.mip.filter = filter;
+        job.out_path = out_pbr.c_str();
         printf("Importing texture %s...\n", out_pbr.c_str());
-        if (hkbcn_compress_chain(fmt, chain.data(), blocks.data(), w, h, nm, 0) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
-        hkbcn_texture_desc d = {HKBCN_TEXTURE_2D, w, h, 1, nm, fmt, HKBCN_STORAGE_NO_ALPHA};
-        if (hkbcn_write_texture(out_pbr.c_str(), &d, blocks.data(), blocks.size()) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
-        mpix += (double)chain.size() / 4e6;
+        if (hkbcn_import_pbr_batch(&job, 1) != HKBCN_OK) { fprintf(stderr, "%s\n", hkbcn_last_error()); return -1; }
+        mpix += (double)w * h * (mips ? 4.0 / 3.0 : 1.0) / 1e6;
     }
     // ---- normal map
     if (!normals.empty()) {

@@ -43,7 +43,7 @@ EXPORTS = [
     "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
     "hkbcn_static_scratch_bytes", "hkbcn_compress_static",
     "hkbcn_plan_image", "hkbcn_create_image", "hkbcn_create_roughness_map", "hkbcn_resample_raw_image", "hkbcn_resample_raw_image_dev",
-    "hkbcn_create_normal_map", "hkbcn_create_normal_and_roughness",
+    "hkbcn_create_normal_map", "hkbcn_create_normal_and_roughness", "hkbcn_import_pbr_batch",
 ]
 
 
@@ -84,6 +84,12 @@ class TextureDesc(C.Structure):
 class ImportJob(C.Structure):
     _fields_ = [("fmt", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("generate_mips", C.c_int), ("mip", MipConfig),
                 ("flags", C.c_uint32), ("src_level0", C.c_void_p), ("out_path", C.c_char_p), ("dst", C.c_void_p), ("status", C.c_int), ("slices", C.c_uint32)]
+
+
+class PbrJob(C.Structure):
+    _fields_ = [("fmt", C.c_int), ("width", C.c_uint32), ("height", C.c_uint32), ("maps", C.c_void_p * 4), ("channel", C.c_uint8 * 4),
+                ("normals", C.c_void_p), ("roughness_bake", C.c_int), ("generate_mips", C.c_int), ("mip", MipConfig),
+                ("out_path", C.c_char_p), ("dst", C.c_void_p), ("status", C.c_int)]
 
 
 _lib = None
@@ -139,6 +145,7 @@ def lib():
         L.hkbcn_write_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t]
         L.hkbcn_read_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.hkbcn_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t]
+        L.hkbcn_import_pbr_batch.argtypes = [C.POINTER(PbrJob), C.c_size_t]
         L.hkbcn_plan_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
         L.hkbcn_batch_stats.argtypes = [C.POINTER(C.c_double), C.c_int]
         L.hkbcn_envprobe_texels.restype = C.c_size_t

@@ -351,6 +351,30 @@ HKBCN_API int hkbcn_plan_import_batch(const hkbcn_import_job* jobs, size_t n_job
  * hkbcn_init's device order; returns the number of devices (at most `capacity` values are written). */
 HKBCN_API int hkbcn_batch_stats(double* busy_ms, int capacity);
 
+/* ---- PBRImporter's ORMX texture as a batch job (Tools/PBRImporter/Main.cpp:284-735) ----------------------------------
+ * One job = one ORMX texture: channel k of the RGBA8 image is channel `channel[k]` of `maps[k]` (occlusion, roughness,
+ * metallic, displacement-or-emission; RGBA8 images of width x height in host memory), a missing map leaves the default
+ * {255, 255, 0, 255} (CreateORMX, Main.cpp:86-190); the mips are those of an RGBA8 storage with IMAGE_STORAGE_NO_ALPHA
+ * (:596-613); with `normals` (width x height normalised Float3, the output of hkbcn_normalize_vectors) and a bake, the
+ * roughness channel of every level >= 1 is updated from the triangle-filtered normals (:616-680); the chain is compressed to
+ * BC1 / BC3 / BC7 (the ORMX_BC1 / ORMX_BC3 / ORMX_BC7 presets, :683-735) and written as a .texture with NO_ALPHA.  Every
+ * step runs on the GPU the job is sent to; only the maps go up and the compressed chain comes back.  Jobs are dealt over
+ * the selected GPUs in order (job i -> GPU i mod n), one worker thread per GPU. */
+typedef struct hkbcn_pbr_job {
+    int              fmt;             /* HKBCN_BC1_UNORM, HKBCN_BC3_UNORM or HKBCN_BC7_UNORM */
+    uint32_t         width, height;   /* multiples of 4; powers of two when generate_mips */
+    const void*      maps[4];         /* host RGBA8 images or NULL; at least one */
+    uint8_t          channel[4];      /* 0..3 */
+    const float*     normals;         /* host, optional */
+    int              roughness_bake;  /* 0, HKBCN_ROUGHNESS_BAKE_VMF or HKBCN_ROUGHNESS_BAKE_TOKSVIG; needs normals and generate_mips */
+    int              generate_mips;
+    hkbcn_mip_config mip;             /* edge mode and filter of the cascade (no_alpha is forced on) */
+    const char*      out_path;        /* .texture file to write; NULL = keep the chain in `dst` only */
+    void*            dst;             /* optional host buffer for the compressed chain (hkbcn_chain_bytes), may be NULL */
+    int              status;          /* out */
+} hkbcn_pbr_job;
+HKBCN_API int hkbcn_import_pbr_batch(hkbcn_pbr_job* jobs, size_t n_jobs);
+
 /* ---- normal maps and roughness anti-aliasing ----------
  * The element-wise work of the PBRImporter path between load and the BC5 / BC4 / BC1 / BC3 encoders:
  *   hkbcn_pack_normals    PackNormals*_Compatible (Hork/Image/ImageEncoders.cpp:693-796): Float3 normals -> RG8 / RGBA8
