@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Tiny driver for ncu captures: one format, one surface size, a few encodes (or decodes) through the C ABI.
-usage: prof_kernel.py <fmt-id> <size> [reps] [decode]"""
+usage: prof_kernel.py <fmt-id> <size> [reps] [decode|decode32|mask]   (HKBCN_PROF_FLAGS=<int>: flags of the encode, e.g. a quality level)"""
 import os
 import sys
 
@@ -39,5 +39,5 @@ else:
     else:
         img = synth.sky_rgba32f(n, n, 6)
     for _ in range(reps):
-        out = hkbcn.compress(fmt, img, n, n)
+        out = hkbcn.compress(fmt, img, n, n, int(os.environ.get("HKBCN_PROF_FLAGS", "0")))
 print("ok", out[:16].tolist(), "launches", hkbcn.lib().hkbcn_launch_count())
