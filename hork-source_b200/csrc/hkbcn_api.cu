@@ -513,6 +513,25 @@ int compress_host_on(Device* D, int fmt, const void* src, void* dst, uint32_t w,
 extern "C" {
 
 const char* hkbcn_last_error(void) { return t_err; }
+
+float hkbcn_srgb_decode_entry(int v)
+{
+    if (v < 0 || v > 255) return 0.0f;
+    const float f = (float)v / 255.0f;
+    const float x = f <= 0.04045f ? f / 12.92f : powf((f + 0.055f) / 1.055f, 2.4f);
+    char buf[32];
+    snprintf(buf, sizeof(buf), "%.6f", (double)x);
+    return strtof(buf, nullptr);
+}
+
+int hkbcn_build_has(int feature)
+{
+    switch (feature) {
+    case HKBCN_BUILD_BC1_ORDERINGS: return bc1_hq_available() ? 1 : 0;
+    case HKBCN_BUILD_STBIR_SRGB: return mip_srgb_is_stbir() ? 1 : 0;
+    default: return 0;
+    }
+}
 const char* hkbcn_version(void) { return "hkbcn 0.1 (sm_100a)"; }
 
 static void destroy_device(Device* D)
@@ -561,11 +580,12 @@ static int create_device(int i, const cudaDeviceProp& prop, Device** out)
     cudaError_t te = bc7_upload_tables();
     if (te != cudaSuccess && te != cudaErrorNotSupported) { set_err("bc7 table upload: %s", cudaGetErrorString(te)); return HKBCN_ERR_CUDA; }
     CK(bc6h_upload_tables());
-    // stbir's uint8 decode: sRGB -> linear (stb_image_resize.h:634-640, tabulated there) and v / 255
+    // stbir's uint8 decode: v / 255, and sRGB -> linear through stbir__srgb_uchar_to_linear_float (stb_image_resize.h:607-633):
+    // 256 six-decimal literals, which are what the transfer function gives in FLOAT arithmetic printed with %.6f -- recomputed
+    // here the same way (tests/test_stbir_tables_cpu.py holds the result to the header's literals)
     float srgb[256], lin[256];
     for (int v = 0; v < 256; v++) {
-        const double f = v / 255.0;
-        srgb[v] = (float)(f <= 0.04045 ? f / 12.92 : pow((f + 0.055) / 1.055, 2.4));
+        srgb[v] = hkbcn_srgb_decode_entry(v);
         lin[v] = (float)v / 255.0f;
     }
     CK(cudaMalloc((void**)&D->lut_srgb, sizeof(srgb)));

@@ -68,6 +68,7 @@ struct ResizeParams {
     float          ux2[16], uy2[16], zero2[2];
 };
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
+bool mip_srgb_is_stbir(); // sRGB channels are encoded with stbir's own segment table (build/stbir_srgb.inc): *_SRGB chains are bit-identical
 // any size to any size, 1..4 channels, alpha weighting for float images too (ResampleRawImage): one thread per output texel
 cudaError_t launch_resample_general(const ResizeParams& P, int channels, bool f32, cudaStream_t stream);
 

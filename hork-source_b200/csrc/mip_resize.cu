@@ -21,6 +21,7 @@
 #include <algorithm>
 #include <vector>
 #include "hkbcn_kernels.h"
+#include "build/stbir_srgb.inc"
 
 namespace hkbcn {
 
@@ -205,12 +206,31 @@ __device__ __forceinline__ uint8_t encode_linear8(float f)
     f = f < 0 ? 0 : f > 1 ? 1 : f;
     return (uint8_t)(int)((double)(f * 255.0f) + 0.5);
 }
+#if HK_HAVE_STBIR_SRGB
+// stbir__linear_to_srgb_uchar (stb_image_resize.h:675-698): a piecewise-linear fit of the transfer function over 104 segments
+// (13 binades x 8), bias and scale of each in build/stbir_srgb.inc (tools/gen_stbir_tables.py reads them from the engine tree)
+static __device__ const uint32_t g_srgb8_tab4[104] = {HK_FP32_TO_SRGB8_TAB4};
+__device__ __forceinline__ uint8_t encode_srgb8(float in)
+{
+    constexpr uint32_t MINU = (127u - 13u) << 23; // 2^-13 maps to 0, 1 - eps to 255; written so that NaN maps to 0
+    if (!(in > __uint_as_float(MINU))) in = __uint_as_float(MINU);
+    if (in > __uint_as_float(0x3f7fffffu)) in = __uint_as_float(0x3f7fffffu);
+    const uint32_t u = __float_as_uint(in);
+    const uint32_t tab = g_srgb8_tab4[(u - MINU) >> 20];
+    const uint32_t bias = (tab >> 16) << 9, scale = tab & 0xffffu, t = (u >> 12) & 0xffu;
+    return (uint8_t)((bias + scale * t) >> 16);
+}
+bool mip_srgb_is_stbir() { return true; }
+#else
+// built without the engine tree: the exact transfer function, within 1 LSB of stbir's piecewise-linear fit
 __device__ __forceinline__ uint8_t encode_srgb8(float f)
 {
     f = !(f > 0) ? 0 : f > 1 ? 1 : f;
     const float v = f <= 0.0031308f ? f * 12.92f : 1.055f * powf(f, 1.0f / 2.4f) - 0.055f;
     return (uint8_t)(int)(v * 255.0f + 0.5f);
 }
+bool mip_srgb_is_stbir() { return false; }
+#endif
 
 template <int CH>
 __global__ void __launch_bounds__(256) mip_resize_u8_kernel(const ResizeParams P)

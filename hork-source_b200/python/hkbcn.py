@@ -23,6 +23,7 @@ FLAG_SRC_F16 = 1 << 0
 FLAG_FAST = 1 << 1
 FLAG_DST_F32 = 1 << 8
 FLAG_BC1_3COLOR = 1 << 9
+BUILD_BC1_ORDERINGS, BUILD_STBIR_SRGB = 1, 2
 FLAG_BC1_TRANSPARENT_BLACK = 1 << 10
 FLAG_SKIP_EXISTING = 1 << 16
 FLAG_SRC_DEVICE = 1 << 17
@@ -43,7 +44,7 @@ EXPORTS = [
     "hkbcn_pack_normals_dev", "hkbcn_unpack_normals_dev", "hkbcn_normalize_vectors_dev", "hkbcn_bake_scratch_bytes", "hkbcn_bake_roughness_dev",
     "hkbcn_static_scratch_bytes", "hkbcn_compress_static",
     "hkbcn_plan_image", "hkbcn_create_image", "hkbcn_create_roughness_map", "hkbcn_resample_raw_image", "hkbcn_resample_raw_image_dev",
-    "hkbcn_create_normal_map", "hkbcn_create_normal_and_roughness", "hkbcn_import_pbr_batch",
+    "hkbcn_create_normal_map", "hkbcn_create_normal_and_roughness", "hkbcn_import_pbr_batch", "hkbcn_build_has", "hkbcn_srgb_decode_entry",
 ]
 
 
@@ -146,6 +147,9 @@ def lib():
         L.hkbcn_read_texture.argtypes = [C.c_char_p, C.POINTER(TextureDesc), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.hkbcn_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t]
         L.hkbcn_import_pbr_batch.argtypes = [C.POINTER(PbrJob), C.c_size_t]
+        L.hkbcn_build_has.argtypes = [C.c_int]
+        L.hkbcn_srgb_decode_entry.argtypes = [C.c_int]
+        L.hkbcn_srgb_decode_entry.restype = C.c_float
         L.hkbcn_plan_import_batch.argtypes = [C.POINTER(ImportJob), C.c_size_t, C.c_int, C.POINTER(C.c_int)]
         L.hkbcn_batch_stats.argtypes = [C.POINTER(C.c_double), C.c_int]
         L.hkbcn_envprobe_texels.restype = C.c_size_t

@@ -103,7 +103,16 @@ enum {
 HKBCN_API int hkbcn_init(uint32_t device_mask);
 HKBCN_API void hkbcn_shutdown(void);
 HKBCN_API int hkbcn_device_count(void);          /* devices selected by hkbcn_init */
-HKBCN_API const char* hkbcn_last_error(void);    /* thread-local message of the last failure */
+HKBCN_API const char* hkbcn_last_error(void);
+/* What this build of the library carries of the reference's DATA tables (they are read out of the engine tree at build time,
+ * csrc/Makefile: RGBCX_DIR, STB_DIR; a build without the tree works, with the stated differences):
+ *   HKBCN_BUILD_BC1_ORDERINGS  rgbcx's total-ordering tables: BC1/2/3 levels 6..18 and the 3-colour options (else HKBCN_ERR_UNSUPPORTED)
+ *   HKBCN_BUILD_STBIR_SRGB     stbir's float -> sRGB8 segments: mip chains of *_SRGB formats bit-identical to stbir (else within 1 LSB) */
+enum { HKBCN_BUILD_BC1_ORDERINGS = 1, HKBCN_BUILD_STBIR_SRGB = 2 };
+HKBCN_API int hkbcn_build_has(int feature);
+/* entry v of stbir's sRGB -> linear decode table (stbir__srgb_uchar_to_linear_float), as hkbcn_init computes it */
+HKBCN_API float hkbcn_srgb_decode_entry(int v);
+    /* thread-local message of the last failure */
 HKBCN_API const char* hkbcn_version(void);
 
 /* ---- format queries (TexFormat[] table, Image.cpp:49-119) -------------------- */
@@ -190,7 +199,8 @@ HKBCN_API int hkbcn_plan_bands(uint32_t height, uint32_t num_mips, int n_gpus, i
 /* ---- device-side mip cascade ------------------------------------------------
  * The importers build every mip level on the CPU from the previous one with stbir_resize and compress it
  * (Image.cpp:1755-1803 for BC1-5/BC7, :1852-1899 for BC6H; ImageMipmapConfig, Image.h:361-371).  These entry points do the
- * same cascade on the device, so only level 0 crosses PCIe.  Contract against stbir: +-1 LSB per uint8 channel. */
+ * same cascade on the device, so only level 0 crosses PCIe.  Against stbir: bit-identical for uint8 formats, linear and sRGB (sRGB
+ * within 1 LSB in a build without stbir's segment table, see hkbcn_build_has); float chains within 1e-6. */
 typedef struct hkbcn_mip_config {
     int edge_mode;            /* IMAGE_RESAMPLE_EDGE_MODE (Image.h:330): 1 clamp, 2 reflect, 3 wrap, 4 zero; 0 = default (wrap) */
     int filter;               /* IMAGE_RESAMPLE_FILTER (Image.h:339): 1 box, 2 triangle, 3 cubic b-spline, 4 catmull-rom, 5 mitchell; 0 = default (mitchell) */
@@ -241,7 +251,7 @@ typedef struct hkbcn_image_plan {
 /* ---- ResampleRawImage (Image.cpp:2188-2243; the -resample pre-pass of the importers, Tools/TextureImporter/Main.cpp:145-200, and
  * CreateImage's resample to a power of two, Image.cpp:1064-1096): stbir_resize of a raw image to scaled_width x scaled_height,
  * up or down, each axis with its own edge mode and filter, on the device.  Bit-identical to stbir for linear data (uint8 and
- * float, with and without alpha weighting); sRGB uint8 within +-1 LSB (as the mip cascade).  Float images in the sRGB colour
+ * float, with and without alpha weighting) and for sRGB uint8 (as the mip cascade).  Float images in the sRGB colour
  * space are refused (no caller in the reference asks for them). */
 enum { HKBCN_RESAMPLE_HAS_ALPHA = 1, HKBCN_RESAMPLE_ALPHA_PREMULTIPLIED = 2, HKBCN_RESAMPLE_COLORSPACE_SRGB = 4 }; /* RAW_IMAGE_RESAMPLE_FLAG, Image.h:518-524 */
 typedef struct hkbcn_resample_params {

@@ -50,6 +50,10 @@ def test_config1_bc1_2048_chain_linear_and_srgb():
         want = refshim.compress_chain(fmt, chain, n, n, mips)
         assert got.size == 349525 * 8
         same_blocks(got, want, 8)
+        # level 0 in, the device cascade, chain out: the same bytes for the linear format always, for the sRGB one when the build
+        # carries stbir's sRGB segment table (hkbcn_build_has)
+        if not srgb or hkbcn.lib().hkbcn_build_has(hkbcn.BUILD_STBIR_SRGB):
+            same_blocks(hkbcn.import_chain(fmt, img, n, n, mips), want, 8)
 
 
 def test_config2_bc4_bc5_4096():

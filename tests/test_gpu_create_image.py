@@ -109,11 +109,17 @@ def test_create_image_hdr_and_srgb_and_refusals():
     assert np.array_equal(got, hkbcn.import_chain(BC6U, img, w, h, desc.num_mips, cfg=hkbcn.MipConfig(0, 0, 1, 0)))
     # level 0 against the reference encoder directly
     assert np.array_equal(got[: (w // 4) * (h // 4) * 16], refshim.compress(BC6U, img, w, h, lib=refshim.ref0()))
-    # sRGB 8-bit: the cascade is within +-1 LSB of stbir's (typed-in tables), so compare with the library's own import of the expanded image
+    # sRGB 8-bit: against the library's own import of the expanded image, and against the reference's cascade + encoder
     rgba = synth.albedo_rgba8(w, h, 0x78, "mask").reshape(h, w, 4)
     rc, desc, got, p = create_image(RGBA8, rgba, w, h, cfg, 0, COMPRESS | SRGB)
     assert rc == 0 and desc.fmt == BC3S
     assert np.array_equal(got, hkbcn.import_chain(BC3S, rgba, w, h, desc.num_mips))
+    if hkbcn.lib().hkbcn_build_has(hkbcn.BUILD_STBIR_SRGB):
+        # with stbir's own sRGB tables in the build the cascade is stbir's bit for bit, and so is the whole compressed chain
+        from test_gpu_mips import ref_cascade
+        levels = ref_cascade(rgba, desc.num_mips, 3, True)
+        chain = np.concatenate([l.ravel() for l in levels])
+        assert np.array_equal(got, refshim.compress_chain(BC3, chain, w, h, desc.num_mips))
     assert np.array_equal(got[: 256 * 16], refshim.compress(BC3, rgba, w, h))
     # no mip config: one level
     rc, desc, got, p = create_image(RGBA8, rgba, w, h, None, 0, COMPRESS)

@@ -55,11 +55,12 @@ def test_uint8_cascade_matches_stbir(fmt, ch, alpha, srgb, kind):
     assert np.array_equal(got[0], img)
     for i in range(1, mips):
         d = np.abs(got[i].astype(int) - want[i].astype(int))
-        if srgb:
+        if srgb and not hkbcn.lib().hkbcn_build_has(hkbcn.BUILD_STBIR_SRGB):
+            # a library built without the engine tree encodes sRGB with the exact transfer function, not stbir's segment table
             assert d.max() <= 1, f"level {i}: max diff {d.max()} LSB"
             assert refshim.psnr(got[i], want[i]) >= 50.0, f"level {i}: {refshim.psnr(got[i], want[i]):.2f} dB"
         else:
-            assert np.array_equal(got[i], want[i]), f"level {i}: {int((d != 0).sum())} values differ from stbir (max {d.max()} LSB) on a linear format"
+            assert np.array_equal(got[i], want[i]), f"level {i}: {int((d != 0).sum())} values differ from stbir (max {d.max()} LSB)"
     frac = np.mean([np.mean(got[i] != want[i]) for i in range(1, mips)])
     print(f"fmt {fmt}: mean fraction of channel values off by one LSB over the chain: {frac:.5f}")
 

@@ -65,13 +65,16 @@ def test_resample_matches_stbir(raw, size):
 
 
 @pytest.mark.gpu
-def test_resample_srgb_within_one_lsb_and_refusals():
+def test_resample_srgb_and_refusals():
     rng = np.random.default_rng(5)
     img = (rng.random((40, 56, 4)) * 255).astype(np.uint8)
     got = resample(RGBA8, img, 64, 32, HAS_ALPHA | SRGB, (1, 1), (4, 4))
     want = refshim.stbir_resize(img, 64, 32, alpha_channel=3, flags=0, edge=1, filt=4, space=1)
     d = np.abs(got.astype(int) - want.astype(int))
-    assert d.max() <= 1 and (d > 0).mean() < 0.1
+    if hkbcn.lib().hkbcn_build_has(hkbcn.BUILD_STBIR_SRGB):
+        assert np.array_equal(got, want), f"{int((d != 0).sum())} values differ from stbir"  # stbir's own decode table and encode segments
+    else:
+        assert d.max() <= 1 and (d > 0).mean() < 0.1
     L = hkbcn.lib()
     p = hkbcn.ResampleParams(SRGB, 0, 0, 0, 0, 8, 8)
     f = np.zeros((4, 4, 4), np.float32)
