@@ -200,7 +200,7 @@ HKBCN_API int hkbcn_plan_bands(uint32_t height, uint32_t num_mips, int n_gpus, i
  * The importers build every mip level on the CPU from the previous one with stbir_resize and compress it
  * (Image.cpp:1755-1803 for BC1-5/BC7, :1852-1899 for BC6H; ImageMipmapConfig, Image.h:361-371).  These entry points do the
  * same cascade on the device, so only level 0 crosses PCIe.  Against stbir: bit-identical for uint8 formats, linear and sRGB (sRGB
- * within 1 LSB in a build without stbir's segment table, see hkbcn_build_has); float chains within 1e-6. */
+ * within 1 LSB in a build without stbir's segment table, see hkbcn_build_has) and for RGBA32F chains (the same bit patterns). */
 typedef struct hkbcn_mip_config {
     int edge_mode;            /* IMAGE_RESAMPLE_EDGE_MODE (Image.h:330): 1 clamp, 2 reflect, 3 wrap, 4 zero; 0 = default (wrap) */
     int filter;               /* IMAGE_RESAMPLE_FILTER (Image.h:339): 1 box, 2 triangle, 3 cubic b-spline, 4 catmull-rom, 5 mitchell; 0 = default (mitchell) */
