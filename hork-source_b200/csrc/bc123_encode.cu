@@ -17,6 +17,18 @@
 #include "bc1_block.cuh"
 #include "bc1_hq.cuh"
 #include "build/bc1_orderings.inc"
+#if HK_HAVE_BC1_ORDERINGS
+// rgbcx's total-ordering tables as one blob (tools/gen_bc1_orderings.py: "HKO1" | histograms4 969 x 4 u8 | histograms3 153 x 3 u8 |
+// pad | best4 969 x 128 u16 | best3 153 x 32 u8), embedded by the assembler
+__asm__(".section .rodata\n"
+        ".balign 16\n"
+        ".hidden hk_bc1_orderings_blob\n"
+        ".global hk_bc1_orderings_blob\n"
+        "hk_bc1_orderings_blob:\n"
+        ".incbin \"build/bc1_orderings.bin\"\n"
+        ".previous\n");
+extern "C" const unsigned char hk_bc1_orderings_blob[];
+#endif
 #include <stdio.h>
 #include <stdlib.h>
 #include <math.h>
@@ -211,22 +223,28 @@ cudaError_t bc1_upload_tables()
     static float fac4[HQ_N4 * 3], fac3[HQ_N3 * 3];
     memset(hash4, 0, sizeof(hash4));
     memset(hash3, 0, sizeof(hash3));
+    const unsigned char* blob = hk_bc1_orderings_blob;
+    if (memcmp(blob, "HKO1", 4) != 0 || HK_BC1_ORDERINGS_BYTES != 4 + HQ_N4 * 4 + HQ_N3 * 3 + 1 + HQ_N4 * HQ_MAX4 * 2 + HQ_N3 * HQ_MAX3) return cudaErrorInvalidValue;
+    const uint8_t* orders4 = blob + 4;
+    const uint8_t* orders3 = orders4 + HQ_N4 * 4;
+    const uint8_t* best4 = orders3 + HQ_N3 * 3 + 1; // u16 little-endian, 2-byte aligned within the 16-byte aligned blob
+    const uint8_t* best3 = best4 + HQ_N4 * HQ_MAX4 * 2;
     for (int i = 0; i < HQ_N4; i++) {
-        const uint8_t* h = HK_ORDERS4[i];
+        const uint8_t* h = orders4 + 4 * i;
         if (h[0] != 16 && h[1] != 16 && h[2] != 16 && h[3] != 16) hash4[h[0] | (h[1] << 4) | (h[2] << 8)] = (uint16_t)i;
         selector_factors(h, 4, fac4 + 3 * i);
     }
     for (int i = 0; i < HQ_N3; i++) {
-        const uint8_t* h = HK_ORDERS3[i];
+        const uint8_t* h = orders3 + 3 * i;
         if (h[0] != 16 && h[1] != 16 && h[2] != 16) hash3[h[0] | (h[1] << 4)] = (uint16_t)i;
         selector_factors(h, 3, fac3 + 3 * i);
     }
-    if ((e = cudaMemcpyToSymbol(g_hq_orders4, HK_ORDERS4, sizeof(HK_ORDERS4))) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(g_hq_best4, HK_BEST4, sizeof(HK_BEST4))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_orders4, orders4, HQ_N4 * 4)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_best4, best4, HQ_N4 * HQ_MAX4 * 2)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(g_hq_hash4, hash4, sizeof(hash4))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(g_hq_fac4, fac4, sizeof(fac4))) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(g_hq_orders3, HK_ORDERS3, sizeof(HK_ORDERS3))) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(g_hq_best3, HK_BEST3, sizeof(HK_BEST3))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_orders3, orders3, HQ_N3 * 3)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(g_hq_best3, best3, HQ_N3 * HQ_MAX3)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(g_hq_hash3, hash3, sizeof(hash3))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(g_hq_fac3, fac3, sizeof(fac3))) != cudaSuccess) return e;
 #endif
