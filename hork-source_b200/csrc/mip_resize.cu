@@ -865,8 +865,104 @@ __global__ void __launch_bounds__(256, M3_MINB) mip_resize_rgba8_t8_kernel(const
     }
 }
 
+// ---- R8 / RG8, exact 2 : 1, four taps per axis (the triangle filter: what the importers mip roughness and packed normal maps
+// with -- BC4 / BC5 chains), no alpha, linear.  A 256-thread CTA owns 64 x 16 outputs and stages their 130 x 34 inputs as raw
+// bytes (4.6 KB for R8); a thread computes four adjacent outputs of one row from its 10 x 4 window: the horizontal pass of each
+// of the four rows in registers, then the vertical one -- the same sums in the same order as the kernels above, no
+// intermediate buffer, no second barrier.  Texel c of a staged row (c = 0 is input 2 ox0 + x0) sits at byte c * CH + M4_SH,
+// which puts the 4-byte words of an interior tile on 4-byte boundaries and a thread's window on an 8- (R8) or 16-byte one.
+constexpr int M4_W = 64, M4_H = 16, M4_SX = 2 * M4_W + 2, M4_SY = 2 * M4_H + 2;
+template <int CH>
+__global__ void __launch_bounds__(256) mip_resize_u8_t4_kernel(const ResizeParams P)
+{
+    constexpr int SH = CH == 1 ? 3 : 2;               // bytes in front of texel 0: (2 ox0 - 1) * CH - SH is a multiple of 4
+    constexpr int PITCH = CH == 1 ? 144 : 272;        // bytes per staged row (>= M4_SX * CH + SH, a multiple of 16)
+    constexpr int WORDS = (M4_SX * CH + SH + 3) / 4;  // 34 / 66 words per row
+    __shared__ __align__(16) uint8_t raw[M4_SY * PITCH];
+    __shared__ float lut[256];
+    __shared__ int s_mx[M4_SX], s_my[M4_SY];
+    const int tid = threadIdx.x;
+    const int ox0 = blockIdx.x * M4_W, oy0 = blockIdx.y * M4_H;
+    const int nx_lo = 2 * ox0 + P.x0, ny_lo = 2 * oy0 + P.y0;
+    lut[tid] = P.lut[tid];
+    const long long ab = (long long)nx_lo * CH - SH; // byte offset within an input row of the first staged word
+    const bool interior = ab >= 0 && (ab & 3) == 0 && ab + 4 * WORDS <= (long long)P.in_w * CH && ((P.in_w * CH) & 3) == 0 && ((uintptr_t)P.src & 3) == 0;
+    const int* __restrict__ my = P.mapy + ny_lo + P.marginy;
+    if (interior) {
+        for (int i = tid; i < M4_SY * WORDS; i += 256) {
+            const int r = i / WORDS, w = i - r * WORDS;
+            *(uint32_t*)(raw + r * PITCH + 4 * w) = __ldg((const uint32_t*)(P.src + (size_t)__ldg(my + r) * P.in_w * CH + ab) + w);
+        }
+    } else {
+        if (tid < M4_SX) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
+        if (tid >= 128 && tid < 128 + M4_SY) s_my[tid - 128] = my[tid - 128];
+        __syncthreads();
+        for (int i = tid; i < M4_SY * M4_SX; i += 256) {
+            const int r = i / M4_SX, c = i - r * M4_SX;
+            const uint8_t* t = P.src + ((size_t)s_my[r] * P.in_w + s_mx[c]) * CH;
+#pragma unroll
+            for (int k = 0; k < CH; k++) raw[r * PITCH + c * CH + SH + k] = t[k];
+        }
+    }
+    __syncthreads();
+    // thread = (row y, four columns 4 xg .. 4 xg + 3): inputs 8 xg .. 8 xg + 9 of staged rows 2 y .. 2 y + 3
+    const int xg = tid & 15, y = tid >> 4;
+    float acc[4][CH];
+#pragma unroll
+    for (int o = 0; o < 4; o++)
+#pragma unroll
+        for (int k = 0; k < CH; k++) acc[o][k] = 0.0f;
+#pragma unroll
+    for (int ky = 0; ky < 4; ky++) {
+        const uint8_t* row = raw + (2 * y + ky) * PITCH + 8 * xg * CH; // the window's bytes start SH further on
+        uint32_t wv[CH == 1 ? 4 : 6];
+        if (CH == 1) {
+            const uint2 a = *(const uint2*)row, b = *(const uint2*)(row + 8);
+            wv[0] = a.x; wv[1] = a.y; wv[2] = b.x; wv[3] = b.y;
+        } else {
+            const uint4 a = *(const uint4*)row;
+            const uint2 b = *(const uint2*)(row + 16);
+            wv[0] = a.x; wv[1] = a.y; wv[2] = a.z; wv[3] = a.w; wv[4] = b.x; wv[5] = b.y;
+        }
+        float t[10][CH];
+#pragma unroll
+        for (int c = 0; c < 10; c++)
+#pragma unroll
+            for (int k = 0; k < CH; k++) {
+                const int byte = c * CH + SH + k;
+                t[c][k] = lut[(wv[byte >> 2] >> (8 * (byte & 3))) & 255u];
+            }
+        const float wy = P.uy[ky];
+#pragma unroll
+        for (int o = 0; o < 4; o++)
+#pragma unroll
+            for (int k = 0; k < CH; k++) {
+                float h = 0.0f;
+#pragma unroll
+                for (int kx = 0; kx < 4; kx++) h += t[2 * o + kx][k] * P.ux[kx];
+                acc[o][k] += h * wy;
+            }
+    }
+    uint8_t* d = P.dst + ((size_t)(oy0 + y) * P.out_w + ox0 + 4 * xg) * CH;
+    if (CH == 1) {
+        *(uchar4*)d = make_uchar4(encode_linear8(acc[0][0]), encode_linear8(acc[1][0]), encode_linear8(acc[2][0]), encode_linear8(acc[3][0]));
+    } else {
+        *(uint2*)d = make_uint2((uint32_t)encode_linear8(acc[0][0]) | ((uint32_t)encode_linear8(acc[0][CH - 1]) << 8) | ((uint32_t)encode_linear8(acc[1][0]) << 16) |
+                                    ((uint32_t)encode_linear8(acc[1][CH - 1]) << 24),
+                                (uint32_t)encode_linear8(acc[2][0]) | ((uint32_t)encode_linear8(acc[2][CH - 1]) << 8) | ((uint32_t)encode_linear8(acc[3][0]) << 16) |
+                                    ((uint32_t)encode_linear8(acc[3][CH - 1]) << 24));
+    }
+}
+
 cudaError_t launch_mip_resize(const ResizeParams& P, int channels, bool f32, cudaStream_t stream)
 {
+    if (P.uniform && P.tileOk && !f32 && (channels == 1 || channels == 2) && P.Tx == 4 && P.Ty == 4 && P.alpha < 0 && !P.srgb && P.out_w % M4_W == 0 &&
+        P.out_h % M4_H == 0 && ((uintptr_t)P.dst & 7) == 0 && !getenv("HKBCN_MIP_TILE2")) {
+        const dim3 grid4((unsigned)P.out_w / M4_W, (unsigned)P.out_h / M4_H);
+        if (channels == 1) mip_resize_u8_t4_kernel<1><<<grid4, 256, 0, stream>>>(P);
+        else mip_resize_u8_t4_kernel<2><<<grid4, 256, 0, stream>>>(P);
+        return cudaGetLastError();
+    }
     if (P.uniform && P.tileOk && !f32 && channels == 4 && P.Tx == 8 && P.Ty == 8 && !getenv("HKBCN_MIP_TILE2")) {
         const dim3 grid3((unsigned)(P.out_w + M3_W - 1) / M3_W, (unsigned)(P.out_h + M3_H - 1) / M3_H);
         if (P.alpha == 3) mip_resize_rgba8_t8_kernel<true><<<grid3, 256, 0, stream>>>(P);

@@ -120,3 +120,18 @@ def test_import_chain_equals_reference_cascade_and_encoder():
     assert off == got.size
     # level 0 is untouched by the cascade: its blocks are the reference's, byte for byte
     assert np.array_equal(got[: (w // 4) * (h // 4) * 16], refshim.compress(BC7, img, w, h))
+
+
+@pytest.mark.parametrize("fmt,ch", [(BC4, 1), (BC5, 2)])
+@pytest.mark.parametrize("edge", [1, 2, 3, 4])
+def test_r8_rg8_triangle_chain_at_size(fmt, ch, edge):
+    """the four-tap R8 / RG8 kernel (levels of at least 64 x 16 outputs) and the kernels below it, every edge mode: interior
+    tiles (aligned word staging) and edge tiles (through the maps) against stbir, bit for bit"""
+    w, h = 1024, 512
+    mips = hkbcn.lib().hkbcn_calc_num_mips(w, h)
+    img = (synth.roughness_r8(w, h, 21).reshape(h, w, 1) if ch == 1 else synth.normals_rg8(w, h, 22).reshape(h, w, 2))
+    cfg = hkbcn.MipConfig(edge, 2, 0, 0)
+    got = split_chain(hkbcn.generate_mips(fmt, img, w, h, mips, cfg), w, h, mips, ch)
+    want = ref_cascade(img, mips, -1, False, edge, 2)
+    for i in range(1, mips):
+        assert np.array_equal(got[i], want[i]), f"level {i}: {int((got[i] != want[i]).sum())} values differ"
