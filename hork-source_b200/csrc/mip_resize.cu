@@ -889,10 +889,19 @@ __global__ void __launch_bounds__(256) mip_resize_u8_t4_kernel(const ResizeParam
     const bool interior = ab >= 0 && (ab & 3) == 0 && ab + 4 * WORDS <= (long long)P.in_w * CH && ((P.in_w * CH) & 3) == 0 && ((uintptr_t)P.src & 3) == 0;
     const int* __restrict__ my = P.mapy + ny_lo + P.marginy;
     if (interior) {
-        for (int i = tid; i < M4_SY * WORDS; i += 256) {
-            const int r = i / WORDS, w = i - r * WORDS;
-            *(uint32_t*)(raw + r * PITCH + 4 * w) = __ldg((const uint32_t*)(P.src + (size_t)__ldg(my + r) * P.in_w * CH + ab) + w);
+        // all of a thread's loads in flight before its first store
+        constexpr int PER = (M4_SY * WORDS + 255) / 256;
+        uint32_t v[PER];
+        int at[PER];
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const int i = tid + 256 * k, r = i / WORDS, w = i - r * WORDS;
+            at[k] = i < M4_SY * WORDS ? r * PITCH + 4 * w : -1;
+            if (at[k] >= 0) v[k] = __ldg((const uint32_t*)(P.src + (size_t)__ldg(my + r) * P.in_w * CH + ab) + w);
         }
+#pragma unroll
+        for (int k = 0; k < PER; k++)
+            if (at[k] >= 0) *(uint32_t*)(raw + at[k]) = v[k];
     } else {
         if (tid < M4_SX) s_mx[tid] = P.mapx[nx_lo + tid + P.marginx];
         if (tid >= 128 && tid < 128 + M4_SY) s_my[tid - 128] = my[tid - 128];
