@@ -362,7 +362,11 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
     std::vector<Piece> pieces;
     const uint32_t nby = h / 4;
     const size_t l0 = (size_t)w * h * bpp;
-    int nb = (int)std::min<size_t>(6, std::max<size_t>(1, l0 / (12u << 20)));
+    // the slow encoders (BC7, BC6H) want pieces of 8 MB or more (their tile rounds, below); for the fast ones the copies are
+    // the larger share of the call and a launch costs little: pieces down to 2 MB
+    const bool slow = codec == C_BC7 || codec == C_BC6H;
+    const size_t min_piece = slow ? ((size_t)8 << 20) : ((size_t)2 << 20);
+    int nb = (int)std::min<size_t>(6, std::max<size_t>(1, l0 / (slow ? (12u << 20) : (3u << 20))));
     if (nb > 1) {
         // Every band is a launch of its own, and a persistent encoder works in rounds of one tile per SM: a band of 2.2 rounds
         // costs three (measured, BC7 4096^2 chain from pageable memory: 5 bands 25.5 ms, 4 bands 22.3, 6 bands 21.9).  Among
@@ -371,7 +375,7 @@ int compress_host_pipelined(Device* D, int fmt, int codec, const uint8_t* src, u
         double best = -1.0;
         int best_nb = nb;
         for (int c = 2; c <= 7; c++) {
-            if (l0 / (size_t)c < ((size_t)8 << 20) || (uint32_t)c > nby) break;
+            if (l0 / (size_t)c < min_piece || (uint32_t)c > nby) break;
             const uint64_t tiles = ((uint64_t)((nby + c - 1) / c) * (w / 4) + tb - 1) / tb;
             const double eff = (double)tiles / (double)(((tiles + sms - 1) / sms) * sms);
             if (eff >= best - 1e-9) { best = eff; best_nb = c; }
