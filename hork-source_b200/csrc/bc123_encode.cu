@@ -7,9 +7,9 @@
 //        (stride 4, radius 3, all modes; see bc4_search.cuh) + the BC1 colour block
 // Bit-exact contract for all three.
 //
-// Mapping: BC1/BC2 one lane per block; BC3 a 2-lane sub-warp per block (lane parity = BC4
-// alpha mode, the even lane also encodes the colour block).  128-thread CTAs, tiles of
-// 128 (BC1/2) or 64 (BC3) blocks staged by TMA bulk copies.  Algorithmic HBM bytes:
+// Mapping: BC1/BC2 one lane per block; BC3 a 2-lane sub-warp per block for the alpha search (lane
+// parity = BC4 alpha mode; a tile's two halves one after the other), then one lane per block for
+// the colour blocks.  128-thread CTAs, tiles of 128 blocks staged by TMA bulk copies.  Algorithmic HBM bytes:
 // 4.5 B/px (BC1), 5 B/px (BC2/BC3).
 #include "hkbcn_common.cuh"
 #include "hkbcn_kernels.h"
@@ -41,11 +41,11 @@ template <int CODEC, bool HQ>
 __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant__ EncodeParams P)
 {
     constexpr int NT = 128;
-    constexpr int G = (CODEC == C_BC3) ? 2 : 1;
-    constexpr int TB = NT / G;
+    constexpr int TB = NT; // BC3 too: the alpha search runs on lane pairs over the tile's two halves, the colour blocks on all lanes
     constexpr int BW = 16;
     constexpr int ROWB = TB * BW;
     __shared__ __align__(128) uint8_t stage[4 * ROWB];
+    __shared__ __align__(8) uint2 s_alpha[CODEC == C_BC3 ? TB : 1];
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) {
         mbar_init(&bar, 1);
@@ -53,8 +53,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
     }
     __syncthreads();
     uint32_t phase = 0;
-    const int k = threadIdx.x / G;
-    const int sub = threadIdx.x % G;
+    const int k = threadIdx.x;
     // HKBCN_FLAG_LEVEL: rgbcx level + 1 in bits 4..8 (0 = the Compress* preset, level 5); HKBCN_FLAG_FAST: non-hq BC3 alpha
     const int level = ((P.flags >> 4) & 31u) ? (int)((P.flags >> 4) & 31u) - 1 : 5;
     const bool fastAlpha = (P.flags & 2u) != 0;
@@ -98,22 +97,36 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(a[0], a[1], c.x, c.y);
             }
         } else { // BC3
-            uint32_t a2[8];
-            int minv = 255, maxv = 0;
+            // ---- alpha (rgbcx::encode_bc4_hq / encode_bc4 on channel 3): a lane pair per block, lane parity = BC4 mode; the tile
+            // in two halves of 64 blocks
+#pragma unroll 1
+            for (int half = 0; half < 2; half++) {
+                const int ka = half * (TB / 2) + (int)(threadIdx.x >> 1), sub = (int)(threadIdx.x & 1u);
+                const bool va = (uint32_t)ka < nb;
+                uint32_t a2[8];
+                int minv = 255, maxv = 0;
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                int p0 = px[2 * i] >> 24, p1 = px[2 * i + 1] >> 24;
-                a2[i] = (uint32_t)p0 | ((uint32_t)p1 << 16);
-                minv = min(minv, min(p0, p1));
-                maxv = max(maxv, max(p0, p1));
+                for (int r = 0; r < 4; r++) {
+                    uint4 v = va ? *(const uint4*)(stage + r * ROWB + ka * BW) : make_uint4(0, 0, 0, 0);
+                    const int p0 = v.x >> 24, p1 = v.y >> 24, p2 = v.z >> 24, p3 = v.w >> 24;
+                    a2[2 * r] = (uint32_t)p0 | ((uint32_t)p1 << 16);
+                    a2[2 * r + 1] = (uint32_t)p2 | ((uint32_t)p3 << 16);
+                    minv = min(minv, min(min(p0, p1), min(p2, p3)));
+                    maxv = max(maxv, max(max(p0, p1), max(p2, p3)));
+                }
+                uint32_t key = 0xFFFFFFFFu;
+                if (minv != maxv && !fastAlpha) key = bc4hq_search_mode(a2, minv, maxv, sub);
+                key = min(key, __shfl_xor_sync(0xFFFFFFFFu, key, 1));
+                if (va && sub == 0) {
+                    // bMaxQuality = false: rgbcx::encode_bc3 = the non-hq encode_bc4 on alpha (rgbcx.cpp:2886-2903)
+                    s_alpha[ka] = fastAlpha ? bc4_fast(a2, minv, maxv) : (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
+                }
             }
-            uint32_t key = 0xFFFFFFFFu;
-            if (minv != maxv && !fastAlpha) key = bc4hq_search_mode(a2, minv, maxv, sub);
-            key = min(key, __shfl_xor_sync(0xFFFFFFFFu, key, 1));
-            if (valid && sub == 0) {
-                // bMaxQuality = false: rgbcx::encode_bc3 = the non-hq encode_bc4 on alpha (rgbcx.cpp:2886-2903)
-                uint2 al = fastAlpha ? bc4_fast(a2, minv, maxv) : (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
-                uint2 c = colour_block(px);
+            __syncthreads();
+            // ---- colour: one lane per block, every lane busy
+            if (valid) {
+                const uint2 al = s_alpha[k];
+                const uint2 c = colour_block(px);
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(al.x, al.y, c.x, c.y);
             }
         }
@@ -121,7 +134,7 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
     }
 }
 
-uint32_t bc123_tile_blocks(int codec) { return codec == C_BC3 ? 64 : 128; }
+uint32_t bc123_tile_blocks(int) { return 128; }
 
 // ---- a12: table generation (host) -------------------------------------------
 // prepare_bc1_single_color_table (rgbcx.cpp:485-527) in cBC1Ideal mode: for each 8-bit value
