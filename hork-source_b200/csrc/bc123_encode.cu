@@ -46,10 +46,13 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
     constexpr int ROWB = TB * BW;
     __shared__ __align__(128) uint8_t stage[4 * ROWB];
     __shared__ __align__(8) uint2 s_alpha[CODEC == C_BC3 ? TB : 1];
+    __shared__ uint8_t s_list[CODEC == C_BC3 ? TB : 1];
+    __shared__ uint32_t s_nsearch;
     __shared__ __align__(8) uint64_t bar;
     if (threadIdx.x == 0) {
         mbar_init(&bar, 1);
         fence_mbar_init();
+        s_nsearch = 0;
     }
     __syncthreads();
     uint32_t phase = 0;
@@ -97,17 +100,41 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
                 *(uint4*)(L.dst + (size_t)(b0 + k) * 16) = make_uint4(a[0], a[1], c.x, c.y);
             }
         } else { // BC3
-            // ---- alpha (rgbcx::encode_bc4_hq / encode_bc4 on channel 3): a lane pair per block, lane parity = BC4 mode; the tile
-            // in two halves of 64 blocks
+            // ---- alpha (rgbcx::encode_bc4_hq / encode_bc4 on channel 3).  Every lane first looks at its own block: a solid alpha
+            // block (and, without bMaxQuality, every block: rgbcx::encode_bc3 = the non-hq encode_bc4, rgbcx.cpp:2886-2903) is
+            // finished on the spot, the others are appended to a list.  The radius-3 search then runs on lane pairs (lane parity =
+            // BC4 mode) over the LIST, 64 entries a round: opaque regions of a texture no longer leave their lane pairs idle.
+            {
+                uint32_t a2[8];
+                int minv = 255, maxv = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int p0 = px[2 * i] >> 24, p1 = px[2 * i + 1] >> 24;
+                    a2[i] = (uint32_t)p0 | ((uint32_t)p1 << 16);
+                    minv = min(minv, min(p0, p1));
+                    maxv = max(maxv, max(p0, p1));
+                }
+                const bool search = valid && !fastAlpha && minv != maxv;
+                if (valid && !search) s_alpha[k] = fastAlpha ? bc4_fast(a2, minv, maxv) : bc4_solid((uint32_t)minv);
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, search);
+                uint32_t base = 0;
+                if ((threadIdx.x & 31u) == 0 && m) base = atomicAdd(&s_nsearch, (uint32_t)__popc(m));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (search) s_list[base + __popc(m & ((1u << (threadIdx.x & 31u)) - 1u))] = (uint8_t)k;
+            }
+            __syncthreads();
+            const uint32_t nsearch = s_nsearch;
 #pragma unroll 1
-            for (int half = 0; half < 2; half++) {
-                const int ka = half * (TB / 2) + (int)(threadIdx.x >> 1), sub = (int)(threadIdx.x & 1u);
-                const bool va = (uint32_t)ka < nb;
+            for (uint32_t e0 = 0; e0 < nsearch; e0 += TB / 2) {
+                const uint32_t e = e0 + (threadIdx.x >> 1);
+                const int sub = (int)(threadIdx.x & 1u);
+                const bool va = e < nsearch;
+                const int ka = va ? (int)s_list[e] : 0;
                 uint32_t a2[8];
                 int minv = 255, maxv = 0;
 #pragma unroll
                 for (int r = 0; r < 4; r++) {
-                    uint4 v = va ? *(const uint4*)(stage + r * ROWB + ka * BW) : make_uint4(0, 0, 0, 0);
+                    const uint4 v = *(const uint4*)(stage + r * ROWB + ka * BW);
                     const int p0 = v.x >> 24, p1 = v.y >> 24, p2 = v.z >> 24, p3 = v.w >> 24;
                     a2[2 * r] = (uint32_t)p0 | ((uint32_t)p1 << 16);
                     a2[2 * r + 1] = (uint32_t)p2 | ((uint32_t)p3 << 16);
@@ -115,14 +142,12 @@ __global__ void __launch_bounds__(128) bc123_encode_kernel(const __grid_constant
                     maxv = max(maxv, max(max(p0, p1), max(p2, p3)));
                 }
                 uint32_t key = 0xFFFFFFFFu;
-                if (minv != maxv && !fastAlpha) key = bc4hq_search_mode(a2, minv, maxv, sub);
+                if (va) key = bc4hq_search_mode(a2, minv, maxv, sub);
                 key = min(key, __shfl_xor_sync(0xFFFFFFFFu, key, 1));
-                if (va && sub == 0) {
-                    // bMaxQuality = false: rgbcx::encode_bc3 = the non-hq encode_bc4 on alpha (rgbcx.cpp:2886-2903)
-                    s_alpha[ka] = fastAlpha ? bc4_fast(a2, minv, maxv) : (minv == maxv) ? bc4_solid((uint32_t)minv) : bc4hq_emit(a2, minv, maxv, key & 127u);
-                }
+                if (va && sub == 0) s_alpha[ka] = bc4hq_emit(a2, minv, maxv, key & 127u);
             }
             __syncthreads();
+            if (threadIdx.x == 0) s_nsearch = 0; // everybody has read it; the barrier that ends the tile orders this before the next appends
             // ---- colour: one lane per block, every lane busy
             if (valid) {
                 const uint2 al = s_alpha[k];
