@@ -11,8 +11,7 @@
 //   level 4  cEncodeBC1UseFullMSEEval | cEncodeBC1Use6PowerIters: the error-tracking branch (:2371-2470) in its simplest form --
 //            six power iterations, selectors by exhaustive search with the block error (bc1_find_sels4_fullerr, :1047-1081), a
 //            least-squares pass is kept only if it lowers the error
-// Levels 6..18 and the 3-colour flags add the total-orderings search and the endpoint search rounds of that branch: not built,
-// the C ABI answers HKBCN_ERR_UNSUPPORTED for them.
+// Levels 6..18 and the 3-colour flags add the total-orderings search and the endpoint search rounds of that branch: bc1_hq.cuh.
 //
 // FP32 discipline: the reference is built without FMA contraction (baseline x86-64,
 // SURVEY.md 7), so every float op here is an explicitly rounded __fmul_rn/__fadd_rn/
